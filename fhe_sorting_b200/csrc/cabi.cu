@@ -1,0 +1,225 @@
+// cabi.cu — extern "C" boundary (include/fhe_b200.h) over the engine.
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/fhe_b200.h"
+#include "engine.h"
+
+using namespace fheb200;
+
+struct fheb200_ctx { std::shared_ptr<Context> c; };
+struct fheb200_keys { Keys k; };
+struct fheb200_ct { Ct c; };
+struct fheb200_pt { Pt p; };
+struct fheb200_pre { std::shared_ptr<Precomp> p; };
+
+static thread_local std::string g_err;
+namespace fheb200 { void set_last_error(const char *m) { g_err = m; } }
+#define GUARD(...)                          \
+    try {                                   \
+        __VA_ARGS__;                            \
+        return 0;                           \
+    } catch (const std::exception &e) {     \
+        g_err = e.what();                   \
+        return 1;                           \
+    } catch (...) {                         \
+        g_err = "unknown error";            \
+        return 1;                           \
+    }
+static void need(const void *p, const char *what) {
+    if (!p) throw std::invalid_argument(std::string("null argument: ") + what);
+}
+static fheb200_ct *wrap(const Ct &c) { return new fheb200_ct{c}; }
+
+extern "C" {
+
+const char *fheb200_last_error(void) { return g_err.c_str(); }
+const char *fheb200_version(void) { return "fheb200 0.1 (sm_100a)"; }
+
+int fheb200_ctx_create(const fheb200_params *p, fheb200_ctx **out) {
+    GUARD({
+        need(p, "params");
+        need(out, "out");
+        auto c = Context::create(p->log_ring_dim, p->mult_depth, p->scaling_mod_size, p->first_mod_size ? p->first_mod_size : 60,
+                                 p->num_large_digits ? p->num_large_digits : 3, p->batch_size, p->device);
+        *out = new fheb200_ctx{c};
+    })
+}
+int fheb200_ctx_release(fheb200_ctx *ctx) { GUARD({ delete ctx; }) }
+int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *s) {
+    GUARD({
+        need(ctx, "ctx");
+        std::lock_guard<std::recursive_mutex> g(ctx->c->mu);
+        ctx->c->sync();
+        if (ctx->c->own_stream && ctx->c->stream) cudaStreamDestroy(ctx->c->stream);
+        ctx->c->stream = (cudaStream_t)s;
+        ctx->c->own_stream = false;
+    })
+}
+int fheb200_ctx_sync(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->sync(); }) }
+int fheb200_ctx_info(fheb200_ctx *ctx, int *n, int *nq, int *np, int *alpha, int *batch) {
+    GUARD({
+        need(ctx, "ctx");
+        const Params &P = *ctx->c->P;
+        if (n) *n = P.n;
+        if (nq) *nq = P.L;
+        if (np) *np = P.K;
+        if (alpha) *alpha = P.alpha;
+        if (batch) *batch = ctx->c->batch;
+    })
+}
+int fheb200_ctx_modulus(fheb200_ctx *ctx, int i, uint64_t *q, uint64_t *psi) {
+    GUARD({
+        need(ctx, "ctx");
+        const Params &P = *ctx->c->P;
+        if (i < 0 || i >= P.L + P.K) throw std::out_of_range("modulus index");
+        if (q) *q = P.moduli[i];
+        if (psi) *psi = P.psi[i];
+    })
+}
+int fheb200_ctx_scaling_factor(fheb200_ctx *ctx, int level, double *sf, double *sfb) {
+    GUARD({
+        need(ctx, "ctx");
+        const Params &P = *ctx->c->P;
+        if (level < 0 || level >= P.L) throw std::out_of_range("level");
+        if (sf) *sf = P.sf[level];
+        if (sfb) *sfb = level < P.L - 1 ? P.sf_big[level] : 0.0;
+    })
+}
+int fheb200_ctx_key_bytes(fheb200_ctx *ctx, uint64_t *bytes) { GUARD({ need(ctx, "ctx"); *bytes = ctx->c->key_bytes(); }) }
+int fheb200_params_chain(const fheb200_params *p, uint64_t *moduli, uint64_t *psi, int cap, int *nq, int *np, int *alpha) {
+    GUARD({
+        need(p, "params");
+        auto P = Params::create(p->log_ring_dim, p->mult_depth, p->scaling_mod_size, p->first_mod_size ? p->first_mod_size : 60,
+                                p->num_large_digits ? p->num_large_digits : 3);
+        if (nq) *nq = P->L;
+        if (np) *np = P->K;
+        if (alpha) *alpha = P->alpha;
+        for (int i = 0; i < P->L + P->K && i < cap; i++) {
+            if (moduli) moduli[i] = P->moduli[i];
+            if (psi) psi[i] = P->psi[i];
+        }
+    })
+}
+
+int fheb200_keygen(fheb200_ctx *ctx, uint64_t seed, fheb200_keys **out) {
+    GUARD({ need(ctx, "ctx"); need(out, "out"); *out = new fheb200_keys{ctx->c->keygen(seed)}; })
+}
+int fheb200_keys_release(fheb200_keys *k) { GUARD({ delete k; }) }
+int fheb200_eval_mult_keygen(fheb200_ctx *ctx, fheb200_keys *k) { GUARD({ need(ctx, "ctx"); need(k, "keys"); ctx->c->gen_mult_key(k->k); }) }
+int fheb200_eval_rotate_keygen(fheb200_ctx *ctx, fheb200_keys *k, const int *idx, size_t count) {
+    GUARD({ need(ctx, "ctx"); need(k, "keys"); ctx->c->gen_rot_keys(k->k, std::vector<int>(idx, idx + count)); })
+}
+
+int fheb200_make_packed_plaintext(fheb200_ctx *ctx, const double *v, size_t count, int nsd, int level, int slots, fheb200_pt **out) {
+    GUARD({
+        need(ctx, "ctx"); need(out, "out");
+        std::vector<std::complex<double>> z(count);
+        for (size_t i = 0; i < count; i++) z[i] = std::complex<double>(v[i], 0.0);
+        *out = new fheb200_pt{ctx->c->make_plaintext(z, nsd, level, slots)};
+    })
+}
+int fheb200_pt_release(fheb200_pt *pt) { GUARD({ delete pt; }) }
+int fheb200_pt_values(fheb200_pt *pt, double *out, size_t cap, size_t *count) {
+    GUARD({
+        need(pt, "pt");
+        size_t nv = std::min(pt->p->length, pt->p->vals.size());
+        if (count) *count = nv;
+        for (size_t i = 0; i < nv && i < cap; i++) out[i] = pt->p->vals[i].real();
+    })
+}
+int fheb200_pt_set_length(fheb200_pt *pt, size_t len) {
+    GUARD({ need(pt, "pt"); pt->p->length = len; if (pt->p->vals.size() < len) pt->p->vals.resize(len); })
+}
+int fheb200_pt_log_precision(fheb200_pt *pt, double *bits) { GUARD({ need(pt, "pt"); *bits = pt->p->log_precision; }) }
+int fheb200_encrypt(fheb200_ctx *ctx, fheb200_keys *k, fheb200_pt *pt, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(k, "keys"); need(pt, "pt"); *out = wrap(ctx->c->encrypt(k->k, pt->p)); })
+}
+int fheb200_decrypt(fheb200_ctx *ctx, fheb200_keys *k, fheb200_ct *ct, fheb200_pt **out) {
+    GUARD({ need(ctx, "ctx"); need(k, "keys"); need(ct, "ct"); *out = new fheb200_pt{ctx->c->decrypt(k->k, ct->c)}; })
+}
+
+int fheb200_ct_release(fheb200_ct *ct) { GUARD({ delete ct; }) }
+int fheb200_ct_clone(fheb200_ctx *ctx, fheb200_ct *ct, fheb200_ct **out) { GUARD({ need(ctx, "ctx"); need(ct, "ct"); *out = wrap(ctx->c->clone(ct->c)); }) }
+int fheb200_ct_info(fheb200_ct *ct, int *level, int *nsd, int *slots, int *limbs, double *scale) {
+    GUARD({
+        need(ct, "ct");
+        if (level) *level = ct->c->level;
+        if (nsd) *nsd = ct->c->nsd;
+        if (slots) *slots = ct->c->slots;
+        if (limbs) *limbs = ct->c->ell;
+        if (scale) *scale = ct->c->scale;
+    })
+}
+int fheb200_ct_set_slots(fheb200_ct *ct, int slots) {
+    GUARD({
+        need(ct, "ct");
+        if (slots <= 0 || (slots & (slots - 1))) throw std::invalid_argument("SetSlots: power of two expected");
+        ct->c->slots = slots;
+    })
+}
+
+#define BIN(name, expr)                                                                       \
+    int name(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out) {              \
+        GUARD({ need(ctx, "ctx"); need(a, "a"); need(b, "b"); need(out, "out"); *out = wrap(expr); }) \
+    }
+BIN(fheb200_eval_add, ctx->c->add(a->c, b->c))
+BIN(fheb200_eval_sub, ctx->c->sub(a->c, b->c))
+BIN(fheb200_eval_mult, ctx->c->mult(a->c, b->c))
+
+int fheb200_eval_add_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->add_pt(a->c, p->p, false)); })
+}
+int fheb200_eval_sub_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->add_pt(a->c, p->p, true)); })
+}
+int fheb200_eval_add_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->add_const(a->c, c)); })
+}
+int fheb200_eval_negate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) { GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->negate(a->c)); }) }
+int fheb200_eval_add_many(fheb200_ctx *ctx, fheb200_ct *const *cts, size_t count, fheb200_ct **out) {
+    GUARD({
+        need(ctx, "ctx"); need(cts, "cts");
+        std::vector<Ct> v;
+        for (size_t i = 0; i < count; i++) { need(cts[i], "cts[i]"); v.push_back(cts[i]->c); }
+        *out = wrap(ctx->c->add_many(v));
+    })
+}
+int fheb200_eval_mult_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->mult_pt(a->c, p->p)); })
+}
+int fheb200_eval_mult_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->mult_const(a->c, c)); })
+}
+int fheb200_eval_rescale(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) { GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->rescale(a->c)); }) }
+
+int fheb200_eval_rotate(fheb200_ctx *ctx, fheb200_ct *a, int index, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->rotate(a->c, index)); })
+}
+int fheb200_fast_rotation_precompute(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pre **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); *out = new fheb200_pre{ctx->c->fast_rotation_precompute(a->c)}; })
+}
+int fheb200_pre_release(fheb200_pre *pre) { GUARD({ delete pre; }) }
+int fheb200_eval_fast_rotation(fheb200_ctx *ctx, fheb200_ct *a, int index, fheb200_pre *pre, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "a"); need(pre, "pre"); *out = wrap(ctx->c->fast_rotation(a->c, index, pre->p)); })
+}
+int fheb200_has_rotation_key(fheb200_ctx *ctx, int index, int *present) {
+    GUARD({ need(ctx, "ctx"); uint32_t g = ctx->c->P->galois_for_rotation(index); *present = (g == 1 || ctx->c->has_rot_key(g)) ? 1 : 0; })
+}
+
+int fheb200_eval_chebyshev_series(fheb200_ctx *ctx, fheb200_ct *x, const double *co, size_t count, double a, double b, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(x, "x"); need(co, "coeffs"); *out = wrap(ctx->c->eval_chebyshev(x->c, std::vector<double>(co, co + count), a, b)); })
+}
+int fheb200_eval_poly(fheb200_ctx *ctx, fheb200_ct *x, const double *co, size_t count, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(x, "x"); need(co, "coeffs"); *out = wrap(ctx->c->eval_poly_linear(x->c, std::vector<double>(co, co + count))); })
+}
+int fheb200_chebyshev_coefficients(double (*f)(double, void *), void *user, double a, double b, int degree, double *out) {
+    GUARD({
+        need((void *)f, "f"); need(out, "out");
+        auto v = chebyshev_coefficients([&](double x) { return f(x, user); }, a, b, degree);
+        memcpy(out, v.data(), v.size() * sizeof(double));
+    })
+}
+
+} // extern "C"

@@ -1,0 +1,214 @@
+// cabi_raw.cu — raw RNS import/export, single-primitive entry points (parity tests) and device timing loops.
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/fhe_b200.h"
+#include "engine.h"
+
+using namespace fheb200;
+
+struct fheb200_ctx { std::shared_ptr<Context> c; };
+struct fheb200_keys { Keys k; };
+struct fheb200_ct { Ct c; };
+struct fheb200_pt { Pt p; };
+
+extern "C" const char *fheb200_last_error(void);
+namespace fheb200 { void set_last_error(const char *); }
+static thread_local std::string g_err_raw;
+#define GUARD(...)                                   \
+    try {                                            \
+        __VA_ARGS__;                                     \
+        return 0;                                    \
+    } catch (const std::exception &e) {              \
+        fheb200::set_last_error(e.what());           \
+        return 1;                                    \
+    } catch (...) {                                  \
+        fheb200::set_last_error("unknown error");    \
+        return 1;                                    \
+    }
+static void need(const void *p, const char *what) {
+    if (!p) throw std::invalid_argument(std::string("null argument: ") + what);
+}
+static void d2h(Context &C, void *dst, const void *src, size_t bytes) {
+    FHE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, C.stream));
+    C.sync();
+}
+static void h2d(Context &C, void *dst, const void *src, size_t bytes) {
+    FHE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, C.stream));
+    C.sync();
+}
+#define LOCKCTX(ctx)                                              \
+    need(ctx, "ctx");                                             \
+    Context &C = *ctx->c;                                         \
+    std::lock_guard<std::recursive_mutex> lock__(C.mu);           \
+    FHE_CUDA(cudaSetDevice(C.device));                            \
+    const int n = C.P->n;                                         \
+    (void)n
+
+extern "C" {
+
+int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(ct, "ct");
+        size_t w = (size_t)ct->c->ell * n;
+        if (words < w) throw std::invalid_argument("ct_export: buffer too small");
+        if (c0) d2h(C, c0, ct->c->poly(0, n), w * 8);
+        if (c1) d2h(C, c1, ct->c->poly(1, n), w * 8);
+    })
+}
+int fheb200_ct_import(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int ell, int nsd, double scale, int slots, fheb200_ct **out) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(c0, "c0"); need(c1, "c1"); need(out, "out");
+        if (ell < 1 || ell > C.P->L) throw std::invalid_argument("ct_import: bad limb count");
+        auto c = std::make_shared<Ciphertext>();
+        c->npoly = 2, c->ell = ell, c->level = C.P->L - ell, c->nsd = nsd, c->scale = scale, c->slots = slots > 0 ? slots : C.batch;
+        c->mem = C.alloc((size_t)2 * ell * n);
+        h2d(C, c->poly(0, n), c0, (size_t)ell * n * 8);
+        h2d(C, c->poly(1, n), c1, (size_t)ell * n * 8);
+        *out = new fheb200_ct{c};
+    })
+}
+int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(pt, "pt");
+        if (!pt->p->mem) throw std::runtime_error("pt_export: plaintext has no encoding");
+        size_t w = (size_t)pt->p->ell * n;
+        if (words < w) throw std::invalid_argument("pt_export: buffer too small");
+        d2h(C, out, pt->p->mem->p, w * 8);
+    })
+}
+int fheb200_keys_export(fheb200_ctx *ctx, fheb200_keys *k, int which, uint64_t *out, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(k, "keys");
+        const int L = C.P->L, F = L + C.P->K;
+        size_t w = (size_t)(which == 0 ? F : L) * n;
+        if (words < w) throw std::invalid_argument("keys_export: buffer too small");
+        if (which == 0) {
+            if (!k->k->s) throw std::runtime_error("keys_export: no secret key");
+            d2h(C, out, k->k->s->p, w * 8);
+        } else {
+            d2h(C, out, k->k->pk->p + (which == 2 ? w : 0), w * 8);
+        }
+    })
+}
+int fheb200_evk_export(fheb200_ctx *ctx, uint32_t galois, uint64_t *out, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        if (words < C.evk_words()) throw std::invalid_argument("evk_export: buffer too small");
+        const u64 *src = nullptr;
+        if (galois == 0) src = C.evk_mult;
+        else if (C.evk_rot.count(galois)) src = C.evk_rot[galois];
+        if (!src) throw std::runtime_error("evk_export: key not present");
+        d2h(C, out, src, C.evk_words() * 8);
+    })
+}
+int fheb200_galois_for_rotation(fheb200_ctx *ctx, int index, uint32_t *g) { GUARD({ need(ctx, "ctx"); *g = ctx->c->P->galois_for_rotation(index); }) }
+
+int fheb200_raw_ntt(fheb200_ctx *ctx, int inverse, int qp, uint64_t *poly) {
+    GUARD({
+        LOCKCTX(ctx);
+        if (qp < 0 || qp >= C.T.F) throw std::out_of_range("raw_ntt: modulus index");
+        Mem m = C.alloc(n);
+        h2d(C, m->p, poly, (size_t)n * 8);
+        const uint32_t *d = C.desc({(uint32_t)qp});
+        if (inverse) k_ntt_inv(C.T, m->p, d, 1, C.stream);
+        else k_ntt_fwd(C.T, m->p, d, 1, C.stream);
+        d2h(C, poly, m->p, (size_t)n * 8);
+    })
+}
+int fheb200_raw_automorphism(fheb200_ctx *ctx, uint32_t g, int limbs, const uint64_t *in, uint64_t *out) {
+    GUARD({
+        LOCKCTX(ctx);
+        Mem a = C.alloc((size_t)limbs * n), b = C.alloc((size_t)limbs * n);
+        h2d(C, a->p, in, (size_t)limbs * n * 8);
+        k_automorphism(C.T, g, limbs, a->p, b->p, C.stream);
+        d2h(C, out, b->p, (size_t)limbs * n * 8);
+    })
+}
+int fheb200_raw_modup(fheb200_ctx *ctx, int ell, const uint64_t *c, uint64_t *digits, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        const DevicePlan &D = C.plan(ell);
+        size_t w = (size_t)D.beta * D.width * n;
+        if (words < w) throw std::invalid_argument("raw_modup: buffer too small");
+        Mem a = C.alloc((size_t)ell * n), dg = C.alloc(w);
+        h2d(C, a->p, c, (size_t)ell * n * 8);
+        C.modup(ell, a->p, dg->p);
+        d2h(C, digits, dg->p, w * 8);
+    })
+}
+int fheb200_raw_rescale(fheb200_ctx *ctx, int ell, const uint64_t *in, uint64_t *out) {
+    GUARD({
+        LOCKCTX(ctx);
+        Mem a = C.alloc((size_t)ell * n), b = C.alloc((size_t)(ell - 1) * n);
+        h2d(C, a->p, in, (size_t)ell * n * 8);
+        C.rescale_poly(ell, 1, a->p, b->p);
+        d2h(C, out, b->p, (size_t)(ell - 1) * n * 8);
+    })
+}
+
+// `reps` rotations of the same ciphertext back to back; device time by CUDA events on the context stream
+int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(ct, "ct");
+        cudaEvent_t e0, e1;
+        FHE_CUDA(cudaEventCreate(&e0));
+        FHE_CUDA(cudaEventCreate(&e1));
+        FHE_CUDA(cudaEventRecord(e0, C.stream));
+        for (int r = 0; r < reps; r++) { Ct o = C.rotate(ct->c, index); }
+        FHE_CUDA(cudaEventRecord(e1, C.stream));
+        FHE_CUDA(cudaEventSynchronize(e1));
+        FHE_CUDA(cudaEventElapsedTime(ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    })
+}
+
+// isolated kernels on scratch data at `ell` active limbs: "ntt_fwd", "ntt_inv", "inner_product", "modup_conv",
+// "moddown_conv", "automorphism", "tensor", "add"
+int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, float *ms, double *algo_bytes) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(name, "name");
+        const DevicePlan &D = C.plan(ell);
+        const std::string k(name);
+        const size_t limb = (size_t)n * 8;
+        Mem a = C.alloc((size_t)D.beta * D.width * n), b = C.alloc((size_t)3 * D.width * n);
+        FHE_CUDA(cudaMemsetAsync(a->p, 0, a->words * 8, C.stream));
+        FHE_CUDA(cudaMemsetAsync(b->p, 0, b->words * 8, C.stream));
+        if (!C.evk_mult && k == "inner_product") throw std::runtime_error("bench_kernel: needs the relinearisation key");
+        double bytes = 0;
+        auto run = [&]() {
+            if (k == "ntt_fwd") { k_ntt_fwd(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
+            else if (k == "ntt_inv") { k_ntt_inv(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
+            else if (k == "inner_product") { k_inner_product(C.T, D, a->p, C.evk_mult, b->p, C.stream); bytes = (3.0 * D.beta + 2.0) * D.width * limb; }
+            else if (k == "modup_conv") { k_modup(C.T, D, b->p, b->p, a->p, C.stream); bytes = (double)(ell + D.beta * D.width) * limb; }
+            else if (k == "moddown_conv") { k_moddown_conv(C.T, D, b->p, a->p, C.stream); bytes = 2.0 * (D.K + ell) * limb; }
+            else if (k == "automorphism") { k_automorphism(C.T, 5, ell, a->p, b->p, C.stream); bytes = 2.0 * ell * limb; }
+            else if (k == "tensor") { k_tensor(C.T, ell, a->p, a->p + (size_t)ell * n, a->p, a->p + (size_t)ell * n, b->p, b->p + (size_t)ell * n, b->p + (size_t)2 * ell * n, C.stream); bytes = 7.0 * ell * limb; }
+            else if (k == "add") { k_binary(C.T, OP_ADD, ell, a->p, a->p + (size_t)ell * n, b->p, C.stream); bytes = 3.0 * ell * limb; }
+            else throw std::invalid_argument("bench_kernel: unknown kernel " + k);
+        };
+        run(); // warm-up
+        cudaEvent_t e0, e1;
+        FHE_CUDA(cudaEventCreate(&e0));
+        FHE_CUDA(cudaEventCreate(&e1));
+        FHE_CUDA(cudaEventRecord(e0, C.stream));
+        for (int r = 0; r < reps; r++) run();
+        FHE_CUDA(cudaEventRecord(e1, C.stream));
+        FHE_CUDA(cudaEventSynchronize(e1));
+        FHE_CUDA(cudaEventElapsedTime(ms, e0, e1));
+        FHE_CUDA(cudaGetLastError());
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (algo_bytes) *algo_bytes = bytes;
+    })
+}
+
+} // extern "C"

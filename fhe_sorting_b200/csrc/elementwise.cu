@@ -1,0 +1,157 @@
+// elementwise.cu — HBM-bound per-limb kernels: add/sub/mul, scalar ops, tensor product, plaintext product,
+// Galois automorphism gather, rescale lift/finish.  One thread handles two adjacent coefficients (128-bit
+// loads/stores); grid = (n / 2 / 256, limbs).  Algorithmic bytes per limb: 8n x (#inputs + #outputs).
+#include "kernels.h"
+#include "modarith.cuh"
+
+namespace fheb200 {
+
+constexpr int EW_THREADS = 256;
+typedef ulonglong2 v2;
+
+__device__ __forceinline__ v2 ld2(const u64 *p, size_t i) { return *reinterpret_cast<const v2 *>(p + i); }
+__device__ __forceinline__ void st2(u64 *p, size_t i, v2 v) { *reinterpret_cast<v2 *>(p + i) = v; }
+#define EW_INDEX                                                         \
+    const int limb = blockIdx.y;                                         \
+    const int j = (blockIdx.x * EW_THREADS + threadIdx.x) * 2;           \
+    if (j >= T.n) return;                                                \
+    const size_t x = (size_t)limb * T.n + j;
+
+static inline dim3 ew_grid(const DeviceTables &T, int limbs) { return dim3((T.n / 2 + EW_THREADS - 1) / EW_THREADS, limbs); }
+
+__global__ void __launch_bounds__(EW_THREADS) ew_binary(DeviceTables T, int op, const u64 *a, const u64 *b, u64 *o) {
+    EW_INDEX
+    const ModConst m = T.mc[limb];
+    v2 A = ld2(a, x), B = ld2(b, x), R;
+    if (op == OP_ADD) {
+        R.x = add_mod(A.x, B.x, m.q), R.y = add_mod(A.y, B.y, m.q);
+    } else if (op == OP_SUB) {
+        R.x = sub_mod(A.x, B.x, m.q), R.y = sub_mod(A.y, B.y, m.q);
+    } else {
+        R.x = mul_mod(A.x, B.x, m), R.y = mul_mod(A.y, B.y, m);
+    }
+    st2(o, x, R);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_negate(DeviceTables T, const u64 *a, u64 *o) {
+    EW_INDEX
+    const u64 q = T.mc[limb].q;
+    v2 A = ld2(a, x);
+    A.x = neg_mod(A.x, q), A.y = neg_mod(A.y, q);
+    st2(o, x, A);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_mul_scalar(DeviceTables T, const u64 *a, LimbScalars s, u64 *o) {
+    EW_INDEX
+    const u64 q = T.mc[limb].q, w = s.v[limb], ws = s.s[limb];
+    v2 A = ld2(a, x);
+    A.x = shoup_mul(A.x, w, ws, q), A.y = shoup_mul(A.y, w, ws, q);
+    st2(o, x, A);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_add_scalar(DeviceTables T, const u64 *a, LimbScalars s, u64 *o) {
+    EW_INDEX
+    const u64 q = T.mc[limb].q, w = s.v[limb];
+    v2 A = ld2(a, x);
+    A.x = add_mod(A.x, w, q), A.y = add_mod(A.y, w, q);
+    st2(o, x, A);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_mul_pt(DeviceTables T, const u64 *a0, const u64 *a1, const u64 *pt, u64 *o0,
+                                                        u64 *o1, int acc) {
+    EW_INDEX
+    const ModConst m = T.mc[limb];
+    v2 P = ld2(pt, x), A0 = ld2(a0, x), A1 = ld2(a1, x), R0, R1;
+    R0.x = mul_mod(A0.x, P.x, m), R0.y = mul_mod(A0.y, P.y, m);
+    R1.x = mul_mod(A1.x, P.x, m), R1.y = mul_mod(A1.y, P.y, m);
+    if (acc) {
+        v2 O0 = ld2(o0, x), O1 = ld2(o1, x);
+        R0.x = add_mod(R0.x, O0.x, m.q), R0.y = add_mod(R0.y, O0.y, m.q);
+        R1.x = add_mod(R1.x, O1.x, m.q), R1.y = add_mod(R1.y, O1.y, m.q);
+    }
+    st2(o0, x, R0);
+    st2(o1, x, R1);
+}
+// d0 = a0 b0 ; d1 = a0 b1 + a1 b0 ; d2 = a1 b1   (d1 through one 128-bit accumulation)
+__device__ __forceinline__ void tensor1(u64 a0, u64 a1, u64 b0, u64 b1, const ModConst &m, unsigned long long &d0,
+                                        unsigned long long &d1, unsigned long long &d2) {
+    d0 = mul_mod(a0, b0, m);
+    d2 = mul_mod(a1, b1, m);
+    Acc128 acc;
+    acc.mac(a0, b1);
+    acc.mac(a1, b0);
+    d1 = reduce128(acc.hi, acc.lo, m);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_tensor(DeviceTables T, const u64 *a0, const u64 *a1, const u64 *b0,
+                                                        const u64 *b1, u64 *d0, u64 *d1, u64 *d2) {
+    EW_INDEX
+    const ModConst m = T.mc[limb];
+    v2 A0 = ld2(a0, x), A1 = ld2(a1, x), B0 = ld2(b0, x), B1 = ld2(b1, x), D0, D1, D2;
+    tensor1(A0.x, A1.x, B0.x, B1.x, m, D0.x, D1.x, D2.x);
+    tensor1(A0.y, A1.y, B0.y, B1.y, m, D0.y, D1.y, D2.y);
+    st2(d0, x, D0);
+    st2(d1, x, D1);
+    st2(d2, x, D2);
+}
+// Galois automorphism in the evaluation domain (bit-reversed storage):
+//   out[rev(j)] = in[rev(((2j+1) g mod 2n) >> 1)].  A warp's 32 consecutive outputs come from one aligned
+//   32-word block of the input (only the high natural-order bits vary), so the gather stays coalesced.
+__global__ void __launch_bounds__(EW_THREADS) ew_automorphism(DeviceTables T, uint32_t g, const u64 *in, u64 *out) {
+    const int limb = blockIdx.y;
+    const uint32_t p = blockIdx.x * EW_THREADS + threadIdx.x;
+    if (p >= (uint32_t)T.n) return;
+    const int sh = 32 - T.logn;
+    uint32_t j = __brev(p) >> sh;
+    uint32_t idx = (((2u * j + 1u) * g) & (2u * T.n - 1u)) >> 1;
+    uint32_t src = __brev(idx) >> sh;
+    out[(size_t)limb * T.n + p] = in[(size_t)limb * T.n + src];
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_rescale_lift(DeviceTables T, int ell, const u64 *last, u64 *tmp) {
+    EW_INDEX
+    const ModConst m = T.mc[limb];
+    const u64 ql = T.mc[ell - 1].q, half = ql >> 1;
+    v2 V = ld2(last, j), R;
+    R.x = switch_modulus(V.x, ql, half, m), R.y = switch_modulus(V.y, ql, half, m);
+    st2(tmp, x, R);
+}
+__global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, const u64 *in, const u64 *tmp, LimbScalars s,
+                                                                u64 *o) {
+    EW_INDEX
+    const u64 q = T.mc[limb].q, w = s.v[limb], ws = s.s[limb];
+    v2 A = ld2(in, x), B = ld2(tmp, x);
+    A.x = shoup_mul(sub_mod(A.x, B.x, q), w, ws, q), A.y = shoup_mul(sub_mod(A.y, B.y, q), w, ws, q);
+    st2(o, x, A);
+}
+
+void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st) {
+    ew_binary<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, (int)op, a, b, out);
+}
+void k_negate(const DeviceTables &T, int ell, const u64 *a, u64 *out, cudaStream_t st) {
+    ew_negate<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, out);
+}
+void k_mul_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
+    ew_mul_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
+}
+void k_add_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
+    ew_add_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
+}
+void k_mul_pt(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *pt, u64 *o0, u64 *o1, int acc,
+              cudaStream_t st) {
+    ew_mul_pt<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, pt, o0, o1, acc);
+}
+void k_tensor(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *b0, const u64 *b1, u64 *d0, u64 *d1,
+              u64 *d2, cudaStream_t st) {
+    ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, b0, b1, d0, d1, d2);
+}
+void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, u64 *d0, u64 *d1, u64 *d2,
+                     cudaStream_t st) {
+    ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, a0, a1, d0, d1, d2);
+}
+void k_automorphism(const DeviceTables &T, uint32_t g, int limbs, const u64 *in, u64 *out, cudaStream_t st) {
+    ew_automorphism<<<dim3((T.n + EW_THREADS - 1) / EW_THREADS, limbs), EW_THREADS, 0, st>>>(T, g, in, out);
+}
+void k_rescale_lift(const DeviceTables &T, int ell, const u64 *last, u64 *tmp, cudaStream_t st) {
+    ew_rescale_lift<<<ew_grid(T, ell - 1), EW_THREADS, 0, st>>>(T, ell, last, tmp);
+}
+void k_rescale_finish(const DeviceTables &T, int ell_out, const u64 *in, const u64 *tmp, const LimbScalars &s, u64 *out,
+                      cudaStream_t st) {
+    ew_rescale_finish<<<ew_grid(T, ell_out), EW_THREADS, 0, st>>>(T, in, tmp, s, out);
+}
+
+} // namespace fheb200

@@ -1,0 +1,161 @@
+// engine.h — B200 RNS-CKKS evaluation engine: context, device-resident keys, ciphertext/plaintext objects
+// and the scheme operations the reference reaches through lbcrypto::CryptoContext<DCRTPoly>.
+// Level / scale bookkeeping follows OpenFHE's FLEXIBLEAUTOEXT mode: lazy rescale before the next
+// multiplication, exact real scaling factors per level, GetLevel() = number of dropped limbs.
+#pragma once
+#include <atomic>
+#include <complex>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "kernels.h"
+#include "params.h"
+
+namespace fheb200 {
+
+class Context;
+
+struct DevMem { // stream-ordered device allocation owned by a context
+    u64 *p = nullptr;
+    size_t words = 0;
+    Context *ctx = nullptr;
+    ~DevMem();
+};
+typedef std::shared_ptr<DevMem> Mem;
+
+struct Ciphertext {
+    Mem mem;          // [npoly][ell][n], evaluation domain
+    int npoly = 2;
+    int ell = 0;      // active Q limbs = L - level
+    int level = 0;    // dropped limbs
+    int nsd = 1;      // noise scale degree (1 or 2; 3 transiently never kept)
+    double scale = 0; // exact real scaling factor
+    int slots = 0;
+    u64 *poly(int i, int n) const { return mem->p + (size_t)i * ell * n; }
+};
+typedef std::shared_ptr<Ciphertext> Ct;
+
+struct Plaintext {
+    std::vector<std::complex<double>> vals; // slot values (kept so the plaintext can be re-encoded at any level)
+    int slots = 0;
+    int level = 0, nsd = 1;
+    double scale = 0;
+    int ell = 0;
+    Mem mem;           // [ell][n] evaluation domain (may be null for decode-only plaintexts)
+    size_t length = 0; // SetLength
+    double log_precision = 0;
+    std::vector<std::tuple<int, double, Mem>> alt; // re-encodings at other (limbs, scale), filled lazily
+};
+typedef std::shared_ptr<Plaintext> Pt;
+
+struct KeySet {
+    Mem s;            // secret key over L+K limbs (null on evaluation-only contexts)
+    Mem pk;           // [2][L][n]: b then a
+};
+typedef std::shared_ptr<KeySet> Keys;
+
+struct Precomp { // EvalFastRotationPrecompute result: ModUp'ed digits of c1
+    Mem digits;
+    int ell = 0;
+};
+
+class Context {
+  public:
+    static std::shared_ptr<Context> create(int logn, int depth, int scale_bits, int first_bits, int dnum, int batch,
+                                           int device);
+    ~Context();
+
+    std::shared_ptr<Params> P;
+    DeviceTables T;
+    int device = 0;
+    int batch = 0; // default slot count (CCParams::SetBatchSize)
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    std::recursive_mutex mu;
+    u64 seed = 0;
+    std::atomic<u64> nonce{1};
+
+    // ---- keys
+    Keys keygen(u64 seed);
+    void gen_mult_key(const Keys &k);
+    void gen_rot_keys(const Keys &k, const std::vector<int> &indices);
+    bool has_rot_key(uint32_t galois) const { return evk_rot.count(galois) != 0; }
+    size_t key_bytes() const;
+
+    // ---- encode / encrypt / decrypt
+    Pt make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots);
+    Mem encode_at(const Plaintext &pt, int ell, double scale); // (re-)encode at a given limb count and scale
+    Mem encoding_for(const Pt &pt, int ell, double scale);     // cached variant
+    Ct encrypt(const Keys &k, const Pt &pt);
+    Pt decrypt(const Keys &k, const Ct &ct);
+
+    // ---- arithmetic (all return fresh objects)
+    Ct clone(const Ct &a);
+    Ct add(const Ct &a, const Ct &b);
+    Ct sub(const Ct &a, const Ct &b);
+    Ct add_pt(const Ct &a, const Pt &p, bool negate_pt = false);
+    Ct add_const(const Ct &a, double c);
+    Ct negate(const Ct &a);
+    Ct mult(const Ct &a, const Ct &b);       // EvalMult / EvalMultAndRelinearize / EvalSquare (a.get()==b.get())
+    Ct mult_pt(const Ct &a, const Pt &p);
+    Ct mult_const(const Ct &a, double c);
+    Ct rotate(const Ct &a, int index);
+    std::shared_ptr<Precomp> fast_rotation_precompute(const Ct &a);
+    Ct fast_rotation(const Ct &a, int index, const std::shared_ptr<Precomp> &pre);
+    Ct add_many(const std::vector<Ct> &v);
+    Ct rescale(const Ct &a);                 // explicit ModReduce (one level)
+    Ct level_reduce(const Ct &a, int levels);
+
+    // ---- polynomial evaluation (poly_eval.cpp)
+    Ct eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, double a, double b);
+    Ct eval_chebyshev_linear(const Ct &x, const std::vector<double> &coeffs, double a, double b);
+    Ct eval_poly_linear(const Ct &x, const std::vector<double> &coeffs);
+
+    // ---- raw access for parity tests and benchmarks
+    const DevicePlan &plan(int ell);
+    const uint32_t *desc(const std::vector<uint32_t> &d);
+    Mem alloc(size_t words);
+    void sync();
+    u64 *evk_mult = nullptr;
+    std::map<uint32_t, u64 *> evk_rot;
+    size_t evk_words() const { return (size_t)P->beta(P->L) * 2 * (P->L + P->K) * P->n; }
+
+    // key switching core on raw device polys (c: ell limbs eval). Results written to out0/out1 (ell limbs each):
+    //   out0 = sigma_g(ks0 + add0), out1 = sigma_g(ks1 + add1)   (add may be null, g = 1 means no automorphism)
+    void modup(int ell, const u64 *c, u64 *digits);
+    void keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const u64 *add0, const u64 *add1, u64 *out0,
+                          u64 *out1, uint32_t galois);
+    void rescale_poly(int ell, int npoly, const u64 *in, u64 *out);
+
+    // scheme helpers
+    Ct mod_reduce(const Ct &a);
+    Ct mult_core_const(const Ct &a, double c);     // multiply by round(c * sf[level]); nsd += 1
+    void adjust_pair(Ct &a, Ct &b);                // AdjustLevelsAndDepthInPlace
+    void adjust_pair_to_one(Ct &a, Ct &b);         // AdjustLevelsAndDepthToOneInPlace
+    LimbScalars scalars_for(long double value, int ell, bool shoup) const;
+
+  private:
+    std::map<int, DevicePlan> plans_;
+    std::map<std::vector<uint32_t>, uint32_t *> descs_;
+    std::vector<void *> owned_;
+    void *owned_alloc(size_t bytes, const void *init);
+    u64 *gen_switch_key(u64 key_id, const u64 *s_old, const u64 *s_new);
+};
+
+void fft_special(std::vector<std::complex<double>> &v);
+void fft_special_inv(std::vector<std::complex<double>> &v);
+std::vector<double> chebyshev_coefficients(const std::function<double(double)> &f, double a, double b, int degree);
+
+#define FHE_CUDA(call)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t e__ = (call);                                                                            \
+        if (e__ != cudaSuccess)                                                                              \
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e__) + " at " #call);  \
+    } while (0)
+
+} // namespace fheb200

@@ -1,0 +1,164 @@
+// engine_arith.cu — EvalAdd / EvalSub / EvalMult (ct, plaintext, constant) with FLEXIBLEAUTOEXT alignment.
+// Reference call sites: src/comparison.cpp:13-38, src/sign.cpp:23-56, src/sort_algo.h:319-364,454-504,706-742.
+#include <cmath>
+#include <stdexcept>
+
+#include "engine.h"
+
+namespace fheb200 {
+
+#define LOCK                                           \
+    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    FHE_CUDA(cudaSetDevice(device))
+
+// bring x (shallower) to the level, degree and scale of t — restates OpenFHE's AdjustLevelsAndDepthInPlace
+static Ct raise_to(Context *C, Ct x, const Ct &t) {
+    const Params &P = *C->P;
+    const double scf1 = x->scale, scf = P.sf[x->level], q1 = (double)P.moduli[x->ell - 1];
+    if (x->nsd == 2) {
+        if (t->nsd == 2) {
+            x = C->mult_core_const(x, t->scale / scf1 * q1 / scf);
+            x = C->mod_reduce(x);
+            if (x->level < t->level) x = C->level_reduce(x, t->level - x->level);
+        } else if (x->level + 1 == t->level) {
+            x = C->mod_reduce(x);
+        } else {
+            x = C->mult_core_const(x, P.sf_big[t->level - 1] / scf1 * q1 / scf);
+            x = C->mod_reduce(x);
+            if (x->level + 1 < t->level) x = C->level_reduce(x, t->level - x->level - 1);
+            x = C->mod_reduce(x);
+        }
+    } else {
+        if (t->nsd == 2) {
+            x = C->mult_core_const(x, t->scale / scf1 / scf);
+            x = C->level_reduce(x, t->level - x->level);
+        } else {
+            x = C->mult_core_const(x, P.sf_big[t->level - 1] / scf1 / scf);
+            if (x->level + 1 < t->level) x = C->level_reduce(x, t->level - x->level - 1);
+            x = C->mod_reduce(x);
+        }
+    }
+    if (x.get() == nullptr || x->level != t->level || x->nsd != t->nsd)
+        throw std::logic_error("fheb200: level alignment failed");
+    if (x.use_count() > 1) x = std::make_shared<Ciphertext>(*x); // never mutate a shared object
+    x->scale = t->scale;
+    return x;
+}
+
+void Context::adjust_pair(Ct &a, Ct &b) {
+    if (a->level < b->level)
+        a = raise_to(this, a, b);
+    else if (b->level < a->level)
+        b = raise_to(this, b, a);
+    else if (a->nsd < b->nsd)
+        a = mult_core_const(a, 1.0);
+    else if (b->nsd < a->nsd)
+        b = mult_core_const(b, 1.0);
+}
+void Context::adjust_pair_to_one(Ct &a, Ct &b) {
+    adjust_pair(a, b);
+    if (a->nsd == 2) {
+        bool same = a.get() == b.get();
+        a = mod_reduce(a);
+        b = same ? a : mod_reduce(b);
+    }
+}
+
+static void check_pair(const Ct &a, const Ct &b) {
+    if (!a || !b) throw std::invalid_argument("fheb200: null ciphertext");
+    if (a->npoly != 2 || b->npoly != 2) throw std::runtime_error("fheb200: expected relinearised ciphertexts");
+}
+
+Ct Context::add(const Ct &a0, const Ct &b0) {
+    LOCK;
+    check_pair(a0, b0);
+    Ct a = a0, b = b0;
+    adjust_pair(a, b);
+    const int n = P->n;
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)2 * a->ell * n);
+    r->slots = std::max(a->slots, b->slots);
+    for (int p = 0; p < 2; p++) k_binary(T, OP_ADD, a->ell, a->poly(p, n), b->poly(p, n), r->poly(p, n), stream);
+    return r;
+}
+Ct Context::sub(const Ct &a0, const Ct &b0) {
+    LOCK;
+    check_pair(a0, b0);
+    Ct a = a0, b = b0;
+    adjust_pair(a, b);
+    const int n = P->n;
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)2 * a->ell * n);
+    r->slots = std::max(a->slots, b->slots);
+    for (int p = 0; p < 2; p++) k_binary(T, OP_SUB, a->ell, a->poly(p, n), b->poly(p, n), r->poly(p, n), stream);
+    return r;
+}
+Ct Context::add_many(const std::vector<Ct> &v) {
+    LOCK;
+    if (v.empty()) throw std::invalid_argument("EvalAddMany: empty input");
+    Ct acc = v[0];
+    for (size_t i = 1; i < v.size(); i++) acc = add(acc, v[i]);
+    return v.size() == 1 ? clone(acc) : acc;
+}
+
+Mem Context::encoding_for(const Pt &pt, int ell, double scale) {
+    if (pt->mem && pt->ell == ell && pt->scale == scale) return pt->mem;
+    for (auto &e : pt->alt)
+        if (std::get<0>(e) == ell && std::get<1>(e) == scale) return std::get<2>(e);
+    Mem m = encode_at(*pt, ell, scale);
+    if (pt->alt.size() >= 4) pt->alt.erase(pt->alt.begin());
+    pt->alt.emplace_back(ell, scale, m);
+    return m;
+}
+
+// ct + plaintext: the plaintext is (re-)encoded at exactly the ciphertext's limbs and scale
+Ct Context::add_pt(const Ct &a, const Pt &p, bool negate_pt) {
+    LOCK;
+    if (!a || !p) throw std::invalid_argument("EvalAdd: null operand");
+    const int n = P->n;
+    Mem enc = encoding_for(p, a->ell, a->scale);
+    Ct r = clone(a);
+    r->slots = std::max(a->slots, p->slots);
+    k_binary(T, negate_pt ? OP_SUB : OP_ADD, a->ell, r->poly(0, n), enc->p, r->poly(0, n), stream);
+    return r;
+}
+// ct * plaintext: ciphertext brought to degree 1, plaintext encoded at sf[level]; result degree 2
+Ct Context::mult_pt(const Ct &a0, const Pt &p) {
+    LOCK;
+    if (!a0 || !p) throw std::invalid_argument("EvalMult: null operand");
+    Ct a = a0->nsd == 2 ? mod_reduce(a0) : a0;
+    const int n = P->n;
+    const double ps = P->sf[a->level];
+    Mem enc = encoding_for(p, a->ell, ps);
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)2 * a->ell * n);
+    r->slots = std::max(a->slots, p->slots);
+    k_mul_pt(T, a->ell, a->poly(0, n), a->poly(1, n), enc->p, r->poly(0, n), r->poly(1, n), 0, stream);
+    r->nsd = a->nsd + 1;
+    r->scale = a->scale * ps;
+    return r;
+}
+// ct * ct with relinearisation (EvalMult, EvalMultAndRelinearize, EvalSquare)
+Ct Context::mult(const Ct &a0, const Ct &b0) {
+    LOCK;
+    check_pair(a0, b0);
+    if (!evk_mult) throw std::runtime_error("EvalMult: relinearisation key missing (call EvalMultKeyGen)");
+    Ct a = a0, b = b0;
+    adjust_pair_to_one(a, b);
+    const int n = P->n, ell = a->ell;
+    const DevicePlan &D = plan(ell);
+    Mem d = alloc((size_t)3 * ell * n);
+    u64 *d0 = d->p, *d1 = d->p + (size_t)ell * n, *d2 = d->p + (size_t)2 * ell * n;
+    k_tensor(T, ell, a->poly(0, n), a->poly(1, n), b->poly(0, n), b->poly(1, n), d0, d1, d2, stream);
+    Mem digits = alloc((size_t)D.beta * D.width * n);
+    modup(ell, d2, digits->p);
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)2 * ell * n);
+    r->slots = std::max(a->slots, b->slots);
+    keyswitch_digits(ell, digits->p, evk_mult, d0, d1, r->poly(0, n), r->poly(1, n), 1u);
+    r->nsd = a->nsd + b->nsd;
+    r->scale = a->scale * b->scale;
+    return r;
+}
+
+} // namespace fheb200

@@ -1,0 +1,158 @@
+// engine_ctx.cu — context lifetime: parameter tables in HBM, level plans, stream-ordered allocation.
+#include <cstring>
+#include <random>
+#include <stdexcept>
+
+#include "engine.h"
+
+namespace fheb200 {
+
+DevMem::~DevMem() {
+    if (p && ctx) cudaFreeAsync(p, ctx->stream);
+}
+
+Mem Context::alloc(size_t words) {
+    auto m = std::make_shared<DevMem>();
+    m->ctx = this;
+    m->words = words;
+    FHE_CUDA(cudaMallocAsync((void **)&m->p, words * sizeof(u64), stream));
+    return m;
+}
+void Context::sync() { FHE_CUDA(cudaStreamSynchronize(stream)); }
+
+void *Context::owned_alloc(size_t bytes, const void *init) {
+    void *d = nullptr;
+    FHE_CUDA(cudaMalloc(&d, bytes));
+    if (init) FHE_CUDA(cudaMemcpy(d, init, bytes, cudaMemcpyHostToDevice));
+    owned_.push_back(d);
+    return d;
+}
+
+std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, int first_bits, int dnum, int batch,
+                                         int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        throw std::runtime_error("fheb200: no CUDA device available (this engine has no CPU fallback)");
+    if (device < 0 || device >= count) throw std::invalid_argument("fheb200: bad device ordinal");
+    auto C = std::make_shared<Context>();
+    C->P = Params::create(logn, depth, scale_bits, first_bits, dnum);
+    const Params &P = *C->P;
+    if (P.L + P.K > MAX_LIMBS) throw std::invalid_argument("fheb200: L+K exceeds MAX_LIMBS");
+    if (batch <= 0) batch = P.n / 2;
+    if (batch > P.n / 2 || (batch & (batch - 1))) throw std::invalid_argument("fheb200: batch size must be a power of two <= n/2");
+    C->batch = batch;
+    C->device = device;
+    FHE_CUDA(cudaSetDevice(device));
+    FHE_CUDA(cudaStreamCreateWithFlags(&C->stream, cudaStreamNonBlocking));
+    cudaMemPool_t pool;
+    FHE_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t keep = UINT64_MAX;
+    FHE_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    C->seed = ((u64)std::random_device{}() << 32) ^ std::random_device{}();
+
+    const int F = P.L + P.K, n = P.n;
+    DeviceTables &T = C->T;
+    T.logn = logn, T.n = n, T.F = F;
+    T.mc = (ModConst *)C->owned_alloc(sizeof(ModConst) * F, P.mc.data());
+    std::vector<u64> ninv(2 * F);
+    for (int i = 0; i < F; i++) ninv[i] = P.n_inv[i], ninv[F + i] = P.n_inv_s[i];
+    T.ninv = (u64 *)C->owned_alloc(sizeof(u64) * 2 * F, ninv.data());
+    size_t tb = sizeof(u64) * (size_t)F * n;
+    T.tw = (u64 *)C->owned_alloc(tb, nullptr);
+    T.tws = (u64 *)C->owned_alloc(tb, nullptr);
+    T.twi = (u64 *)C->owned_alloc(tb, nullptr);
+    T.twis = (u64 *)C->owned_alloc(tb, nullptr);
+    std::vector<std::vector<u64>> w(F), ws(F), wi(F), wis(F);
+#pragma omp parallel for schedule(dynamic)
+    for (int i = 0; i < F; i++) P.twiddles(i, w[i], ws[i], wi[i], wis[i]);
+    for (int i = 0; i < F; i++) {
+        size_t off = (size_t)i * n, b = sizeof(u64) * n;
+        FHE_CUDA(cudaMemcpy(T.tw + off, w[i].data(), b, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.tws + off, ws[i].data(), b, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.twi + off, wi[i].data(), b, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.twis + off, wis[i].data(), b, cudaMemcpyHostToDevice));
+    }
+    return C;
+}
+
+Context::~Context() {
+    if (stream) cudaStreamSynchronize(stream);
+    if (evk_mult) cudaFree(evk_mult);
+    for (auto &kv : evk_rot) cudaFree(kv.second);
+    for (void *p : owned_) cudaFree(p);
+    if (stream && own_stream) cudaStreamDestroy(stream);
+}
+
+size_t Context::key_bytes() const { return (evk_rot.size() + (evk_mult ? 1 : 0)) * evk_words() * sizeof(u64); }
+
+const uint32_t *Context::desc(const std::vector<uint32_t> &d) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = descs_.find(d);
+    if (it != descs_.end()) return it->second;
+    uint32_t *p = (uint32_t *)owned_alloc(sizeof(uint32_t) * d.size(), d.data());
+    descs_[d] = p;
+    return p;
+}
+
+const DevicePlan &Context::plan(int ell) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = plans_.find(ell);
+    if (it != plans_.end()) return it->second;
+    const LevelPlan &H = P->plan(ell);
+    if (H.beta > 8) throw std::runtime_error("fheb200: more than 8 digits unsupported");
+    DevicePlan D;
+    D.ell = ell, D.beta = H.beta, D.width = H.width, D.K = P->K;
+    auto up64 = [&](const std::vector<u64> &v) { return (u64 *)owned_alloc(sizeof(u64) * v.size(), v.data()); };
+    D.qp = (int *)owned_alloc(sizeof(int) * H.qp.size(), H.qp.data());
+    for (int j = 0; j < H.beta; j++) {
+        D.dstart[j] = H.dstart[j], D.dsize[j] = H.dsize[j];
+        D.hat_inv[j] = up64(H.hat_inv[j]), D.hat_inv_s[j] = up64(H.hat_inv_s[j]), D.hat[j] = up64(H.hat[j]);
+    }
+    D.p_hat_inv = up64(H.p_hat_inv), D.p_hat_inv_s = up64(H.p_hat_inv_s), D.p_hat = up64(H.p_hat);
+    D.p_inv = up64(H.p_inv), D.p_inv_s = up64(H.p_inv_s);
+    std::vector<uint32_t> dq, dm, dp2, dq2;
+    for (int i = 0; i < ell; i++) dq.push_back(((uint32_t)i << 8) | (uint32_t)i);
+    for (int j = 0; j < H.beta; j++)
+        for (int t = 0; t < H.width; t++)
+            if (t < H.dstart[j] || t >= H.dstart[j] + H.dsize[j])
+                dm.push_back(((uint32_t)(j * H.width + t) << 8) | (uint32_t)H.qp[t]);
+    for (int b = 0; b < 2; b++) {
+        for (int k = 0; k < P->K; k++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
+        for (int i = 0; i < ell; i++) dq2.push_back(((uint32_t)(b * ell + i) << 8) | (uint32_t)i);
+    }
+    D.desc_q = (uint32_t *)desc(dq);
+    D.desc_modup = (uint32_t *)desc(dm);
+    D.n_modup = (int)dm.size();
+    D.desc_p2 = (uint32_t *)desc(dp2);
+    D.desc_q2 = (uint32_t *)desc(dq2);
+    return plans_.emplace(ell, D).first->second;
+}
+
+LimbScalars Context::scalars_for(long double value, int ell, bool shoup) const {
+    // round(value) as a signed 128-bit integer, reduced modulo each active modulus
+    LimbScalars s;
+    memset(&s, 0, sizeof(s));
+    bool neg = value < 0;
+    long double a = neg ? -value : value;
+    u128 mag;
+    if (a < 9.0e18L) {
+        mag = (u128)(u64)llroundl(a);
+    } else { // >= 2^62.9: the 64-bit mantissa already holds an integer
+        int ex;
+        long double mant = frexpl(a, &ex);
+        u64 mi = (u64)ldexpl(mant, 64);
+        if (ex > 126) throw std::overflow_error("fheb200: scaled constant exceeds 126 bits");
+        mag = ex >= 64 ? ((u128)mi << (ex - 64)) : ((u128)mi >> (64 - ex));
+    }
+    for (int i = 0; i < ell; i++) {
+        u64 q = P->moduli[i];
+        u64 r = (u64)(mag % q);
+        if (neg && r) r = q - r;
+        s.v[i] = r;
+        s.s[i] = shoup ? shoup_h(r, q) : 0;
+    }
+    return s;
+}
+
+} // namespace fheb200

@@ -1,0 +1,164 @@
+// engine_ops.cu — scheme operations: key switching pipeline, rotation (plain and hoisted), multiplication with
+// relinearisation, rescale, and the FLEXIBLEAUTOEXT level/scale alignment used by add/sub/mult.
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+
+#include "engine.h"
+
+namespace fheb200 {
+
+#define LOCK                                           \
+    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    FHE_CUDA(cudaSetDevice(device))
+
+static Ct new_like(Context *C, const Ct &a, int npoly, int ell) {
+    auto c = std::make_shared<Ciphertext>(*a);
+    c->npoly = npoly;
+    c->ell = ell;
+    c->level = C->P->L - ell;
+    c->mem = C->alloc((size_t)npoly * ell * C->P->n);
+    return c;
+}
+
+Ct Context::clone(const Ct &a) {
+    LOCK;
+    Ct c = new_like(this, a, a->npoly, a->ell);
+    FHE_CUDA(cudaMemcpyAsync(c->mem->p, a->mem->p, (size_t)a->npoly * a->ell * P->n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
+    return c;
+}
+
+// ------------------------------------------------------------------ key switching pipeline
+void Context::modup(int ell, const u64 *c, u64 *digits) {
+    const DevicePlan &D = plan(ell);
+    const int n = P->n;
+    Mem coef = alloc((size_t)ell * n);
+    FHE_CUDA(cudaMemcpyAsync(coef->p, c, (size_t)ell * n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
+    k_ntt_inv(T, coef->p, D.desc_q, ell, stream);
+    k_modup(T, D, coef->p, c, digits, stream);
+    k_ntt_fwd(T, digits, D.desc_modup, D.n_modup, stream);
+}
+void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const u64 *add0, const u64 *add1, u64 *out0,
+                               u64 *out1, uint32_t galois) {
+    const DevicePlan &D = plan(ell);
+    const int n = P->n;
+    Mem acc = alloc((size_t)2 * D.width * n), conv = alloc((size_t)2 * ell * n);
+    k_inner_product(T, D, digits, evk, acc->p, stream);
+    k_ntt_inv(T, acc->p, D.desc_p2, 2 * D.K, stream);
+    k_moddown_conv(T, D, acc->p, conv->p, stream);
+    k_ntt_fwd(T, conv->p, D.desc_q2, 2 * ell, stream);
+    k_moddown_finish(T, D, acc->p, conv->p, add0, add1, out0, out1, galois, stream);
+}
+
+Ct Context::rotate(const Ct &a, int index) {
+    LOCK;
+    if (a->npoly != 2) throw std::runtime_error("EvalRotate: relinearise first");
+    uint32_t g = P->galois_for_rotation(index);
+    if (g == 1) return clone(a);
+    auto it = evk_rot.find(g);
+    if (it == evk_rot.end()) throw std::runtime_error("EvalRotate: no evaluation key for rotation index " + std::to_string(index));
+    const int n = P->n, ell = a->ell;
+    const DevicePlan &D = plan(ell);
+    Mem digits = alloc((size_t)D.beta * D.width * n);
+    modup(ell, a->poly(1, n), digits->p);
+    Ct r = new_like(this, a, 2, ell);
+    keyswitch_digits(ell, digits->p, it->second, a->poly(0, n), nullptr, r->poly(0, n), r->poly(1, n), g);
+    return r;
+}
+std::shared_ptr<Precomp> Context::fast_rotation_precompute(const Ct &a) {
+    LOCK;
+    if (a->npoly != 2) throw std::runtime_error("EvalFastRotationPrecompute: relinearise first");
+    const DevicePlan &D = plan(a->ell);
+    auto pre = std::make_shared<Precomp>();
+    pre->ell = a->ell;
+    pre->digits = alloc((size_t)D.beta * D.width * P->n);
+    modup(a->ell, a->poly(1, P->n), pre->digits->p);
+    return pre;
+}
+Ct Context::fast_rotation(const Ct &a, int index, const std::shared_ptr<Precomp> &pre) {
+    LOCK;
+    uint32_t g = P->galois_for_rotation(index);
+    if (g == 1) return clone(a);
+    if (!pre || pre->ell != a->ell) throw std::runtime_error("EvalFastRotation: precomputation does not match the ciphertext");
+    auto it = evk_rot.find(g);
+    if (it == evk_rot.end()) throw std::runtime_error("EvalFastRotation: no evaluation key for rotation index " + std::to_string(index));
+    const int n = P->n;
+    Ct r = new_like(this, a, 2, a->ell);
+    keyswitch_digits(a->ell, pre->digits->p, it->second, a->poly(0, n), nullptr, r->poly(0, n), r->poly(1, n), g);
+    return r;
+}
+
+// ------------------------------------------------------------------ rescale / level reduce
+void Context::rescale_poly(int ell, int npoly, const u64 *in, u64 *out) {
+    const int n = P->n;
+    const LevelPlan &H = P->plan(ell);
+    LimbScalars qi;
+    memset(&qi, 0, sizeof(qi));
+    for (int i = 0; i < ell - 1; i++) qi.v[i] = H.ql_inv[i], qi.s[i] = H.ql_inv_s[i];
+    Mem last = alloc((size_t)npoly * n), tmp = alloc((size_t)npoly * (ell - 1) * n);
+    std::vector<uint32_t> dl, dt;
+    for (int p = 0; p < npoly; p++) {
+        dl.push_back(((uint32_t)p << 8) | (uint32_t)(ell - 1));
+        for (int i = 0; i < ell - 1; i++) dt.push_back(((uint32_t)(p * (ell - 1) + i) << 8) | (uint32_t)i);
+        FHE_CUDA(cudaMemcpyAsync(last->p + (size_t)p * n, in + ((size_t)p * ell + ell - 1) * n, n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
+    }
+    k_ntt_inv(T, last->p, desc(dl), npoly, stream);
+    for (int p = 0; p < npoly; p++) k_rescale_lift(T, ell, last->p + (size_t)p * n, tmp->p + (size_t)p * (ell - 1) * n, stream);
+    k_ntt_fwd(T, tmp->p, desc(dt), npoly * (ell - 1), stream);
+    for (int p = 0; p < npoly; p++)
+        k_rescale_finish(T, ell - 1, in + (size_t)p * ell * n, tmp->p + (size_t)p * (ell - 1) * n, qi, out + (size_t)p * (ell - 1) * n, stream);
+}
+Ct Context::mod_reduce(const Ct &a) {
+    LOCK;
+    if (a->ell < 2) throw std::runtime_error("rescale: no limbs left (multiplicative depth exhausted)");
+    Ct r = new_like(this, a, a->npoly, a->ell - 1);
+    rescale_poly(a->ell, a->npoly, a->mem->p, r->mem->p);
+    r->nsd = a->nsd - 1;
+    r->scale = a->scale / (double)P->moduli[a->ell - 1];
+    return r;
+}
+Ct Context::rescale(const Ct &a) { return mod_reduce(a); }
+Ct Context::level_reduce(const Ct &a, int levels) {
+    LOCK;
+    if (levels <= 0) return a;
+    if (a->ell - levels < 1) throw std::runtime_error("LevelReduce: not enough limbs");
+    const int n = P->n, ne = a->ell - levels;
+    Ct r = new_like(this, a, a->npoly, ne);
+    for (int p = 0; p < a->npoly; p++)
+        FHE_CUDA(cudaMemcpyAsync(r->poly(p, n), a->poly(p, n), (size_t)ne * n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
+    return r;
+}
+
+// ------------------------------------------------------------------ scalar helpers
+Ct Context::mult_core_const(const Ct &a, double c) { // EvalMultCoreInPlace: times round(c * sf[level])
+    LOCK;
+    const int n = P->n;
+    double sfl = P->sf[a->level];
+    LimbScalars s = scalars_for((long double)c * (long double)sfl, a->ell, true);
+    Ct r = new_like(this, a, a->npoly, a->ell);
+    for (int p = 0; p < a->npoly; p++) k_mul_scalar(T, a->ell, a->poly(p, n), s, r->poly(p, n), stream);
+    r->nsd = a->nsd + 1;
+    r->scale = a->scale * sfl;
+    return r;
+}
+Ct Context::mult_const(const Ct &a, double c) {
+    LOCK;
+    Ct x = a->nsd == 2 ? mod_reduce(a) : a;
+    return mult_core_const(x, c);
+}
+Ct Context::add_const(const Ct &a, double c) {
+    LOCK;
+    const int n = P->n;
+    LimbScalars s = scalars_for((long double)c * (long double)a->scale, a->ell, false);
+    Ct r = clone(a);
+    k_add_scalar(T, a->ell, r->poly(0, n), s, r->poly(0, n), stream);
+    return r;
+}
+Ct Context::negate(const Ct &a) {
+    LOCK;
+    Ct r = new_like(this, a, a->npoly, a->ell);
+    for (int p = 0; p < a->npoly; p++) k_negate(T, a->ell, a->poly(p, P->n), r->poly(p, P->n), stream);
+    return r;
+}
+
+} // namespace fheb200

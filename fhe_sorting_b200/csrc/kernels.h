@@ -1,0 +1,98 @@
+// kernels.h — launch wrappers of the sm_100a kernels (raw device pointers + stream; no scheme logic).
+// Polynomials are [limb][n] u64.  "desc" arrays describe a batch of limbs: desc[b] = (slot << 8) | qp,
+// slot = limb position inside the buffer, qp = modulus index (QP order).
+#pragma once
+#include <cuda_runtime.h>
+#include "params.h"
+
+namespace fheb200 {
+
+struct DeviceTables {            // resident per context
+    int logn = 0, n = 0, F = 0;  // F = L + K moduli
+    ModConst *mc = nullptr;      // [F]
+    u64 *tw = nullptr;           // forward twiddles  [F][n]
+    u64 *tws = nullptr;          // Shoup companions  [F][n]
+    u64 *twi = nullptr;          // inverse twiddles  [F][n]
+    u64 *twis = nullptr;         // Shoup companions  [F][n]
+    u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
+};
+
+constexpr int MAX_LIMBS = 64;    // upper bound on L+K (by-value kernel parameter blocks)
+struct LimbScalars {             // per-limb scalar + Shoup companion, passed by value
+    u64 v[MAX_LIMBS];
+    u64 s[MAX_LIMBS];
+};
+
+// ---- NTT (batched over limbs) ----
+void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st);
+void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st);
+
+// ---- elementwise over ell limbs; qp of limb i is qp0 + i ----
+enum BinOp { OP_ADD = 0, OP_SUB = 1, OP_MUL = 2 };
+void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st);
+void k_negate(const DeviceTables &T, int ell, const u64 *a, u64 *out, cudaStream_t st);
+void k_mul_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st);
+void k_add_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st);
+// out0/out1 += a0/a1 * pt (pt eval domain) ; accumulate = 0 writes, 1 adds
+void k_mul_pt(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *pt, u64 *o0, u64 *o1,
+              int accumulate, cudaStream_t st);
+void k_tensor(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *b0, const u64 *b1, u64 *d0,
+              u64 *d1, u64 *d2, cudaStream_t st);
+void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, u64 *d0, u64 *d1, u64 *d2,
+                     cudaStream_t st);
+// Galois automorphism (eval domain, bit-reversed order) on `limbs` limbs
+void k_automorphism(const DeviceTables &T, uint32_t galois, int limbs, const u64 *in, u64 *out, cudaStream_t st);
+
+// ---- rescale ----
+// last: coefficient-domain last limb [n]; tmp[ell-1][n] <- centred lift of last into q_i (then NTT it)
+void k_rescale_lift(const DeviceTables &T, int ell, const u64 *last_coeff, u64 *tmp, cudaStream_t st);
+// out_i = (in_i - tmp_i) * ql_inv_i
+void k_rescale_finish(const DeviceTables &T, int ell_out, const u64 *in, const u64 *tmp, const LimbScalars &qlinv,
+                      u64 *out, cudaStream_t st);
+
+// ---- hybrid key switching ----
+struct DevicePlan {              // device copy of a LevelPlan
+    int ell = 0, beta = 0, width = 0, K = 0;
+    int *qp = nullptr;           // [width]
+    int dstart[8] = {0}, dsize[8] = {0};
+    u64 *hat_inv[8] = {nullptr}, *hat_inv_s[8] = {nullptr}, *hat[8] = {nullptr}; // per digit
+    u64 *p_hat_inv = nullptr, *p_hat_inv_s = nullptr, *p_hat = nullptr, *p_inv = nullptr, *p_inv_s = nullptr;
+    uint32_t *desc_q = nullptr;        // NTT batch: Q limbs 0..ell-1 in place
+    uint32_t *desc_modup = nullptr;    // NTT batch over digits buffer, skipping own-digit limbs
+    int n_modup = 0;
+    uint32_t *desc_p2 = nullptr;       // iNTT batch: P limbs of two stacked accumulators [2][width]
+    uint32_t *desc_q2 = nullptr;       // NTT batch: Q limbs of two stacked [2][ell] buffers
+};
+// digits[j][t][k] for t outside digit j <- base conversion of coef (coefficient domain, ell limbs);
+// own-digit limbs <- copy of c_eval.
+void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits,
+             cudaStream_t st);
+// acc[2][width][n] = sum_j digits[j] * evk[j][{b,a}]   (evk stored at full chain: [digit][2][F][n])
+void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc,
+                     cudaStream_t st);
+// conv[2][ell][n] (coefficient domain) <- base conversion of the (already inverse-NTT'd) P limbs of acc
+void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st);
+// out_b = (acc_b[Q part] - conv_b) * P^-1 (+ add0 on b = 0 if non-null); optional automorphism on the way out
+void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *conv, const u64 *add0,
+                      const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st);
+
+// ---- samplers / encode helpers ----
+void k_sample_uniform(const DeviceTables &T, u64 seed, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st);
+enum SmallKind { SMALL_TERNARY = 0, SMALL_GAUSS = 1 };
+void k_sample_small(const DeviceTables &T, SmallKind kind, u64 seed, u64 stream, int *out, cudaStream_t st);
+// signed small ints [n] -> residues for the limbs listed in desc (slot,qp); coefficient domain
+void k_expand_small(const DeviceTables &T, const int *small, u64 *out, const uint32_t *d_desc, int count,
+                    cudaStream_t st);
+// 128-bit signed coefficients (lo,hi pairs) at stride `gap` -> residues on Q limbs 0..ell-1, zero elsewhere
+void k_expand_i128(const DeviceTables &T, const u64 *coef_lohi, int ncoef, int gap, int ell, u64 *out,
+                   cudaStream_t st);
+// b = e - a*s_new + [limb in digit] * pmod * s_old   over F limbs (one digit of a switching key)
+void k_evk_finish(const DeviceTables &T, int F, const u64 *a, const u64 *e, const u64 *s_new, const u64 *s_old,
+                  const LimbScalars &pmod, u64 *b, cudaStream_t st);
+// c0 = pkb*v + e0 + pt ; c1 = pka*v + e1
+void k_encrypt_finish(const DeviceTables &T, int ell, const u64 *pkb, const u64 *pka, const u64 *v, const u64 *e0,
+                      const u64 *e1, const u64 *pt, u64 *c0, u64 *c1, cudaStream_t st);
+// m = c0 + c1*s on k limbs
+void k_decrypt_core(const DeviceTables &T, int k, const u64 *c0, const u64 *c1, const u64 *s, u64 *m, cudaStream_t st);
+
+} // namespace fheb200

@@ -1,0 +1,81 @@
+// modarith.cuh — 64-bit modular arithmetic for sm_100a integer pipes (IMAD.WIDE based 64x64 products).
+// All moduli satisfy q < 2^61, so lazy values up to 4q fit in a word (Harvey butterflies).
+#pragma once
+#include <cstdint>
+#include "params.h"
+
+namespace fheb200 {
+
+__device__ __forceinline__ u64 mulhi64(u64 a, u64 b) { return __umul64hi(a, b); }
+
+// a*w mod q with precomputed ws = floor(w 2^64 / q). Any 64-bit a; result in [0, 2q).
+__device__ __forceinline__ u64 shoup_lazy(u64 a, u64 w, u64 ws, u64 q) {
+    u64 h = mulhi64(a, ws);
+    return a * w - h * q;
+}
+// fully reduced variant
+__device__ __forceinline__ u64 shoup_mul(u64 a, u64 w, u64 ws, u64 q) {
+    u64 r = shoup_lazy(a, w, ws, q);
+    return r >= q ? r - q : r;
+}
+__device__ __forceinline__ u64 add_mod(u64 a, u64 b, u64 q) {
+    u64 s = a + b;
+    return s >= q ? s - q : s;
+}
+__device__ __forceinline__ u64 sub_mod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }
+__device__ __forceinline__ u64 neg_mod(u64 a, u64 q) { return a ? q - a : 0; }
+
+// single word x (any 64-bit value) mod q
+__device__ __forceinline__ u64 reduce64(u64 x, const ModConst &m) {
+    u64 r = x - mulhi64(x, m.r64) * m.q;
+    r = r >= m.q ? r - m.q : r;
+    return r >= m.q ? r - m.q : r;
+}
+// (hi:lo) mod q for any 128-bit value: hi is folded through 2^64 mod q
+__device__ __forceinline__ u64 reduce128(u64 hi, u64 lo, const ModConst &m) {
+    u64 h = reduce64(hi, m);
+    u64 t = shoup_mul(h, m.c64, m.c64s, m.q);
+    u64 l = reduce64(lo, m);
+    return add_mod(t, l, m.q);
+}
+// Barrett product of two reduced operands (a, b < q)
+__device__ __forceinline__ u64 mul_mod(u64 a, u64 b, const ModConst &m) {
+    u64 lo = a * b, hi = mulhi64(a, b);
+    u64 z1 = (hi << (65 - m.bits)) | (lo >> (m.bits - 1)); // z >> (bits-1), fits: z < 2^(2 bits)
+    u64 r = lo - mulhi64(z1, m.mu) * m.q;
+    r = r >= m.q ? r - m.q : r;
+    return r >= m.q ? r - m.q : r;
+}
+// 128-bit accumulator for lazy inner products (sum of < 2^4 products of 61-bit values)
+struct Acc128 {
+    u64 lo, hi;
+    __device__ __forceinline__ Acc128() : lo(0), hi(0) {}
+    __device__ __forceinline__ void mac(u64 a, u64 b) {
+        u64 pl = a * b, ph = mulhi64(a, b);
+        lo += pl;
+        hi += ph + (lo < pl);
+    }
+};
+
+// centred lift of x mod q_from (half = q_from >> 1) into modulus q_to
+__device__ __forceinline__ u64 switch_modulus(u64 x, u64 q_from, u64 half, const ModConst &to) {
+    if (x > half) {
+        u64 d = reduce64(q_from - x, to);
+        return d ? to.q - d : 0;
+    }
+    return reduce64(x, to);
+}
+
+// counter-based generator shared with the oracle (spec: DESIGN.md "Randomness")
+__host__ __device__ __forceinline__ u64 mix64(u64 z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ u64 rng_u64(u64 seed, u64 stream, u64 idx, u64 word) {
+    u64 a = mix64(seed ^ (0x9E3779B97F4A7C15ULL * (stream + 1)));
+    u64 b = mix64(a + idx);
+    return mix64(b + 0xD1B54A32D192ED03ULL * (word + 1));
+}
+
+} // namespace fheb200

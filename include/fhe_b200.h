@@ -1,0 +1,147 @@
+/*
+ * fhe_b200.h — C ABI of the B200 RNS-CKKS engine (libfheb200.so).
+ *
+ * This is the drop-in boundary for the hot path of oksuman/FHE-Sorting: the subset of OpenFHE's
+ * lbcrypto::CryptoContext<DCRTPoly> API that the reference's host code calls.  Each entry
+ * point names the OpenFHE method it replaces and one reference call site (paths relative to the reference
+ * repository).  The header-only C++ shim under fhe_sorting_b200/shim/ re-exposes these as namespace
+ * lbcrypto so that src/sort_algo.h, rotation.h, sign.cpp, comparison.cpp, encryption.cpp compile against it
+ * (binding shown in INTEGRATION.md).
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure; fheb200_last_error() returns a
+ * thread-local message.  Handles are reference counted; *_release drops one reference.  Results are fresh
+ * handles (the reference's *InPlace calls are expressed in the shim as "replace the handle").
+ * Plain pointers and sizes only; no CUDA or torch types (streams travel as void*).
+ * There is no CPU fallback: context creation fails when no CUDA device is present.
+ */
+#ifndef FHE_B200_H
+#define FHE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fheb200_ctx fheb200_ctx;   /* lbcrypto::CryptoContext<DCRTPoly>          */
+typedef struct fheb200_keys fheb200_keys; /* lbcrypto::KeyPair<DCRTPoly> (pk [+ sk])     */
+typedef struct fheb200_ct fheb200_ct;     /* lbcrypto::Ciphertext<DCRTPoly>              */
+typedef struct fheb200_pt fheb200_pt;     /* lbcrypto::Plaintext                         */
+typedef struct fheb200_pre fheb200_pre;   /* std::shared_ptr<std::vector<DCRTPoly>> from EvalFastRotationPrecompute */
+
+const char *fheb200_last_error(void);
+const char *fheb200_version(void);
+
+/* ---- context: CCParams<CryptoContextCKKSRNS> setters + GenCryptoContext (tests/DirectSortTest.cpp:24-41) ---- */
+typedef struct {
+    int log_ring_dim;    /* SetRingDim(1 << log_ring_dim)            */
+    int mult_depth;      /* SetMultiplicativeDepth                   */
+    int scaling_mod_size;/* SetScalingModSize                        */
+    int first_mod_size;  /* SetFirstModSize (OpenFHE default 60)     */
+    int batch_size;      /* SetBatchSize (0 = ring_dim / 2)          */
+    int num_large_digits;/* OpenFHE default 3                        */
+    int device;          /* CUDA device ordinal                      */
+} fheb200_params;
+int fheb200_ctx_create(const fheb200_params *p, fheb200_ctx **out);
+int fheb200_ctx_release(fheb200_ctx *ctx);
+/* run every later operation of this context on an existing CUDA stream (cudaStream_t passed as void*) */
+int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *cuda_stream);
+int fheb200_ctx_sync(fheb200_ctx *ctx);
+/* GetRingDimension / GetCyclotomicOrder (src/rotation.h:262, src/sort_algo.h:80) and chain geometry */
+int fheb200_ctx_info(fheb200_ctx *ctx, int *ring_dim, int *num_q, int *num_p, int *digit_size, int *batch);
+int fheb200_ctx_modulus(fheb200_ctx *ctx, int qp_index, uint64_t *q, uint64_t *psi);
+int fheb200_ctx_scaling_factor(fheb200_ctx *ctx, int level, double *sf, double *sf_big);
+int fheb200_ctx_key_bytes(fheb200_ctx *ctx, uint64_t *bytes);
+/* host-only: the modulus chain for a parameter set, without touching a GPU (used by CPU-side tests) */
+int fheb200_params_chain(const fheb200_params *p, uint64_t *moduli, uint64_t *psi, int capacity, int *num_q, int *num_p,
+                         int *digit_size);
+
+/* ---- keys: KeyGen / EvalMultKeyGen / EvalRotateKeyGen (tests/DirectSortTest.cpp:43-47) ---- */
+int fheb200_keygen(fheb200_ctx *ctx, uint64_t seed, fheb200_keys **out);
+int fheb200_keys_release(fheb200_keys *k);
+int fheb200_eval_mult_keygen(fheb200_ctx *ctx, fheb200_keys *k);
+int fheb200_eval_rotate_keygen(fheb200_ctx *ctx, fheb200_keys *k, const int *indices, size_t count);
+
+/* ---- encode / encrypt / decrypt ---- */
+/* MakeCKKSPackedPlaintext(values, noiseScaleDeg, level, nullptr, slots) (src/sort_algo.h:317,341,609,706) */
+int fheb200_make_packed_plaintext(fheb200_ctx *ctx, const double *values, size_t count, int noise_scale_deg, int level,
+                                  int slots, fheb200_pt **out);
+int fheb200_pt_release(fheb200_pt *pt);
+/* GetRealPackedValue / SetLength / GetLogPrecision (src/encryption.cpp:20, src/encryption.h:41) */
+int fheb200_pt_values(fheb200_pt *pt, double *out, size_t capacity, size_t *count);
+int fheb200_pt_set_length(fheb200_pt *pt, size_t length);
+int fheb200_pt_log_precision(fheb200_pt *pt, double *bits);
+/* Encrypt(publicKey, plaintext) (src/encryption.cpp:10) ; Decrypt(secretKey, ct, &pt) (src/encryption.cpp:19) */
+int fheb200_encrypt(fheb200_ctx *ctx, fheb200_keys *k, fheb200_pt *pt, fheb200_ct **out);
+int fheb200_decrypt(fheb200_ctx *ctx, fheb200_keys *k, fheb200_ct *ct, fheb200_pt **out);
+
+/* ---- ciphertext object: Clone / GetLevel / GetSlots / SetSlots (src/sort_algo.h:429,501,614) ---- */
+int fheb200_ct_release(fheb200_ct *ct);
+int fheb200_ct_clone(fheb200_ctx *ctx, fheb200_ct *ct, fheb200_ct **out);
+int fheb200_ct_info(fheb200_ct *ct, int *level, int *noise_scale_deg, int *slots, int *num_limbs, double *scale);
+int fheb200_ct_set_slots(fheb200_ct *ct, int slots);
+
+/* ---- arithmetic ---- */
+/* EvalAdd / EvalSub / EvalAddInPlace(ct, ct) (src/sort_algo.h:454,495 ; src/comparison.cpp:13) */
+int fheb200_eval_add(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
+int fheb200_eval_sub(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
+/* EvalAdd(ct, pt) / EvalSub(ct, pt) / EvalSub(pt, ct) (src/sort_algo.h:611,622,708,720) */
+int fheb200_eval_add_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
+int fheb200_eval_sub_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
+/* EvalAdd(ct, double) / EvalSub(ct, double) (src/comparison.cpp:19,29-30 ; src/sort_algo.h:504) */
+int fheb200_eval_add_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out);
+/* EvalNegate (src/mehp24/mehp24_utils.h) */
+int fheb200_eval_negate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
+/* EvalAddMany (src/sort_algo.h:364) */
+int fheb200_eval_add_many(fheb200_ctx *ctx, fheb200_ct *const *cts, size_t count, fheb200_ct **out);
+/* EvalMult(ct, ct) / EvalMultAndRelinearize / EvalSquare when a == b (src/sign.cpp:23-33 ; src/sort_algo.h:730) */
+int fheb200_eval_mult(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
+/* EvalMult(ct, pt) (src/sort_algo.h:319,344,359,576) */
+int fheb200_eval_mult_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
+/* EvalMult(ct, double) / EvalMultInPlace(ct, double) (src/sign.cpp:26-30 ; src/sort_algo.h:723) */
+int fheb200_eval_mult_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out);
+/* explicit rescale (ModReduce) — a no-op at the OpenFHE API level in FLEXIBLEAUTOEXT, exposed for tests */
+int fheb200_eval_rescale(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
+
+/* ---- rotation ---- */
+/* EvalRotate(ct, index) (src/rotation.h:224,231,350) */
+int fheb200_eval_rotate(fheb200_ctx *ctx, fheb200_ct *a, int index, fheb200_ct **out);
+/* EvalFastRotationPrecompute(ct) / EvalFastRotation(ct, index, M, precomp) (src/rotation.h:286,344-346) */
+int fheb200_fast_rotation_precompute(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pre **out);
+int fheb200_pre_release(fheb200_pre *pre);
+int fheb200_eval_fast_rotation(fheb200_ctx *ctx, fheb200_ct *a, int index, fheb200_pre *pre, fheb200_ct **out);
+int fheb200_has_rotation_key(fheb200_ctx *ctx, int index, int *present);
+
+/* ---- polynomial evaluation ---- */
+/* EvalChebyshevSeries / EvalChebyshevSeriesPS(ct, coeffs, a, b) (src/sort_algo.h:629,728 ; src/sign.cpp:76,448) */
+int fheb200_eval_chebyshev_series(fheb200_ctx *ctx, fheb200_ct *x, const double *coeffs, size_t count, double a, double b,
+                                  fheb200_ct **out);
+/* EvalPolyLinear(ct, coeffs) (src/mehp24/mehp24_utils.cpp:256-259) */
+int fheb200_eval_poly(fheb200_ctx *ctx, fheb200_ct *x, const double *coeffs, size_t count, fheb200_ct **out);
+/* lbcrypto::EvalChebyshevCoefficients(f, a, b, degree) (utils/generate_cheb_coeffs.cpp:17); host only */
+int fheb200_chebyshev_coefficients(double (*f)(double, void *), void *user, double a, double b, int degree, double *out);
+
+/* ---- raw RNS access: parity tests against the oracle and the primitive micro-benchmarks ----
+ * Polynomials are uint64 [limb][ring_dim] host arrays, limb i reduced mod modulus i (evaluation domain). */
+int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words_each);
+int fheb200_ct_import(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int num_limbs, int noise_scale_deg,
+                      double scale, int slots, fheb200_ct **out);
+int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t words);
+/* keys: which = 0 secret [L+K][n] ; 1 public b [L][n] ; 2 public a [L][n] */
+int fheb200_keys_export(fheb200_ctx *ctx, fheb200_keys *k, int which, uint64_t *out, size_t words);
+/* evaluation key [digit][2][L+K][n]; galois = 0 selects the relinearisation key */
+int fheb200_evk_export(fheb200_ctx *ctx, uint32_t galois, uint64_t *out, size_t words);
+int fheb200_galois_for_rotation(fheb200_ctx *ctx, int index, uint32_t *galois);
+/* single primitives on host buffers (H2D, kernel, D2H) */
+int fheb200_raw_ntt(fheb200_ctx *ctx, int inverse, int qp_index, uint64_t *poly);
+int fheb200_raw_automorphism(fheb200_ctx *ctx, uint32_t galois, int limbs, const uint64_t *in, uint64_t *out);
+int fheb200_raw_modup(fheb200_ctx *ctx, int num_limbs, const uint64_t *c, uint64_t *digits, size_t digit_words);
+int fheb200_raw_rescale(fheb200_ctx *ctx, int num_limbs, const uint64_t *in, uint64_t *out);
+/* timing loops for bench.py: `reps` back-to-back launches on the context stream with inputs resident in HBM;
+ * returns the elapsed device time in milliseconds measured with CUDA events on that stream. */
+int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms);
+int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int num_limbs, int reps, float *ms, double *algo_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
