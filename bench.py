@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""bench.py — key-switch rotations per second (BASELINE.json metric, configs[1]) on the DirectSort N=1024 parameter set.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one pass of EvalRotate over ROT_PER_STEP distinct rotation indices of one fresh ciphertext (ring 2^17,
+depth 39, scale 40 bits: L = 41 Q limbs, K P limbs, dnum 3 — reference src/sort_algo.h:87-201 for N = 1024, the
+rotation pattern of constructRank's baby steps, src/sort_algo.h:425-431).  Each index streams its own 300 MiB
+evaluation key, so the working set (5 GiB of keys) is far larger than the 126 MB L2.
+
+value      rotations/s over all ranks, ciphertext and keys resident in HBM, CUDA events on the engine's stream
+e2e        same step through the C ABI with HOST ciphertext buffers: fheb200_ct_import (pinned host -> HBM),
+           ROT_PER_STEP x fheb200_eval_rotate, fheb200_ct_export of the last result (HBM -> host)
+roofline   dominant kernel of the step, algorithmic bytes / CUDA-event time, against MEASURED_PEAKS.json
+cpu_baseline  the CPU oracle (a port of the OpenFHE algorithm; OpenFHE itself is absent) on the host cores
+Multi-GPU: rotations of a sort are independent work items; keys are replicated, every rank rotates its own
+ciphertexts, no data-path collective ("weak" scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOGN, DEPTH, SCALE_BITS, FIRST_BITS, DNUM = 17, 39, 40, 60, 3
+ROT_PER_STEP = 16
+INDICES = list(range(1, ROT_PER_STEP + 1))
+SEED = 1170
+METRIC = "key-switch rotations/sec (EvalRotate, ring 2^17, 41 limbs, DirectSort N=1024 parameters)"
+UNIT = "rotations/s"
+
+
+def workload_config(extra=None):
+    c = {"workload": "EvalRotate microbench (RotationBenchmark BM_Rotations pattern) at the DirectSort N=1024 "
+                     "CKKS parameters: ring 2^17, depth 39, scale 40, dnum 3, fresh ciphertext (41 limbs), "
+                     "%d distinct rotation indices per step" % ROT_PER_STEP,
+         "rotations_per_step": ROT_PER_STEP, "log_ring_dim": LOGN, "mult_depth": DEPTH, "scaling_mod_size": SCALE_BITS,
+         "l2": "inputs larger than L2 (each rotation streams its own ~300 MiB key)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def algo_bytes_rotate(n, ell, K, alpha):
+    """read c0,c1 + stream beta digit keys of 2 polys x (ell+K) limbs + write c0',c1'."""
+    beta = (ell + alpha - 1) // alpha
+    return 8.0 * n * (4 * ell + 2 * beta * (ell + K))
+
+
+def cpu_rotations(nrot, threads, c0=None, c1=None, check=None):
+    """Time `nrot` EvalRotate calls of the CPU oracle at the bench parameters; optional parity check."""
+    from oracle.oracle import Oracle
+    orc = Oracle(LOGN, DEPTH, SCALE_BITS, FIRST_BITS, DNUM, threads=threads)
+    s = orc.keygen_secret(SEED)
+    if c0 is None:
+        rng = np.random.default_rng(1)
+        c0, c1 = orc.random_poly(rng, orc.L), orc.random_poly(rng, orc.L)
+    g = orc.galois(1)
+    evk = orc.keygen_rot(SEED, g, s)
+    orc.rotate(g, c0, c1, evk)  # warm-up (page in tables)
+    t0 = time.perf_counter()
+    for _ in range(nrot):
+        r0, r1 = orc.rotate(g, c0, c1, evk)
+    dt = time.perf_counter() - t0
+    ok = None
+    if check is not None:
+        ok = bool(np.array_equal(r0, check[0]) and np.array_equal(r1, check[1]))
+    return nrot / dt, ok
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the path's CPU implementation on the host cores.  The reference's arithmetic is OpenFHE, which
+    is neither vendored nor installed (no oracle/_ref), so this times the oracle port with every host thread."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = 1  # bounded sample: one EvalRotate per step
+    from oracle.oracle import Oracle
+    orc = Oracle(LOGN, DEPTH, SCALE_BITS, FIRST_BITS, DNUM, threads=cores)
+    s = orc.keygen_secret(SEED)
+    rng = np.random.default_rng(1)
+    c0, c1 = orc.random_poly(rng, orc.L), orc.random_poly(rng, orc.L)
+    g = orc.galois(1)
+    evk = orc.keygen_rot(SEED, g, s)
+    for _ in range(max(1, args.warmup)):
+        orc.rotate(g, c0, c1, evk)
+    t0 = time.perf_counter()
+    for _ in range(args.steps * per_step):
+        orc.rotate(g, c0, c1, evk)
+    dt = time.perf_counter() - t0
+    v = args.steps * per_step / dt
+    sample = ("bounded sample: %d EvalRotate per step (not %d) at the full parameter set (41 limbs), OpenMP over "
+              "limbs" % (per_step, ROT_PER_STEP))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import fhe_sorting_b200 as F
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    ctx = F.Context(LOGN, DEPTH, SCALE_BITS, FIRST_BITS, batch=0, dnum=DNUM, device=local_rank)
+    keys = ctx.keygen(SEED)
+    ctx.eval_rotate_keygen(keys, INDICES)
+    ctx.eval_mult_keygen(keys)
+    rng = np.random.default_rng(100 + rank)
+    ct = ctx.encrypt(keys, ctx.make_plaintext(rng.uniform(-1, 1, 1024), 1, 0, 1024))
+    ell, n, K, alpha = ct.limbs, ctx.n, ctx.K, ctx.alpha
+    ctx.sync()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    # ---- device-resident throughput
+    ctx.bench_rotations(ct, INDICES, max(3, args.warmup))
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = F.launch_count()
+    if rank == 0:
+        print("launches before the timed region: %d" % l0, file=sys.stderr)
+    ms = ctx.bench_rotations(ct, INDICES, args.steps)
+    launches = F.launch_count() - l0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * ROT_PER_STEP * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers (pinned)
+    pin = [torch.empty((ell, n), dtype=torch.int64).pin_memory() for _ in range(4)]
+    h_in0, h_in1, h_out0, h_out1 = [p.numpy().view(np.uint64) for p in pin]
+    ctx.ct_export(ct, out=(h_in0, h_in1))
+    info = ct.info()
+
+    def e2e_step():
+        c = ctx.ct_import(h_in0, h_in1, info["nsd"], info["scale"], info["slots"])
+        r = None
+        for i in INDICES:
+            r = ctx.rotate(c, i)
+        ctx.ct_export(r, out=(h_out0, h_out1))
+
+    for _ in range(max(3, args.warmup)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = world * ROT_PER_STEP * args.steps / float(dt.item())
+    limb_bytes = 2 * ell * n * 8
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel roofline (isolated kernels, CUDA events inside the library, inputs > L2)
+    peak, peak_src = peaks()
+    D = ctx.beta(ell) * (ell + K)
+    per_rot = {  # launches-equivalents per EvalRotate, in units of one bench_kernel call at `ell`
+        "ntt_fwd": (D - ell + 2 * ell) / ell, "ntt_inv": (ell + 2 * K) / ell, "inner_product": 1.0,
+        "modup_conv": 1.0, "moddown_conv": 1.0,
+    }
+    kernels = {}
+    for name in per_rot:
+        reps = 20
+        kms, kb = ctx.bench_kernel(name, ell, reps)
+        kms /= reps
+        kernels[name] = {"ms": kms, "algo_bytes": kb, "gbs": kb / (kms * 1e-3) / 1e9,
+                         "share_of_rotate": kms * per_rot[name] / (ms / (ROT_PER_STEP * args.steps))}
+    top = max(kernels, key=lambda k: kernels[k]["share_of_rotate"])
+    rot_ms = ms / (ROT_PER_STEP * args.steps)
+    ab = algo_bytes_rotate(n, ell, K, alpha)
+    roofline = {"bound": "hbm", "kernel": top, "achieved": kernels[top]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kernels[top]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                "kernels": kernels,
+                "whole_rotate": {"algo_bytes": ab, "ms": rot_ms, "gbs": ab / (rot_ms * 1e-3) / 1e9,
+                                 "frac": ab / (rot_ms * 1e-3) / 1e9 / peak}}
+
+    # ---- CPU baseline (oracle port) on a bounded sample + full-size parity of one rotation
+    cores = os.cpu_count() or 1
+    c0, c1 = ctx.ct_export(ct)
+    chk = ctx.ct_export(ctx.rotate(ct, 1))
+    cpu_v, parity = cpu_rotations(3, cores, c0, c1, chk)
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic", "config": workload_config({"key_bytes_resident": ctx.key_bytes()}),
+        "clocks": clocks, "gpu_launches": int(launches),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": limb_bytes, "d2h_bytes_per_step": limb_bytes},
+        "roofline": roofline,
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "3 EvalRotate of the same ciphertext at the full parameter set (41 limbs)",
+                         "bit_exact_vs_gpu": parity},
+    }
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -48,6 +48,8 @@ static void h2d(Context &C, void *dst, const void *src, size_t bytes) {
 
 extern "C" {
 
+unsigned long long fheb200_launch_count(void) { return g_launches.load(); }
+
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words) {
     GUARD({
         LOCKCTX(ctx);
@@ -165,6 +167,35 @@ int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, 
         FHE_CUDA(cudaEventRecord(e1, C.stream));
         FHE_CUDA(cudaEventSynchronize(e1));
         FHE_CUDA(cudaEventElapsedTime(ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    })
+}
+
+// `reps` passes over `count` rotation indices of the same ciphertext (each index has its own evk, so the key stream is
+// never L2 resident); hoisted != 0 shares one EvalFastRotationPrecompute per pass. Device time by CUDA events.
+int fheb200_bench_rotations(fheb200_ctx *ctx, fheb200_ct *ct, const int *indices, size_t count, int reps, int hoisted,
+                            float *ms) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(ct, "ct");
+        need(indices, "indices");
+        cudaEvent_t e0, e1;
+        FHE_CUDA(cudaEventCreate(&e0));
+        FHE_CUDA(cudaEventCreate(&e1));
+        FHE_CUDA(cudaEventRecord(e0, C.stream));
+        for (int r = 0; r < reps; r++) {
+            if (hoisted) {
+                auto pre = C.fast_rotation_precompute(ct->c);
+                for (size_t i = 0; i < count; i++) { Ct o = C.fast_rotation(ct->c, indices[i], pre); }
+            } else {
+                for (size_t i = 0; i < count; i++) { Ct o = C.rotate(ct->c, indices[i]); }
+            }
+        }
+        FHE_CUDA(cudaEventRecord(e1, C.stream));
+        FHE_CUDA(cudaEventSynchronize(e1));
+        FHE_CUDA(cudaEventElapsedTime(ms, e0, e1));
+        FHE_CUDA(cudaGetLastError());
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
     })

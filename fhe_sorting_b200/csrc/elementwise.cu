@@ -120,38 +120,38 @@ __global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, 
 }
 
 void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st) {
-    ew_binary<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, (int)op, a, b, out);
+    g_launches++, ew_binary<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, (int)op, a, b, out);
 }
 void k_negate(const DeviceTables &T, int ell, const u64 *a, u64 *out, cudaStream_t st) {
-    ew_negate<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, out);
+    g_launches++, ew_negate<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, out);
 }
 void k_mul_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
-    ew_mul_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
+    g_launches++, ew_mul_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
 }
 void k_add_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
-    ew_add_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
+    g_launches++, ew_add_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
 }
 void k_mul_pt(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *pt, u64 *o0, u64 *o1, int acc,
               cudaStream_t st) {
-    ew_mul_pt<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, pt, o0, o1, acc);
+    g_launches++, ew_mul_pt<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, pt, o0, o1, acc);
 }
 void k_tensor(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *b0, const u64 *b1, u64 *d0, u64 *d1,
               u64 *d2, cudaStream_t st) {
-    ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, b0, b1, d0, d1, d2);
+    g_launches++, ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, b0, b1, d0, d1, d2);
 }
 void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, u64 *d0, u64 *d1, u64 *d2,
                      cudaStream_t st) {
-    ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, a0, a1, d0, d1, d2);
+    g_launches++, ew_tensor<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a0, a1, a0, a1, d0, d1, d2);
 }
 void k_automorphism(const DeviceTables &T, uint32_t g, int limbs, const u64 *in, u64 *out, cudaStream_t st) {
-    ew_automorphism<<<dim3((T.n + EW_THREADS - 1) / EW_THREADS, limbs), EW_THREADS, 0, st>>>(T, g, in, out);
+    g_launches++, ew_automorphism<<<dim3((T.n + EW_THREADS - 1) / EW_THREADS, limbs), EW_THREADS, 0, st>>>(T, g, in, out);
 }
 void k_rescale_lift(const DeviceTables &T, int ell, const u64 *last, u64 *tmp, cudaStream_t st) {
-    ew_rescale_lift<<<ew_grid(T, ell - 1), EW_THREADS, 0, st>>>(T, ell, last, tmp);
+    g_launches++, ew_rescale_lift<<<ew_grid(T, ell - 1), EW_THREADS, 0, st>>>(T, ell, last, tmp);
 }
 void k_rescale_finish(const DeviceTables &T, int ell_out, const u64 *in, const u64 *tmp, const LimbScalars &s, u64 *out,
                       cudaStream_t st) {
-    ew_rescale_finish<<<ew_grid(T, ell_out), EW_THREADS, 0, st>>>(T, in, tmp, s, out);
+    g_launches++, ew_rescale_finish<<<ew_grid(T, ell_out), EW_THREADS, 0, st>>>(T, in, tmp, s, out);
 }
 
 } // namespace fheb200

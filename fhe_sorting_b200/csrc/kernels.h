@@ -3,9 +3,12 @@
 // slot = limb position inside the buffer, qp = modulus index (QP order).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include "params.h"
 
 namespace fheb200 {
+
+extern std::atomic<unsigned long long> g_launches; // kernels launched by this library (bench.py gpu_launches)
 
 struct DeviceTables {            // resident per context
     int logn = 0, n = 0, F = 0;  // F = L + K moduli

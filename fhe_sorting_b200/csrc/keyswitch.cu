@@ -112,17 +112,17 @@ __global__ void __launch_bounds__(KS_THREADS) ks_moddown_finish(DeviceTables T, 
 }
 
 void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits, cudaStream_t st) {
-    ks_modup<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.beta), KS_THREADS, 0, st>>>(T, P, coef, c_eval, digits);
+    g_launches++, ks_modup<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.beta), KS_THREADS, 0, st>>>(T, P, coef, c_eval, digits);
 }
 void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc, cudaStream_t st) {
-    ks_inner<<<dim3((T.n / 2 + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, digits, evk, acc);
+    g_launches++, ks_inner<<<dim3((T.n / 2 + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, digits, evk, acc);
 }
 void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st) {
-    ks_moddown_conv<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, 2), KS_THREADS, 0, st>>>(T, P, acc, conv);
+    g_launches++, ks_moddown_conv<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, 2), KS_THREADS, 0, st>>>(T, P, acc, conv);
 }
 void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *conv, const u64 *add0,
                       const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st) {
-    ks_moddown_finish<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.ell, 2), KS_THREADS, 0, st>>>(T, P, acc, conv, add0, add1,
+    g_launches++, ks_moddown_finish<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.ell, 2), KS_THREADS, 0, st>>>(T, P, acc, conv, add0, add1,
                                                                                                   out0, out1, galois);
 }
 

@@ -12,6 +12,8 @@
 
 namespace fheb200 {
 
+std::atomic<unsigned long long> g_launches{0};
+
 constexpr int NTT_THREADS = 256;
 constexpr int NTT_TILE = 4096; // elements per CTA tile (32 KB of shared memory)
 
@@ -181,16 +183,16 @@ void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int coun
     int SA, SB, TE;
     split(T.logn, SA, SB, TE);
     dim3 grid(T.n / TE, count);
-    if (SA > 0) ntt_fwd_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
-    ntt_fwd_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE);
+    if (SA > 0) g_launches++, ntt_fwd_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
+    g_launches++, ntt_fwd_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE);
 }
 void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
     if (count <= 0) return;
     int SA, SB, TE;
     split(T.logn, SA, SB, TE);
     dim3 grid(T.n / TE, count);
-    ntt_inv_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE, SA == 0);
-    if (SA > 0) ntt_inv_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
+    g_launches++, ntt_inv_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE, SA == 0);
+    if (SA > 0) g_launches++, ntt_inv_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
 }
 
 } // namespace fheb200

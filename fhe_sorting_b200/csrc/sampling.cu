@@ -101,27 +101,27 @@ __global__ void __launch_bounds__(SP_THREADS) sp_decrypt_core(DeviceTables T, co
 static inline dim3 g1(const DeviceTables &T, int y) { return dim3((T.n + SP_THREADS - 1) / SP_THREADS, y); }
 
 void k_sample_uniform(const DeviceTables &T, u64 seed, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st) {
-    sp_uniform<<<g1(T, limbs), SP_THREADS, 0, st>>>(T, seed, stream, qp0, out);
+    g_launches++, sp_uniform<<<g1(T, limbs), SP_THREADS, 0, st>>>(T, seed, stream, qp0, out);
 }
 void k_sample_small(const DeviceTables &T, SmallKind kind, u64 seed, u64 stream, int *out, cudaStream_t st) {
-    sp_small<<<g1(T, 1), SP_THREADS, 0, st>>>(T, (int)kind, seed, stream, out);
+    g_launches++, sp_small<<<g1(T, 1), SP_THREADS, 0, st>>>(T, (int)kind, seed, stream, out);
 }
 void k_expand_small(const DeviceTables &T, const int *small, u64 *out, const uint32_t *d_desc, int count, cudaStream_t st) {
-    sp_expand_small<<<g1(T, count), SP_THREADS, 0, st>>>(T, small, out, d_desc);
+    g_launches++, sp_expand_small<<<g1(T, count), SP_THREADS, 0, st>>>(T, small, out, d_desc);
 }
 void k_expand_i128(const DeviceTables &T, const u64 *coef, int ncoef, int gap, int ell, u64 *out, cudaStream_t st) {
-    sp_expand_i128<<<g1(T, ell), SP_THREADS, 0, st>>>(T, coef, ncoef, gap, out);
+    g_launches++, sp_expand_i128<<<g1(T, ell), SP_THREADS, 0, st>>>(T, coef, ncoef, gap, out);
 }
 void k_evk_finish(const DeviceTables &T, int F, const u64 *a, const u64 *e, const u64 *s_new, const u64 *s_old,
                   const LimbScalars &pmod, u64 *b, cudaStream_t st) {
-    sp_evk_finish<<<g1(T, F), SP_THREADS, 0, st>>>(T, a, e, s_new, s_old, pmod, b);
+    g_launches++, sp_evk_finish<<<g1(T, F), SP_THREADS, 0, st>>>(T, a, e, s_new, s_old, pmod, b);
 }
 void k_encrypt_finish(const DeviceTables &T, int ell, const u64 *pkb, const u64 *pka, const u64 *v, const u64 *e0,
                       const u64 *e1, const u64 *pt, u64 *c0, u64 *c1, cudaStream_t st) {
-    sp_encrypt_finish<<<g1(T, ell), SP_THREADS, 0, st>>>(T, pkb, pka, v, e0, e1, pt, c0, c1);
+    g_launches++, sp_encrypt_finish<<<g1(T, ell), SP_THREADS, 0, st>>>(T, pkb, pka, v, e0, e1, pt, c0, c1);
 }
 void k_decrypt_core(const DeviceTables &T, int k, const u64 *c0, const u64 *c1, const u64 *s, u64 *m, cudaStream_t st) {
-    sp_decrypt_core<<<g1(T, k), SP_THREADS, 0, st>>>(T, c0, c1, s, m);
+    g_launches++, sp_decrypt_core<<<g1(T, k), SP_THREADS, 0, st>>>(T, c0, c1, s, m);
 }
 
 } // namespace fheb200

@@ -49,6 +49,13 @@ def _ck(rc):
         raise FheError(load().fheb200_last_error().decode())
 
 
+def launch_count():
+    """CUDA kernels launched by libfheb200.so in this process so far."""
+    L = load()
+    L.fheb200_launch_count.restype = C.c_ulonglong
+    return int(L.fheb200_launch_count())
+
+
 def params_chain(logn, depth, scale_bits=40, first_bits=60, dnum=3):
     """Host-only: modulus chain / roots / (L, K, alpha) for a parameter set (no GPU needed)."""
     L = load()
@@ -267,10 +274,16 @@ class Context(_Handle):
         return self._un("fheb200_eval_poly", x, v.ctypes.data_as(C.c_void_p), C.c_size_t(len(v)))
 
     # -- raw RNS access (parity tests)
-    def ct_export(self, ct):
+    def ct_export(self, ct, out=None):
+        """Raw limbs of a ciphertext; `out` = (c0, c1) preallocated (e.g. pinned) uint64 [limbs][n] host arrays."""
         ell = ct.limbs
-        c0 = np.zeros((ell, self.n), dtype=np.uint64)
-        c1 = np.zeros((ell, self.n), dtype=np.uint64)
+        if out is not None:
+            c0, c1 = out
+            assert c0.dtype == np.uint64 and c0.shape == (ell, self.n) and c0.flags.c_contiguous
+            assert c1.dtype == np.uint64 and c1.shape == (ell, self.n) and c1.flags.c_contiguous
+        else:
+            c0 = np.zeros((ell, self.n), dtype=np.uint64)
+            c1 = np.zeros((ell, self.n), dtype=np.uint64)
         _ck(_lib.fheb200_ct_export(self.h, ct.h, c0.ctypes.data_as(C.c_void_p), c1.ctypes.data_as(C.c_void_p),
                                    C.c_size_t(c0.size)))
         return c0, c1
@@ -329,6 +342,13 @@ class Context(_Handle):
     def bench_rotate(self, ct, index, reps):
         ms = C.c_float()
         _ck(_lib.fheb200_bench_rotate(self.h, ct.h, index, reps, C.byref(ms)))
+        return ms.value
+
+    def bench_rotations(self, ct, indices, reps, hoisted=False):
+        ms = C.c_float()
+        arr = (C.c_int * len(indices))(*indices)
+        _ck(_lib.fheb200_bench_rotations(self.h, ct.h, arr, C.c_size_t(len(indices)), reps, 1 if hoisted else 0,
+                                         C.byref(ms)))
         return ms.value
 
     def bench_kernel(self, name, ell, reps):

@@ -30,6 +30,8 @@ typedef struct fheb200_pre fheb200_pre;   /* std::shared_ptr<std::vector<DCRTPol
 
 const char *fheb200_last_error(void);
 const char *fheb200_version(void);
+/* number of CUDA kernels this library has launched in the process so far */
+unsigned long long fheb200_launch_count(void);
 
 /* ---- context: CCParams<CryptoContextCKKSRNS> setters + GenCryptoContext (tests/DirectSortTest.cpp:24-41) ---- */
 typedef struct {
@@ -139,6 +141,8 @@ int fheb200_raw_rescale(fheb200_ctx *ctx, int num_limbs, const uint64_t *in, uin
 /* timing loops for bench.py: `reps` back-to-back launches on the context stream with inputs resident in HBM;
  * returns the elapsed device time in milliseconds measured with CUDA events on that stream. */
 int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms);
+int fheb200_bench_rotations(fheb200_ctx *ctx, fheb200_ct *ct, const int *indices, size_t count, int reps, int hoisted,
+                            float *ms);
 int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int num_limbs, int reps, float *ms, double *algo_bytes);
 
 #ifdef __cplusplus
