@@ -58,20 +58,24 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
     std::vector<u64> ninv(2 * F);
     for (int i = 0; i < F; i++) ninv[i] = P.n_inv[i], ninv[F + i] = P.n_inv_s[i];
     T.ninv = (u64 *)C->owned_alloc(sizeof(u64) * 2 * F, ninv.data());
-    size_t tb = sizeof(u64) * (size_t)F * n;
-    T.tw = (u64 *)C->owned_alloc(tb, nullptr);
-    T.tws = (u64 *)C->owned_alloc(tb, nullptr);
-    T.twi = (u64 *)C->owned_alloc(tb, nullptr);
-    T.twis = (u64 *)C->owned_alloc(tb, nullptr);
-    std::vector<std::vector<u64>> w(F), ws(F), wi(F), wis(F);
+    size_t tb = sizeof(ulonglong2) * (size_t)F * n;
+    T.tw = (ulonglong2 *)C->owned_alloc(tb, nullptr);
+    T.twi = (ulonglong2 *)C->owned_alloc(tb, nullptr);
+    std::vector<std::vector<u64>> fw(F), iw(F);
 #pragma omp parallel for schedule(dynamic)
-    for (int i = 0; i < F; i++) P.twiddles(i, w[i], ws[i], wi[i], wis[i]);
     for (int i = 0; i < F; i++) {
-        size_t off = (size_t)i * n, b = sizeof(u64) * n;
-        FHE_CUDA(cudaMemcpy(T.tw + off, w[i].data(), b, cudaMemcpyHostToDevice));
-        FHE_CUDA(cudaMemcpy(T.tws + off, ws[i].data(), b, cudaMemcpyHostToDevice));
-        FHE_CUDA(cudaMemcpy(T.twi + off, wi[i].data(), b, cudaMemcpyHostToDevice));
-        FHE_CUDA(cudaMemcpy(T.twis + off, wis[i].data(), b, cudaMemcpyHostToDevice));
+        std::vector<u64> w, ws, wi, wis;
+        P.twiddles(i, w, ws, wi, wis);
+        fw[i].resize(2 * (size_t)n), iw[i].resize(2 * (size_t)n);
+        for (int k = 0; k < n; k++) {
+            fw[i][2 * k] = w[k], fw[i][2 * k + 1] = ws[k];
+            iw[i][2 * k] = wi[k], iw[i][2 * k + 1] = wis[k];
+        }
+    }
+    for (int i = 0; i < F; i++) {
+        size_t off = (size_t)i * n, b = sizeof(ulonglong2) * n;
+        FHE_CUDA(cudaMemcpy(T.tw + off, fw[i].data(), b, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.twi + off, iw[i].data(), b, cudaMemcpyHostToDevice));
     }
     return C;
 }
@@ -104,12 +108,25 @@ const DevicePlan &Context::plan(int ell) {
     DevicePlan D;
     D.ell = ell, D.beta = H.beta, D.width = H.width, D.K = P->K;
     auto up64 = [&](const std::vector<u64> &v) { return (u64 *)owned_alloc(sizeof(u64) * v.size(), v.data()); };
+    // [src][tgt] u64 table -> [tgt][src padded to even] (lo30, hi30) pairs for the split dot products
+    auto split = [&](const std::vector<u64> &v, int nsrc, int ntgt) {
+        const int sp = nsrc + (nsrc & 1);
+        std::vector<uint32_t> o((size_t)ntgt * sp * 2, 0);
+        for (int i = 0; i < nsrc; i++)
+            for (int t = 0; t < ntgt; t++) {
+                u64 h = v[(size_t)i * ntgt + t];
+                o[((size_t)t * sp + i) * 2] = (uint32_t)(h & 0x3fffffffu), o[((size_t)t * sp + i) * 2 + 1] = (uint32_t)(h >> 30);
+            }
+        return (uint2 *)owned_alloc(sizeof(uint32_t) * o.size(), o.data());
+    };
     D.qp = (int *)owned_alloc(sizeof(int) * H.qp.size(), H.qp.data());
     for (int j = 0; j < H.beta; j++) {
         D.dstart[j] = H.dstart[j], D.dsize[j] = H.dsize[j];
-        D.hat_inv[j] = up64(H.hat_inv[j]), D.hat_inv_s[j] = up64(H.hat_inv_s[j]), D.hat[j] = up64(H.hat[j]);
+        D.hat_inv[j] = up64(H.hat_inv[j]), D.hat_inv_s[j] = up64(H.hat_inv_s[j]);
+        D.hat2[j] = split(H.hat[j], H.dsize[j], H.width);
     }
-    D.p_hat_inv = up64(H.p_hat_inv), D.p_hat_inv_s = up64(H.p_hat_inv_s), D.p_hat = up64(H.p_hat);
+    D.p_hat_inv = up64(H.p_hat_inv), D.p_hat_inv_s = up64(H.p_hat_inv_s);
+    D.p_hat2 = split(H.p_hat, P->K, ell);
     D.p_inv = up64(H.p_inv), D.p_inv_s = up64(H.p_inv_s);
     std::vector<uint32_t> dq, dm, dp2, dq2;
     for (int i = 0; i < ell; i++) dq.push_back(((uint32_t)i << 8) | (uint32_t)i);

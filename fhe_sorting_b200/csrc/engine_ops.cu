@@ -33,8 +33,7 @@ void Context::modup(int ell, const u64 *c, u64 *digits) {
     const DevicePlan &D = plan(ell);
     const int n = P->n;
     Mem coef = alloc((size_t)ell * n);
-    FHE_CUDA(cudaMemcpyAsync(coef->p, c, (size_t)ell * n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
-    k_ntt_inv(T, coef->p, D.desc_q, ell, stream);
+    k_ntt_inv(T, c, coef->p, D.desc_q, ell, stream);
     k_modup(T, D, coef->p, c, digits, stream);
     k_ntt_fwd(T, digits, D.desc_modup, D.n_modup, stream);
 }

@@ -13,10 +13,8 @@ extern std::atomic<unsigned long long> g_launches; // kernels launched by this l
 struct DeviceTables {            // resident per context
     int logn = 0, n = 0, F = 0;  // F = L + K moduli
     ModConst *mc = nullptr;      // [F]
-    u64 *tw = nullptr;           // forward twiddles  [F][n]
-    u64 *tws = nullptr;          // Shoup companions  [F][n]
-    u64 *twi = nullptr;          // inverse twiddles  [F][n]
-    u64 *twis = nullptr;         // Shoup companions  [F][n]
+    ulonglong2 *tw = nullptr;    // forward twiddles  [F][n] as (w, Shoup companion) pairs
+    ulonglong2 *twi = nullptr;   // inverse twiddles  [F][n] as (w, Shoup companion) pairs
     u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
 };
 
@@ -27,8 +25,15 @@ struct LimbScalars {             // per-limb scalar + Shoup companion, passed by
 };
 
 // ---- NTT (batched over limbs) ----
-void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st);
-void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st);
+// src and dst share the slot layout of the descriptors; src == dst transforms in place
+void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
+void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
+inline void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
+    k_ntt_fwd(T, buf, buf, d_desc, count, st);
+}
+inline void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
+    k_ntt_inv(T, buf, buf, d_desc, count, st);
+}
 
 // ---- elementwise over ell limbs; qp of limb i is qp0 + i ----
 enum BinOp { OP_ADD = 0, OP_SUB = 1, OP_MUL = 2 };
@@ -58,8 +63,10 @@ struct DevicePlan {              // device copy of a LevelPlan
     int ell = 0, beta = 0, width = 0, K = 0;
     int *qp = nullptr;           // [width]
     int dstart[8] = {0}, dsize[8] = {0};
-    u64 *hat_inv[8] = {nullptr}, *hat_inv_s[8] = {nullptr}, *hat[8] = {nullptr}; // per digit
-    u64 *p_hat_inv = nullptr, *p_hat_inv_s = nullptr, *p_hat = nullptr, *p_inv = nullptr, *p_inv_s = nullptr;
+    u64 *hat_inv[8] = {nullptr}, *hat_inv_s[8] = {nullptr}; // per digit
+    uint2 *hat2[8] = {nullptr};  // per digit: [width][dsize rounded up to even] (lo30, hi30) of Q_j/q_i mod p_t
+    u64 *p_hat_inv = nullptr, *p_hat_inv_s = nullptr, *p_inv = nullptr, *p_inv_s = nullptr;
+    uint2 *p_hat2 = nullptr;     // [ell][K rounded up to even] (lo30, hi30) of P/p_i mod q_t
     uint32_t *desc_q = nullptr;        // NTT batch: Q limbs 0..ell-1 in place
     uint32_t *desc_modup = nullptr;    // NTT batch over digits buffer, skipping own-digit limbs
     int n_modup = 0;

@@ -7,86 +7,126 @@
 //   modup conversion : read ell, write beta*width
 //   inner product    : read beta*width (digits) + 2*beta*width (evk), write 2*width      <- evk streaming, HBM bound
 //   moddown conv     : read 2K, write 2 ell ; finish: read 2 ell + 2 ell (+ adds), write 2 ell
+#include <stdexcept>
+
 #include "kernels.h"
 #include "modarith.cuh"
 
 namespace fheb200 {
 
 constexpr int KS_THREADS = 256;
-constexpr int MAXD = 24; // max limbs per digit / max K held in registers
+constexpr int CONV_THREADS = 128;
+constexpr int MAXD = 24; // max limbs per digit / max K
 
-// one thread = one coefficient of one digit
-__global__ void __launch_bounds__(KS_THREADS) ks_modup(DeviceTables T, DevicePlan P, const u64 *coef, const u64 *c_eval,
-                                                       u64 *digits) {
-    const int j = blockIdx.y, k = blockIdx.x * KS_THREADS + threadIdx.x, n = T.n;
-    if (k >= n) return;
-    const int s = P.dstart[j], d = P.dsize[j], W = P.width;
-    const u64 *hat_inv = P.hat_inv[j], *hat_inv_s = P.hat_inv_s[j], *hat = P.hat[j];
-    u64 x[MAXD];
+// Fast base conversion core (ModUp and ModDown share it).  The DS source residues of one coefficient are multiplied by
+// their (Q_j/q_i)^-1 constants, split into 30-bit halves and kept in registers; every target limb is then a DS-term dot
+// product with the pre-split (Q_j/q_i mod p_t) table.  With both factors < 2^30 each partial product is < 2^60, so up
+// to 16 terms accumulate in plain 64-bit IMAD.WIDE chains (4 per term, no carry handling); the four partial sums are
+// recombined into 128 bits and reduced once.  Table layout: [target][DSP] uint2 (lo30, hi30), DSP = DS rounded up to even.
+template <int DS>
+struct ConvRegs {
+    uint32_t lo[DS], hi[DS];
+};
+template <int DS>
+__device__ __forceinline__ u64 conv_dot(const ConvRegs<DS> &x, const uint2 *__restrict__ row, const ModConst &m) {
+    constexpr int DSP = DS + (DS & 1);
+    u64 rlo = 0, rhi = 0;
 #pragma unroll
-    for (int i = 0; i < MAXD; i++) {
-        x[i] = 0;
-        if (i < d) {
-            u64 v = coef[(size_t)(s + i) * n + k];
-            x[i] = shoup_mul(v, __ldg(hat_inv + i), __ldg(hat_inv_s + i), T.mc[s + i].q);
+    for (int i0 = 0; i0 < DS; i0 += 16) {
+        u64 ll = 0, lh = 0, hl = 0, hh = 0;
+#pragma unroll
+        for (int i = i0; i < (i0 + 16 < DSP ? i0 + 16 : DSP); i += 2) {
+            const uint4 h = __ldg(reinterpret_cast<const uint4 *>(row + i));
+            ll += (u64)x.lo[i] * h.x, lh += (u64)x.lo[i] * h.y, hl += (u64)x.hi[i] * h.x, hh += (u64)x.hi[i] * h.y;
+            if (i + 1 < DS) {
+                ll += (u64)x.lo[i + 1] * h.z, lh += (u64)x.lo[i + 1] * h.w;
+                hl += (u64)x.hi[i + 1] * h.z, hh += (u64)x.hi[i + 1] * h.w;
+            }
         }
+        acc_split30(rlo, rhi, ll, lh, hl, hh);
     }
-    u64 *D = digits + (size_t)j * W * n;
+    return reduce128(rhi, rlo, m);
+}
+
+// ModUp: one thread = one coefficient of one digit; own-digit limbs are copied from the evaluation-domain input
+template <int DS>
+__global__ void __launch_bounds__(CONV_THREADS) ks_modup(DeviceTables T, DevicePlan P, const u64 *__restrict__ coef,
+                                                         const u64 *__restrict__ c_eval, u64 *__restrict__ digits) {
+    const int j = blockIdx.y, k = blockIdx.x * CONV_THREADS + threadIdx.x, n = T.n;
+    if (k >= n) return;
+    constexpr int DSP = DS + (DS & 1);
+    const int s = P.dstart[j], W = P.width;
+    const u64 *hat_inv = P.hat_inv[j], *hat_inv_s = P.hat_inv_s[j];
+    ConvRegs<DS> x;
+#pragma unroll
+    for (int i = 0; i < DS; i++) {
+        u64 v = shoup_mul(coef[(size_t)(s + i) * n + k], __ldg(hat_inv + i), __ldg(hat_inv_s + i), T.mc[s + i].q);
+        x.lo[i] = (uint32_t)v & 0x3fffffffu, x.hi[i] = (uint32_t)(v >> 30);
+    }
+    u64 *D = digits + (size_t)j * W * n + k;
+    const uint2 *tab = P.hat2[j];
     for (int t = 0; t < W; t++) {
-        if (t >= s && t < s + d) {
-            D[(size_t)t * n + k] = c_eval[(size_t)t * n + k];
+        if (t >= s && t < s + DS) {
+            D[(size_t)t * n] = c_eval[(size_t)t * n + k];
             continue;
         }
-        Acc128 acc;
-#pragma unroll
-        for (int i = 0; i < MAXD; i++)
-            if (i < d) acc.mac(x[i], __ldg(hat + (size_t)i * W + t));
-        D[(size_t)t * n + k] = reduce128(acc.hi, acc.lo, T.mc[P.qp[t]]);
+        D[(size_t)t * n] = conv_dot<DS>(x, tab + (size_t)t * DSP, T.mc[P.qp[t]]);
     }
 }
 
-// one thread = two coefficients of one level limb; both key halves accumulated lazily in 128 bits
-__global__ void __launch_bounds__(KS_THREADS) ks_inner(DeviceTables T, DevicePlan P, const u64 *digits, const u64 *evk,
-                                                       u64 *acc) {
+// ModDown: P -> Q base conversion of the (coefficient-domain) P limbs of accumulator blockIdx.y
+template <int DS>
+__global__ void __launch_bounds__(CONV_THREADS) ks_moddown_conv(DeviceTables T, DevicePlan P, const u64 *__restrict__ acc,
+                                                                u64 *__restrict__ conv) {
+    const int b = blockIdx.y, k = blockIdx.x * CONV_THREADS + threadIdx.x, n = T.n;
+    if (k >= n) return;
+    constexpr int DSP = DS + (DS & 1);
+    const int ell = P.ell, W = P.width;
+    const u64 *src = acc + ((size_t)b * W + ell) * n + k;
+    ConvRegs<DS> x;
+#pragma unroll
+    for (int i = 0; i < DS; i++) {
+        u64 v = shoup_mul(src[(size_t)i * n], __ldg(P.p_hat_inv + i), __ldg(P.p_hat_inv_s + i), T.mc[P.qp[ell + i]].q);
+        x.lo[i] = (uint32_t)v & 0x3fffffffu, x.hi[i] = (uint32_t)(v >> 30);
+    }
+    u64 *dst = conv + (size_t)b * ell * n + k;
+    for (int t = 0; t < ell; t++) dst[(size_t)t * n] = conv_dot<DS>(x, P.p_hat2 + (size_t)t * DSP, T.mc[t]);
+}
+
+// evk inner product: one thread = two coefficients of one level limb; both key halves accumulated over the digits as
+// 30-bit split dot products (beta <= 8 terms)
+__global__ void __launch_bounds__(KS_THREADS) ks_inner(DeviceTables T, DevicePlan P, const u64 *__restrict__ digits,
+                                                       const u64 *__restrict__ evk, u64 *__restrict__ acc) {
     const int t = blockIdx.y, k = (blockIdx.x * KS_THREADS + threadIdx.x) * 2, n = T.n;
     if (k >= n) return;
     const int W = P.width, qp = P.qp[t], F = T.F;
     const ModConst m = T.mc[qp];
-    Acc128 b0, b1, a0, a1;
+    u64 s[2][2][4] = {}; // [coefficient][b|a][ll, lh, hl, hh]
     for (int j = 0; j < P.beta; j++) {
-        ulonglong2 dv = *reinterpret_cast<const ulonglong2 *>(digits + ((size_t)j * W + t) * n + k);
-        ulonglong2 kb = *reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 0) * F + qp) * n + k);
-        ulonglong2 ka = *reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 1) * F + qp) * n + k);
-        b0.mac(dv.x, kb.x), b1.mac(dv.y, kb.y);
-        a0.mac(dv.x, ka.x), a1.mac(dv.y, ka.y);
-    }
-    ulonglong2 rb, ra;
-    rb.x = reduce128(b0.hi, b0.lo, m), rb.y = reduce128(b1.hi, b1.lo, m);
-    ra.x = reduce128(a0.hi, a0.lo, m), ra.y = reduce128(a1.hi, a1.lo, m);
-    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)0 * W + t) * n + k) = rb;
-    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)1 * W + t) * n + k) = ra;
-}
-
-// P -> Q base conversion of the (coefficient-domain) P limbs of accumulator blockIdx.y
-__global__ void __launch_bounds__(KS_THREADS) ks_moddown_conv(DeviceTables T, DevicePlan P, const u64 *acc, u64 *conv) {
-    const int b = blockIdx.y, k = blockIdx.x * KS_THREADS + threadIdx.x, n = T.n;
-    if (k >= n) return;
-    const int ell = P.ell, K = P.K, W = P.width;
-    const u64 *src = acc + ((size_t)b * W + ell) * n;
-    u64 x[MAXD];
+        const ulonglong2 dv = *reinterpret_cast<const ulonglong2 *>(digits + ((size_t)j * W + t) * n + k);
+        const ulonglong2 kb = __ldcs(reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 0) * F + qp) * n + k));
+        const ulonglong2 ka = __ldcs(reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 1) * F + qp) * n + k));
+        const u64 dd[2] = {dv.x, dv.y}, bb[2] = {kb.x, kb.y}, aa[2] = {ka.x, ka.y};
 #pragma unroll
-    for (int i = 0; i < MAXD; i++) {
-        x[i] = 0;
-        if (i < K) x[i] = shoup_mul(src[(size_t)i * n + k], __ldg(P.p_hat_inv + i), __ldg(P.p_hat_inv_s + i), T.mc[P.qp[ell + i]].q);
+        for (int c = 0; c < 2; c++) {
+            const uint32_t dl = (uint32_t)dd[c] & 0x3fffffffu, dh = (uint32_t)(dd[c] >> 30);
+            const uint32_t bl = (uint32_t)bb[c] & 0x3fffffffu, bh = (uint32_t)(bb[c] >> 30);
+            const uint32_t al = (uint32_t)aa[c] & 0x3fffffffu, ah = (uint32_t)(aa[c] >> 30);
+            s[c][0][0] += (u64)dl * bl, s[c][0][1] += (u64)dl * bh, s[c][0][2] += (u64)dh * bl, s[c][0][3] += (u64)dh * bh;
+            s[c][1][0] += (u64)dl * al, s[c][1][1] += (u64)dl * ah, s[c][1][2] += (u64)dh * al, s[c][1][3] += (u64)dh * ah;
+        }
     }
-    u64 *dst = conv + (size_t)b * ell * n;
-    for (int t = 0; t < ell; t++) {
-        Acc128 a;
+    u64 r[2][2];
 #pragma unroll
-        for (int i = 0; i < MAXD; i++)
-            if (i < K) a.mac(x[i], __ldg(P.p_hat + (size_t)i * ell + t));
-        dst[(size_t)t * n + k] = reduce128(a.hi, a.lo, T.mc[t]);
-    }
+    for (int c = 0; c < 2; c++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            u64 lo = 0, hi = 0;
+            acc_split30(lo, hi, s[c][h][0], s[c][h][1], s[c][h][2], s[c][h][3]);
+            r[c][h] = reduce128(hi, lo, m);
+        }
+    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)0 * W + t) * n + k) = make_ulonglong2(r[0][0], r[1][0]);
+    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)1 * W + t) * n + k) = make_ulonglong2(r[0][1], r[1][1]);
 }
 
 // out_b[i][p] = ((acc_b[i] - conv_b[i]) * P^-1 + add_b[i]) [src(p)], src = Galois gather (identity when g == 1)
@@ -111,14 +151,43 @@ __global__ void __launch_bounds__(KS_THREADS) ks_moddown_finish(DeviceTables T, 
     (b ? out1 : out0)[(size_t)i * n + p] = r;
 }
 
+#define DS_SWITCH(ds, CALL)                                                                                              \
+    switch (ds) {                                                                                                        \
+        case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break; case 4: CALL(4); break;                 \
+        case 5: CALL(5); break; case 6: CALL(6); break; case 7: CALL(7); break; case 8: CALL(8); break;                 \
+        case 9: CALL(9); break; case 10: CALL(10); break; case 11: CALL(11); break; case 12: CALL(12); break;           \
+        case 13: CALL(13); break; case 14: CALL(14); break; case 15: CALL(15); break; case 16: CALL(16); break;         \
+        case 17: CALL(17); break; case 18: CALL(18); break; case 19: CALL(19); break; case 20: CALL(20); break;         \
+        case 21: CALL(21); break; case 22: CALL(22); break; case 23: CALL(23); break; case 24: CALL(24); break;         \
+        default: throw std::invalid_argument("fheb200: digit size / K beyond 24 limbs unsupported");                     \
+    }
+
 void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits, cudaStream_t st) {
-    g_launches++, ks_modup<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.beta), KS_THREADS, 0, st>>>(T, P, coef, c_eval, digits);
+    // digits can differ in size (the last one may be shorter): one launch per distinct size
+    const int gx = (T.n + CONV_THREADS - 1) / CONV_THREADS;
+    for (int j = 0; j < P.beta; j++) {
+        if (j > 0 && P.dsize[j] == P.dsize[j - 1]) continue;
+        int cnt = 1;
+        while (j + cnt < P.beta && P.dsize[j + cnt] == P.dsize[j]) cnt++;
+        DevicePlan Q = P; // shift so that blockIdx.y = 0 is digit j
+        for (int u = 0; u < cnt; u++) {
+            Q.dstart[u] = P.dstart[j + u], Q.dsize[u] = P.dsize[j + u];
+            Q.hat_inv[u] = P.hat_inv[j + u], Q.hat_inv_s[u] = P.hat_inv_s[j + u], Q.hat2[u] = P.hat2[j + u];
+        }
+        u64 *dj = digits + (size_t)j * P.width * T.n;
+#define CALL(D) g_launches++, ks_modup<D><<<dim3(gx, cnt), CONV_THREADS, 0, st>>>(T, Q, coef, c_eval, dj)
+        DS_SWITCH(P.dsize[j], CALL)
+#undef CALL
+    }
 }
 void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc, cudaStream_t st) {
     g_launches++, ks_inner<<<dim3((T.n / 2 + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, digits, evk, acc);
 }
 void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st) {
-    g_launches++, ks_moddown_conv<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, 2), KS_THREADS, 0, st>>>(T, P, acc, conv);
+    const int gx = (T.n + CONV_THREADS - 1) / CONV_THREADS;
+#define CALL(D) g_launches++, ks_moddown_conv<D><<<dim3(gx, 2), CONV_THREADS, 0, st>>>(T, P, acc, conv)
+    DS_SWITCH(P.K, CALL)
+#undef CALL
 }
 void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *conv, const u64 *add0,
                       const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st) {

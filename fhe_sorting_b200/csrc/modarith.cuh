@@ -13,6 +13,8 @@ __device__ __forceinline__ u64 shoup_lazy(u64 a, u64 w, u64 ws, u64 q) {
     u64 h = mulhi64(a, ws);
     return a * w - h * q;
 }
+// same with nq = 2^64 - q: a*w + h*nq keeps the whole expression on the IMAD accumulate path (no 64-bit subtract)
+__device__ __forceinline__ u64 shoup_lazy_n(u64 a, u64 w, u64 ws, u64 nq) { return a * w + mulhi64(a, ws) * nq; }
 // fully reduced variant
 __device__ __forceinline__ u64 shoup_mul(u64 a, u64 w, u64 ws, u64 q) {
     u64 r = shoup_lazy(a, w, ws, q);
@@ -27,16 +29,24 @@ __device__ __forceinline__ u64 neg_mod(u64 a, u64 q) { return a ? q - a : 0; }
 
 // single word x (any 64-bit value) mod q
 __device__ __forceinline__ u64 reduce64(u64 x, const ModConst &m) {
-    u64 r = x - mulhi64(x, m.r64) * m.q;
-    r = r >= m.q ? r - m.q : r;
+    u64 r = x - mulhi64(x, m.r64) * m.q; // quotient estimate is at most one short: r in [0, 2q)
     return r >= m.q ? r - m.q : r;
 }
-// (hi:lo) mod q for any 128-bit value: hi is folded through 2^64 mod q
+// (hi:lo) mod q for any 128-bit value: hi is folded through 2^64 mod q (Shoup), lo by single-word Barrett, both lazy
 __device__ __forceinline__ u64 reduce128(u64 hi, u64 lo, const ModConst &m) {
-    u64 h = reduce64(hi, m);
-    u64 t = shoup_mul(h, m.c64, m.c64s, m.q);
-    u64 l = reduce64(lo, m);
-    return add_mod(t, l, m.q);
+    const u64 nq = 0 - m.q;
+    u64 r = shoup_lazy_n(hi, m.c64, m.c64s, nq) + (lo + mulhi64(lo, m.r64) * nq); // [0,2q) + [0,2q)
+    const u64 q2 = m.q << 1;
+    r = r >= q2 ? r - q2 : r;
+    return r >= m.q ? r - m.q : r;
+}
+// (lo, hi) += ll + (lh + hl) * 2^30 + hh * 2^60   (recombination of a 30-bit split dot product)
+__device__ __forceinline__ void acc_split30(u64 &lo, u64 &hi, u64 ll, u64 lh, u64 hl, u64 hh) {
+    u64 c;
+    lo += ll, hi += (lo < ll);
+    c = lh << 30, lo += c, hi += (lh >> 34) + (lo < c);
+    c = hl << 30, lo += c, hi += (hl >> 34) + (lo < c);
+    c = hh << 60, lo += c, hi += (hh >> 4) + (lo < c);
 }
 // Barrett product of two reduced operands (a, b < q)
 __device__ __forceinline__ u64 mul_mod(u64 a, u64 b, const ModConst &m) {

@@ -1,12 +1,18 @@
-// ntt.cu — negacyclic NTT / iNTT over 64-bit prime moduli, batched over limbs.
+// ntt.cu — negacyclic NTT / iNTT over 64-bit prime moduli (q < 2^60), batched over limbs.
 //
-// Forward  : Cooley-Tukey, natural order in, bit-reversed order out, twiddles psi^bitrev(i) (Harvey lazy
-//            butterflies, values kept in [0,4q), q < 2^61).
-// Inverse  : Gentleman-Sande mirror image, values kept in [0,2q), n^-1 folded into the last store.
-// The log2(n) radix-2 stages are split in two passes so that each pass works on a shared-memory tile:
-//   pass A : the SA large-stride stages; a tile is 2^SA rows x C contiguous columns (coalesced 8C-byte rows)
-//   pass B : the SB small-stride stages; a tile is TE contiguous coefficients (TE / 2^SB independent blocks)
-// n <= 2^11 runs as a single pass-B launch.  Algorithmic traffic: 16 n bytes per limb per pass.
+// Forward  : Cooley-Tukey, natural order in, bit-reversed order out, twiddles psi^bitrev(i); Harvey lazy butterflies
+//            (values in [0,4q)).   Inverse: Gentleman-Sande mirror image, values in [0,2q), n^-1 applied on the way out.
+// Work split: the log2(n) radix-2 stages run in at most two launches ("passes"); each CTA owns a tile of up to 4096
+// coefficients and each thread 8 of them, so three stages at a time (a radix-8 step, 12 butterflies) run in registers and
+// the tile only goes through shared memory between radix-8 steps (two exchanges for 9 stages, padded against bank
+// conflicts).  The first load and the last store of a pass go straight between HBM and registers.
+//   pass A : the SA = log2(n) - 9 large-stride stages; tile = 2^SA rows x C contiguous columns (C >= 16 words = 128 B)
+//   pass B : the last 9 stages; tile = 4096 contiguous coefficients.   n <= 4096 is a single pass-B launch.
+// Values stay lazy (unreduced) between the two passes.  Twiddles are stored interleaved with their Shoup companions
+// (one 16-byte load per butterfly group).  Algorithmic traffic: 16 n bytes per limb per pass (+ twiddles, L2 resident
+// when limbs of equal modulus are adjacent in the batch).
+// Warp shuffles were considered for the 8x8 exchange between the last two radix-8 steps; 8 STS.64 + 8 LDS.64 per
+// thread is fewer issue slots than the 48 SHFL a 64-bit 8x8 lane transpose needs, so shared memory is used.
 #include "kernels.h"
 #include "modarith.cuh"
 
@@ -14,185 +20,236 @@ namespace fheb200 {
 
 std::atomic<unsigned long long> g_launches{0};
 
-constexpr int NTT_THREADS = 256;
-constexpr int NTT_TILE = 4096; // elements per CTA tile (32 KB of shared memory)
+constexpr int NTT_TILE_LOG = 12;
+constexpr int NTT_TILE = 1 << NTT_TILE_LOG;            // coefficients per CTA tile
+constexpr int NTT_PAD_WORDS = NTT_TILE + NTT_TILE / 8; // e -> e + (e >> 3) keeps every exchange pattern conflict free
 
-__device__ __forceinline__ void ct_butterfly(u64 &x, u64 &y, u64 w, u64 ws, u64 q, u64 q2) {
+__device__ __forceinline__ void ct_bf(u64 &x, u64 &y, const ulonglong2 w, u64 q, u64 nq, u64 q2) {
     u64 a = x >= q2 ? x - q2 : x;
-    u64 t = shoup_lazy(y, w, ws, q);
+    u64 t = shoup_lazy_n(y, w.x, w.y, nq);
     x = a + t;
     y = a + q2 - t;
+    (void)q;
 }
-__device__ __forceinline__ void gs_butterfly(u64 &x, u64 &y, u64 w, u64 ws, u64 q, u64 q2) {
+__device__ __forceinline__ void gs_bf(u64 &x, u64 &y, const ulonglong2 w, u64 q, u64 nq, u64 q2) {
     u64 s = x + y;
     u64 d = x + q2 - y;
     x = s >= q2 ? s - q2 : s;
-    y = shoup_lazy(d, w, ws, q);
+    y = shoup_lazy_n(d, w.x, w.y, nq);
+    (void)q;
 }
+__device__ __forceinline__ int pad(int e) { return e + (e >> 3); }
 
-// ---------------------------------------------------------------- forward
-__global__ void __launch_bounds__(NTT_THREADS) ntt_fwd_passA(DeviceTables T, u64 *buf, const uint32_t *desc, int SA) {
-    extern __shared__ u64 sm[];
-    const uint32_t d = desc[blockIdx.y];
-    const int qp = d & 0xff, n = T.n;
-    u64 *data = buf + (size_t)(d >> 8) * n;
-    const u64 q = T.mc[qp].q, q2 = q << 1;
-    const u64 *tw = T.tw + (size_t)qp * n, *tws = T.tws + (size_t)qp * n;
-    const int R = 1 << SA, C = NTT_TILE >> SA, rowstride = n >> SA, col0 = blockIdx.x * C;
-    for (int e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
-        int r = e / C, c = e - r * C;
-        sm[e] = data[(size_t)r * rowstride + col0 + c];
+// three (or the top NS of three) forward stages on the thread's 8 values; s = global stage of the triple's top bit
+template <int NS>
+__device__ __forceinline__ void fwd_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 q,
+                                          u64 nq, u64 q2) {
+    {
+        const ulonglong2 w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+#pragma unroll
+        for (int k = 0; k < 4; k++) ct_bf(v[k], v[k + 4], w, q, nq, q2);
     }
-    __syncthreads();
-    for (int u = 0; u < SA; u++) {
-        const int sh = SA - 1 - u;
-        for (int id = threadIdx.x; id < NTT_TILE / 2; id += NTT_THREADS) {
-            int h = id / C, c = id - h * C;
-            int hi = h >> sh, lo = h & ((1 << sh) - 1);
-            int r = (hi << (sh + 1)) | lo;
-            int i0 = r * C + c, i1 = i0 + (C << sh);
-            int ti = (1 << u) + hi;
-            u64 x = sm[i0], y = sm[i1];
-            ct_butterfly(x, y, __ldg(tw + ti), __ldg(tws + ti), q, q2);
-            sm[i0] = x;
-            sm[i1] = y;
-        }
-        __syncthreads();
+    if (NS >= 2) {
+        const ulonglong2 *p = tw + (2u << s) + (g0 >> (logn - s - 1));
+        const ulonglong2 w0 = __ldg(p), w1 = __ldg(p + 1);
+        ct_bf(v[0], v[2], w0, q, nq, q2), ct_bf(v[1], v[3], w0, q, nq, q2);
+        ct_bf(v[4], v[6], w1, q, nq, q2), ct_bf(v[5], v[7], w1, q, nq, q2);
     }
-    for (int e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
-        int r = e / C, c = e - r * C;
-        data[(size_t)r * rowstride + col0 + c] = sm[e];
+    if (NS >= 3) {
+        const ulonglong2 *p = tw + (4u << s) + (g0 >> (logn - s - 2));
+#pragma unroll
+        for (int k = 0; k < 4; k++) ct_bf(v[2 * k], v[2 * k + 1], __ldg(p + k), q, nq, q2);
     }
-    (void)R;
 }
-
-// tile = TE contiguous elements; SA = number of stages already done (twiddle offset), SB stages here
-__global__ void __launch_bounds__(NTT_THREADS) ntt_fwd_passB(DeviceTables T, u64 *buf, const uint32_t *desc, int SA, int SB,
-                                                             int TE) {
-    extern __shared__ u64 sm[];
-    const uint32_t d = desc[blockIdx.y];
-    const int qp = d & 0xff, n = T.n;
-    u64 *data = buf + (size_t)(d >> 8) * n + (size_t)blockIdx.x * TE;
-    const u64 q = T.mc[qp].q, q2 = q << 1;
-    const u64 *tw = T.tw + (size_t)qp * n, *tws = T.tws + (size_t)qp * n;
-    for (int e = threadIdx.x; e < TE; e += NTT_THREADS) sm[e] = data[e];
-    __syncthreads();
-    const int blocks_per_tile = TE >> SB, halfB = 1 << (SB - 1);
-    for (int u = 0; u < SB; u++) {
-        const int sh = SB - 1 - u;
-        for (int id = threadIdx.x; id < TE / 2; id += NTT_THREADS) {
-            int p = id >> (SB - 1), h = id & (halfB - 1);
-            int hi = h >> sh, lo = h & ((1 << sh) - 1);
-            int e = (p << SB) | (hi << (sh + 1)) | lo;
-            int b = blockIdx.x * blocks_per_tile + p;
-            int ti = (((1 << SA) + b) << u) + hi;
-            u64 x = sm[e], y = sm[e + (1 << sh)];
-            ct_butterfly(x, y, __ldg(tw + ti), __ldg(tws + ti), q, q2);
-            sm[e] = x;
-            sm[e + (1 << sh)] = y;
-        }
-        __syncthreads();
+template <int NS>
+__device__ __forceinline__ void inv_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 q,
+                                          u64 nq, u64 q2) {
+    if (NS >= 3) {
+        const ulonglong2 *p = tw + (4u << s) + (g0 >> (logn - s - 2));
+#pragma unroll
+        for (int k = 0; k < 4; k++) gs_bf(v[2 * k], v[2 * k + 1], __ldg(p + k), q, nq, q2);
     }
-    for (int e = threadIdx.x; e < TE; e += NTT_THREADS) {
-        u64 x = sm[e];
-        x = x >= q2 ? x - q2 : x;
-        data[e] = x >= q ? x - q : x;
+    if (NS >= 2) {
+        const ulonglong2 *p = tw + (2u << s) + (g0 >> (logn - s - 1));
+        const ulonglong2 w0 = __ldg(p), w1 = __ldg(p + 1);
+        gs_bf(v[0], v[2], w0, q, nq, q2), gs_bf(v[1], v[3], w0, q, nq, q2);
+        gs_bf(v[4], v[6], w1, q, nq, q2), gs_bf(v[5], v[7], w1, q, nq, q2);
+    }
+    {
+        const ulonglong2 w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+#pragma unroll
+        for (int k = 0; k < 4; k++) gs_bf(v[k], v[k + 4], w, q, nq, q2);
     }
 }
 
-// ---------------------------------------------------------------- inverse
-__global__ void __launch_bounds__(NTT_THREADS) ntt_inv_passB(DeviceTables T, u64 *buf, const uint32_t *desc, int SA, int SB,
-                                                             int TE, int last) {
+// Geometry of one pass.  Tile index e (0..tile-1) -> coefficient index g inside the limb:
+//   pass A: g = (e >> lc) * rowstride + blockIdx.x * C + (e & (C-1)),  lc = log2 C ; stage u acts on bit (S-1-u) + lc of e
+//   pass B: g = blockIdx.x * tile + e                                           ; stage u acts on bit (S-1-u) of e
+struct PassGeom {
+    int logn, S, S0, lc, log_tile; // S stages starting at global stage S0; lc = 0 for pass B
+    int pass_a;
+};
+__device__ __forceinline__ uint32_t tile_to_g(const PassGeom &G, int e) {
+    if (G.pass_a) return ((uint32_t)(e >> G.lc) << (G.logn - G.S)) + (blockIdx.x << G.lc) + (e & ((1 << G.lc) - 1));
+    return (blockIdx.x << G.log_tile) + e;
+}
+__device__ __forceinline__ int triple_base(int tid, int p) { return ((tid >> p) << (p + 3)) | (tid & ((1 << p) - 1)); }
+
+__device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
+    return G.pass_a ? (1u << (p - G.lc + G.logn - G.S)) : (1u << p);
+}
+
+// ---------------------------------------------------------------- forward pass
+// final_reduce: bring values to [0,q) on the way out (last pass), otherwise they stay in [0,4q)
+__global__ void __launch_bounds__(NTT_TILE / 8) ntt_fwd_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                             const uint32_t *__restrict__ desc, PassGeom G, int final_reduce) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
-    const int qp = d & 0xff, n = T.n;
-    u64 *data = buf + (size_t)(d >> 8) * n + (size_t)blockIdx.x * TE;
-    const u64 q = T.mc[qp].q, q2 = q << 1;
-    const u64 *tw = T.twi + (size_t)qp * n, *tws = T.twis + (size_t)qp * n;
-    for (int e = threadIdx.x; e < TE; e += NTT_THREADS) sm[e] = data[e];
-    __syncthreads();
-    const int blocks_per_tile = TE >> SB, halfB = 1 << (SB - 1);
-    for (int u = SB - 1; u >= 0; u--) {
-        const int sh = SB - 1 - u;
-        for (int id = threadIdx.x; id < TE / 2; id += NTT_THREADS) {
-            int p = id >> (SB - 1), h = id & (halfB - 1);
-            int hi = h >> sh, lo = h & ((1 << sh) - 1);
-            int e = (p << SB) | (hi << (sh + 1)) | lo;
-            int b = blockIdx.x * blocks_per_tile + p;
-            int ti = (((1 << SA) + b) << u) + hi;
-            u64 x = sm[e], y = sm[e + (1 << sh)];
-            gs_butterfly(x, y, __ldg(tw + ti), __ldg(tws + ti), q, q2);
-            sm[e] = x;
-            sm[e + (1 << sh)] = y;
-        }
-        __syncthreads();
+    const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
+    const size_t off = (size_t)(d >> 8) * n;
+    const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
+    const ulonglong2 *tw = T.tw + (size_t)qp * n;
+    const int lowbit = G.pass_a ? G.lc : 0;
+    const int c_first = (G.S - 1) % 3 + 1;
+    int p = G.S - 3 + lowbit; // low bit of the current triple
+    int base = triple_base(tid, p);
+    uint32_t g0 = tile_to_g(G, base);
+    u64 v[8];
+    {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
     }
-    if (last) {
+    int s = G.S0;
+    if (c_first == 1) fwd_chunk<1>(v, tw, s, G.logn, g0, q, nq, q2);
+    else if (c_first == 2) fwd_chunk<2>(v, tw, s, G.logn, g0, q, nq, q2);
+    else fwd_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+    s += c_first;
+    bool first = true;
+    for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
+        if (!first) __syncthreads();
+        first = false;
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
+        __syncthreads();
+        p = pn;
+        base = triple_base(tid, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+        g0 = tile_to_g(G, base);
+        fwd_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+        s += 3;
+    }
+    if (final_reduce) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            u64 x = v[k];
+            x = x >= q2 ? x - q2 : x;
+            v[k] = x >= q ? x - q : x;
+        }
+    }
+    if (!G.pass_a && p == 0) {
+        ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst + off + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) o[k] = make_ulonglong2(v[2 * k], v[2 * k + 1]);
+    } else {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = v[k];
+    }
+}
+
+// ---------------------------------------------------------------- inverse pass
+// scale: multiply by n^-1 and reduce to [0,q) on the way out (last pass); otherwise values leave in [0,2q)
+__global__ void __launch_bounds__(NTT_TILE / 8) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                             const uint32_t *__restrict__ desc, PassGeom G, int scale) {
+    extern __shared__ u64 sm[];
+    const uint32_t d = desc[blockIdx.y];
+    const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
+    const size_t off = (size_t)(d >> 8) * n;
+    const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
+    const ulonglong2 *tw = T.twi + (size_t)qp * n;
+    const int lowbit = G.pass_a ? G.lc : 0;
+    const int c_last = (G.S - 1) % 3 + 1, ptop = G.S - 3 + lowbit, m = (G.S - c_last) / 3; // m full radix-8 steps first
+    int p = m > 0 ? lowbit : ptop;
+    int base = triple_base(tid, p);
+    uint32_t g0 = tile_to_g(G, base);
+    u64 v[8];
+    if (!G.pass_a && p == 0) {
+        const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            ulonglong2 t = in[k];
+            v[2 * k] = t.x, v[2 * k + 1] = t.y;
+        }
+    } else {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
+    }
+    for (int i = 0; i < m; i++) {
+        const int s = G.S0 + G.S - 1 - (p + 2 - lowbit); // global stage of the triple's top bit
+        inv_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+        if (i > 0) __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
+        __syncthreads();
+        p = i + 1 < m ? p + 3 : ptop;
+        base = triple_base(tid, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+        g0 = tile_to_g(G, base);
+    }
+    // last (possibly partial) step on the top triple: stages S0 + c_last - 1 ... S0
+    if (c_last == 1) inv_chunk<1>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    else if (c_last == 2) inv_chunk<2>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    else inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    if (scale) {
         const u64 ni = T.ninv[qp], nis = T.ninv[T.F + qp];
-        for (int e = threadIdx.x; e < TE; e += NTT_THREADS) data[e] = shoup_mul(sm[e], ni, nis, q);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = shoup_mul(v[k], ni, nis, q);
+    }
+    const uint32_t st = g_step(G, p);
+#pragma unroll
+    for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = v[k];
+}
+
+static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
+    const int logn = T.logn;
+    if (logn <= NTT_TILE_LOG) {
+        tile = T.n;
+        A = PassGeom{logn, 0, 0, 0, 0, 0};
+        B = PassGeom{logn, logn, 0, 0, logn, 0};
     } else {
-        for (int e = threadIdx.x; e < TE; e += NTT_THREADS) data[e] = sm[e];
+        tile = NTT_TILE;
+        const int SB = 9, SA = logn - SB;
+        A = PassGeom{logn, SA, 0, NTT_TILE_LOG - SA, NTT_TILE_LOG, 1};
+        B = PassGeom{logn, SB, SA, 0, NTT_TILE_LOG, 0};
     }
 }
 
-__global__ void __launch_bounds__(NTT_THREADS) ntt_inv_passA(DeviceTables T, u64 *buf, const uint32_t *desc, int SA) {
-    extern __shared__ u64 sm[];
-    const uint32_t d = desc[blockIdx.y];
-    const int qp = d & 0xff, n = T.n;
-    u64 *data = buf + (size_t)(d >> 8) * n;
-    const u64 q = T.mc[qp].q, q2 = q << 1;
-    const u64 *tw = T.twi + (size_t)qp * n, *tws = T.twis + (size_t)qp * n;
-    const int C = NTT_TILE >> SA, rowstride = n >> SA, col0 = blockIdx.x * C;
-    for (int e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
-        int r = e / C, c = e - r * C;
-        sm[e] = data[(size_t)r * rowstride + col0 + c];
-    }
-    __syncthreads();
-    for (int u = SA - 1; u >= 0; u--) {
-        const int sh = SA - 1 - u;
-        for (int id = threadIdx.x; id < NTT_TILE / 2; id += NTT_THREADS) {
-            int h = id / C, c = id - h * C;
-            int hi = h >> sh, lo = h & ((1 << sh) - 1);
-            int r = (hi << (sh + 1)) | lo;
-            int i0 = r * C + c, i1 = i0 + (C << sh);
-            int ti = (1 << u) + hi;
-            u64 x = sm[i0], y = sm[i1];
-            gs_butterfly(x, y, __ldg(tw + ti), __ldg(tws + ti), q, q2);
-            sm[i0] = x;
-            sm[i1] = y;
-        }
-        __syncthreads();
-    }
-    const u64 ni = T.ninv[qp], nis = T.ninv[T.F + qp];
-    for (int e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
-        int r = e / C, c = e - r * C;
-        data[(size_t)r * rowstride + col0 + c] = shoup_mul(sm[e], ni, nis, q);
-    }
-}
-
-static void split(int logn, int &SA, int &SB, int &TE) {
-    if (logn <= 11) {
-        SA = 0, SB = logn, TE = 1 << logn;
-    } else {
-        SB = 9, SA = logn - SB, TE = NTT_TILE; // SA = 3..8: a pass-A row is C = 4096 >> SA >= 16 contiguous words
-    }
-}
-
-void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
+void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st) {
     if (count <= 0) return;
-    int SA, SB, TE;
-    split(T.logn, SA, SB, TE);
-    dim3 grid(T.n / TE, count);
-    if (SA > 0) g_launches++, ntt_fwd_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
-    g_launches++, ntt_fwd_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE);
+    PassGeom A, B;
+    int tile;
+    passes(T, A, B, tile);
+    dim3 grid(T.n / tile, count);
+    const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    if (A.S > 0) {
+        g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, A, 0);
+        src = dst;
+    }
+    g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1);
 }
-void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
+void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st) {
     if (count <= 0) return;
-    int SA, SB, TE;
-    split(T.logn, SA, SB, TE);
-    dim3 grid(T.n / TE, count);
-    g_launches++, ntt_inv_passB<<<grid, NTT_THREADS, TE * sizeof(u64), st>>>(T, buf, d_desc, SA, SB, TE, SA == 0);
-    if (SA > 0) g_launches++, ntt_inv_passA<<<grid, NTT_THREADS, NTT_TILE * sizeof(u64), st>>>(T, buf, d_desc, SA);
+    PassGeom A, B;
+    int tile;
+    passes(T, A, B, tile);
+    dim3 grid(T.n / tile, count);
+    const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, A.S == 0);
+    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 1);
 }
 
 } // namespace fheb200
