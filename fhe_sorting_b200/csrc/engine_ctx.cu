@@ -61,12 +61,20 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
     size_t tb = sizeof(ulonglong2) * (size_t)F * n;
     T.tw = (ulonglong2 *)C->owned_alloc(tb, nullptr);
     T.twi = (ulonglong2 *)C->owned_alloc(tb, nullptr);
+    T.twf = (double *)C->owned_alloc(sizeof(double) * (size_t)F * n, nullptr);
+    T.twif = (double *)C->owned_alloc(sizeof(double) * (size_t)F * n, nullptr);
+    std::vector<double> qd(2 * (size_t)F);
+    for (int i = 0; i < F; i++) qd[2 * i] = (double)P.moduli[i], qd[2 * i + 1] = (double)(1.0L / (long double)P.moduli[i]);
+    T.qd = (double2 *)C->owned_alloc(sizeof(double) * qd.size(), qd.data());
+    std::vector<std::vector<double>> fwd(F), iwd(F);
     std::vector<std::vector<u64>> fw(F), iw(F);
 #pragma omp parallel for schedule(dynamic)
     for (int i = 0; i < F; i++) {
         std::vector<u64> w, ws, wi, wis;
         P.twiddles(i, w, ws, wi, wis);
         fw[i].resize(2 * (size_t)n), iw[i].resize(2 * (size_t)n);
+        fwd[i].resize(n), iwd[i].resize(n);
+        for (int k = 0; k < n; k++) fwd[i][k] = (double)w[k], iwd[i][k] = (double)wi[k];
         for (int k = 0; k < n; k++) {
             fw[i][2 * k] = w[k], fw[i][2 * k + 1] = ws[k];
             iw[i][2 * k] = wi[k], iw[i][2 * k + 1] = wis[k];
@@ -76,6 +84,8 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
         size_t off = (size_t)i * n, b = sizeof(ulonglong2) * n;
         FHE_CUDA(cudaMemcpy(T.tw + off, fw[i].data(), b, cudaMemcpyHostToDevice));
         FHE_CUDA(cudaMemcpy(T.twi + off, iw[i].data(), b, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.twf + off, fwd[i].data(), sizeof(double) * n, cudaMemcpyHostToDevice));
+        FHE_CUDA(cudaMemcpy(T.twif + off, iwd[i].data(), sizeof(double) * n, cudaMemcpyHostToDevice));
     }
     return C;
 }

@@ -15,6 +15,9 @@ struct DeviceTables {            // resident per context
     ModConst *mc = nullptr;      // [F]
     ulonglong2 *tw = nullptr;    // forward twiddles  [F][n] as (w, Shoup companion) pairs
     ulonglong2 *twi = nullptr;   // inverse twiddles  [F][n] as (w, Shoup companion) pairs
+    double *twf = nullptr;       // forward twiddles as doubles [F][n] (FP64 NTT path, moduli <= 42 bits)
+    double *twif = nullptr;      // inverse twiddles as doubles [F][n]
+    double2 *qd = nullptr;       // [F] (q, 1/q) as doubles
     u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
 };
 

@@ -37,10 +37,11 @@ __device__ __forceinline__ u64 conv_dot(const ConvRegs<DS> &x, const uint2 *__re
 #pragma unroll
         for (int i = i0; i < (i0 + 16 < DSP ? i0 + 16 : DSP); i += 2) {
             const uint4 h = __ldg(reinterpret_cast<const uint4 *>(row + i));
-            ll += (u64)x.lo[i] * h.x, lh += (u64)x.lo[i] * h.y, hl += (u64)x.hi[i] * h.x, hh += (u64)x.hi[i] * h.y;
+            ll = mad_wide(x.lo[i], h.x, ll), lh = mad_wide(x.lo[i], h.y, lh);
+            hl = mad_wide(x.hi[i], h.x, hl), hh = mad_wide(x.hi[i], h.y, hh);
             if (i + 1 < DS) {
-                ll += (u64)x.lo[i + 1] * h.z, lh += (u64)x.lo[i + 1] * h.w;
-                hl += (u64)x.hi[i + 1] * h.z, hh += (u64)x.hi[i + 1] * h.w;
+                ll = mad_wide(x.lo[i + 1], h.z, ll), lh = mad_wide(x.lo[i + 1], h.w, lh);
+                hl = mad_wide(x.hi[i + 1], h.z, hl), hh = mad_wide(x.hi[i + 1], h.w, hh);
             }
         }
         acc_split30(rlo, rhi, ll, lh, hl, hh);
@@ -112,8 +113,10 @@ __global__ void __launch_bounds__(KS_THREADS) ks_inner(DeviceTables T, DevicePla
             const uint32_t dl = (uint32_t)dd[c] & 0x3fffffffu, dh = (uint32_t)(dd[c] >> 30);
             const uint32_t bl = (uint32_t)bb[c] & 0x3fffffffu, bh = (uint32_t)(bb[c] >> 30);
             const uint32_t al = (uint32_t)aa[c] & 0x3fffffffu, ah = (uint32_t)(aa[c] >> 30);
-            s[c][0][0] += (u64)dl * bl, s[c][0][1] += (u64)dl * bh, s[c][0][2] += (u64)dh * bl, s[c][0][3] += (u64)dh * bh;
-            s[c][1][0] += (u64)dl * al, s[c][1][1] += (u64)dl * ah, s[c][1][2] += (u64)dh * al, s[c][1][3] += (u64)dh * ah;
+            s[c][0][0] = mad_wide(dl, bl, s[c][0][0]), s[c][0][1] = mad_wide(dl, bh, s[c][0][1]);
+            s[c][0][2] = mad_wide(dh, bl, s[c][0][2]), s[c][0][3] = mad_wide(dh, bh, s[c][0][3]);
+            s[c][1][0] = mad_wide(dl, al, s[c][1][0]), s[c][1][1] = mad_wide(dl, ah, s[c][1][1]);
+            s[c][1][2] = mad_wide(dh, al, s[c][1][2]), s[c][1][3] = mad_wide(dh, ah, s[c][1][3]);
         }
     }
     u64 r[2][2];

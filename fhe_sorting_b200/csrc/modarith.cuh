@@ -7,6 +7,13 @@
 namespace fheb200 {
 
 __device__ __forceinline__ u64 mulhi64(u64 a, u64 b) { return __umul64hi(a, b); }
+// c + a*b with 32-bit factors and a 64-bit accumulator: exactly one IMAD.WIDE.U32 (the C++ form `c += (u64)a * b`
+// makes nvcc 12.9 append a dead carry add per term)
+__device__ __forceinline__ u64 mad_wide(uint32_t a, uint32_t b, u64 c) {
+    u64 r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+    return r;
+}
 
 // a*w mod q with precomputed ws = floor(w 2^64 / q). Any 64-bit a; result in [0, 2q).
 __device__ __forceinline__ u64 shoup_lazy(u64 a, u64 w, u64 ws, u64 q) {

@@ -24,61 +24,68 @@ constexpr int NTT_TILE_LOG = 12;
 constexpr int NTT_TILE = 1 << NTT_TILE_LOG;            // coefficients per CTA tile
 constexpr int NTT_PAD_WORDS = NTT_TILE + NTT_TILE / 8; // e -> e + (e >> 3) keeps every exchange pattern conflict free
 
-__device__ __forceinline__ void ct_bf(u64 &x, u64 &y, const ulonglong2 w, u64 q, u64 nq, u64 q2) {
-    u64 a = x >= q2 ? x - q2 : x;
+// LAZY (moduli with bits + log2(n) + 1 <= 63, i.e. every 40..45-bit scaling prime at n = 2^17): no conditional
+// subtraction at all; forward values grow by 2q per stage (< 35q), inverse sums double per stage (< 2^logn q).
+template <bool LAZY>
+__device__ __forceinline__ void ct_bf(u64 &x, u64 &y, const ulonglong2 w, u64 nq, u64 q2) {
+    u64 a = LAZY ? x : (x >= q2 ? x - q2 : x);
     u64 t = shoup_lazy_n(y, w.x, w.y, nq);
     x = a + t;
     y = a + q2 - t;
-    (void)q;
 }
-__device__ __forceinline__ void gs_bf(u64 &x, u64 &y, const ulonglong2 w, u64 q, u64 nq, u64 q2) {
+// c = multiple of q that bounds y: 2q in the strict variant, q << (stages already done) in the lazy one
+template <bool LAZY>
+__device__ __forceinline__ void gs_bf(u64 &x, u64 &y, const ulonglong2 w, u64 nq, u64 q2, u64 c) {
     u64 s = x + y;
-    u64 d = x + q2 - y;
-    x = s >= q2 ? s - q2 : s;
+    u64 d = x + (LAZY ? c : q2) - y;
+    x = LAZY ? s : (s >= q2 ? s - q2 : s);
     y = shoup_lazy_n(d, w.x, w.y, nq);
-    (void)q;
 }
 __device__ __forceinline__ int pad(int e) { return e + (e >> 3); }
 
 // three (or the top NS of three) forward stages on the thread's 8 values; s = global stage of the triple's top bit
-template <int NS>
-__device__ __forceinline__ void fwd_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 q,
-                                          u64 nq, u64 q2) {
+template <int NS, bool LAZY>
+__device__ __forceinline__ void fwd_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 nq,
+                                          u64 q2) {
     {
         const ulonglong2 w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
 #pragma unroll
-        for (int k = 0; k < 4; k++) ct_bf(v[k], v[k + 4], w, q, nq, q2);
+        for (int k = 0; k < 4; k++) ct_bf<LAZY>(v[k], v[k + 4], w, nq, q2);
     }
     if (NS >= 2) {
         const ulonglong2 *p = tw + (2u << s) + (g0 >> (logn - s - 1));
         const ulonglong2 w0 = __ldg(p), w1 = __ldg(p + 1);
-        ct_bf(v[0], v[2], w0, q, nq, q2), ct_bf(v[1], v[3], w0, q, nq, q2);
-        ct_bf(v[4], v[6], w1, q, nq, q2), ct_bf(v[5], v[7], w1, q, nq, q2);
+        ct_bf<LAZY>(v[0], v[2], w0, nq, q2), ct_bf<LAZY>(v[1], v[3], w0, nq, q2);
+        ct_bf<LAZY>(v[4], v[6], w1, nq, q2), ct_bf<LAZY>(v[5], v[7], w1, nq, q2);
     }
     if (NS >= 3) {
         const ulonglong2 *p = tw + (4u << s) + (g0 >> (logn - s - 2));
 #pragma unroll
-        for (int k = 0; k < 4; k++) ct_bf(v[2 * k], v[2 * k + 1], __ldg(p + k), q, nq, q2);
+        for (int k = 0; k < 4; k++) ct_bf<LAZY>(v[2 * k], v[2 * k + 1], __ldg(p + k), nq, q2);
     }
 }
-template <int NS>
+template <int NS, bool LAZY>
 __device__ __forceinline__ void inv_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 q,
                                           u64 nq, u64 q2) {
+    // stage g has (logn - 1 - g) stages before it
     if (NS >= 3) {
         const ulonglong2 *p = tw + (4u << s) + (g0 >> (logn - s - 2));
+        const u64 c = q << (logn - 3 - s);
 #pragma unroll
-        for (int k = 0; k < 4; k++) gs_bf(v[2 * k], v[2 * k + 1], __ldg(p + k), q, nq, q2);
+        for (int k = 0; k < 4; k++) gs_bf<LAZY>(v[2 * k], v[2 * k + 1], __ldg(p + k), nq, q2, c);
     }
     if (NS >= 2) {
         const ulonglong2 *p = tw + (2u << s) + (g0 >> (logn - s - 1));
         const ulonglong2 w0 = __ldg(p), w1 = __ldg(p + 1);
-        gs_bf(v[0], v[2], w0, q, nq, q2), gs_bf(v[1], v[3], w0, q, nq, q2);
-        gs_bf(v[4], v[6], w1, q, nq, q2), gs_bf(v[5], v[7], w1, q, nq, q2);
+        const u64 c = q << (logn - 2 - s);
+        gs_bf<LAZY>(v[0], v[2], w0, nq, q2, c), gs_bf<LAZY>(v[1], v[3], w0, nq, q2, c);
+        gs_bf<LAZY>(v[4], v[6], w1, nq, q2, c), gs_bf<LAZY>(v[5], v[7], w1, nq, q2, c);
     }
     {
         const ulonglong2 w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+        const u64 c = q << (logn - 1 - s);
 #pragma unroll
-        for (int k = 0; k < 4; k++) gs_bf(v[k], v[k + 4], w, q, nq, q2);
+        for (int k = 0; k < 4; k++) gs_bf<LAZY>(v[k], v[k + 4], w, nq, q2, c);
     }
 }
 
@@ -101,13 +108,13 @@ __device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
 
 // ---------------------------------------------------------------- forward pass
 // final_reduce: bring values to [0,q) on the way out (last pass), otherwise they stay in [0,4q)
-__global__ void __launch_bounds__(NTT_TILE / 8) ntt_fwd_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                             const uint32_t *__restrict__ desc, PassGeom G, int final_reduce) {
-    extern __shared__ u64 sm[];
-    const uint32_t d = desc[blockIdx.y];
+template <bool LAZY>
+__device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                              const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
-    const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
+    const ModConst mc = T.mc[qp];
+    const u64 q = mc.q, q2 = q << 1, nq = 0 - q;
     const ulonglong2 *tw = T.tw + (size_t)qp * n;
     const int lowbit = G.pass_a ? G.lc : 0;
     const int c_first = (G.S - 1) % 3 + 1;
@@ -121,9 +128,9 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_fwd_pass(DeviceTables T, con
         for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
     }
     int s = G.S0;
-    if (c_first == 1) fwd_chunk<1>(v, tw, s, G.logn, g0, q, nq, q2);
-    else if (c_first == 2) fwd_chunk<2>(v, tw, s, G.logn, g0, q, nq, q2);
-    else fwd_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+    if (c_first == 1) fwd_chunk<1, LAZY>(v, tw, s, G.logn, g0, nq, q2);
+    else if (c_first == 2) fwd_chunk<2, LAZY>(v, tw, s, G.logn, g0, nq, q2);
+    else fwd_chunk<3, LAZY>(v, tw, s, G.logn, g0, nq, q2);
     s += c_first;
     bool first = true;
     for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
@@ -137,15 +144,19 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_fwd_pass(DeviceTables T, con
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
         g0 = tile_to_g(G, base);
-        fwd_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+        fwd_chunk<3, LAZY>(v, tw, s, G.logn, g0, nq, q2);
         s += 3;
     }
     if (final_reduce) {
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             u64 x = v[k];
-            x = x >= q2 ? x - q2 : x;
-            v[k] = x >= q ? x - q : x;
+            if (LAZY) {
+                v[k] = reduce64(x, mc);
+            } else {
+                x = x >= q2 ? x - q2 : x;
+                v[k] = x >= q ? x - q : x;
+            }
         }
     }
     if (!G.pass_a && p == 0) {
@@ -159,12 +170,231 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_fwd_pass(DeviceTables T, con
     }
 }
 
-// ---------------------------------------------------------------- inverse pass
-// scale: multiply by n^-1 and reduce to [0,q) on the way out (last pass); otherwise values leave in [0,2q)
-__global__ void __launch_bounds__(NTT_TILE / 8) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                             const uint32_t *__restrict__ desc, PassGeom G, int scale) {
+// ---------------------------------------------------------------- FP64 path (moduli of at most 42 bits)
+// B200 issues DFMA at the same rate as IMAD (tools/ubench_int.cu: 3.4 vs 3.6 warp-inst/clk/SM), and a modular product
+// of two < 2^53 integers is 7 double-precision instructions (error-free product + rounded quotient) against ~25
+// integer ones for the 64-bit Shoup form.  Values are kept as exact signed integers in doubles:
+//   c = rint(y * (w/q)) ; h = RN(y*w) ; l = fma(y,w,-h) (exact) ; d = fma(-c,q,h) (exact: |h - c q| < 2q + |l|) ; g = d + l
+// g == y*w (mod q) and |g| < 0.7 q for |y| < 2^50 (emulated exhaustively in tests/test_fp_modmul.py).  No conditional
+// corrections inside the butterflies: forward values grow by < q per stage, inverse sums are re-centred every <= 8 stages.
+constexpr double FP_MAGIC = 6755399441055744.0; // 1.5 * 2^52: (x + M) - M rounds |x| < 2^51 to the nearest integer
+constexpr double FP_2P52 = 4503599627370496.0;
+__device__ __forceinline__ double fp_rint(double x) { return __dadd_rn(__dadd_rn(x, FP_MAGIC), -FP_MAGIC); }
+__device__ __forceinline__ double fp_mulmod(double y, double w, double wq, double q) {
+    const double c = fp_rint(__dmul_rn(y, wq));
+    const double h = __dmul_rn(y, w);
+    const double l = __fma_rn(y, w, -h);
+    const double d = __fma_rn(-c, q, h);
+    return __dadd_rn(d, l);
+}
+__device__ __forceinline__ double fp_center(double v, double q, double qinv) { // v - q*rint(v/q), |result| <= q/2 + 1
+    return __fma_rn(-fp_rint(__dmul_rn(v, qinv)), q, v);
+}
+__device__ __forceinline__ double fp_from_u64(u64 x) { // exact for x < 2^52
+    return __dadd_rn(__longlong_as_double((long long)(x | 0x4330000000000000ull)), -FP_2P52);
+}
+__device__ __forceinline__ u64 fp_to_u64(double v, double q, double qinv) { // any |v| < 2^51 -> [0, q)
+    double r = fp_center(v, q, qinv);
+    r = r < 0.0 ? __dadd_rn(r, q) : r;
+    r = r >= q ? __dadd_rn(r, -q) : r;
+    return (u64)__double_as_longlong(__dadd_rn(r, FP_2P52)) & 0x000fffffffffffffull;
+}
+__device__ __forceinline__ void fp_ct(double &x, double &y, double w, double qinv, double q) {
+    const double g = fp_mulmod(y, w, __dmul_rn(w, qinv), q);
+    y = __dadd_rn(x, -g);
+    x = __dadd_rn(x, g);
+}
+__device__ __forceinline__ void fp_gs(double &x, double &y, double w, double qinv, double q) {
+    const double d = __dadd_rn(x, -y);
+    x = __dadd_rn(x, y);
+    y = fp_mulmod(d, w, __dmul_rn(w, qinv), q);
+}
+template <int NS>
+__device__ __forceinline__ void fp_fwd_chunk(double (&v)[8], const double *__restrict__ tw, int s, int logn, uint32_t g0,
+                                             double q, double qinv) {
+    {
+        const double w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+#pragma unroll
+        for (int k = 0; k < 4; k++) fp_ct(v[k], v[k + 4], w, qinv, q);
+    }
+    if (NS >= 2) {
+        const double2 w = __ldg(reinterpret_cast<const double2 *>(tw + (2u << s) + (g0 >> (logn - s - 1))));
+        fp_ct(v[0], v[2], w.x, qinv, q), fp_ct(v[1], v[3], w.x, qinv, q);
+        fp_ct(v[4], v[6], w.y, qinv, q), fp_ct(v[5], v[7], w.y, qinv, q);
+    }
+    if (NS >= 3) {
+        const double2 *p = reinterpret_cast<const double2 *>(tw + (4u << s) + (g0 >> (logn - s - 2)));
+        const double2 w0 = __ldg(p), w1 = __ldg(p + 1);
+        fp_ct(v[0], v[1], w0.x, qinv, q), fp_ct(v[2], v[3], w0.y, qinv, q);
+        fp_ct(v[4], v[5], w1.x, qinv, q), fp_ct(v[6], v[7], w1.y, qinv, q);
+    }
+}
+template <int NS>
+__device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__restrict__ tw, int s, int logn, uint32_t g0,
+                                             double q, double qinv) {
+    if (NS >= 3) {
+        const double2 *p = reinterpret_cast<const double2 *>(tw + (4u << s) + (g0 >> (logn - s - 2)));
+        const double2 w0 = __ldg(p), w1 = __ldg(p + 1);
+        fp_gs(v[0], v[1], w0.x, qinv, q), fp_gs(v[2], v[3], w0.y, qinv, q);
+        fp_gs(v[4], v[5], w1.x, qinv, q), fp_gs(v[6], v[7], w1.y, qinv, q);
+    }
+    if (NS >= 2) {
+        const double2 w = __ldg(reinterpret_cast<const double2 *>(tw + (2u << s) + (g0 >> (logn - s - 1))));
+        fp_gs(v[0], v[2], w.x, qinv, q), fp_gs(v[1], v[3], w.x, qinv, q);
+        fp_gs(v[4], v[6], w.y, qinv, q), fp_gs(v[5], v[7], w.y, qinv, q);
+    }
+    {
+        const double w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+#pragma unroll
+        for (int k = 0; k < 4; k++) fp_gs(v[k], v[k + 4], w, qinv, q);
+    }
+}
+
+// first: the pass reads reduced u64 input (otherwise doubles left by the previous pass); last: writes reduced u64
+__device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu) {
+    double *sm = reinterpret_cast<double *>(smu);
+    const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
+    const size_t off = (size_t)(d >> 8) * n;
+    const double2 qd = T.qd[qp];
+    const double q = qd.x, qinv = qd.y;
+    const double *tw = T.twf + (size_t)qp * n;
+    const int lowbit = G.pass_a ? G.lc : 0;
+    const int c_first = (G.S - 1) % 3 + 1;
+    int p = G.S - 3 + lowbit;
+    int base = triple_base(tid, p);
+    uint32_t g0 = tile_to_g(G, base);
+    double v[8];
+    {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const u64 x = src[off + g0 + k * st];
+            v[k] = first ? fp_from_u64(x) : __longlong_as_double((long long)x);
+        }
+    }
+    int s = G.S0;
+    if (c_first == 1) fp_fwd_chunk<1>(v, tw, s, G.logn, g0, q, qinv);
+    else if (c_first == 2) fp_fwd_chunk<2>(v, tw, s, G.logn, g0, q, qinv);
+    else fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
+    s += c_first;
+    bool firstx = true;
+    for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
+        if (!firstx) __syncthreads();
+        firstx = false;
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
+        __syncthreads();
+        p = pn;
+        base = triple_base(tid, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+        g0 = tile_to_g(G, base);
+        fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
+        s += 3;
+    }
+    u64 o[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = last ? fp_to_u64(v[k], q, qinv) : (u64)__double_as_longlong(v[k]);
+    if (!G.pass_a && p == 0) {
+        ulonglong2 *op = reinterpret_cast<ulonglong2 *>(dst + off + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) op[k] = make_ulonglong2(o[2 * k], o[2 * k + 1]);
+    } else {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = o[k];
+    }
+}
+
+__device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu) {
+    double *sm = reinterpret_cast<double *>(smu);
+    const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
+    const size_t off = (size_t)(d >> 8) * n;
+    const double2 qd = T.qd[qp];
+    const double q = qd.x, qinv = qd.y;
+    const double *tw = T.twif + (size_t)qp * n;
+    const int lowbit = G.pass_a ? G.lc : 0;
+    const int c_last = (G.S - 1) % 3 + 1, ptop = G.S - 3 + lowbit, m = (G.S - c_last) / 3;
+    int p = m > 0 ? lowbit : ptop;
+    int base = triple_base(tid, p);
+    uint32_t g0 = tile_to_g(G, base);
+    double v[8];
+    if (!G.pass_a && p == 0) {
+        const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const ulonglong2 t = in[k];
+            v[2 * k] = first ? fp_from_u64(t.x) : __longlong_as_double((long long)t.x);
+            v[2 * k + 1] = first ? fp_from_u64(t.y) : __longlong_as_double((long long)t.y);
+        }
+    } else {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const u64 x = src[off + g0 + k * st];
+            v[k] = first ? fp_from_u64(x) : __longlong_as_double((long long)x);
+        }
+    }
+    int growth = 0; // stages since the values were last known to be within (-q, q)
+    if (!first) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = fp_center(v[k], q, qinv);
+    }
+    for (int i = 0; i < m; i++) {
+        if (growth + 3 > 8) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) v[k] = fp_center(v[k], q, qinv);
+            growth = 0;
+        }
+        const int s = G.S0 + G.S - 1 - (p + 2 - lowbit);
+        fp_inv_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
+        growth += 3;
+        if (i > 0) __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
+        __syncthreads();
+        p = i + 1 < m ? p + 3 : ptop;
+        base = triple_base(tid, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+        g0 = tile_to_g(G, base);
+    }
+    if (growth + c_last > 8) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = fp_center(v[k], q, qinv);
+    }
+    if (c_last == 1) fp_inv_chunk<1>(v, tw, G.S0, G.logn, g0, q, qinv);
+    else if (c_last == 2) fp_inv_chunk<2>(v, tw, G.S0, G.logn, g0, q, qinv);
+    else fp_inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, qinv);
+    const uint32_t st = g_step(G, p);
+    if (last) {
+        const double ni = (double)T.ninv[qp], niq = __dmul_rn(ni, qinv);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = fp_to_u64(fp_mulmod(v[k], ni, niq, q), q, qinv);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = (u64)__double_as_longlong(v[k]);
+    }
+}
+__device__ __forceinline__ bool fp_ok(const DeviceTables &T, int qp) { return T.mc[qp].bits <= 42 && T.logn <= 17; }
+
+__device__ __forceinline__ bool lazy_ok(const DeviceTables &T, int qp) { return T.mc[qp].bits + T.logn + 1 <= 63; }
+__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_fwd_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                             const uint32_t *__restrict__ desc, PassGeom G, int first, int final_reduce) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
+    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body(T, src, dst, d, G, first, final_reduce, sm);
+    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true>(T, src, dst, d, G, final_reduce, sm);
+    else fwd_pass_body<false>(T, src, dst, d, G, final_reduce, sm);
+}
+
+// ---------------------------------------------------------------- inverse pass
+// scale: multiply by n^-1 and reduce to [0,q) on the way out (last pass); otherwise values leave in [0,2q)
+template <bool LAZY>
+__device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                              const uint32_t d, const PassGeom &G, int scale, u64 *sm) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
@@ -189,7 +419,7 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_inv_pass(DeviceTables T, con
     }
     for (int i = 0; i < m; i++) {
         const int s = G.S0 + G.S - 1 - (p + 2 - lowbit); // global stage of the triple's top bit
-        inv_chunk<3>(v, tw, s, G.logn, g0, q, nq, q2);
+        inv_chunk<3, LAZY>(v, tw, s, G.logn, g0, q, nq, q2);
         if (i > 0) __syncthreads();
 #pragma unroll
         for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
@@ -201,9 +431,9 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_inv_pass(DeviceTables T, con
         g0 = tile_to_g(G, base);
     }
     // last (possibly partial) step on the top triple: stages S0 + c_last - 1 ... S0
-    if (c_last == 1) inv_chunk<1>(v, tw, G.S0, G.logn, g0, q, nq, q2);
-    else if (c_last == 2) inv_chunk<2>(v, tw, G.S0, G.logn, g0, q, nq, q2);
-    else inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    if (c_last == 1) inv_chunk<1, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    else if (c_last == 2) inv_chunk<2, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
+    else inv_chunk<3, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     if (scale) {
         const u64 ni = T.ninv[qp], nis = T.ninv[T.F + qp];
 #pragma unroll
@@ -212,6 +442,15 @@ __global__ void __launch_bounds__(NTT_TILE / 8) ntt_inv_pass(DeviceTables T, con
     const uint32_t st = g_step(G, p);
 #pragma unroll
     for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = v[k];
+}
+
+__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                             const uint32_t *__restrict__ desc, PassGeom G, int first, int scale) {
+    extern __shared__ u64 sm[];
+    const uint32_t d = desc[blockIdx.y];
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm);
 }
 
 static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
@@ -236,10 +475,10 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (A.S > 0) {
-        g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, A, 0);
+        g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, A, 1, 0);
         src = dst;
     }
-    g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1);
+    g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, A.S == 0, 1);
 }
 void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st) {
     if (count <= 0) return;
@@ -248,8 +487,8 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     passes(T, A, B, tile);
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
-    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, A.S == 0);
-    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 1);
+    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0);
+    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1);
 }
 
 } // namespace fheb200

@@ -7,7 +7,7 @@ pytestmark = pytest.mark.gpu
 SEED = 0xC0FFEE
 
 
-@pytest.fixture(scope="module", params=[(10, 6, 40), (12, 9, 50), (13, 5, 59)], ids=lambda p: "n2^%d_d%d_s%d" % p)
+@pytest.fixture(scope="module", params=[(10, 6, 40), (12, 9, 50), (13, 5, 59), (14, 4, 40)], ids=lambda p: "n2^%d_d%d_s%d" % p)
 def pair(request):
     import fhe_sorting_b200 as F
     from oracle.oracle import Oracle
