@@ -24,6 +24,7 @@ struct DevMem { // stream-ordered device allocation owned by a context
     u64 *p = nullptr;
     size_t words = 0;
     Context *ctx = nullptr;
+    std::shared_ptr<Context> keep; // a buffer keeps its context (stream, memory pool) alive
     ~DevMem();
 };
 typedef std::shared_ptr<DevMem> Mem;
@@ -64,7 +65,7 @@ struct Precomp { // EvalFastRotationPrecompute result: ModUp'ed digits of c1
     int ell = 0;
 };
 
-class Context {
+class Context : public std::enable_shared_from_this<Context> {
   public:
     static std::shared_ptr<Context> create(int logn, int depth, int scale_bits, int first_bits, int dnum, int batch,
                                            int device);

@@ -14,6 +14,7 @@ DevMem::~DevMem() {
 Mem Context::alloc(size_t words) {
     auto m = std::make_shared<DevMem>();
     m->ctx = this;
+    m->keep = weak_from_this().lock(); // null only while the context is being constructed or destroyed
     m->words = words;
     FHE_CUDA(cudaMallocAsync((void **)&m->p, words * sizeof(u64), stream));
     return m;

@@ -94,42 +94,32 @@ __global__ void __launch_bounds__(CONV_THREADS) ks_moddown_conv(DeviceTables T, 
     for (int t = 0; t < ell; t++) dst[(size_t)t * n] = conv_dot<DS>(x, P.p_hat2 + (size_t)t * DSP, T.mc[t]);
 }
 
-// evk inner product: one thread = two coefficients of one level limb; both key halves accumulated over the digits as
-// 30-bit split dot products (beta <= 8 terms)
+// evk inner product: one thread = one coefficient of one level limb; both key halves accumulated over the digits as
+// 30-bit split dot products (beta <= 8 terms).  HBM bound: streams beta digits + 2 beta key limbs per level limb.
 __global__ void __launch_bounds__(KS_THREADS) ks_inner(DeviceTables T, DevicePlan P, const u64 *__restrict__ digits,
                                                        const u64 *__restrict__ evk, u64 *__restrict__ acc) {
-    const int t = blockIdx.y, k = (blockIdx.x * KS_THREADS + threadIdx.x) * 2, n = T.n;
+    const int t = blockIdx.y, k = blockIdx.x * KS_THREADS + threadIdx.x, n = T.n;
     if (k >= n) return;
     const int W = P.width, qp = P.qp[t], F = T.F;
     const ModConst m = T.mc[qp];
-    u64 s[2][2][4] = {}; // [coefficient][b|a][ll, lh, hl, hh]
+    u64 sb[4] = {0, 0, 0, 0}, sa[4] = {0, 0, 0, 0}; // ll, lh, hl, hh
+    const u64 *dp = digits + (size_t)t * n + k, *kp = evk + (size_t)qp * n + k;
+#pragma unroll 3
     for (int j = 0; j < P.beta; j++) {
-        const ulonglong2 dv = *reinterpret_cast<const ulonglong2 *>(digits + ((size_t)j * W + t) * n + k);
-        const ulonglong2 kb = __ldcs(reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 0) * F + qp) * n + k));
-        const ulonglong2 ka = __ldcs(reinterpret_cast<const ulonglong2 *>(evk + (((size_t)j * 2 + 1) * F + qp) * n + k));
-        const u64 dd[2] = {dv.x, dv.y}, bb[2] = {kb.x, kb.y}, aa[2] = {ka.x, ka.y};
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-            const uint32_t dl = (uint32_t)dd[c] & 0x3fffffffu, dh = (uint32_t)(dd[c] >> 30);
-            const uint32_t bl = (uint32_t)bb[c] & 0x3fffffffu, bh = (uint32_t)(bb[c] >> 30);
-            const uint32_t al = (uint32_t)aa[c] & 0x3fffffffu, ah = (uint32_t)(aa[c] >> 30);
-            s[c][0][0] = mad_wide(dl, bl, s[c][0][0]), s[c][0][1] = mad_wide(dl, bh, s[c][0][1]);
-            s[c][0][2] = mad_wide(dh, bl, s[c][0][2]), s[c][0][3] = mad_wide(dh, bh, s[c][0][3]);
-            s[c][1][0] = mad_wide(dl, al, s[c][1][0]), s[c][1][1] = mad_wide(dl, ah, s[c][1][1]);
-            s[c][1][2] = mad_wide(dh, al, s[c][1][2]), s[c][1][3] = mad_wide(dh, ah, s[c][1][3]);
-        }
+        const u64 dv = dp[(size_t)j * W * n];
+        const u64 kb = __ldcs(kp + (size_t)(2 * j) * F * n), ka = __ldcs(kp + (size_t)(2 * j + 1) * F * n);
+        const uint32_t dl = (uint32_t)dv & 0x3fffffffu, dh = (uint32_t)(dv >> 30);
+        const uint32_t bl = (uint32_t)kb & 0x3fffffffu, bh = (uint32_t)(kb >> 30);
+        const uint32_t al = (uint32_t)ka & 0x3fffffffu, ah = (uint32_t)(ka >> 30);
+        sb[0] = mad_wide(dl, bl, sb[0]), sb[1] = mad_wide(dl, bh, sb[1]), sb[2] = mad_wide(dh, bl, sb[2]), sb[3] = mad_wide(dh, bh, sb[3]);
+        sa[0] = mad_wide(dl, al, sa[0]), sa[1] = mad_wide(dl, ah, sa[1]), sa[2] = mad_wide(dh, al, sa[2]), sa[3] = mad_wide(dh, ah, sa[3]);
     }
-    u64 r[2][2];
-#pragma unroll
-    for (int c = 0; c < 2; c++)
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            u64 lo = 0, hi = 0;
-            acc_split30(lo, hi, s[c][h][0], s[c][h][1], s[c][h][2], s[c][h][3]);
-            r[c][h] = reduce128(hi, lo, m);
-        }
-    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)0 * W + t) * n + k) = make_ulonglong2(r[0][0], r[1][0]);
-    *reinterpret_cast<ulonglong2 *>(acc + ((size_t)1 * W + t) * n + k) = make_ulonglong2(r[0][1], r[1][1]);
+    u64 lo = 0, hi = 0;
+    acc_split30(lo, hi, sb[0], sb[1], sb[2], sb[3]);
+    acc[((size_t)0 * W + t) * n + k] = reduce128(hi, lo, m);
+    lo = 0, hi = 0;
+    acc_split30(lo, hi, sa[0], sa[1], sa[2], sa[3]);
+    acc[((size_t)1 * W + t) * n + k] = reduce128(hi, lo, m);
 }
 
 // out_b[i][p] = ((acc_b[i] - conv_b[i]) * P^-1 + add_b[i]) [src(p)], src = Galois gather (identity when g == 1)
@@ -184,7 +174,7 @@ void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const 
     }
 }
 void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc, cudaStream_t st) {
-    g_launches++, ks_inner<<<dim3((T.n / 2 + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, digits, evk, acc);
+    g_launches++, ks_inner<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, digits, evk, acc);
 }
 void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st) {
     const int gx = (T.n + CONV_THREADS - 1) / CONV_THREADS;

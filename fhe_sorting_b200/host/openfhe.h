@@ -1,0 +1,454 @@
+// openfhe.h — lbcrypto-shaped C++ shim over the C ABI of libfheb200.so (include/fhe_b200.h).
+//
+// This header gives the reference's host code (src/sort_algo.h, rotation.h, sign.cpp, comparison.cpp, encryption.cpp of
+// oksuman/FHE-Sorting) the subset of OpenFHE's CryptoContext<DCRTPoly> API that it calls: same names,
+// argument meaning and error behaviour (exceptions), every call forwarding to the CUDA engine.  There is no arithmetic
+// in this file.  Semantics mirrored from OpenFHE: FLEXIBLEAUTOEXT level bookkeeping (done inside the engine), in-place
+// operations mutate the shared ciphertext object, SetSlots is metadata on a shared handle (src/sort_algo.h:429,614).
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <functional>
+#include <iostream>
+#include <memory>
+#include <random>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/fhe_b200.h"
+
+namespace lbcrypto {
+
+typedef unsigned int usint;
+struct DCRTPoly {};                 // tag only: polynomials live in HBM behind the C ABI
+struct CryptoContextCKKSRNS {};
+enum SecurityLevel { HEStd_128_classic, HEStd_192_classic, HEStd_256_classic, HEStd_NotSet };
+enum PKESchemeFeature { PKE = 1, KEYSWITCH = 2, PRE = 4, LEVELEDSHE = 8, ADVANCEDSHE = 16, MULTIPARTY = 32, FHE = 64 };
+
+inline void fheb200_check(int rc) {
+    if (rc != 0) throw std::runtime_error(std::string("fheb200: ") + fheb200_last_error());
+}
+
+template <typename Scheme> class CCParams {
+    usint depth_ = 1, scale_ = 50, first_ = 60, batch_ = 0, ring_ = 0, dnum_ = 3;
+    SecurityLevel sec_ = HEStd_128_classic;
+
+  public:
+    void SetMultiplicativeDepth(usint d) { depth_ = d; }
+    void SetScalingModSize(usint s) { scale_ = s; }
+    void SetFirstModSize(usint s) { first_ = s; }
+    void SetBatchSize(usint b) { batch_ = b; }
+    void SetRingDim(usint r) { ring_ = r; }
+    void SetSecurityLevel(SecurityLevel s) { sec_ = s; }
+    void SetNumLargeDigits(usint d) { dnum_ = d; }
+    usint GetMultiplicativeDepth() const { return depth_; }
+    usint GetScalingModSize() const { return scale_; }
+    usint GetFirstModSize() const { return first_; }
+    usint GetBatchSize() const { return batch_; }
+    usint GetRingDim() const { return ring_; }
+    usint GetNumLargeDigits() const { return dnum_; }
+    SecurityLevel GetSecurityLevel() const { return sec_; }
+};
+
+class CryptoContextImpl;
+typedef std::shared_ptr<CryptoContextImpl> ContextPtr;
+
+// ---- plaintext
+class PlaintextImpl {
+  public:
+    fheb200_pt *h = nullptr;
+    ~PlaintextImpl() {
+        if (h) fheb200_pt_release(h);
+    }
+    std::vector<double> GetRealPackedValue() const {
+        size_t n = 0;
+        fheb200_check(fheb200_pt_values(h, nullptr, 0, &n));
+        std::vector<double> v(n);
+        fheb200_check(fheb200_pt_values(h, v.data(), n, &n));
+        return v;
+    }
+    void SetLength(size_t n) { fheb200_check(fheb200_pt_set_length(h, n)); }
+    double GetLogPrecision() const {
+        double b = 0;
+        fheb200_check(fheb200_pt_log_precision(h, &b));
+        return b;
+    }
+};
+typedef std::shared_ptr<PlaintextImpl> Plaintext;
+typedef std::shared_ptr<const PlaintextImpl> ConstPlaintext;
+inline std::ostream &operator<<(std::ostream &os, const Plaintext &p) {
+    os << "(";
+    for (double v : p->GetRealPackedValue()) os << v << ", ";
+    return os << " ... ); Estimated precision: " << p->GetLogPrecision() << " bits";
+}
+
+// ---- ciphertext: a nullable, copyable handle to a shared mutable object (as lbcrypto::Ciphertext<DCRTPoly>)
+template <typename P> class Ciphertext;
+class CiphertextImpl {
+  public:
+    fheb200_ct *h = nullptr;
+    ContextPtr cc;
+    CiphertextImpl(fheb200_ct *h_, ContextPtr cc_) : h(h_), cc(std::move(cc_)) {}
+    CiphertextImpl(const CiphertextImpl &) = delete;
+    ~CiphertextImpl() {
+        if (h) fheb200_ct_release(h);
+    }
+    void replace(fheb200_ct *n) { // in-place operations swap the engine object under the shared handle
+        if (h) fheb200_ct_release(h);
+        h = n;
+    }
+    size_t GetLevel() const {
+        int lv = 0;
+        fheb200_check(fheb200_ct_info(h, &lv, nullptr, nullptr, nullptr, nullptr));
+        return (size_t)lv;
+    }
+    usint GetSlots() const {
+        int s = 0;
+        fheb200_check(fheb200_ct_info(h, nullptr, nullptr, &s, nullptr, nullptr));
+        return (usint)s;
+    }
+    usint GetNoiseScaleDeg() const {
+        int d = 0;
+        fheb200_check(fheb200_ct_info(h, nullptr, &d, nullptr, nullptr, nullptr));
+        return (usint)d;
+    }
+    double GetScalingFactor() const {
+        double s = 0;
+        fheb200_check(fheb200_ct_info(h, nullptr, nullptr, nullptr, nullptr, &s));
+        return s;
+    }
+    void SetSlots(usint s) const { fheb200_check(fheb200_ct_set_slots(h, (int)s)); }
+    ContextPtr GetCryptoContext() const { return cc; }
+    Ciphertext<DCRTPoly> Clone() const;
+};
+template <typename P> class Ciphertext {
+    std::shared_ptr<CiphertextImpl> p_;
+
+  public:
+    Ciphertext() = default;
+    Ciphertext(std::nullptr_t) {}
+    explicit Ciphertext(std::shared_ptr<CiphertextImpl> p) : p_(std::move(p)) {}
+    CiphertextImpl *operator->() const { return p_.get(); }
+    CiphertextImpl &operator*() const { return *p_; }
+    explicit operator bool() const { return (bool)p_; }
+    bool operator==(std::nullptr_t) const { return !p_; }
+    bool operator!=(std::nullptr_t) const { return (bool)p_; }
+    CiphertextImpl *get() const { return p_.get(); }
+};
+template <typename P> using ConstCiphertext = Ciphertext<P>;
+
+// ---- keys
+struct KeySetImpl {
+    fheb200_keys *h = nullptr;
+    ~KeySetImpl() {
+        if (h) fheb200_keys_release(h);
+    }
+};
+template <typename P> class PublicKey {
+  public:
+    std::shared_ptr<KeySetImpl> k;
+    explicit operator bool() const { return (bool)k; }
+};
+template <typename P> class PrivateKey {
+  public:
+    std::shared_ptr<KeySetImpl> k;
+    explicit operator bool() const { return (bool)k; }
+};
+template <typename P> struct KeyPair {
+    PublicKey<P> publicKey;
+    PrivateKey<P> secretKey;
+    bool good() const { return (bool)publicKey.k; }
+};
+struct EncodingParamsImpl {
+    usint batch = 0;
+    usint GetBatchSize() const { return batch; }
+};
+struct FastRotationPrecomp { // stands for std::shared_ptr<std::vector<DCRTPoly>>
+    fheb200_pre *h = nullptr;
+    ~FastRotationPrecomp() {
+        if (h) fheb200_pre_release(h);
+    }
+};
+
+// ---- the crypto context
+class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl> {
+    typedef Ciphertext<DCRTPoly> CT;
+    CT wrap(fheb200_ct *h) { return CT(std::make_shared<CiphertextImpl>(h, shared_from_this())); }
+    CT unary(int (*fn)(fheb200_ctx *, fheb200_ct *, fheb200_ct **), const CT &a) {
+        need(a);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fn(ctx, a->h, &o));
+        return wrap(o);
+    }
+    static void need(const CT &a) {
+        if (!a) throw std::runtime_error("null ciphertext passed to the crypto context");
+    }
+
+  public:
+    fheb200_ctx *ctx = nullptr;
+    usint ringDim = 0, batch = 0, depth = 0, features = 0;
+    std::shared_ptr<KeySetImpl> evalKeys; // keys whose evaluation keys live in HBM (EvalMultKeyGen / EvalRotateKeyGen)
+    ~CryptoContextImpl() {
+        evalKeys.reset();
+        if (ctx) fheb200_ctx_release(ctx);
+    }
+    void Enable(usint f) { features |= f; }
+    void Enable(PKESchemeFeature f) { features |= (usint)f; }
+    usint GetRingDimension() const { return ringDim; }
+    usint GetCyclotomicOrder() const { return 2 * ringDim; }
+    std::shared_ptr<EncodingParamsImpl> GetEncodingParams() const {
+        auto e = std::make_shared<EncodingParamsImpl>();
+        e->batch = batch;
+        return e;
+    }
+
+    // ---- keys (tests/DirectSortTest.cpp:43-47)
+    KeyPair<DCRTPoly> KeyGen() {
+        auto k = std::make_shared<KeySetImpl>();
+        fheb200_check(fheb200_keygen(ctx, seed_next(), &k->h));
+        KeyPair<DCRTPoly> kp;
+        kp.publicKey.k = k;
+        kp.secretKey.k = k;
+        return kp;
+    }
+    void EvalMultKeyGen(const PrivateKey<DCRTPoly> &sk) {
+        fheb200_check(fheb200_eval_mult_keygen(ctx, sk.k->h));
+        evalKeys = sk.k;
+    }
+    void EvalRotateKeyGen(const PrivateKey<DCRTPoly> &sk, const std::vector<int> &idx) {
+        fheb200_check(fheb200_eval_rotate_keygen(ctx, sk.k->h, idx.data(), idx.size()));
+        evalKeys = sk.k;
+    }
+    void EvalBootstrapSetup(const std::vector<uint32_t> &, const std::vector<uint32_t> & = {0, 0}, uint32_t = 0) {
+        throw std::runtime_error("EvalBootstrapSetup: CKKS bootstrapping is not built yet (DESIGN.md, out of scope this round)");
+    }
+    void EvalBootstrapKeyGen(const PrivateKey<DCRTPoly> &, uint32_t) {
+        throw std::runtime_error("EvalBootstrapKeyGen: CKKS bootstrapping is not built yet");
+    }
+    CT EvalBootstrap(const CT &, uint32_t = 1, uint32_t = 0) {
+        throw std::runtime_error("EvalBootstrap: CKKS bootstrapping is not built yet");
+    }
+
+    // ---- encode / encrypt / decrypt (src/encryption.cpp:5-27)
+    Plaintext MakeCKKSPackedPlaintext(const std::vector<double> &v, size_t noiseScaleDeg = 1, uint32_t level = 0,
+                                      const void *params = nullptr, usint slots = 0) {
+        (void)params;
+        auto p = std::make_shared<PlaintextImpl>();
+        fheb200_check(fheb200_make_packed_plaintext(ctx, v.data(), v.size(), (int)noiseScaleDeg, (int)level, (int)slots, &p->h));
+        return p;
+    }
+    CT Encrypt(const PublicKey<DCRTPoly> &pk, const Plaintext &pt) {
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_encrypt(ctx, pk.k->h, pt->h, &o));
+        return wrap(o);
+    }
+    void Decrypt(const PrivateKey<DCRTPoly> &sk, const CT &ct, Plaintext *out) {
+        need(ct);
+        auto p = std::make_shared<PlaintextImpl>();
+        fheb200_check(fheb200_decrypt(ctx, sk.k->h, ct->h, &p->h));
+        *out = p;
+    }
+
+    // ---- additions / subtractions
+    CT EvalAdd(const CT &a, const CT &b) { return binary(fheb200_eval_add, a, b); }
+    CT EvalSub(const CT &a, const CT &b) { return binary(fheb200_eval_sub, a, b); }
+    CT EvalAdd(const CT &a, const Plaintext &p) { return plain(fheb200_eval_add_plain, a, p); }
+    CT EvalAdd(const Plaintext &p, const CT &a) { return plain(fheb200_eval_add_plain, a, p); }
+    CT EvalSub(const CT &a, const Plaintext &p) { return plain(fheb200_eval_sub_plain, a, p); }
+    CT EvalSub(const Plaintext &p, const CT &a) { return EvalNegate(plain(fheb200_eval_sub_plain, a, p)); }
+    CT EvalAdd(const CT &a, double c) { return constant(fheb200_eval_add_const, a, c); }
+    CT EvalAdd(double c, const CT &a) { return constant(fheb200_eval_add_const, a, c); }
+    CT EvalSub(const CT &a, double c) { return constant(fheb200_eval_add_const, a, -c); }
+    CT EvalSub(double c, const CT &a) { return EvalNegate(constant(fheb200_eval_add_const, a, -c)); }
+    CT EvalNegate(const CT &a) { return unary(fheb200_eval_negate, a); }
+    void EvalNegateInPlace(CT &a) { inplace(a, EvalNegate(a)); }
+    void EvalAddInPlace(CT &a, const CT &b) { inplace(a, EvalAdd(a, b)); }
+    void EvalAddInPlace(CT &a, const Plaintext &p) { inplace(a, EvalAdd(a, p)); }
+    void EvalAddInPlace(CT &a, double c) { inplace(a, EvalAdd(a, c)); }
+    void EvalSubInPlace(CT &a, const CT &b) { inplace(a, EvalSub(a, b)); }
+    void EvalSubInPlace(CT &a, double c) { inplace(a, EvalSub(a, c)); }
+    CT EvalAddMany(const std::vector<CT> &v) {
+        if (v.empty()) throw std::runtime_error("EvalAddMany: empty input");
+        std::vector<fheb200_ct *> hs;
+        for (auto &c : v) {
+            need(c);
+            hs.push_back(c->h);
+        }
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_add_many(ctx, hs.data(), hs.size(), &o));
+        return wrap(o);
+    }
+
+    // ---- multiplications (src/sign.cpp:23-56, src/sort_algo.h:344,730)
+    CT EvalMult(const CT &a, const CT &b) { return binary(fheb200_eval_mult, a, b); }
+    CT EvalMultAndRelinearize(const CT &a, const CT &b) { return binary(fheb200_eval_mult, a, b); }
+    CT EvalSquare(const CT &a) { return binary(fheb200_eval_mult, a, a); }
+    CT EvalMult(const CT &a, const Plaintext &p) { return plain(fheb200_eval_mult_plain, a, p); }
+    CT EvalMult(const Plaintext &p, const CT &a) { return plain(fheb200_eval_mult_plain, a, p); }
+    CT EvalMult(const CT &a, double c) { return constant(fheb200_eval_mult_const, a, c); }
+    CT EvalMult(double c, const CT &a) { return constant(fheb200_eval_mult_const, a, c); }
+    void EvalMultInPlace(CT &a, double c) { inplace(a, EvalMult(a, c)); }
+    CT Rescale(const CT &a) { return unary(fheb200_eval_rescale, a); }
+
+    // ---- rotations (src/rotation.h:224-350)
+    CT EvalRotate(const CT &a, int index) {
+        need(a);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_rotate(ctx, a->h, index, &o));
+        return wrap(o);
+    }
+    std::shared_ptr<FastRotationPrecomp> EvalFastRotationPrecompute(const CT &a) {
+        need(a);
+        auto p = std::make_shared<FastRotationPrecomp>();
+        fheb200_check(fheb200_fast_rotation_precompute(ctx, a->h, &p->h));
+        return p;
+    }
+    CT EvalFastRotation(const CT &a, usint index, usint /*cyclotomic order*/, const std::shared_ptr<FastRotationPrecomp> &pre) {
+        need(a);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_fast_rotation(ctx, a->h, (int)index, pre->h, &o));
+        return wrap(o);
+    }
+    bool HasRotationKey(int index) const {
+        int present = 0;
+        fheb200_check(fheb200_has_rotation_key(ctx, index, &present));
+        return present != 0;
+    }
+
+    // ---- polynomial evaluation (src/sort_algo.h:629,728 ; src/sign.cpp:76,448,616 ; src/mehp24/mehp24_utils.cpp:256)
+    CT EvalChebyshevSeries(const CT &x, const std::vector<double> &coeffs, double a, double b) {
+        need(x);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_chebyshev_series(ctx, x->h, coeffs.data(), coeffs.size(), a, b, &o));
+        return wrap(o);
+    }
+    CT EvalChebyshevSeriesPS(const CT &x, const std::vector<double> &coeffs, double a, double b) {
+        return EvalChebyshevSeries(x, coeffs, a, b);
+    }
+    CT EvalChebyshevFunction(std::function<double(double)> f, const CT &x, double a, double b, uint32_t degree);
+    CT EvalPolyLinear(const CT &x, const std::vector<double> &coeffs) {
+        need(x);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_poly(ctx, x->h, coeffs.data(), coeffs.size(), &o));
+        return wrap(o);
+    }
+    CT EvalPoly(const CT &x, const std::vector<double> &coeffs) { return EvalPolyLinear(x, coeffs); }
+    CT CloneCt(const CiphertextImpl &a) {
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_ct_clone(ctx, a.h, &o));
+        return wrap(o);
+    }
+    void Sync() { fheb200_check(fheb200_ctx_sync(ctx)); }
+    static void SetKeySeed(uint64_t s) { seed_state() = s; }
+
+  private:
+    static uint64_t &seed_state() {
+        static uint64_t s = 0;
+        return s;
+    }
+    static uint64_t seed_next() {
+        uint64_t &s = seed_state();
+        if (s == 0) s = ((uint64_t)std::random_device{}() << 32) ^ std::random_device{}();
+        return s++;
+    }
+    CT binary(int (*fn)(fheb200_ctx *, fheb200_ct *, fheb200_ct *, fheb200_ct **), const CT &a, const CT &b) {
+        need(a), need(b);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fn(ctx, a->h, b->h, &o));
+        return wrap(o);
+    }
+    CT plain(int (*fn)(fheb200_ctx *, fheb200_ct *, fheb200_pt *, fheb200_ct **), const CT &a, const Plaintext &p) {
+        need(a);
+        if (!p) throw std::runtime_error("null plaintext passed to the crypto context");
+        fheb200_ct *o = nullptr;
+        fheb200_check(fn(ctx, a->h, p->h, &o));
+        return wrap(o);
+    }
+    CT constant(int (*fn)(fheb200_ctx *, fheb200_ct *, double, fheb200_ct **), const CT &a, double c) {
+        need(a);
+        fheb200_ct *o = nullptr;
+        fheb200_check(fn(ctx, a->h, c, &o));
+        return wrap(o);
+    }
+    void inplace(CT &a, const CT &r) { // move the result under a's shared handle
+        fheb200_ct *n = r->h;
+        r->h = nullptr;
+        a->replace(n);
+    }
+};
+
+inline Ciphertext<DCRTPoly> CiphertextImpl::Clone() const { return cc->CloneCt(*this); }
+
+template <typename P> class CryptoContext {
+    ContextPtr p_;
+
+  public:
+    CryptoContext() = default;
+    CryptoContext(std::nullptr_t) {}
+    explicit CryptoContext(ContextPtr p) : p_(std::move(p)) {}
+    CryptoContext(const ContextPtr &p, int) : p_(p) {}
+    CryptoContextImpl *operator->() const { return p_.get(); }
+    explicit operator bool() const { return (bool)p_; }
+    const ContextPtr &ptr() const { return p_; }
+};
+// ct->GetCryptoContext() returns a ContextPtr; let it convert where the reference stores a CryptoContext<DCRTPoly>
+template <typename P> inline CryptoContext<P> ToContext(const ContextPtr &p) { return CryptoContext<P>(p); }
+
+// lbcrypto::EvalChebyshevCoefficients(f, a, b, degree) (utils/generate_cheb_coeffs.cpp:17): host-only double math
+inline std::vector<double> EvalChebyshevCoefficients(std::function<double(double)> f, double a, double b, uint32_t degree) {
+    std::vector<double> out(degree + 1);
+    auto tramp = [](double x, void *u) { return (*static_cast<std::function<double(double)> *>(u))(x); };
+    fheb200_check(fheb200_chebyshev_coefficients(tramp, &f, a, b, (int)degree, out.data()));
+    return out;
+}
+inline Ciphertext<DCRTPoly> CryptoContextImpl::EvalChebyshevFunction(std::function<double(double)> f, const CT &x, double a,
+                                                                       double b, uint32_t degree) {
+    return EvalChebyshevSeries(x, EvalChebyshevCoefficients(std::move(f), a, b, degree), a, b);
+}
+
+// ring dimension OpenFHE would pick for HEStd_128_classic (uniform ternary) when SetRingDim is not called:
+// smallest power of two whose log(QP) bound (HomomorphicEncryption.org standard table, extended) covers the chain
+inline usint StdRingDim128(double logQP) {
+    static const struct { usint n; double bits; } tab[] = {{1024, 27},   {2048, 54},    {4096, 109},    {8192, 218},
+                                                           {16384, 438}, {32768, 881}, {65536, 1747}, {131072, 3523}};
+    for (auto &t : tab)
+        if (logQP <= t.bits) return t.n;
+    throw std::runtime_error("GenCryptoContext: modulus too large for 128-bit security at ring dimension <= 2^17");
+}
+
+// GenCryptoContext(CCParams<CryptoContextCKKSRNS>) (tests/DirectSortTest.cpp:24-41).  OpenFHE defaults for everything the
+// reference does not set: FLEXIBLEAUTOEXT, HYBRID key switching with 3 digits, uniform ternary secret, first modulus 60.
+inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKSRNS> &p, int device = -1) {
+    usint ring = p.GetRingDim();
+    const usint L = p.GetMultiplicativeDepth() + 2; // FLEXIBLEAUTOEXT keeps one extra level
+    const usint dnum = p.GetNumLargeDigits();
+    const double logQ = p.GetFirstModSize() + (double)(L - 1) * p.GetScalingModSize();
+    const double logP = 60.0 * std::ceil(((double)((L + dnum - 1) / dnum) * p.GetScalingModSize() + 20) / 60.0);
+    if (ring == 0) {
+        if (p.GetSecurityLevel() == HEStd_NotSet) throw std::runtime_error("GenCryptoContext: SetRingDim is required with HEStd_NotSet");
+        ring = StdRingDim128(logQ + logP);
+        if (ring < 2 * p.GetBatchSize()) ring = 2 * p.GetBatchSize();
+    } else if (p.GetSecurityLevel() == HEStd_128_classic && ring < StdRingDim128(logQ + logP)) {
+        throw std::runtime_error("GenCryptoContext: ring dimension too small for HEStd_128_classic at this depth");
+    }
+    int logn = 0;
+    while ((1u << logn) < ring) logn++;
+    if ((1u << logn) != ring) throw std::runtime_error("GenCryptoContext: ring dimension must be a power of two");
+    if (device < 0) {
+        const char *e = getenv("FHEB200_DEVICE");
+        device = e ? atoi(e) : 0;
+    }
+    fheb200_params q;
+    q.log_ring_dim = logn, q.mult_depth = (int)p.GetMultiplicativeDepth(), q.scaling_mod_size = (int)p.GetScalingModSize();
+    q.first_mod_size = (int)p.GetFirstModSize(), q.batch_size = (int)p.GetBatchSize(), q.num_large_digits = (int)dnum;
+    q.device = device;
+    auto impl = std::make_shared<CryptoContextImpl>();
+    fheb200_check(fheb200_ctx_create(&q, &impl->ctx));
+    impl->ringDim = ring, impl->depth = p.GetMultiplicativeDepth();
+    impl->batch = p.GetBatchSize() ? p.GetBatchSize() : ring / 2;
+    return CryptoContext<DCRTPoly>(impl);
+}
+
+} // namespace lbcrypto

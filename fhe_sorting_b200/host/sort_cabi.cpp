@@ -1,0 +1,212 @@
+// sort_cabi.cpp — C entry points of the host-side sort drivers (libfhesort.so), declared in include/fhe_sort.h.
+// A session owns what the reference's test fixture owns (tests/DirectSortTest.cpp:22-51): CryptoContext, key pair,
+// rotation / relinearisation keys resident in HBM, a DebugEncryption and a DirectSort<N>.
+#include <chrono>
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "../../include/fhe_sort.h"
+#include "comparison.h"
+#include "rotation.h"
+#include "sort_algo.h"
+
+namespace {
+thread_local std::string g_err;
+
+struct SessionBase {
+    CryptoContext<DCRTPoly> cc;
+    KeyPair<DCRTPoly> keys;
+    std::shared_ptr<DebugEncryption> enc;
+    std::vector<int> rotations;
+    int len = 0, depth = 0;
+    double setup_ms = 0;
+    virtual ~SessionBase() = default;
+    virtual Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
+    virtual Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
+    virtual Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &rank, const Ciphertext<DCRTPoly> &in) = 0;
+    virtual Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) = 0;
+};
+template <int N> struct Session : SessionBase {
+    std::unique_ptr<DirectSort<N>> sorter;
+    std::unique_ptr<RotationComposer<N>> composer;
+    Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        return sorter->sort(in, SignFunc::CompositeSign, cfg);
+    }
+    Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        return sorter->constructRank(in, SignFunc::CompositeSign, cfg);
+    }
+    Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &rk, const Ciphertext<DCRTPoly> &in) override {
+        return sorter->rotationIndexCheckN(rk, in);
+    }
+    Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) override { return composer->rotate(in, r); }
+};
+
+template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
+    auto t0 = std::chrono::steady_clock::now();
+    auto s = std::make_unique<Session<N>>();
+    CCParams<CryptoContextCKKSRNS> p;
+    p.SetRingDim(1u << log_ring_dim);
+    DirectSort<N>::getSizeParameters(p, s->rotations);
+    if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
+    p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
+    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    s->cc = GenCryptoContext(p, device);
+    s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE);
+    s->keys = s->cc->KeyGen();
+    s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
+    s->cc->EvalMultKeyGen(s->keys.secretKey);
+    s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);
+    s->sorter = std::make_unique<DirectSort<N>>(s->cc, s->keys.publicKey, s->rotations, s->enc);
+    s->composer = std::make_unique<RotationComposer<N>>(s->cc, s->enc, s->rotations);
+    s->len = N, s->depth = (int)p.GetMultiplicativeDepth();
+    s->cc->Sync();
+    s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s.release();
+}
+SignConfig sign_config(int n, int dg, int df, int N) {
+    if (n == 0) { // the reference tests' choice per array length (tests/DirectSortTest.cpp:103-111)
+        n = 3, df = 2;
+        dg = N <= 16 ? 2 : N <= 128 ? 3 : N <= 512 ? 4 : 5;
+    }
+    return SignConfig(CompositeSignConfig(n, dg, df));
+}
+} // namespace
+
+struct fhesort_session {
+    std::unique_ptr<SessionBase> s;
+};
+
+#define GUARD(...)                  \
+    try {                           \
+        __VA_ARGS__;                \
+        return 0;                   \
+    } catch (const std::exception &e) { \
+        g_err = e.what();           \
+        return 1;                   \
+    } catch (...) {                 \
+        g_err = "unknown error";    \
+        return 1;                   \
+    }
+
+extern "C" {
+
+const char *fhesort_last_error(void) { return g_err.c_str(); }
+
+int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out) throw std::invalid_argument("null argument: out");
+        SessionBase *b = nullptr;
+        switch (N) {
+        case 4: b = make_session<4>(log_ring_dim, mult_depth, seed, device); break;
+        case 8: b = make_session<8>(log_ring_dim, mult_depth, seed, device); break;
+        case 16: b = make_session<16>(log_ring_dim, mult_depth, seed, device); break;
+        case 32: b = make_session<32>(log_ring_dim, mult_depth, seed, device); break;
+        case 64: b = make_session<64>(log_ring_dim, mult_depth, seed, device); break;
+        case 128: b = make_session<128>(log_ring_dim, mult_depth, seed, device); break;
+        case 256: b = make_session<256>(log_ring_dim, mult_depth, seed, device); break;
+        case 512: b = make_session<512>(log_ring_dim, mult_depth, seed, device); break;
+        case 1024: b = make_session<1024>(log_ring_dim, mult_depth, seed, device); break;
+        default: throw std::invalid_argument("DirectSort: array length must be a power of two in 4..1024");
+        }
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(b)};
+    })
+}
+int fhesort_session_free(fhesort_session *s) {
+    GUARD({ delete s; })
+}
+int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_keys, double *setup_ms) {
+    GUARD({
+        if (!s) throw std::invalid_argument("null argument: session");
+        if (mult_depth) *mult_depth = s->s->depth;
+        if (num_rotation_keys) *num_rotation_keys = (int)s->s->rotations.size();
+        if (setup_ms) *setup_ms = s->s->setup_ms;
+    })
+}
+
+// which: 0 = full sort, 1 = constructRank only (output = ranks), 2 = rotationIndexCheckN on plaintext ranks given in aux
+int fhesort_run(fhesort_session *s, int which, const double *input, const double *aux, int sign_n, int dg, int df,
+                double *output, double *elapsed_ms, int *out_level) {
+    GUARD({
+        if (!s || !input || !output) throw std::invalid_argument("null argument");
+        SessionBase &S = *s->s;
+        std::vector<double> in(input, input + S.len);
+        SignConfig cfg = sign_config(sign_n, dg, df, S.len);
+        S.cc->Sync();
+        auto t0 = std::chrono::steady_clock::now();
+        auto ct = S.enc->encryptInput(in);
+        Ciphertext<DCRTPoly> r;
+        if (which == 0) r = S.sort(ct, cfg);
+        else if (which == 1) r = S.rank(ct, cfg);
+        else if (which == 2) {
+            if (!aux) throw std::invalid_argument("null argument: aux (ranks)");
+            r = S.place(S.enc->encryptInput(std::vector<double>(aux, aux + S.len)), ct);
+        } else throw std::invalid_argument("fhesort_run: unknown stage");
+        std::vector<double> v = S.enc->getPlaintext(r, 0.0); // decrypt synchronises the stream
+        double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        for (int i = 0; i < S.len; i++) output[i] = i < (int)v.size() ? v[i] : 0.0;
+        if (elapsed_ms) *elapsed_ms = ms;
+        if (out_level) *out_level = (int)r->GetLevel();
+    })
+}
+
+// RotationComposer::rotate on a fresh encryption of `input` (count values, `slots` slots)
+int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output) {
+    GUARD({
+        if (!s || !input || !output) throw std::invalid_argument("null argument");
+        SessionBase &S = *s->s;
+        auto ct = S.enc->encryptInput(std::vector<double>(input, input + count));
+        auto v = S.enc->getPlaintext(S.composed_rotate(ct, rotation), 0.0);
+        for (int i = 0; i < count; i++) output[i] = v[i];
+    })
+}
+
+// host-only helpers (no GPU): the rotation-key list and Chebyshev table sizes the drivers would use
+int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count) {
+    GUARD({
+        std::vector<int> r;
+        switch (N) {
+        case 4: r = DirectSort<4>::rotationIndices(1 << log_ring_dim); break;
+        case 8: r = DirectSort<8>::rotationIndices(1 << log_ring_dim); break;
+        case 16: r = DirectSort<16>::rotationIndices(1 << log_ring_dim); break;
+        case 32: r = DirectSort<32>::rotationIndices(1 << log_ring_dim); break;
+        case 64: r = DirectSort<64>::rotationIndices(1 << log_ring_dim); break;
+        case 128: r = DirectSort<128>::rotationIndices(1 << log_ring_dim); break;
+        case 256: r = DirectSort<256>::rotationIndices(1 << log_ring_dim); break;
+        case 512: r = DirectSort<512>::rotationIndices(1 << log_ring_dim); break;
+        case 1024: r = DirectSort<1024>::rotationIndices(1 << log_ring_dim); break;
+        default: throw std::invalid_argument("unsupported N");
+        }
+        if (count) *count = (int)r.size();
+        for (int i = 0; i < (int)r.size() && i < capacity; i++) out[i] = r[i];
+    })
+}
+int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity, int *count) {
+    GUARD({
+        Decomposer<1024> d(std::vector<int>(key_indices, key_indices + num_keys));
+        auto st = d.decompose(rotation, wrap, algo == 0 ? DecomposeAlgo::NAF : algo == 1 ? DecomposeAlgo::BNAF : DecomposeAlgo::BINARY);
+        if (count) *count = (int)st.size();
+        for (int i = 0; i < (int)st.size() && i < capacity; i++) steps[i] = st[i].value * st[i].stepSize;
+    })
+}
+int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count) {
+    GUARD({
+        const std::vector<double> *c = nullptr;
+        switch (N) {
+        case 4: c = &selectDoubledSincCoefficients<4>(); break;
+        case 8: c = &selectDoubledSincCoefficients<8>(); break;
+        case 16: c = &selectDoubledSincCoefficients<16>(); break;
+        case 32: c = &selectDoubledSincCoefficients<32>(); break;
+        case 64: c = &selectDoubledSincCoefficients<64>(); break;
+        case 128: c = &selectDoubledSincCoefficients<128>(); break;
+        case 256: c = &selectDoubledSincCoefficients<256>(); break;
+        case 512: c = &selectDoubledSincCoefficients<512>(); break;
+        case 1024: c = &selectDoubledSincCoefficients<1024>(); break;
+        default: throw std::invalid_argument("unsupported N");
+        }
+        if (count) *count = (int)c->size();
+        for (int i = 0; i < (int)c->size() && i < capacity; i++) out[i] = (*c)[i];
+    })
+}
+
+} // extern "C"

@@ -1,0 +1,111 @@
+"""ctypes binding of libfhesort.so (include/fhe_sort.h): the C++ sort drivers (host/sort_algo.h ...) over the CUDA engine."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .lib import FheError
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SORT_LIB_PATH = os.path.join(_HERE, "libfhesort.so")
+_lib = None
+
+
+def load_sort():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SORT_LIB_PATH):
+            raise FheError("libfhesort.so is missing: build it with `make -C fhe_sorting_b200`")
+        _lib = C.CDLL(SORT_LIB_PATH)
+        _lib.fhesort_last_error.restype = C.c_char_p
+    return _lib
+
+
+def _ck(rc):
+    if rc != 0:
+        raise FheError(load_sort().fhesort_last_error().decode())
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def uniform_gap_input(n, seed=None):
+    """tests/utils.h:28-51 getVectorWithMinDiff(N, 0, 1, 1/N): the multiples of 1/N, shuffled (seeded here)."""
+    rng = np.random.default_rng(n if seed is None else seed)
+    return rng.permutation(n).astype(np.float64) / n
+
+
+class DirectSortSession:
+    """What tests/DirectSortTest.cpp's fixture sets up: context, keys in HBM, DirectSort<N>."""
+
+    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0):
+        L = load_sort()
+        h = C.c_void_p()
+        _ck(L.fhesort_session_create(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)))
+        self.h, self.n = h, n
+        d, k, ms = C.c_int(), C.c_int(), C.c_double()
+        _ck(L.fhesort_session_info(h, C.byref(d), C.byref(k), C.byref(ms)))
+        self.mult_depth, self.num_rotation_keys, self.setup_ms = d.value, k.value, ms.value
+
+    def close(self):
+        if self.h:
+            load_sort().fhesort_session_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _run(self, stage, values, aux=None, sign=(0, 0, 0)):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        assert v.shape == (self.n,)
+        out = np.zeros(self.n)
+        a = np.ascontiguousarray(aux, dtype=np.float64) if aux is not None else None
+        ms, lv = C.c_double(), C.c_int()
+        _ck(_lib.fhesort_run(self.h, stage, _dp(v), _dp(a) if a is not None else None, sign[0], sign[1], sign[2], _dp(out),
+                             C.byref(ms), C.byref(lv)))
+        return out, ms.value, lv.value
+
+    def sort(self, values, sign=(0, 0, 0)):
+        """DirectSort<N>::sort; returns (sorted values, elapsed ms incl. encrypt/decrypt, final level)."""
+        return self._run(0, values, None, sign)
+
+    def rank(self, values, sign=(0, 0, 0)):
+        return self._run(1, values, None, sign)
+
+    def place(self, values, ranks):
+        return self._run(2, values, ranks)
+
+    def composed_rotate(self, values, rotation):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        out = np.zeros(len(v))
+        _ck(_lib.fhesort_composed_rotate(self.h, _dp(v), len(v), rotation, _dp(out)))
+        return out
+
+
+def rotation_indices(n, log_ring_dim=17):
+    L = load_sort()
+    out = (C.c_int * 4096)()
+    cnt = C.c_int()
+    _ck(L.fhesort_rotation_indices(n, log_ring_dim, out, 4096, C.byref(cnt)))
+    return list(out[:cnt.value])
+
+
+def decompose(keys, rotation, wrap, algo="BINARY"):
+    L = load_sort()
+    k = (C.c_int * len(keys))(*keys)
+    out = (C.c_int * 64)()
+    cnt = C.c_int()
+    _ck(L.fhesort_decompose(k, len(keys), rotation, wrap, {"NAF": 0, "BNAF": 1, "BINARY": 2}[algo], out, 64, C.byref(cnt)))
+    return list(out[:cnt.value])
+
+
+def doubled_sinc_coefficients(n):
+    L = load_sort()
+    buf = np.zeros(16384)
+    cnt = C.c_int()
+    _ck(L.fhesort_doubled_sinc_coefficients(n, _dp(buf), len(buf), C.byref(cnt)))
+    return buf[:cnt.value].copy()

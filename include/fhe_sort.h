@@ -1,0 +1,38 @@
+/*
+ * fhe_sort.h — C ABI of the host-side sort drivers (libfhesort.so): the reference's DirectSort test fixture as a
+ * session object.  The drivers themselves are C++ (fhe_sorting_b200/host/: sort_algo.h, rotation.h, sign.h,
+ * comparison.h, encryption.h — same class and method names as the reference's src/ headers) running over the
+ * lbcrypto-shaped shim host/openfhe.h, which forwards every call to libfheb200.so (include/fhe_b200.h).
+ */
+#ifndef FHE_SORT_H
+#define FHE_SORT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fhesort_session fhesort_session;
+const char *fhesort_last_error(void);
+
+/* CCParams via DirectSort<N>::getSizeParameters, GenCryptoContext, KeyGen, EvalRotateKeyGen, EvalMultKeyGen, DirectSort<N>
+ * (tests/DirectSortTest.cpp:24-51, 96-100).  mult_depth = 0 keeps the per-N depth; seed = 0 draws one from the OS. */
+int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
+int fhesort_session_free(fhesort_session *s);
+int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_keys, double *setup_ms);
+/* encrypt(input[N]) -> stage -> decrypt(output[N]).  stage 0: DirectSort<N>::sort (src/sort_algo.h:752) ;
+ * 1: constructRank (:368) ; 2: rotationIndexCheckN (:658) on encrypted aux[N] ranks.  sign_n = 0 selects the
+ * reference tests' CompositeSign configuration for N.  elapsed_ms covers encrypt + stage + decrypt (host clock). */
+int fhesort_run(fhesort_session *s, int stage, const double *input, const double *aux, int sign_n, int dg, int df,
+                double *output, double *elapsed_ms, int *out_level);
+/* RotationComposer<N>::rotate (src/rotation.h:215-233) */
+int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output);
+/* host-only (no GPU needed) */
+int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count);
+int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity,
+                      int *count);
+int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

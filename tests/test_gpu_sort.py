@@ -1,0 +1,60 @@
+"""DirectSort through the C++ host drivers (libfhesort.so -> libfheb200.so): the reference's DirectSortTest /
+DirectSortNTest assertions (tests/DirectSortTest.cpp:128,169 ; tests/DirectSortNTest.cpp:124,199), -m gpu."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", params=[(8, 12), (16, 13), (64, 13), (128, 13)], ids=lambda p: "N%d_ring2^%d" % p)
+def session(request):
+    from fhe_sorting_b200.sort import DirectSortSession
+    n, logn = request.param
+    s = DirectSortSession(n, logn, seed=77 + n)
+    yield s
+    s.close()
+
+
+def test_sort_matches_plain_sort(session):
+    from fhe_sorting_b200.sort import uniform_gap_input
+    x = uniform_gap_input(session.n)
+    out, ms, level = session.sort(x)
+    assert np.abs(out - np.sort(x)).max() < 0.01          # tests/DirectSortTest.cpp:169
+    assert level == session.mult_depth                     # tests/DirectSortTest.cpp:128
+
+
+def test_construct_rank(session):
+    from fhe_sorting_b200.sort import uniform_gap_input
+    x = uniform_gap_input(session.n, seed=5)
+    ranks, _, _ = session.rank(x)
+    want = np.argsort(np.argsort(x)).astype(float)
+    assert np.abs(ranks - want).max() < 0.01
+
+
+def test_rotation_index_check_with_plain_ranks(session):
+    from fhe_sorting_b200.sort import uniform_gap_input
+    x = uniform_gap_input(session.n, seed=6)
+    ranks = np.argsort(np.argsort(x)).astype(float)
+    out, _, _ = session.place(x, ranks)
+    assert np.abs(out - np.sort(x)).max() < 0.01          # tests/DirectSortNTest.cpp:199
+    noisy = ranks + np.random.default_rng(1).uniform(-1e-3, 1e-3, session.n)
+    out, _, _ = session.place(x, noisy)
+    assert np.abs(out - np.sort(x)).max() < 0.01          # tests/DirectSortNTest.cpp:281
+
+
+def test_composed_rotation(session):
+    x = np.arange(1, session.n + 1, dtype=float)
+    for r in (1, 3, session.n // 2 + 1, session.n - 1):
+        got = session.composed_rotate(x, r)
+        assert np.abs(got - np.roll(x, -r)).max() < 1e-5
+
+
+def test_direct_sort_n16_reference_parameters():
+    """BASELINE config 1: DirectSort N=16 at ring 2^17, depth 25, CompositeSign(3,2,2)."""
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input
+    s = DirectSortSession(16, 17, seed=16)
+    x = uniform_gap_input(16)
+    out, ms, level = s.sort(x)
+    s.close()
+    assert np.abs(out - np.sort(x)).max() < 0.01
+    assert level == 25

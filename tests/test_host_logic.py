@@ -1,0 +1,57 @@
+"""Host-side logic of the sort drivers that needs no GPU: rotation-key schedule, index decomposition, Chebyshev tables."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+from fhe_sorting_b200 import sort as S
+
+
+def test_rotation_indices_cover_the_schedule():
+    for n in (4, 16, 64, 256, 1024):
+        idx = S.rotation_indices(n, 17)
+        P = min(n, 65536 // n)
+        assert all(0 < r < n * P for r in idx) and idx == sorted(set(idx))
+        # folds over the P copies
+        span = n * P // 2
+        while span >= n:
+            assert span in idx
+            span //= 2
+    assert len(S.rotation_indices(1024, 17)) == 161   # same key count as the reference's N = 1024 table
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/src/sort_algo.h"), reason="reference checkout not present")
+def test_rotation_indices_match_reference_tables_up_to_128():
+    import re
+    src = open("/root/reference/src/sort_algo.h").read()
+    body = src[src.index("static void getSizeParameters"):src.index("parameters.SetScalingModSize(modSize)")]
+    for m in re.finditer(r"case (\d+):(.*?)break;", body, re.S):
+        n = int(m.group(1))
+        if n > 128:
+            continue
+        ref = {int(x) for x in re.findall(r"\d+", re.search(r"rotations = \{(.*?)\};", m.group(2), re.S).group(1))}
+        slots = n * min(n, 65536 // n)
+        assert {r for r in ref if r % slots} == set(S.rotation_indices(n, 17))
+
+
+def test_decompose_sums_to_rotation():
+    """tests/DecomposeTest.cpp:64-74: the signed steps always add up to the requested rotation."""
+    keys = [1, 2, 4, 8, 16, 32, 64, 512]
+    for algo, rot in itertools.product(("NAF", "BNAF", "BINARY"), list(range(1, 130)) + [511, 513, 1000]):
+        steps = S.decompose(keys, rot, 1 << 20, algo)
+        assert sum(steps) == rot, (algo, rot, steps)
+    assert S.decompose(keys, 5, 1 << 20, "BINARY") == [1, 4]
+    assert sorted(S.decompose(keys, 7, 1 << 20, "NAF")) == [-1, 8]
+
+
+def test_doubled_sinc_table_is_a_one_hot_at_rank_offsets():
+    n = 16
+    c = S.doubled_sinc_coefficients(n)
+    assert 100 < len(c) < 160
+    assert all(float("%g" % v) == v for v in c)          # 6 significant digits, as the reference's generated header
+    k = np.arange(-2 * n + 1, n)                        # index - rank - r ranges over (-2N, N)
+    x = k / (2.0 * n)
+    y = np.polynomial.chebyshev.chebval(x, np.concatenate([[c[0] / 2], c[1:]]))
+    want = ((k == 0) | (k == -n)).astype(float)
+    assert np.abs(y - want).max() < 2e-3
