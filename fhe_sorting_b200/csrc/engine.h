@@ -141,6 +141,8 @@ class Context : public std::enable_shared_from_this<Context> {
     LimbScalars scalars_for(long double value, int ell, bool shoup) const;
 
   private:
+    std::map<int, std::pair<double2 *, int *>> fft_tabs_; // per slot count: (ksi, rot) tables of the special FFT in HBM
+    std::pair<double2 *, int *> fft_device_tables(int slots);
     std::map<int, DevicePlan> plans_;
     std::map<std::vector<uint32_t>, uint32_t *> descs_;
     std::vector<void *> owned_;

@@ -182,22 +182,28 @@ static void to_i128_words(long double x, u64 &lo, u64 &hi) {
     lo = (u64)(u128)v, hi = (u64)((u128)v >> 64);
 }
 
+std::pair<double2 *, int *> Context::fft_device_tables(int slots) {
+    auto it = fft_tabs_.find(slots);
+    if (it != fft_tabs_.end()) return it->second;
+    const FftTables &t = fft_tables(slots);
+    static_assert(sizeof(std::complex<double>) == sizeof(double2), "complex layout");
+    double2 *ksi = (double2 *)owned_alloc(sizeof(double2) * t.ksi.size(), t.ksi.data());
+    int *rot = (int *)owned_alloc(sizeof(int) * t.rot.size(), t.rot.data());
+    return fft_tabs_[slots] = std::make_pair(ksi, rot);
+}
+
+// slots values -> special inverse FFT -> * scale, round -> residues on `ell` limbs -> NTT; everything after the upload of
+// the slot values runs on the device (encode.cu)
 Mem Context::encode_at(const Plaintext &pt, int ell, double scale) {
     std::lock_guard<std::recursive_mutex> g(mu);
     FHE_CUDA(cudaSetDevice(device));
     const int n = P->n, slots = pt.slots, gap = n / (2 * slots);
-    std::vector<std::complex<double>> v(slots, std::complex<double>(0, 0));
-    for (int i = 0; i < slots && i < (int)pt.vals.size(); i++) v[i] = pt.vals[i];
-    if (slots == 1) { /* single slot: constant polynomial parts */ } else fft_special_inv(v);
-    std::vector<u64> words((size_t)4 * slots);
-    for (int i = 0; i < slots; i++) {
-        to_i128_words((long double)v[i].real() * (long double)scale, words[2 * (size_t)i], words[2 * (size_t)i + 1]);
-        to_i128_words((long double)v[i].imag() * (long double)scale, words[2 * (size_t)(slots + i)],
-                      words[2 * (size_t)(slots + i) + 1]);
-    }
-    Mem staging = alloc(words.size());
-    FHE_CUDA(cudaMemcpyAsync(staging->p, words.data(), words.size() * sizeof(u64), cudaMemcpyHostToDevice, stream));
-    FHE_CUDA(cudaStreamSynchronize(stream)); // `words` is pageable host memory
+    const size_t nv = std::min((size_t)slots, pt.vals.size());
+    Mem vbuf = alloc((size_t)2 * slots), staging = alloc((size_t)4 * slots);
+    if (nv < (size_t)slots) FHE_CUDA(cudaMemsetAsync(vbuf->p, 0, sizeof(double2) * slots, stream));
+    if (nv) FHE_CUDA(cudaMemcpyAsync(vbuf->p, pt.vals.data(), sizeof(double2) * nv, cudaMemcpyHostToDevice, stream));
+    auto tabs = fft_device_tables(slots);
+    k_encode_fft((double2 *)vbuf->p, slots, scale, tabs.first, tabs.second, staging->p, stream);
     Mem out = alloc((size_t)ell * n);
     k_expand_i128(T, staging->p, 2 * slots, gap, ell, out->p, stream);
     k_ntt_fwd(T, out->p, plan(ell).desc_q, ell, stream);

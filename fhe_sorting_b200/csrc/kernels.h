@@ -99,6 +99,9 @@ void k_expand_small(const DeviceTables &T, const int *small, u64 *out, const uin
 // 128-bit signed coefficients (lo,hi pairs) at stride `gap` -> residues on Q limbs 0..ell-1, zero elsewhere
 void k_expand_i128(const DeviceTables &T, const u64 *coef_lohi, int ncoef, int gap, int ell, u64 *out,
                    cudaStream_t st);
+// device CKKS encode: in-place special inverse FFT of v[size], then words (lo,hi pairs) <- round(v * scale / size) in the
+// layout k_expand_i128 consumes (real parts first, imaginary parts after); ksi = exp(2 pi i k / 4 size), rot = 5^j mod 4 size
+void k_encode_fft(double2 *v, int size, double scale, const double2 *ksi, const int *rot, u64 *words, cudaStream_t st);
 // b = e - a*s_new + [limb in digit] * pmod * s_old   over F limbs (one digit of a switching key)
 void k_evk_finish(const DeviceTables &T, int F, const u64 *a, const u64 *e, const u64 *s_new, const u64 *s_old,
                   const LimbScalars &pmod, u64 *b, cudaStream_t st);
