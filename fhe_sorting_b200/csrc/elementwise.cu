@@ -119,6 +119,50 @@ __global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, 
     st2(o, x, A);
 }
 
+// fused linear combination (Paterson-Stockmeyer leaves): each input coefficient is loaded once and feeds G accumulators
+template <int G>
+__global__ void __launch_bounds__(EW_THREADS) ew_lincomb(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
+                                                         const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
+    const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    if (k >= n) return;
+    const size_t idx = (size_t)blockIdx.y * n + k;
+    u64 lo[G], hi[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) lo[g] = 0, hi[g] = 0;
+    for (int t0 = 0; t0 < count; t0 += 16) {
+        u64 a0[G], a1[G], a2[G], a3[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) a0[g] = a1[g] = a2[g] = a3[g] = 0;
+        const int t1 = t0 + 16 < count ? t0 + 16 : count;
+        for (int t = t0; t < t1; t++) {
+            const u64 a = in[t][idx];
+            const uint32_t al = (uint32_t)a & 0x3fffffffu, ah = (uint32_t)(a >> 30);
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const uint2 h = __ldg(w + ((size_t)g * count + t) * ell + li);
+                a0[g] = mad_wide(al, h.x, a0[g]), a1[g] = mad_wide(al, h.y, a1[g]);
+                a2[g] = mad_wide(ah, h.x, a2[g]), a3[g] = mad_wide(ah, h.y, a3[g]);
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) acc_split30(lo[g], hi[g], a0[g], a1[g], a2[g], a3[g]);
+    }
+    const ModConst m = T.mc[li];
+#pragma unroll
+    for (int g = 0; g < G; g++) out[g][idx] = reduce128(hi[g], lo[g], m);
+}
+void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
+               u64 *const *out, cudaStream_t st) {
+    dim3 grid((T.n + EW_THREADS - 1) / EW_THREADS, limbs2);
+    g_launches++;
+    switch (G) {
+    case 1: ew_lincomb<1><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
+    case 2: ew_lincomb<2><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
+    case 3: ew_lincomb<3><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
+    default: ew_lincomb<4><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
+    }
+}
+
 void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st) {
     g_launches++, ew_binary<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, (int)op, a, b, out);
 }

@@ -136,6 +136,8 @@ class Context : public std::enable_shared_from_this<Context> {
     // scheme helpers
     Ct mod_reduce(const Ct &a);
     Ct mult_core_const(const Ct &a, double c);     // multiply by round(c * sf[level]); nsd += 1
+    // out[r] = sum_t round(w[r][t] * sf[level]) * in[t]  (all inputs at the same level and degree 1); null where all w vanish
+    std::vector<Ct> lincomb(const std::vector<Ct> &in, const std::vector<std::vector<double>> &w);
     void adjust_pair(Ct &a, Ct &b);                // AdjustLevelsAndDepthInPlace
     void adjust_pair_to_one(Ct &a, Ct &b);         // AdjustLevelsAndDepthToOneInPlace
     LimbScalars scalars_for(long double value, int ell, bool shoup) const;

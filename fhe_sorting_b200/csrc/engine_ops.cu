@@ -140,6 +140,45 @@ Ct Context::mult_core_const(const Ct &a, double c) { // EvalMultCoreInPlace: tim
     r->scale = a->scale * sfl;
     return r;
 }
+std::vector<Ct> Context::lincomb(const std::vector<Ct> &in, const std::vector<std::vector<double>> &w) {
+    LOCK;
+    std::vector<Ct> out(w.size());
+    if (in.empty() || w.empty()) return out;
+    const int n = P->n, ell = in[0]->ell, npoly = in[0]->npoly, count = (int)in.size();
+    for (auto &c : in)
+        if (c->ell != ell || c->npoly != npoly || c->nsd != in[0]->nsd)
+            throw std::runtime_error("lincomb: inputs must share level, degree and size");
+    const double sfl = P->sf[in[0]->level];
+    std::vector<int> live; // outputs with at least one non-zero weight
+    for (size_t r = 0; r < w.size(); r++) {
+        bool any = false;
+        for (double x : w[r]) any = any || x != 0.0;
+        if (any) live.push_back((int)r);
+    }
+    for (size_t g0 = 0; g0 < live.size(); g0 += 4) {
+        const int G = (int)std::min<size_t>(4, live.size() - g0);
+        // one blob: count input pointers, G output pointers, G*count*ell split weights
+        std::vector<u64> blob((size_t)count + G + (size_t)G * count * ell);
+        for (int t = 0; t < count; t++) blob[t] = (u64)(uintptr_t)in[t]->mem->p;
+        for (int g = 0; g < G; g++) {
+            Ct o = new_like(this, in[0], npoly, ell);
+            o->nsd = in[0]->nsd + 1;
+            o->scale = in[0]->scale * sfl;
+            out[live[g0 + g]] = o;
+            blob[count + g] = (u64)(uintptr_t)o->mem->p;
+            for (int t = 0; t < count; t++) {
+                LimbScalars sc = scalars_for((long double)w[live[g0 + g]][t] * (long double)sfl, ell, false);
+                for (int i = 0; i < ell; i++)
+                    blob[(size_t)count + G + ((size_t)g * count + t) * ell + i] = (sc.v[i] & 0x3fffffffull) | ((sc.v[i] >> 30) << 32);
+            }
+        }
+        Mem d = alloc(blob.size());
+        FHE_CUDA(cudaMemcpyAsync(d->p, blob.data(), blob.size() * sizeof(u64), cudaMemcpyHostToDevice, stream));
+        k_lincomb(T, ell, npoly * ell, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G),
+                  (u64 *const *)(d->p + count), stream);
+    }
+    return out;
+}
 Ct Context::mult_const(const Ct &a, double c) {
     LOCK;
     Ct x = a->nsd == 2 ? mod_reduce(a) : a;

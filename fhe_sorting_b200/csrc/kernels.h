@@ -51,6 +51,10 @@ void k_tensor(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, cons
               u64 *d1, u64 *d2, cudaStream_t st);
 void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, u64 *d0, u64 *d1, u64 *d2,
                      cudaStream_t st);
+// G <= 4 weighted sums of `count` polynomials in one pass: out[g][limb] = sum_t in[t][limb] * w[(g * count + t) * ell + limb % ell]
+// over limbs2 = npoly * ell limbs; weights are residues pre-split as (lo30, hi30); all pointer tables live in HBM
+void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
+               u64 *const *out, cudaStream_t st);
 // Galois automorphism (eval domain, bit-reversed order) on `limbs` limbs
 void k_automorphism(const DeviceTables &T, uint32_t galois, int limbs, const u64 *in, u64 *out, cudaStream_t st);
 

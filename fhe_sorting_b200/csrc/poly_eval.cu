@@ -63,6 +63,8 @@ struct PSState {
     std::vector<Ct> T;  // T[i] = T_{i+1}(u), i < k   (all aligned to T[k-1])
     std::vector<Ct> T2; // T2[i] = T_{k 2^i}(u)
     std::vector<Ct> Tr; // T[i] brought to degree 1 once (the scalar products of every leaf start from these)
+    std::vector<Ct> ready; // weighted sums of the baby steps, precomputed in traversal order by one fused kernel family
+    size_t next = 0;
     const Ct &reduced(int i) {
         if (Tr.empty()) Tr.resize(T.size());
         if (!Tr[i]) Tr[i] = T[i]->nsd == 2 ? C->mod_reduce(T[i]) : T[i];
@@ -74,6 +76,10 @@ static Ct double_ct(Context *C, const Ct &a) { return C->add(a, a); }
 
 // sum_{i=1..deg} w_i T_i + c0 ; returns null if everything vanishes
 static Ct weighted_sum(PSState &S, const Poly &p, int upto) {
+    if (!S.ready.empty()) {
+        if (S.next >= S.ready.size()) throw std::logic_error("chebyshev PS: weighted-sum queue exhausted");
+        return S.ready[S.next++];
+    }
     Ct acc;
     for (int i = 1; i <= upto && i < (int)p.size(); i++) {
         if (p[i] == 0.0) continue;
@@ -103,22 +109,39 @@ static Ct eval_leaf(PSState &S, const Poly &p) {
     if (p[0] != 0.0) r = S.C->add_const(r, p[0]);
     return r;
 }
-// f has degree exactly k(2^m - 1) with power-of-two leading coefficient
-static Ct eval_inner(PSState &S, const Poly &f, int m) {
-    const int k = S.k;
-    if (m == 1) return eval_leaf(S, f);
+// f = (T_{k 2^(m-1)} + c) q + s2 with deg q = deg s2 = k(2^(m-1) - 1), both with power-of-two leading coefficient
+static void ps_split(int k, int m, const Poly &f, Poly &q, Poly &c, Poly &s2) {
     const int k2m2k = k * (1 << (m - 1)) - k;
     Poly Tkm(k2m2k + k + 1, 0.0);
     Tkm.back() = 1.0;
-    Poly q, r, c, s;
+    Poly r, s;
     cheb_divide(f, Tkm, q, r);
     Poly r2 = r;
     if ((int)r2.size() < k2m2k + 1) r2.resize(k2m2k + 1, 0.0);
     r2[k2m2k] -= 1.0;
     cheb_divide(r2, q, c, s);
-    Poly s2 = s;
+    s2 = s;
     s2.resize(k2m2k + 1, 0.0);
     s2[k2m2k] += 1.0;
+}
+// the weight vectors eval_inner will ask weighted_sum for, in the order it asks
+static void ps_collect(int k, int m, const Poly &f, std::vector<Poly> &req) {
+    if (m == 1) {
+        req.push_back(f);
+        return;
+    }
+    Poly q, c, s2;
+    ps_split(k, m, f, q, c, s2);
+    req.push_back(c);
+    ps_collect(k, m - 1, q, req);
+    ps_collect(k, m - 1, s2, req);
+}
+// f has degree exactly k(2^m - 1) with power-of-two leading coefficient
+static Ct eval_inner(PSState &S, const Poly &f, int m) {
+    const int k = S.k;
+    if (m == 1) return eval_leaf(S, f);
+    Poly q, c, s2;
+    ps_split(k, m, f, q, c, s2);
     Ct cu = weighted_sum(S, c, k - 1);
     Ct qu = eval_inner(S, q, m - 1);
     Ct su = eval_inner(S, s2, m - 1);
@@ -208,6 +231,16 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
     const int top = k * ((1 << m) - 1);
     f.resize(top + 1, 0.0);
     f[top] += 1.0;
+    if (k > 2) { // every weighted sum of T_1..T_{k-1} the recursion needs, four outputs per pass over the baby steps
+        std::vector<Poly> req;
+        ps_collect(k, m, f, req);
+        std::vector<Ct> in(k - 1);
+        for (int i = 0; i + 1 < k; i++) in[i] = S.reduced(i);
+        std::vector<std::vector<double>> w(req.size(), std::vector<double>(k - 1, 0.0));
+        for (size_t r = 0; r < req.size(); r++)
+            for (int i = 1; i < k && i < (int)req[r].size(); i++) w[r][i - 1] = req[r][i];
+        S.ready = lincomb(in, w);
+    }
     Ct r = eval_inner(S, f, m);
     return sub(r, T2km1);
 }
