@@ -16,8 +16,54 @@ struct fheb200_pre { std::shared_ptr<Precomp> p; };
 
 static thread_local std::string g_err;
 namespace fheb200 { void set_last_error(const char *m) { g_err = m; } }
+// FHEB200_TRACE=1: per entry point, number of calls, kernels launched and synchronised wall time (printed at exit).
+// Tracing synchronises the device after every call, so it measures GPU time per operation, not pipelined latency.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+namespace {
+struct TraceRow { unsigned long long calls = 0, launches = 0; double ms = 0; };
+std::map<std::string, TraceRow> g_trace;
+std::mutex g_trace_mu;
+bool trace_on() {
+    static const bool on = [] {
+        const char *e = getenv("FHEB200_TRACE");
+        bool v = e && *e && *e != '0';
+        if (v) atexit([] {
+            double tot = 0;
+            for (auto &kv : g_trace) tot += kv.second.ms;
+            fprintf(stderr, "%-36s %9s %10s %11s %7s\n", "fheb200 entry point", "calls", "launches", "ms (sync)", "share");
+            for (auto &kv : g_trace)
+                fprintf(stderr, "%-36s %9llu %10llu %11.2f %7.3f\n", kv.first.c_str(), kv.second.calls, kv.second.launches,
+                        kv.second.ms, kv.second.ms / (tot > 0 ? tot : 1));
+        });
+        return v;
+    }();
+    return on;
+}
+struct OpTrace {
+    const char *name;
+    unsigned long long l0 = 0;
+    std::chrono::steady_clock::time_point t0;
+    bool on;
+    explicit OpTrace(const char *n) : name(n), on(trace_on()) {
+        if (on) l0 = g_launches.load(), t0 = std::chrono::steady_clock::now();
+    }
+    ~OpTrace() {
+        if (!on) return;
+        cudaDeviceSynchronize();
+        double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        std::lock_guard<std::mutex> g(g_trace_mu);
+        TraceRow &r = g_trace[name];
+        r.calls++, r.launches += g_launches.load() - l0, r.ms += ms;
+    }
+};
+} // namespace
 #define GUARD(...)                          \
     try {                                   \
+        OpTrace trace__(__func__);          \
         __VA_ARGS__;                            \
         return 0;                           \
     } catch (const std::exception &e) {     \

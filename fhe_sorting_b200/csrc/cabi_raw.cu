@@ -77,10 +77,10 @@ int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t wo
     GUARD({
         LOCKCTX(ctx);
         need(pt, "pt");
-        if (!pt->p->mem) throw std::runtime_error("pt_export: plaintext has no encoding");
+        Mem ptmem = C.encoding_for(pt->p, pt->p->ell, pt->p->scale);
         size_t w = (size_t)pt->p->ell * n;
         if (words < w) throw std::invalid_argument("pt_export: buffer too small");
-        d2h(C, out, pt->p->mem->p, w * 8);
+        d2h(C, out, ptmem->p, w * 8);
     })
 }
 int fheb200_keys_export(fheb200_ctx *ctx, fheb200_keys *k, int which, uint64_t *out, size_t words) {

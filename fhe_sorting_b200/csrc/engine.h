@@ -37,7 +37,19 @@ struct Ciphertext {
     int nsd = 1;      // noise scale degree (1 or 2; 3 transiently never kept)
     double scale = 0; // exact real scaling factor
     int slots = 0;
+    // Rescaled copy, filled the first time a multiplication needs this (immutable) ciphertext at degree 1: the sort
+    // drivers multiply one baby-step ciphertext by dozens of masks (src/sort_algo.h:339-345), each of which would
+    // otherwise repeat the same rescale.  Never copied along with the object.
+    mutable std::shared_ptr<Ciphertext> reduced_cache;
     u64 *poly(int i, int n) const { return mem->p + (size_t)i * ell * n; }
+    Ciphertext() = default;
+    Ciphertext(const Ciphertext &o)
+        : mem(o.mem), npoly(o.npoly), ell(o.ell), level(o.level), nsd(o.nsd), scale(o.scale), slots(o.slots) {}
+    Ciphertext &operator=(const Ciphertext &o) {
+        mem = o.mem, npoly = o.npoly, ell = o.ell, level = o.level, nsd = o.nsd, scale = o.scale, slots = o.slots;
+        reduced_cache.reset();
+        return *this;
+    }
 };
 typedef std::shared_ptr<Ciphertext> Ct;
 
@@ -135,6 +147,7 @@ class Context : public std::enable_shared_from_this<Context> {
 
     // scheme helpers
     Ct mod_reduce(const Ct &a);
+    Ct reduced(const Ct &a);                       // memoised mod_reduce of a degree-2 ciphertext
     Ct mult_core_const(const Ct &a, double c);     // multiply by round(c * sf[level]); nsd += 1
     // out[r] = sum_t round(w[r][t] * sf[level]) * in[t]  (all inputs at the same level and degree 1); null where all w vanish
     std::vector<Ct> lincomb(const std::vector<Ct> &in, const std::vector<std::vector<double>> &w);

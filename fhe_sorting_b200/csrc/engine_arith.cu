@@ -59,8 +59,8 @@ void Context::adjust_pair_to_one(Ct &a, Ct &b) {
     adjust_pair(a, b);
     if (a->nsd == 2) {
         bool same = a.get() == b.get();
-        a = mod_reduce(a);
-        b = same ? a : mod_reduce(b);
+        a = reduced(a);
+        b = same ? a : reduced(b);
     }
 }
 
@@ -126,7 +126,7 @@ Ct Context::add_pt(const Ct &a, const Pt &p, bool negate_pt) {
 Ct Context::mult_pt(const Ct &a0, const Pt &p) {
     LOCK;
     if (!a0 || !p) throw std::invalid_argument("EvalMult: null operand");
-    Ct a = a0->nsd == 2 ? mod_reduce(a0) : a0;
+    Ct a = a0->nsd == 2 ? reduced(a0) : a0;
     const int n = P->n;
     const double ps = P->sf[a->level];
     Mem enc = encoding_for(p, a->ell, ps);

@@ -229,7 +229,7 @@ Pt Context::make_plaintext(const std::vector<std::complex<double>> &vals, int ns
         p->scale = std::pow(P->sf[level], (double)p->nsd);
     }
     p->ell = P->L - level;
-    p->mem = encode_at(*p, p->ell, p->scale);
+    // encoded lazily (encoding_for): a mask built at level 0 is only ever used at the level of the ciphertext it multiplies
     return p;
 }
 
@@ -237,7 +237,8 @@ Ct Context::encrypt(const Keys &k, const Pt &pt) {
     std::lock_guard<std::recursive_mutex> g(mu);
     FHE_CUDA(cudaSetDevice(device));
     if (!k || !k->pk) throw std::runtime_error("Encrypt: public key required");
-    if (!pt || !pt->mem) throw std::runtime_error("Encrypt: plaintext is not encoded");
+    if (!pt) throw std::runtime_error("Encrypt: null plaintext");
+    Mem ptmem = encoding_for(pt, pt->ell, pt->scale);
     const int n = P->n, L = P->L, ell = pt->ell;
     u64 nc = nonce.fetch_add(1);
     auto c = std::make_shared<Ciphertext>();
@@ -253,7 +254,7 @@ Ct Context::encrypt(const Keys &k, const Pt &pt) {
         k_ntt_fwd(T, dst, dq, ell, stream);
     }
     k_encrypt_finish(T, ell, k->pk->p, k->pk->p + (size_t)L * n, tmp->p, tmp->p + (size_t)ell * n,
-                     tmp->p + (size_t)2 * ell * n, pt->mem->p, c->poly(0, n), c->poly(1, n), stream);
+                     tmp->p + (size_t)2 * ell * n, ptmem->p, c->poly(0, n), c->poly(1, n), stream);
     return c;
 }
 

@@ -117,6 +117,12 @@ Ct Context::mod_reduce(const Ct &a) {
     return r;
 }
 Ct Context::rescale(const Ct &a) { return mod_reduce(a); }
+Ct Context::reduced(const Ct &a) {
+    LOCK;
+    if (!a->reduced_cache) a->reduced_cache = mod_reduce(a);
+    a->reduced_cache->slots = a->slots; // SetSlots may have been called on the handle since
+    return a->reduced_cache;
+}
 Ct Context::level_reduce(const Ct &a, int levels) {
     LOCK;
     if (levels <= 0) return a;
@@ -181,7 +187,7 @@ std::vector<Ct> Context::lincomb(const std::vector<Ct> &in, const std::vector<st
 }
 Ct Context::mult_const(const Ct &a, double c) {
     LOCK;
-    Ct x = a->nsd == 2 ? mod_reduce(a) : a;
+    Ct x = a->nsd == 2 ? reduced(a) : a;
     return mult_core_const(x, c);
 }
 Ct Context::add_const(const Ct &a, double c) {

@@ -453,6 +453,29 @@ __global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass(DeviceTables T, 
     else inv_pass_body<false>(T, src, dst, d, G, scale, sm);
 }
 
+// Compile-time geometry for the production ring (n = 2^17): every shift, stride and loop trip count of the pass bodies
+// becomes an immediate, which removes most of the index arithmetic around the butterflies.
+template <int LOGN, int S, int S0, int LC, int PA>
+__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_fwd_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                  const uint32_t *__restrict__ desc, int first, int final_reduce) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    const uint32_t d = desc[blockIdx.y];
+    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body(T, src, dst, d, G, first, final_reduce, sm);
+    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true>(T, src, dst, d, G, final_reduce, sm);
+    else fwd_pass_body<false>(T, src, dst, d, G, final_reduce, sm);
+}
+template <int LOGN, int S, int S0, int LC, int PA>
+__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                  const uint32_t *__restrict__ desc, int first, int scale) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    const uint32_t d = desc[blockIdx.y];
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm);
+}
+
 static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
     const int logn = T.logn;
     if (logn <= NTT_TILE_LOG) {
@@ -474,6 +497,11 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     passes(T, A, B, tile);
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    if (T.logn == 17) {
+        g_launches++, ntt_fwd_pass_c<17, 8, 0, 4, 1><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
+        g_launches++, ntt_fwd_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
+        return;
+    }
     if (A.S > 0) {
         g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, A, 1, 0);
         src = dst;
@@ -487,6 +515,11 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     passes(T, A, B, tile);
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    if (T.logn == 17) {
+        g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
+        g_launches++, ntt_inv_pass_c<17, 8, 0, 4, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
+        return;
+    }
     g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0);
     if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1);
 }
