@@ -154,6 +154,23 @@ int fheb200_raw_rescale(fheb200_ctx *ctx, int ell, const uint64_t *in, uint64_t 
     })
 }
 
+int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words) {
+    GUARD({
+        need(ct, "ct");
+        need(device_ptr, "device_ptr");
+        *device_ptr = ct->c->mem->p;
+        if (words) *words = (size_t)ct->c->npoly * ct->c->ell * ct->c->mem->ctx->P->n;
+    })
+}
+int fheb200_ct_reduce_partial_sums(fheb200_ctx *ctx, fheb200_ct *ct) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(ct, "ct");
+        ct->c->reduced_cache.reset();
+        for (int p = 0; p < ct->c->npoly; p++) k_reduce_words(C.T, ct->c->ell, ct->c->poly(p, n), C.stream);
+    })
+}
+
 // `reps` rotations of the same ciphertext back to back; device time by CUDA events on the context stream
 int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms) {
     GUARD({

@@ -163,6 +163,16 @@ void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, con
     }
 }
 
+__global__ void __launch_bounds__(EW_THREADS) ew_reduce_words(DeviceTables T, u64 *__restrict__ a) {
+    const int k = blockIdx.x * EW_THREADS + threadIdx.x;
+    if (k >= T.n) return;
+    const size_t idx = (size_t)blockIdx.y * T.n + k;
+    a[idx] = reduce64(a[idx], T.mc[blockIdx.y]);
+}
+void k_reduce_words(const DeviceTables &T, int ell, u64 *a, cudaStream_t st) {
+    g_launches++, ew_reduce_words<<<dim3((T.n + EW_THREADS - 1) / EW_THREADS, ell), EW_THREADS, 0, st>>>(T, a);
+}
+
 void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st) {
     g_launches++, ew_binary<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, (int)op, a, b, out);
 }

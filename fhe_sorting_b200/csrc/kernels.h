@@ -55,6 +55,8 @@ void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a
 // over limbs2 = npoly * ell limbs; weights are residues pre-split as (lo30, hi30); all pointer tables live in HBM
 void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
                u64 *const *out, cudaStream_t st);
+// a[limb][k] <- a[limb][k] mod q_limb for arbitrary 64-bit words (sums of residues from several ranks)
+void k_reduce_words(const DeviceTables &T, int ell, u64 *a, cudaStream_t st);
 // Galois automorphism (eval domain, bit-reversed order) on `limbs` limbs
 void k_automorphism(const DeviceTables &T, uint32_t galois, int limbs, const u64 *in, u64 *out, cudaStream_t st);
 

@@ -341,6 +341,19 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         return wrap(o);
     }
     void Sync() { fheb200_check(fheb200_ctx_sync(ctx)); }
+    // Multi-GPU extension (not an OpenFHE call): sum a partial ciphertext over the ranks that share this job.  `reduce`
+    // sums the device buffer in place across ranks as 64-bit integers (NCCL all-reduce supplied by the launcher).
+    std::function<void(void *device_ptr, size_t words)> allReduceWords;
+    void AllReduceSum(CT &a) {
+        need(a);
+        if (!allReduceWords) return;
+        void *ptr = nullptr;
+        size_t words = 0;
+        fheb200_check(fheb200_ct_device_view(a->h, &ptr, &words));
+        Sync();
+        allReduceWords(ptr, words);
+        fheb200_check(fheb200_ct_reduce_partial_sums(ctx, a->h));
+    }
     static void SetKeySeed(uint64_t s) { seed_state() = s; }
 
   private:

@@ -60,6 +60,14 @@ struct DirectSortShape {
     }
 };
 
+// which of the B batches process `rank` of `world` evaluates (all of them when B is not a multiple of world: replicated)
+inline std::vector<int> DirectSortBatchesOf(int B, int rank, int world) {
+    std::vector<int> mine;
+    for (int b = 0; b < B; b++)
+        if (world <= 1 || B % world != 0 || b % world == rank) mine.push_back(b);
+    return mine;
+}
+
 template <int N> class DirectSort : public SortBase<N> {
     CryptoContext<DCRTPoly> m_cc;
     PublicKey<DCRTPoly> m_PublicKey;
@@ -69,6 +77,14 @@ template <int N> class DirectSort : public SortBase<N> {
     std::set<int> m_keys;
 
     typedef Ciphertext<DCRTPoly> CT;
+    int m_rank = 0, m_world = 1; // multi-GPU: this process evaluates the batches b with b % m_world == m_rank
+
+    bool mine(int b, int B) const {
+        for (int x : DirectSortBatchesOf(B, m_rank, m_world))
+            if (x == b) return true;
+        return false;
+    }
+    bool sharded(int B) const { return m_world > 1 && B % m_world == 0; }
 
     // rotations 0..count-1 of `in`; one hoisted ModUp when every key exists
     std::vector<CT> babySteps(const CT &in, int count, int num_slots) {
@@ -97,6 +113,11 @@ template <int N> class DirectSort : public SortBase<N> {
           max_batch(cc->GetRingDimension() / 2), m_keys(rotIndices.begin(), rotIndices.end()), m_enc(enc) {}
 
     const std::set<int> &getRotationCalls() const { return rot.getRotationCalls(); }
+
+    // Shard the B independent batches of both phases over `world` processes (one per GPU, keys replicated); partial rank
+    // and output ciphertexts are summed with CryptoContextImpl::AllReduceSum.  Lengths with fewer batches than processes
+    // (N <= 256 on ring 2^17: a single comparison ciphertext) run replicated.
+    void setShard(int rank, int world) { m_rank = rank, m_world = world; }
 
     // multiplicative depth per array length (reference table sort_algo.h:94-198), scaling modulus 40 bits, batch N, and
     // the rotation indices the schedule below uses on a ring of dimension `ringDim`
@@ -187,6 +208,7 @@ template <int N> class DirectSort : public SortBase<N> {
         std::vector<CT> baby = babySteps(input_array, sh.np_rank, sh.S);
         CT rank;
         for (int b = 0; b < sh.B; b++) {
+            if (!mine(b, sh.B)) continue;
             CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b);
             CT dup = input_array->Clone();
             dup->SetSlots(sh.S);
@@ -194,6 +216,7 @@ template <int N> class DirectSort : public SortBase<N> {
             if (rank) m_cc->EvalAddInPlace(rank, c);
             else rank = c;
         }
+        if (sharded(sh.B)) m_cc->AllReduceSum(rank);
         foldCopies(rank, sh.S, sh.P);
         rank->SetSlots(N);
         return m_cc->EvalSub(rank, 0.5); // the self comparison contributed 1/2
@@ -230,6 +253,7 @@ template <int N> class DirectSort : public SortBase<N> {
         static const std::vector<double> &coeffs = selectDoubledSincCoefficients<N>();
         CT output;
         for (int b = 0; b < sh.B; b++) {
+            if (!mine(b, sh.B)) continue;
             auto chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(sh.S, b * sh.P), 1, index_minus_rank->GetLevel(),
                                                      nullptr, sh.S);
             CT r = m_cc->EvalSub(index_minus_rank, chk);
@@ -241,6 +265,7 @@ template <int N> class DirectSort : public SortBase<N> {
             if (output) m_cc->EvalAddInPlace(output, placed);
             else output = placed;
         }
+        if (sharded(sh.B)) m_cc->AllReduceSum(output);
         foldCopies(output, sh.S, sh.P);
         output->SetSlots(N);
         return output;

@@ -26,6 +26,7 @@ struct SessionBase {
     virtual Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
     virtual Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &rank, const Ciphertext<DCRTPoly> &in) = 0;
     virtual Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) = 0;
+    virtual void shard(int rank, int world) = 0;
 };
 template <int N> struct Session : SessionBase {
     std::unique_ptr<DirectSort<N>> sorter;
@@ -40,6 +41,7 @@ template <int N> struct Session : SessionBase {
         return sorter->rotationIndexCheckN(rk, in);
     }
     Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) override { return composer->rotate(in, r); }
+    void shard(int rank, int world) override { sorter->setShard(rank, world); }
 };
 
 template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
@@ -124,6 +126,20 @@ int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_
     })
 }
 
+int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_allreduce_fn fn, void *user) {
+    GUARD({
+        if (!s) throw std::invalid_argument("null argument: session");
+        if (world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("set_shard: bad rank / world");
+        if (world > 1 && !fn) throw std::invalid_argument("set_shard: an all-reduce callback is required when world > 1");
+        s->s->shard(rank, world);
+        if (world > 1)
+            s->s->cc->allReduceWords = [fn, user](void *p, size_t w) {
+                if (fn(user, p, w) != 0) throw std::runtime_error("all-reduce callback failed");
+            };
+        else s->s->cc->allReduceWords = nullptr;
+    })
+}
+
 // which: 0 = full sort, 1 = constructRank only (output = ranks), 2 = rotationIndexCheckN on plaintext ranks given in aux
 int fhesort_run(fhesort_session *s, int which, const double *input, const double *aux, int sign_n, int dg, int df,
                 double *output, double *elapsed_ms, int *out_level) {
@@ -179,6 +195,15 @@ int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, in
         }
         if (count) *count = (int)r.size();
         for (int i = 0; i < (int)r.size() && i < capacity; i++) out[i] = r[i];
+    })
+}
+int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out, int capacity, int *count, int *sharded) {
+    GUARD({
+        const DirectSortShape sh(N, (1 << log_ring_dim) / 2);
+        std::vector<int> b = DirectSortBatchesOf(sh.B, rank, world);
+        if (count) *count = (int)b.size();
+        if (sharded) *sharded = world > 1 && sh.B % world == 0;
+        for (int i = 0; i < (int)b.size() && i < capacity; i++) out[i] = b[i];
     })
 }
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity, int *count) {

@@ -59,6 +59,32 @@ class DirectSortSession:
         except Exception:
             pass
 
+    def set_shard(self, rank, world):
+        """Shard the sort's batches over `world` ranks of an initialised torch.distributed NCCL group (one GPU each)."""
+        if world <= 1:
+            _ck(_lib.fhesort_session_set_shard(self.h, 0, 1, None, None))
+            self._cb = None
+            return
+        import torch
+        import torch.distributed as dist
+
+        class _View:  # a borrowed device buffer seen through __cuda_array_interface__
+            def __init__(self, ptr, words):
+                self.__cuda_array_interface__ = {"shape": (words,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+
+        def allreduce(user, ptr, words):
+            try:
+                t = torch.as_tensor(_View(ptr, words), device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                torch.cuda.current_stream().synchronize()
+                return 0
+            except Exception as e:  # noqa: BLE001 - reported through the C ABI status
+                print("all-reduce failed:", e)
+                return 1
+
+        self._cb = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t)(allreduce)
+        _ck(_lib.fhesort_session_set_shard(self.h, rank, world, self._cb, None))
+
     def _run(self, stage, values, aux=None, sign=(0, 0, 0)):
         v = np.ascontiguousarray(values, dtype=np.float64)
         assert v.shape == (self.n,)
@@ -109,3 +135,24 @@ def doubled_sinc_coefficients(n):
     cnt = C.c_int()
     _ck(L.fhesort_doubled_sinc_coefficients(n, _dp(buf), len(buf), C.byref(cnt)))
     return buf[:cnt.value].copy()
+
+
+def shard_batches(n, rank, world, log_ring_dim=17):
+    """(batches evaluated by `rank`, whether the sort is sharded at all) — host-only mirror of DirectSort::setShard."""
+    L = load_sort()
+    out = (C.c_int * 4096)()
+    cnt, sh = C.c_int(), C.c_int()
+    _ck(L.fhesort_shard_batches(n, log_ring_dim, rank, world, out, 4096, C.byref(cnt), C.byref(sh)))
+    return list(out[:cnt.value]), bool(sh.value)
+
+
+def combine_partial_residues(partial, moduli, dist=None):
+    """Sum per-rank partial residue arrays [limbs][n] (uint64 < q) over a torch.distributed group and bring the sums
+    back to [0, q): the host-side statement of AllReduceSum + fheb200_ct_reduce_partial_sums (used by the gloo tests)."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(partial).view(np.int64).copy())
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    s = t.numpy().view(np.uint64)
+    q = np.asarray(moduli, dtype=np.uint64).reshape(-1, 1)
+    return s % q

@@ -122,6 +122,12 @@ int fheb200_eval_poly(fheb200_ctx *ctx, fheb200_ct *x, const double *coeffs, siz
 /* lbcrypto::EvalChebyshevCoefficients(f, a, b, degree) (utils/generate_cheb_coeffs.cpp:17); host only */
 int fheb200_chebyshev_coefficients(double (*f)(double, void *), void *user, double a, double b, int degree, double *out);
 
+/* ---- multi-GPU combine of partial ciphertexts: the device buffer [2][limbs][n] of a ciphertext, to be
+ * summed element-wise across ranks as 64-bit integers (NCCL all-reduce; <= 16 summands of < 2^60 cannot wrap), then
+ * brought back to [0, q_limb) by fheb200_ct_reduce_partial_sums.  The caller orders the streams (fheb200_ctx_sync). */
+int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words);
+int fheb200_ct_reduce_partial_sums(fheb200_ctx *ctx, fheb200_ct *ct);
+
 /* ---- raw RNS access: parity tests against the oracle and the primitive micro-benchmarks ----
  * Polynomials are uint64 [limb][ring_dim] host arrays, limb i reduced mod modulus i (evaluation domain). */
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words_each);

@@ -6,6 +6,7 @@
  */
 #ifndef FHE_SORT_H
 #define FHE_SORT_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -24,10 +25,16 @@ int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_
  * reference tests' CompositeSign configuration for N.  elapsed_ms covers encrypt + stage + decrypt (host clock). */
 int fhesort_run(fhesort_session *s, int stage, const double *input, const double *aux, int sign_n, int dg, int df,
                 double *output, double *elapsed_ms, int *out_level);
+/* Multi-GPU: shard the independent batches of both phases of the sort over `world` processes (one per GPU, same seed so
+ * that keys are replicated).  `fn` must sum `words` 64-bit integers at device_ptr in place over all processes (NCCL
+ * all-reduce, SUM, int64) and return 0 after the result is visible to other streams. */
+typedef int (*fhesort_allreduce_fn)(void *user, void *device_ptr, size_t words);
+int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_allreduce_fn fn, void *user);
 /* RotationComposer<N>::rotate (src/rotation.h:215-233) */
 int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output);
 /* host-only (no GPU needed) */
 int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count);
+int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out, int capacity, int *count, int *sharded);
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity,
                       int *count);
 int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count);

@@ -1,0 +1,61 @@
+"""world_size-2 gloo tests (CPU) of the multi-GPU plan: batch sharding of DirectSort and the integer all-reduce +
+mod-q fix-up that combines partial rank / output ciphertexts."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from fhe_sorting_b200 import sort as S
+
+
+def test_shard_partition_covers_every_batch_once():
+    for n, world in [(1024, 2), (1024, 4), (1024, 8), (1024, 16), (512, 4)]:
+        B = n // min(n, 65536 // n)
+        seen = []
+        for r in range(world):
+            b, sharded = S.shard_batches(n, r, world)
+            assert sharded and len(b) == B // world
+            seen += b
+        assert sorted(seen) == list(range(B))
+    for n, world in [(256, 8), (16, 2), (1024, 3)]:     # fewer batches than ranks (or not divisible): replicated
+        B = n // min(n, 65536 // n)
+        b, sharded = S.shard_batches(n, 1, world)
+        assert not sharded and b == list(range(B))
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    moduli = [1152921504606584833, 1099512938497, 1099510054913]
+    rng = np.random.default_rng(7)                       # same stream on both ranks: rank r takes slice r
+    parts = np.stack([np.stack([rng.integers(0, m, 64, dtype=np.uint64) for m in moduli]) for _ in range(world)])
+    got = S.combine_partial_residues(parts[rank], moduli, dist)
+    want = np.zeros_like(parts[0])
+    for i, m in enumerate(moduli):
+        acc = np.zeros(64, dtype=object)
+        for r in range(world):
+            acc = acc + parts[r][i].astype(object)
+        want[i] = np.array([int(x) % m for x in acc], dtype=np.uint64)
+    ok = bool(np.array_equal(got, want))
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, ok))
+
+
+def test_partial_ciphertext_combine_world2_gloo():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]
