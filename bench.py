@@ -162,6 +162,33 @@ def run_reference(args, rank, world):
     }))
 
 
+def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)):
+    """DirectSort<N>::sort at the reference's per-N parameters (ring 2^17, src/sort_algo.h:87-201), uniform-gap input
+    (tests/utils.h:28-51), CompositeSign(3, dg, 2) as in tests/DirectSortTest.cpp:103-111.  Timed on the host clock from
+    plain input values to decrypted sorted values (encrypt and decrypt included), max over ranks.  With N GPUs the
+    B = N / P independent batches of both phases are sharded over the ranks (N = 1024: 16 batches) and partial
+    ciphertexts combined by NCCL all-reduce; lengths with a single batch run replicated."""
+    import torch
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input, shard_batches
+    out = {}
+    for n in sizes:
+        s = DirectSortSession(n, 17, seed=SEED + n, device=local_rank)
+        s.set_shard(rank, world)
+        x = uniform_gap_input(n)
+        s.sort(x)  # warm-up: Chebyshev tables, memory pool, plans for every level
+        barrier()
+        t0 = time.perf_counter()
+        res, _, level = s.sort(x)
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        out[str(n)] = {"seconds": float(dt.item()), "max_abs_err": float(np.abs(res - np.sort(x)).max()),
+                       "final_level": level, "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys,
+                       "sharded_over_ranks": shard_batches(n, rank, world)[1]}
+        s.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import fhe_sorting_b200 as F
@@ -230,6 +257,9 @@ def run_ours(args, rank, world, local_rank):
     e2e_value = world * ROT_PER_STEP * args.steps / float(dt.item())
     limb_bytes = 2 * ell * n * 8
 
+    # ---- the other half of the metric: encrypted DirectSort latency, host values in -> sorted host values out
+    sort_latency = sort_latencies(rank, world, local_rank, dist, barrier)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -270,6 +300,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": limb_bytes, "d2h_bytes_per_step": limb_bytes},
         "roofline": roofline,
+        "sort_latency": sort_latency,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "3 EvalRotate of the same ciphertext at the full parameter set (41 limbs)",
                          "bit_exact_vs_gpu": parity},

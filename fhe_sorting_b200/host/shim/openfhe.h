@@ -6,7 +6,15 @@
 // in this file.  Semantics mirrored from OpenFHE: FLEXIBLEAUTOEXT level bookkeeping (done inside the engine), in-place
 // operations mutate the shared ciphertext object, SetSlots is metadata on a shared handle (src/sort_algo.h:429,614).
 #pragma once
+#include <algorithm>
+#include <cassert>
+#include <chrono>
 #include <cmath>
+#include <fstream>
+#include <iomanip>
+#include <map>
+#include <numeric>
+#include <set>
 #include <cstdint>
 #include <functional>
 #include <iostream>
@@ -17,7 +25,7 @@
 #include <string>
 #include <vector>
 
-#include "../../include/fhe_b200.h"
+#include "../../../include/fhe_b200.h"
 
 namespace lbcrypto {
 

@@ -6,10 +6,14 @@
 #include <memory>
 #include <string>
 
+// Built twice: (1) libfhesort.so from this repository's drivers (host/sort_algo.h ...); (2) with -DREFERENCE_DRIVERS and
+// the reference's src/ first on the include path, oracle/_ref/libref_sort.so — the reference's own unmodified
+// sort_algo.h / rotation.h / sign.cpp / comparison.cpp / encryption.cpp running on the B200 engine through the shim
+// (built only where /root/reference exists; see oracle/Makefile).
+#include <omp.h>
+
 #include "../../include/fhe_sort.h"
-#include "comparison.h"
-#include "rotation.h"
-#include "sort_algo.h"
+#include "sort_algo.h" // the reference's rotation.h has no include guard: reach it through sort_algo.h only
 
 namespace {
 thread_local std::string g_err;
@@ -41,7 +45,13 @@ template <int N> struct Session : SessionBase {
         return sorter->rotationIndexCheckN(rk, in);
     }
     Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) override { return composer->rotate(in, r); }
+#ifdef REFERENCE_DRIVERS
+    void shard(int, int world) override {
+        if (world > 1) throw std::runtime_error("the reference's DirectSort has no multi-GPU sharding");
+    }
+#else
     void shard(int rank, int world) override { sorter->setShard(rank, world); }
+#endif
 };
 
 template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
@@ -53,7 +63,12 @@ template <int N> SessionBase *make_session(int log_ring_dim, int depth_override,
     if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
     if (seed) CryptoContextImpl::SetKeySeed(seed);
+#ifdef REFERENCE_DRIVERS
+    setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
+    s->cc = GenCryptoContext(p);
+#else
     s->cc = GenCryptoContext(p, device);
+#endif
     s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE);
     s->keys = s->cc->KeyGen();
     s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
@@ -177,6 +192,7 @@ int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, 
     })
 }
 
+#ifndef REFERENCE_DRIVERS
 // host-only helpers (no GPU): the rotation-key list and Chebyshev table sizes the drivers would use
 int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count) {
     GUARD({
@@ -206,6 +222,7 @@ int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out
         for (int i = 0; i < (int)b.size() && i < capacity; i++) out[i] = b[i];
     })
 }
+#endif
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity, int *count) {
     GUARD({
         Decomposer<1024> d(std::vector<int>(key_indices, key_indices + num_keys));
@@ -214,6 +231,7 @@ int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wr
         for (int i = 0; i < (int)st.size() && i < capacity; i++) steps[i] = st[i].value * st[i].stepSize;
     })
 }
+#ifndef REFERENCE_DRIVERS
 int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count) {
     GUARD({
         const std::vector<double> *c = nullptr;
@@ -233,5 +251,7 @@ int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *cou
         for (int i = 0; i < (int)c->size() && i < capacity; i++) out[i] = (*c)[i];
     })
 }
+
+#endif
 
 } // extern "C"

@@ -8,22 +8,30 @@ from .lib import FheError
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SORT_LIB_PATH = os.path.join(_HERE, "libfhesort.so")
+# the reference's own unmodified drivers compiled against the shim (oracle/Makefile `ref`; exists only where it was built)
+REFERENCE_DRIVERS_PATH = os.path.join(os.path.dirname(_HERE), "oracle", "_ref", "libref_sort.so")
+_libs = {}
 _lib = None
 
 
-def load_sort():
+def load_sort(drivers="ours"):
     global _lib
-    if _lib is None:
-        if not os.path.exists(SORT_LIB_PATH):
-            raise FheError("libfhesort.so is missing: build it with `make -C fhe_sorting_b200`")
-        _lib = C.CDLL(SORT_LIB_PATH)
-        _lib.fhesort_last_error.restype = C.c_char_p
-    return _lib
+    if drivers not in _libs:
+        path = SORT_LIB_PATH if drivers == "ours" else REFERENCE_DRIVERS_PATH
+        if not os.path.exists(path):
+            raise FheError("%s is missing: build it with `make -C fhe_sorting_b200`%s"
+                           % (path, "" if drivers == "ours" else " and `make -C oracle ref` (needs /root/reference)"))
+        L = C.CDLL(path)
+        L.fhesort_last_error.restype = C.c_char_p
+        _libs[drivers] = L
+    if drivers == "ours":
+        _lib = _libs[drivers]
+    return _libs[drivers]
 
 
-def _ck(rc):
+def _ck(rc, L=None):
     if rc != 0:
-        raise FheError(load_sort().fhesort_last_error().decode())
+        raise FheError((L or load_sort()).fhesort_last_error().decode())
 
 
 def _dp(a):
@@ -39,18 +47,19 @@ def uniform_gap_input(n, seed=None):
 class DirectSortSession:
     """What tests/DirectSortTest.cpp's fixture sets up: context, keys in HBM, DirectSort<N>."""
 
-    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0):
-        L = load_sort()
+    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0, drivers="ours"):
+        """drivers="reference" runs the reference's own sort_algo.h / sign.cpp ... (oracle/_ref) on the same engine."""
+        L = self.L = load_sort(drivers)
         h = C.c_void_p()
-        _ck(L.fhesort_session_create(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)))
+        _ck(L.fhesort_session_create(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
         self.h, self.n = h, n
         d, k, ms = C.c_int(), C.c_int(), C.c_double()
-        _ck(L.fhesort_session_info(h, C.byref(d), C.byref(k), C.byref(ms)))
+        _ck(L.fhesort_session_info(h, C.byref(d), C.byref(k), C.byref(ms)), L)
         self.mult_depth, self.num_rotation_keys, self.setup_ms = d.value, k.value, ms.value
 
     def close(self):
         if self.h:
-            load_sort().fhesort_session_free(self.h)
+            self.L.fhesort_session_free(self.h)
             self.h = None
 
     def __del__(self):
@@ -62,7 +71,7 @@ class DirectSortSession:
     def set_shard(self, rank, world):
         """Shard the sort's batches over `world` ranks of an initialised torch.distributed NCCL group (one GPU each)."""
         if world <= 1:
-            _ck(_lib.fhesort_session_set_shard(self.h, 0, 1, None, None))
+            _ck(self.L.fhesort_session_set_shard(self.h, 0, 1, None, None), self.L)
             self._cb = None
             return
         import torch
@@ -83,7 +92,7 @@ class DirectSortSession:
                 return 1
 
         self._cb = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t)(allreduce)
-        _ck(_lib.fhesort_session_set_shard(self.h, rank, world, self._cb, None))
+        _ck(self.L.fhesort_session_set_shard(self.h, rank, world, self._cb, None), self.L)
 
     def _run(self, stage, values, aux=None, sign=(0, 0, 0)):
         v = np.ascontiguousarray(values, dtype=np.float64)
@@ -91,8 +100,8 @@ class DirectSortSession:
         out = np.zeros(self.n)
         a = np.ascontiguousarray(aux, dtype=np.float64) if aux is not None else None
         ms, lv = C.c_double(), C.c_int()
-        _ck(_lib.fhesort_run(self.h, stage, _dp(v), _dp(a) if a is not None else None, sign[0], sign[1], sign[2], _dp(out),
-                             C.byref(ms), C.byref(lv)))
+        _ck(self.L.fhesort_run(self.h, stage, _dp(v), _dp(a) if a is not None else None, sign[0], sign[1], sign[2], _dp(out),
+                               C.byref(ms), C.byref(lv)), self.L)
         return out, ms.value, lv.value
 
     def sort(self, values, sign=(0, 0, 0)):
@@ -108,7 +117,7 @@ class DirectSortSession:
     def composed_rotate(self, values, rotation):
         v = np.ascontiguousarray(values, dtype=np.float64)
         out = np.zeros(len(v))
-        _ck(_lib.fhesort_composed_rotate(self.h, _dp(v), len(v), rotation, _dp(out)))
+        _ck(self.L.fhesort_composed_rotate(self.h, _dp(v), len(v), rotation, _dp(out)), self.L)
         return out
 
 

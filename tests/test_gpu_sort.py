@@ -58,3 +58,27 @@ def test_direct_sort_n16_reference_parameters():
     s.close()
     assert np.abs(out - np.sort(x)).max() < 0.01
     assert level == 25
+
+
+def test_reference_drivers_unmodified_on_the_engine():
+    """The reference's own src/sort_algo.h, rotation.h, sign.cpp, comparison.cpp, encryption.cpp, compiled unmodified
+    against the lbcrypto shim (oracle/_ref/libref_sort.so, built where /root/reference exists), sort on the B200 engine
+    and agree with this repository's restated drivers."""
+    import os
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input, REFERENCE_DRIVERS_PATH
+    if not os.path.exists(REFERENCE_DRIVERS_PATH):
+        pytest.skip("oracle/_ref/libref_sort.so not built (no reference checkout on the build machine)")
+    for n, logn in ((16, 13), (64, 13), (16, 17)):
+        x = uniform_gap_input(n, seed=99)
+        ref = DirectSortSession(n, logn, seed=5, drivers="reference")
+        out_ref, _, level_ref = ref.sort(x)
+        ranks_ref, _, _ = ref.rank(x)
+        ref.close()
+        ours = DirectSortSession(n, logn, seed=5)
+        out, _, level = ours.sort(x)
+        ranks, _, _ = ours.rank(x)
+        ours.close()
+        assert np.abs(out_ref - np.sort(x)).max() < 0.01 and level_ref == ours.mult_depth
+        assert level == level_ref
+        assert np.abs(out - out_ref).max() < 1e-3
+        assert np.abs(ranks - ranks_ref).max() < 1e-3

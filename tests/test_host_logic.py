@@ -55,3 +55,18 @@ def test_doubled_sinc_table_is_a_one_hot_at_rank_offsets():
     y = np.polynomial.chebyshev.chebval(x, np.concatenate([[c[0] / 2], c[1:]]))
     want = ((k == 0) | (k == -n)).astype(float)
     assert np.abs(y - want).max() < 2e-3
+
+
+def test_tables_equal_the_reference_generator_output():
+    """oracle/_ref/gen/*.h are written by the reference's own utils/generate_cheb_*_coeffs.cpp (compiled unmodified
+    against the shim); the tables built at run time must be identical, value for value."""
+    import re
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "gen",
+                        "generated_doubled_sinc_coeffs.h")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref not built")
+    txt = open(path).read()
+    for n in (4, 16, 64, 256):
+        m = re.search(r"generatedDoubledSincCoefficients_%d = \{(.*?)\};" % n, txt, re.S)
+        ref = np.array([float(v) for v in m.group(1).replace("\n", " ").split(",")])
+        assert np.array_equal(ref, S.doubled_sinc_coefficients(n))
