@@ -15,13 +15,13 @@ cat $OUT/bench.json
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err
 cat $OUT/bench_ref.json | cut -c1-200
 if [ "$2" != "noncu" ]; then
-timeout 300 python bench.py --steps 2 --warmup 1 > $OUT/plain.log 2> $OUT/plain.err && {
+timeout 300 python bench.py --skip-sort --steps 2 --warmup 1 > $OUT/plain.log 2> $OUT/plain.err && {
   SKIP=$(grep -o 'timed region: [0-9]*' $OUT/plain.err | grep -o '[0-9]*$')
   echo "ncu skip $SKIP"
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s $SKIP -c 400 --csv \
-      --log-file $OUT/launches.csv python bench.py --steps 2 --warmup 1 > $OUT/ncu_launches.log 2>&1
+      --log-file $OUT/launches.csv python bench.py --skip-sort --steps 2 --warmup 1 > $OUT/ncu_launches.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -s $SKIP -c ${NCU_FULL_COUNT:-14} \
-      -o $OUT/prof python bench.py --steps 2 --warmup 1 > $OUT/ncu_full.log 2>&1
+      -o $OUT/prof python bench.py --skip-sort --steps 2 --warmup 1 > $OUT/ncu_full.log 2>&1
   ls -la $OUT
 }
 fi

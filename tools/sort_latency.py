@@ -16,12 +16,15 @@ for n in [int(a) for a in sys.argv[1:]] or [16]:
     setup = time.time() - t0
     x = uniform_gap_input(n)
     res = []
-    for rep in range(2):
+    wall = []
+    for rep in range(4):
         l0 = F.launch_count()
+        t1 = time.perf_counter()
         out, ms, level = s.sort(x)
+        wall.append(round(1e3 * (time.perf_counter() - t1), 1))
         res.append(ms)
         launches = F.launch_count() - l0
     err = float(np.abs(out - np.sort(x)).max())
-    print(json.dumps({"N": n, "sort_ms": res, "max_err": err, "level": level, "depth": s.mult_depth,
+    print(json.dumps({"N": n, "sort_ms": res, "wall_ms": wall, "max_err": err, "level": level, "depth": s.mult_depth,
                       "rot_keys": s.num_rotation_keys, "setup_s": round(setup, 2), "kernel_launches": launches}), flush=True)
     s.close()
