@@ -161,22 +161,23 @@ int fheb200_eval_rotate_keygen(fheb200_ctx *ctx, fheb200_keys *k, const int *idx
 int fheb200_make_packed_plaintext(fheb200_ctx *ctx, const double *v, size_t count, int nsd, int level, int slots, fheb200_pt **out) {
     GUARD({
         need(ctx, "ctx"); need(out, "out");
-        std::vector<std::complex<double>> z(count);
-        for (size_t i = 0; i < count; i++) z[i] = std::complex<double>(v[i], 0.0);
-        *out = new fheb200_pt{ctx->c->make_plaintext(z, nsd, level, slots)};
+        *out = new fheb200_pt{ctx->c->make_plaintext_real(v, count, nsd, level, slots)};
     })
 }
 int fheb200_pt_release(fheb200_pt *pt) { GUARD({ delete pt; }) }
 int fheb200_pt_values(fheb200_pt *pt, double *out, size_t cap, size_t *count) {
     GUARD({
         need(pt, "pt");
-        size_t nv = std::min(pt->p->length, pt->p->vals.size());
+        const Plaintext &P = *pt->p;
+        size_t nv = std::min(P.length, P.real_only ? P.re.size() : P.vals.size());
         if (count) *count = nv;
-        for (size_t i = 0; i < nv && i < cap; i++) out[i] = pt->p->vals[i].real();
+        for (size_t i = 0; i < nv && i < cap; i++) out[i] = P.real_only ? P.re[i] : P.vals[i].real();
     })
 }
 int fheb200_pt_set_length(fheb200_pt *pt, size_t len) {
-    GUARD({ need(pt, "pt"); pt->p->length = len; if (pt->p->vals.size() < len) pt->p->vals.resize(len); })
+    GUARD({ need(pt, "pt"); pt->p->length = len;
+            if (pt->p->real_only) { if (pt->p->re.size() < len) pt->p->re.resize(len); }
+            else if (pt->p->vals.size() < len) pt->p->vals.resize(len); })
 }
 int fheb200_pt_log_precision(fheb200_pt *pt, double *bits) { GUARD({ need(pt, "pt"); *bits = pt->p->log_precision; }) }
 int fheb200_encrypt(fheb200_ctx *ctx, fheb200_keys *k, fheb200_pt *pt, fheb200_ct **out) {

@@ -102,19 +102,26 @@ __global__ void __launch_bounds__(EW_THREADS) ew_automorphism(DeviceTables T, ui
     uint32_t src = __brev(idx) >> sh;
     out[(size_t)limb * T.n + p] = in[(size_t)limb * T.n + src];
 }
-__global__ void __launch_bounds__(EW_THREADS) ew_rescale_lift(DeviceTables T, int ell, const u64 *last, u64 *tmp) {
-    EW_INDEX
+// blockIdx.y = poly * (ell - 1) + limb; last: the dropped limb of poly p in coefficient form at last + p * last_stride
+__global__ void __launch_bounds__(EW_THREADS) ew_rescale_lift(DeviceTables T, int ell, const u64 *last, size_t last_stride, u64 *tmp) {
+    const int poly = blockIdx.y / (ell - 1), limb = blockIdx.y - poly * (ell - 1);
+    const int j = (blockIdx.x * EW_THREADS + threadIdx.x) * 2;
+    if (j >= T.n) return;
     const ModConst m = T.mc[limb];
     const u64 ql = T.mc[ell - 1].q, half = ql >> 1;
-    v2 V = ld2(last, j), R;
+    v2 V = ld2(last + poly * last_stride, j), R;
     R.x = switch_modulus(V.x, ql, half, m), R.y = switch_modulus(V.y, ql, half, m);
-    st2(tmp, x, R);
+    st2(tmp, (size_t)blockIdx.y * T.n + j, R);
 }
-__global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, const u64 *in, const u64 *tmp, LimbScalars s,
-                                                                u64 *o) {
-    EW_INDEX
+// blockIdx.y = poly * ell_out + limb; in has ell_out + 1 limbs per poly, tmp and o have ell_out
+__global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, int ell_out, const u64 *in, const u64 *tmp,
+                                                                LimbScalars s, u64 *o) {
+    const int poly = blockIdx.y / ell_out, limb = blockIdx.y - poly * ell_out;
+    const int j = (blockIdx.x * EW_THREADS + threadIdx.x) * 2;
+    if (j >= T.n) return;
+    const size_t x = (size_t)blockIdx.y * T.n + j;
     const u64 q = T.mc[limb].q, w = s.v[limb], ws = s.s[limb];
-    v2 A = ld2(in, x), B = ld2(tmp, x);
+    v2 A = ld2(in, x + (size_t)poly * T.n), B = ld2(tmp, x);
     A.x = shoup_mul(sub_mod(A.x, B.x, q), w, ws, q), A.y = shoup_mul(sub_mod(A.y, B.y, q), w, ws, q);
     st2(o, x, A);
 }
@@ -200,12 +207,12 @@ void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a
 void k_automorphism(const DeviceTables &T, uint32_t g, int limbs, const u64 *in, u64 *out, cudaStream_t st) {
     g_launches++, ew_automorphism<<<dim3((T.n + EW_THREADS - 1) / EW_THREADS, limbs), EW_THREADS, 0, st>>>(T, g, in, out);
 }
-void k_rescale_lift(const DeviceTables &T, int ell, const u64 *last, u64 *tmp, cudaStream_t st) {
-    g_launches++, ew_rescale_lift<<<ew_grid(T, ell - 1), EW_THREADS, 0, st>>>(T, ell, last, tmp);
+void k_rescale_lift(const DeviceTables &T, int ell, int npoly, const u64 *last, size_t last_stride, u64 *tmp, cudaStream_t st) {
+    g_launches++, ew_rescale_lift<<<ew_grid(T, npoly * (ell - 1)), EW_THREADS, 0, st>>>(T, ell, last, last_stride, tmp);
 }
-void k_rescale_finish(const DeviceTables &T, int ell_out, const u64 *in, const u64 *tmp, const LimbScalars &s, u64 *out,
+void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *in, const u64 *tmp, const LimbScalars &s, u64 *out,
                       cudaStream_t st) {
-    g_launches++, ew_rescale_finish<<<ew_grid(T, ell_out), EW_THREADS, 0, st>>>(T, in, tmp, s, out);
+    g_launches++, ew_rescale_finish<<<ew_grid(T, npoly * ell_out), EW_THREADS, 0, st>>>(T, ell_out, in, tmp, s, out);
 }
 
 } // namespace fheb200

@@ -55,6 +55,8 @@ typedef std::shared_ptr<Ciphertext> Ct;
 
 struct Plaintext {
     std::vector<std::complex<double>> vals; // slot values (kept so the plaintext can be re-encoded at any level)
+    std::vector<double> re;                 // ... or just their real parts (MakeCKKSPackedPlaintext of a real vector)
+    bool real_only = false;
     int slots = 0;
     int level = 0, nsd = 1;
     double scale = 0;
@@ -102,6 +104,7 @@ class Context : public std::enable_shared_from_this<Context> {
 
     // ---- encode / encrypt / decrypt
     Pt make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots);
+    Pt make_plaintext_real(const double *vals, size_t count, int nsd, int level, int slots);
     Mem encode_at(const Plaintext &pt, int ell, double scale); // (re-)encode at a given limb count and scale
     Mem encoding_for(const Pt &pt, int ell, double scale);     // cached variant
     Ct encrypt(const Keys &k, const Pt &pt);
@@ -156,6 +159,13 @@ class Context : public std::enable_shared_from_this<Context> {
     LimbScalars scalars_for(long double value, int ell, bool shoup) const;
 
   private:
+    // pinned staging ring for host -> device uploads of slot values: the host never waits for the stream unless it is a
+    // whole ring ahead of it (a pageable cudaMemcpyAsync would stall the launching thread at every plaintext)
+    struct Stage { void *host = nullptr; cudaEvent_t done = nullptr; };
+    std::vector<Stage> stage_;
+    size_t stage_bytes_ = 0, stage_next_ = 0;
+    void upload(void *dst, const void *src, size_t bytes);
+    Pt new_plaintext(size_t count, int nsd, int level, int slots);
     std::map<int, std::pair<double2 *, int *>> fft_tabs_; // per slot count: (ksi, rot) tables of the special FFT in HBM
     std::pair<double2 *, int *> fft_device_tables(int slots);
     std::map<int, DevicePlan> plans_;

@@ -96,6 +96,10 @@ Context::~Context() {
     if (evk_mult) cudaFree(evk_mult);
     for (auto &kv : evk_rot) cudaFree(kv.second);
     for (void *p : owned_) cudaFree(p);
+    for (auto &s : stage_) {
+        if (s.host) cudaFreeHost(s.host);
+        if (s.done) cudaEventDestroy(s.done);
+    }
     if (stream && own_stream) cudaStreamDestroy(stream);
 }
 

@@ -194,31 +194,57 @@ std::pair<double2 *, int *> Context::fft_device_tables(int slots) {
 
 // slots values -> special inverse FFT -> * scale, round -> residues on `ell` limbs -> NTT; everything after the upload of
 // the slot values runs on the device (encode.cu)
+void Context::upload(void *dst, const void *src, size_t bytes) {
+    if (stage_.empty()) {
+        stage_bytes_ = sizeof(double2) * (size_t)(P->n / 2);
+        stage_.resize(8);
+        for (auto &s : stage_) {
+            FHE_CUDA(cudaHostAlloc(&s.host, stage_bytes_, cudaHostAllocDefault));
+            FHE_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        }
+    }
+    while (bytes) {
+        Stage &s = stage_[stage_next_++ % stage_.size()];
+        const size_t part = std::min(bytes, stage_bytes_);
+        FHE_CUDA(cudaEventSynchronize(s.done)); // returns at once unless the copy that last used this slot is still queued
+        std::memcpy(s.host, src, part);
+        FHE_CUDA(cudaMemcpyAsync(dst, s.host, part, cudaMemcpyHostToDevice, stream));
+        FHE_CUDA(cudaEventRecord(s.done, stream));
+        dst = (char *)dst + part, src = (const char *)src + part, bytes -= part;
+    }
+}
+
 Mem Context::encode_at(const Plaintext &pt, int ell, double scale) {
     std::lock_guard<std::recursive_mutex> g(mu);
     FHE_CUDA(cudaSetDevice(device));
-    const int n = P->n, slots = pt.slots, gap = n / (2 * slots);
-    const size_t nv = std::min((size_t)slots, pt.vals.size());
-    Mem vbuf = alloc((size_t)2 * slots), staging = alloc((size_t)4 * slots);
-    if (nv < (size_t)slots) FHE_CUDA(cudaMemsetAsync(vbuf->p, 0, sizeof(double2) * slots, stream));
-    if (nv) FHE_CUDA(cudaMemcpyAsync(vbuf->p, pt.vals.data(), sizeof(double2) * nv, cudaMemcpyHostToDevice, stream));
+    const int n = P->n, slots = pt.slots;
+    Mem vbuf = alloc((size_t)2 * slots), rbuf;
+    size_t nv;
+    if (pt.real_only) {
+        nv = std::min((size_t)slots, pt.re.size());
+        rbuf = alloc(std::max<size_t>(nv, 1));
+        if (nv) upload(rbuf->p, pt.re.data(), sizeof(double) * nv);
+    } else {
+        nv = std::min((size_t)slots, pt.vals.size());
+        if (nv < (size_t)slots) FHE_CUDA(cudaMemsetAsync(vbuf->p, 0, sizeof(double2) * slots, stream));
+        if (nv) upload(vbuf->p, pt.vals.data(), sizeof(double2) * nv);
+    }
     auto tabs = fft_device_tables(slots);
-    k_encode_fft((double2 *)vbuf->p, slots, scale, tabs.first, tabs.second, staging->p, stream);
     Mem out = alloc((size_t)ell * n);
-    k_expand_i128(T, staging->p, 2 * slots, gap, ell, out->p, stream);
+    k_encode(T, (double2 *)vbuf->p, pt.real_only ? (const double *)rbuf->p : nullptr, (int)nv, slots, scale, tabs.first,
+             tabs.second, ell, out->p, stream);
     k_ntt_fwd(T, out->p, plan(ell).desc_q, ell, stream);
     return out;
 }
 
-Pt Context::make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots) {
+Pt Context::new_plaintext(size_t count, int nsd, int level, int slots) {
     if (slots <= 0) slots = batch;
     if ((slots & (slots - 1)) || slots > P->n / 2) throw std::invalid_argument("MakeCKKSPackedPlaintext: slots must be a power of two <= n/2");
-    if ((int)vals.size() > slots) throw std::invalid_argument("MakeCKKSPackedPlaintext: more values than slots");
+    if ((int)count > slots) throw std::invalid_argument("MakeCKKSPackedPlaintext: more values than slots");
     if (level < 0 || level >= P->L) throw std::invalid_argument("MakeCKKSPackedPlaintext: bad level");
     auto p = std::make_shared<Plaintext>();
-    p->vals = vals;
     p->slots = slots;
-    p->length = vals.size();
+    p->length = count;
     p->level = level;
     // FLEXIBLEAUTOEXT: level-0 plaintexts live at the big scale with degree 2; deeper ones at sf[level]^nsd
     if (level == 0) {
@@ -230,6 +256,17 @@ Pt Context::make_plaintext(const std::vector<std::complex<double>> &vals, int ns
     }
     p->ell = P->L - level;
     // encoded lazily (encoding_for): a mask built at level 0 is only ever used at the level of the ciphertext it multiplies
+    return p;
+}
+Pt Context::make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots) {
+    Pt p = new_plaintext(vals.size(), nsd, level, slots);
+    p->vals = vals;
+    return p;
+}
+Pt Context::make_plaintext_real(const double *vals, size_t count, int nsd, int level, int slots) {
+    Pt p = new_plaintext(count, nsd, level, slots);
+    p->re.assign(vals, vals + count);
+    p->real_only = true;
     return p;
 }
 

@@ -94,18 +94,17 @@ void Context::rescale_poly(int ell, int npoly, const u64 *in, u64 *out) {
     LimbScalars qi;
     memset(&qi, 0, sizeof(qi));
     for (int i = 0; i < ell - 1; i++) qi.v[i] = H.ql_inv[i], qi.s[i] = H.ql_inv_s[i];
-    Mem last = alloc((size_t)npoly * n), tmp = alloc((size_t)npoly * (ell - 1) * n);
+    // the dropped limb of poly p goes through the inverse NTT straight out of `in` (slot p * ell of both views)
+    Mem last = alloc(((size_t)(npoly - 1) * ell + 1) * n), tmp = alloc((size_t)npoly * (ell - 1) * n);
     std::vector<uint32_t> dl, dt;
     for (int p = 0; p < npoly; p++) {
-        dl.push_back(((uint32_t)p << 8) | (uint32_t)(ell - 1));
+        dl.push_back(((uint32_t)(p * ell) << 8) | (uint32_t)(ell - 1));
         for (int i = 0; i < ell - 1; i++) dt.push_back(((uint32_t)(p * (ell - 1) + i) << 8) | (uint32_t)i);
-        FHE_CUDA(cudaMemcpyAsync(last->p + (size_t)p * n, in + ((size_t)p * ell + ell - 1) * n, n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
     }
-    k_ntt_inv(T, last->p, desc(dl), npoly, stream);
-    for (int p = 0; p < npoly; p++) k_rescale_lift(T, ell, last->p + (size_t)p * n, tmp->p + (size_t)p * (ell - 1) * n, stream);
+    k_ntt_inv(T, in + (size_t)(ell - 1) * n, last->p, desc(dl), npoly, stream);
+    k_rescale_lift(T, ell, npoly, last->p, (size_t)ell * n, tmp->p, stream);
     k_ntt_fwd(T, tmp->p, desc(dt), npoly * (ell - 1), stream);
-    for (int p = 0; p < npoly; p++)
-        k_rescale_finish(T, ell - 1, in + (size_t)p * ell * n, tmp->p + (size_t)p * (ell - 1) * n, qi, out + (size_t)p * (ell - 1) * n, stream);
+    k_rescale_finish(T, ell - 1, npoly, in, tmp->p, qi, out, stream);
 }
 Ct Context::mod_reduce(const Ct &a) {
     LOCK;

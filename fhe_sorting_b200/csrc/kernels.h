@@ -62,9 +62,9 @@ void k_automorphism(const DeviceTables &T, uint32_t galois, int limbs, const u64
 
 // ---- rescale ----
 // last: coefficient-domain last limb [n]; tmp[ell-1][n] <- centred lift of last into q_i (then NTT it)
-void k_rescale_lift(const DeviceTables &T, int ell, const u64 *last_coeff, u64 *tmp, cudaStream_t st);
-// out_i = (in_i - tmp_i) * ql_inv_i
-void k_rescale_finish(const DeviceTables &T, int ell_out, const u64 *in, const u64 *tmp, const LimbScalars &qlinv,
+void k_rescale_lift(const DeviceTables &T, int ell, int npoly, const u64 *last_coeff, size_t last_stride, u64 *tmp, cudaStream_t st);
+// out[p][i] = (in[p][i] - tmp[p][i]) * q_last^-1 mod q_i for all polys in one launch (in: ell_out + 1 limbs per poly)
+void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *in, const u64 *tmp, const LimbScalars &qlinv,
                       u64 *out, cudaStream_t st);
 
 // ---- hybrid key switching ----
@@ -107,7 +107,8 @@ void k_expand_i128(const DeviceTables &T, const u64 *coef_lohi, int ncoef, int g
                    cudaStream_t st);
 // device CKKS encode: in-place special inverse FFT of v[size], then words (lo,hi pairs) <- round(v * scale / size) in the
 // layout k_expand_i128 consumes (real parts first, imaginary parts after); ksi = exp(2 pi i k / 4 size), rot = 5^j mod 4 size
-void k_encode_fft(double2 *v, int size, double scale, const double2 *ksi, const int *rot, u64 *words, cudaStream_t st);
+void k_encode(const DeviceTables &T, double2 *v, const double *real_in, int nv, int size, double scale, const double2 *ksi,
+              const int *rot, int ell, u64 *out, cudaStream_t st);
 // b = e - a*s_new + [limb in digit] * pmod * s_old   over F limbs (one digit of a switching key)
 void k_evk_finish(const DeviceTables &T, int F, const u64 *a, const u64 *e, const u64 *s_new, const u64 *s_old,
                   const LimbScalars &pmod, u64 *b, cudaStream_t st);

@@ -20,7 +20,11 @@ namespace fheb200 {
 
 std::atomic<unsigned long long> g_launches{0};
 
-constexpr int NTT_TILE_LOG = 12;
+#ifndef NTT_TILE_LOG_V
+#define NTT_TILE_LOG_V 11
+#endif
+constexpr int NTT_TILE_LOG = NTT_TILE_LOG_V;
+constexpr int NTT_CTAS = 8192 / (1 << NTT_TILE_LOG_V); // resident CTAs per SM: 1024 threads of 64 registers
 constexpr int NTT_TILE = 1 << NTT_TILE_LOG;            // coefficients per CTA tile
 constexpr int NTT_PAD_WORDS = NTT_TILE + NTT_TILE / 8; // e -> e + (e >> 3) keeps every exchange pattern conflict free
 
@@ -133,6 +137,7 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
     else fwd_chunk<3, LAZY>(v, tw, s, G.logn, g0, nq, q2);
     s += c_first;
     bool first = true;
+#pragma unroll
     for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
         if (!first) __syncthreads();
         first = false;
@@ -174,16 +179,17 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
 // B200 issues DFMA at the same rate as IMAD (tools/ubench_int.cu: 3.4 vs 3.6 warp-inst/clk/SM), and a modular product
 // of two < 2^53 integers is 7 double-precision instructions (error-free product + rounded quotient) against ~25
 // integer ones for the 64-bit Shoup form.  Values are kept as exact signed integers in doubles:
-//   c = rint(y * (w/q)) ; h = RN(y*w) ; l = fma(y,w,-h) (exact) ; d = fma(-c,q,h) (exact: |h - c q| < 2q + |l|) ; g = d + l
+//   h = RN(y*w) ; l = fma(y,w,-h) (exact) ; c = rint(h * (1/q)) ; d = fma(-c,q,h) (exact: |h - c q| < 2q + |l|) ; g = d + l
+// (6 DP instructions, no per-twiddle companion value to load or compute)
 // g == y*w (mod q) and |g| < 0.7 q for |y| < 2^50 (emulated exhaustively in tests/test_fp_modmul.py).  No conditional
 // corrections inside the butterflies: forward values grow by < q per stage, inverse sums are re-centred every <= 8 stages.
 constexpr double FP_MAGIC = 6755399441055744.0; // 1.5 * 2^52: (x + M) - M rounds |x| < 2^51 to the nearest integer
 constexpr double FP_2P52 = 4503599627370496.0;
 __device__ __forceinline__ double fp_rint(double x) { return __dadd_rn(__dadd_rn(x, FP_MAGIC), -FP_MAGIC); }
-__device__ __forceinline__ double fp_mulmod(double y, double w, double wq, double q) {
-    const double c = fp_rint(__dmul_rn(y, wq));
+__device__ __forceinline__ double fp_mulmod(double y, double w, double qinv, double q) {
     const double h = __dmul_rn(y, w);
     const double l = __fma_rn(y, w, -h);
+    const double c = __dadd_rn(__fma_rn(h, qinv, FP_MAGIC), -FP_MAGIC); // rint(h / q), off by at most one from rint(y w / q)
     const double d = __fma_rn(-c, q, h);
     return __dadd_rn(d, l);
 }
@@ -200,14 +206,14 @@ __device__ __forceinline__ u64 fp_to_u64(double v, double q, double qinv) { // a
     return (u64)__double_as_longlong(__dadd_rn(r, FP_2P52)) & 0x000fffffffffffffull;
 }
 __device__ __forceinline__ void fp_ct(double &x, double &y, double w, double qinv, double q) {
-    const double g = fp_mulmod(y, w, __dmul_rn(w, qinv), q);
+    const double g = fp_mulmod(y, w, qinv, q);
     y = __dadd_rn(x, -g);
     x = __dadd_rn(x, g);
 }
 __device__ __forceinline__ void fp_gs(double &x, double &y, double w, double qinv, double q) {
     const double d = __dadd_rn(x, -y);
     x = __dadd_rn(x, y);
-    y = fp_mulmod(d, w, __dmul_rn(w, qinv), q);
+    y = fp_mulmod(d, w, qinv, q);
 }
 template <int NS>
 __device__ __forceinline__ void fp_fwd_chunk(double (&v)[8], const double *__restrict__ tw, int s, int logn, uint32_t g0,
@@ -279,6 +285,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
     else fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
     s += c_first;
     bool firstx = true;
+#pragma unroll
     for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
         if (!firstx) __syncthreads();
         firstx = false;
@@ -342,6 +349,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = fp_center(v[k], q, qinv);
     }
+#pragma unroll
     for (int i = 0; i < m; i++) {
         if (growth + 3 > 8) {
 #pragma unroll
@@ -370,9 +378,9 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
     else fp_inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, qinv);
     const uint32_t st = g_step(G, p);
     if (last) {
-        const double ni = (double)T.ninv[qp], niq = __dmul_rn(ni, qinv);
+        const double ni = (double)T.ninv[qp];
 #pragma unroll
-        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = fp_to_u64(fp_mulmod(v[k], ni, niq, q), q, qinv);
+        for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = fp_to_u64(fp_mulmod(v[k], ni, qinv, q), q, qinv);
     } else {
 #pragma unroll
         for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = (u64)__double_as_longlong(v[k]);
@@ -381,7 +389,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
 __device__ __forceinline__ bool fp_ok(const DeviceTables &T, int qp) { return T.mc[qp].bits <= 42 && T.logn <= 17; }
 
 __device__ __forceinline__ bool lazy_ok(const DeviceTables &T, int qp) { return T.mc[qp].bits + T.logn + 1 <= 63; }
-__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_fwd_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                              const uint32_t *__restrict__ desc, PassGeom G, int first, int final_reduce) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
@@ -417,6 +425,7 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
     }
+#pragma unroll
     for (int i = 0; i < m; i++) {
         const int s = G.S0 + G.S - 1 - (p + 2 - lowbit); // global stage of the triple's top bit
         inv_chunk<3, LAZY>(v, tw, s, G.logn, g0, q, nq, q2);
@@ -444,7 +453,7 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
     for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = v[k];
 }
 
-__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                              const uint32_t *__restrict__ desc, PassGeom G, int first, int scale) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
@@ -456,7 +465,7 @@ __global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass(DeviceTables T, 
 // Compile-time geometry for the production ring (n = 2^17): every shift, stride and loop trip count of the pass bodies
 // becomes an immediate, which removes most of the index arithmetic around the butterflies.
 template <int LOGN, int S, int S0, int LC, int PA>
-__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_fwd_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                                   const uint32_t *__restrict__ desc, int first, int final_reduce) {
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
@@ -466,7 +475,7 @@ __global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_fwd_pass_c(DeviceTables T
     else fwd_pass_body<false>(T, src, dst, d, G, final_reduce, sm);
 }
 template <int LOGN, int S, int S0, int LC, int PA>
-__global__ void __launch_bounds__(NTT_TILE / 8, 2) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                                   const uint32_t *__restrict__ desc, int first, int scale) {
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
@@ -498,7 +507,7 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (T.logn == 17) {
-        g_launches++, ntt_fwd_pass_c<17, 8, 0, 4, 1><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
+        g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
         g_launches++, ntt_fwd_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
         return;
     }
@@ -517,7 +526,7 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (T.logn == 17) {
         g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
-        g_launches++, ntt_inv_pass_c<17, 8, 0, 4, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
+        g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
         return;
     }
     g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0);

@@ -1,0 +1,19 @@
+#!/usr/bin/env python
+"""One encrypted DirectSort at ring 2^17 (for profiling under ncu): python tools/sort_once.py N [reps]"""
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, ".")
+from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input  # noqa: E402
+
+n = int(sys.argv[1])
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+s = DirectSortSession(n, 17, seed=1000 + n)
+x = uniform_gap_input(n)
+for _ in range(reps):
+    t0 = time.perf_counter()
+    out, ms, level = s.sort(x)
+    print("N=%d sort %.1f ms wall %.1f ms err %.2e" % (n, ms, 1e3 * (time.perf_counter() - t0), np.abs(out - np.sort(x)).max()),
+          flush=True)
