@@ -189,6 +189,25 @@ def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)
                        "final_level": level, "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys,
                        "sharded_over_ranks": shard_batches(n, rank, world)[1]}
         s.close()
+    # MEHP24 ranking sort, N = 256 (BASELINE.json config 4; tests/mehp24/Mehp24SortTest.cpp): one 65536-slot ciphertext,
+    # strictly sequential -> every rank runs the same sort ("replicas only"), the slowest is reported
+    from fhe_sorting_b200.sort import Mehp24SortSession
+    s = Mehp24SortSession(256, 17, seed=SEED + 24, device=local_rank)
+    x = uniform_gap_input(256)
+    s.sort(x)
+    runs = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        res, _, level = s.sort(x)
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        runs.append(float(dt.item()))
+    out["mehp24_256"] = {"seconds": sorted(runs)[1], "runs": runs, "max_abs_err": float(np.abs(res - np.sort(x)).max()),
+                         "final_level": level, "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys,
+                         "sharded_over_ranks": False}
+    s.close()
     return out
 
 

@@ -21,7 +21,7 @@ struct DeviceTables {            // resident per context
     u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
 };
 
-constexpr int MAX_LIMBS = 64;    // upper bound on L+K (by-value kernel parameter blocks)
+constexpr int MAX_LIMBS = 96;    // upper bound on L+K (by-value kernel parameter blocks)
 struct LimbScalars {             // per-limb scalar + Shoup companion, passed by value
     u64 v[MAX_LIMBS];
     u64 s[MAX_LIMBS];

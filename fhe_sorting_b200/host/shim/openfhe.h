@@ -408,7 +408,7 @@ template <typename P> class CryptoContext {
   public:
     CryptoContext() = default;
     CryptoContext(std::nullptr_t) {}
-    explicit CryptoContext(ContextPtr p) : p_(std::move(p)) {}
+    CryptoContext(ContextPtr p) : p_(std::move(p)) {} // implicit: `CryptoContext<Element> cc = ct->GetCryptoContext();`
     CryptoContext(const ContextPtr &p, int) : p_(p) {}
     CryptoContextImpl *operator->() const { return p_.get(); }
     explicit operator bool() const { return (bool)p_; }
@@ -416,6 +416,21 @@ template <typename P> class CryptoContext {
 };
 // ct->GetCryptoContext() returns a ContextPtr; let it convert where the reference stores a CryptoContext<DCRTPoly>
 template <typename P> inline CryptoContext<P> ToContext(const ContextPtr &p) { return CryptoContext<P>(p); }
+
+// ciphertext operators of OpenFHE's ciphertext.h (used by src/mehp24/*.cpp: `c += c >> k`, `c1 * (1 - c2)`, `c1 - c2`)
+template <typename P> inline Ciphertext<P> operator+(const Ciphertext<P> &a, const Ciphertext<P> &b) {
+    return a->GetCryptoContext()->EvalAdd(a, b);
+}
+template <typename P> inline Ciphertext<P> operator-(const Ciphertext<P> &a, const Ciphertext<P> &b) {
+    return a->GetCryptoContext()->EvalSub(a, b);
+}
+template <typename P> inline Ciphertext<P> operator*(const Ciphertext<P> &a, const Ciphertext<P> &b) {
+    return a->GetCryptoContext()->EvalMult(a, b);
+}
+template <typename P> inline Ciphertext<P> operator-(const Ciphertext<P> &a) { return a->GetCryptoContext()->EvalNegate(a); }
+template <typename P> inline const Ciphertext<P> &operator+=(Ciphertext<P> &a, const Ciphertext<P> &b) { return a = a + b; }
+template <typename P> inline const Ciphertext<P> &operator-=(Ciphertext<P> &a, const Ciphertext<P> &b) { return a = a - b; }
+template <typename P> inline const Ciphertext<P> &operator*=(Ciphertext<P> &a, const Ciphertext<P> &b) { return a = a * b; }
 
 // lbcrypto::EvalChebyshevCoefficients(f, a, b, degree) (utils/generate_cheb_coeffs.cpp:17): host-only double math
 inline std::vector<double> EvalChebyshevCoefficients(std::function<double(double)> f, double a, double b, uint32_t degree) {

@@ -2,6 +2,7 @@
 // A session owns what the reference's test fixture owns (tests/DirectSortTest.cpp:22-51): CryptoContext, key pair,
 // rotation / relinearisation keys resident in HBM, a DebugEncryption and a DirectSort<N>.
 #include <chrono>
+#include <cmath>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -13,7 +14,15 @@
 #include <omp.h>
 
 #include "../../include/fhe_sort.h"
-#include "sort_algo.h" // the reference's rotation.h has no include guard: reach it through sort_algo.h only
+// the reference's rotation.h has no include guard: reach it through sort_algo.h only.  Angle brackets in the reference
+// build: a quoted include would find this directory's own drivers first.
+#ifdef REFERENCE_DRIVERS
+#include <sort_algo.h>
+#include <mehp24/mehp24_sort.h>
+#else
+#include "sort_algo.h"
+#include "mehp24.h"
+#endif
 
 namespace {
 thread_local std::string g_err;
@@ -53,6 +62,67 @@ template <int N> struct Session : SessionBase {
     void shard(int rank, int world) override { sorter->setShard(rank, world); }
 #endif
 };
+
+// MEHP24 ranking sort (reference fixture: tests/mehp24/Mehp24SortTest.cpp:22-93): N values in the first row of an
+// N x N slot matrix (N <= 256), longer arrays split into 256-value ciphertexts
+struct Mehp24Session : SessionBase {
+    std::unique_ptr<Comparison> comp;
+    Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        const uint32_t dg_i = (uint32_t)((std::log2((double)len) + 1) / 2), df_i = 2;
+        if (len <= 256) return mehp24::sortFG(in, (size_t)len, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
+        return mehp24::sortLargeArrayFG(in, (size_t)len, 256, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
+    }
+    Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("mehp24: sort only"); }
+    Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &, const Ciphertext<DCRTPoly> &) override {
+        throw std::runtime_error("mehp24: sort only");
+    }
+    Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &, int) override { throw std::runtime_error("mehp24: sort only"); }
+    void shard(int, int world) override {
+        if (world > 1) throw std::runtime_error("mehp24: the single-ciphertext sort is sequential (replicas only)");
+    }
+};
+int mehp24_depth(int N) { // tests/mehp24/Mehp24SortTest.cpp:31-62
+    switch (N) {
+    case 4: return 31;
+    case 8: case 16: return 35;
+    case 32: case 64: return 42;
+    case 128: return 46;
+    case 256: return 49;
+    case 512: return 57;
+    case 1024: return 60;
+    default: throw std::invalid_argument("mehp24: array length must be a power of two in 4..1024");
+    }
+}
+SessionBase *make_mehp24_session(int N, int log_ring_dim, int depth_override, uint64_t seed, int device) {
+    auto t0 = std::chrono::steady_clock::now();
+    auto s = std::make_unique<Mehp24Session>();
+    const int side = N < 256 ? N : 256, slots = std::min(side * side, (1 << log_ring_dim) / 2);
+    if (side * side > slots) throw std::invalid_argument("mehp24: the N x N matrix does not fit the slots of this ring");
+    CCParams<CryptoContextCKKSRNS> p;
+    p.SetRingDim(1u << log_ring_dim);
+    p.SetBatchSize(slots);
+    p.SetMultiplicativeDepth(depth_override > 0 ? depth_override : mehp24_depth(N));
+    p.SetScalingModSize(40);
+    p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
+    if (seed) CryptoContextImpl::SetKeySeed(seed);
+#ifdef REFERENCE_DRIVERS
+    setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
+    s->cc = GenCryptoContext(p);
+#else
+    s->cc = GenCryptoContext(p, device);
+#endif
+    s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE);
+    s->keys = s->cc->KeyGen();
+    s->rotations = mehp24::utils::getRotationIndices((size_t)N);
+    s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
+    s->cc->EvalMultKeyGen(s->keys.secretKey);
+    s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);
+    s->comp = std::make_unique<Comparison>(s->enc);
+    s->len = N, s->depth = (int)p.GetMultiplicativeDepth();
+    s->cc->Sync();
+    s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s.release();
+}
 
 template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
     auto t0 = std::chrono::steady_clock::now();
@@ -127,6 +197,12 @@ int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t see
         default: throw std::invalid_argument("DirectSort: array length must be a power of two in 4..1024");
         }
         *out = new fhesort_session{std::unique_ptr<SessionBase>(b)};
+    })
+}
+int fhesort_mehp24_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out) throw std::invalid_argument("null argument: out");
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(make_mehp24_session(N, log_ring_dim, mult_depth, seed, device))};
     })
 }
 int fhesort_session_free(fhesort_session *s) {

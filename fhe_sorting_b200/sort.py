@@ -47,11 +47,13 @@ def uniform_gap_input(n, seed=None):
 class DirectSortSession:
     """What tests/DirectSortTest.cpp's fixture sets up: context, keys in HBM, DirectSort<N>."""
 
+    _create = "fhesort_session_create"
+
     def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0, drivers="ours"):
         """drivers="reference" runs the reference's own sort_algo.h / sign.cpp ... (oracle/_ref) on the same engine."""
         L = self.L = load_sort(drivers)
         h = C.c_void_p()
-        _ck(L.fhesort_session_create(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
+        _ck(getattr(L, self._create)(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
         self.h, self.n = h, n
         d, k, ms = C.c_int(), C.c_int(), C.c_double()
         _ck(L.fhesort_session_info(h, C.byref(d), C.byref(k), C.byref(ms)), L)
@@ -165,3 +167,9 @@ def combine_partial_residues(partial, moduli, dist=None):
     s = t.numpy().view(np.uint64)
     q = np.asarray(moduli, dtype=np.uint64).reshape(-1, 1)
     return s % q
+
+
+class Mehp24SortSession(DirectSortSession):
+    """tests/mehp24/Mehp24SortTest.cpp's fixture: N values in the first row of an N x N slot matrix, mehp24::sortFG
+    (sortLargeArrayFG above 256 values).  Only sort() applies."""
+    _create = "fhesort_mehp24_session_create"

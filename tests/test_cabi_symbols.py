@@ -25,6 +25,16 @@ def test_every_declared_symbol_is_exported():
     assert not missing, "declared in fhe_b200.h but not exported: %s" % missing
 
 
+def test_every_declared_sort_symbol_is_exported():
+    from fhe_sorting_b200.sort import load_sort
+    text = re.sub(r"/\*.*?\*/", "", open(HEADER.replace("fhe_b200.h", "fhe_sort.h")).read(), flags=re.S)
+    names = sorted(set(re.findall(r"\b(fhesort_[a-z0-9_]+)\s*\(", text)) - {"fhesort_allreduce_fn"})
+    lib = load_sort()
+    assert len(names) >= 10
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, "declared in fhe_sort.h but not exported: %s" % missing
+
+
 def test_version_and_error_strings():
     lib = F.load()
     assert lib.fheb200_version().decode().startswith("fheb200")
