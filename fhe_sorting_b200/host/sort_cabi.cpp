@@ -328,6 +328,26 @@ int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *cou
     })
 }
 
+int fhesort_sinc_coefficients(int N, double *out, int capacity, int *count) {
+    GUARD({
+        const std::vector<double> *c = nullptr;
+        switch (N) {
+        case 4: c = &selectCoefficients<4>(); break;
+        case 8: c = &selectCoefficients<8>(); break;
+        case 16: c = &selectCoefficients<16>(); break;
+        case 32: c = &selectCoefficients<32>(); break;
+        case 64: c = &selectCoefficients<64>(); break;
+        case 128: c = &selectCoefficients<128>(); break;
+        case 256: c = &selectCoefficients<256>(); break;
+        case 512: c = &selectCoefficients<512>(); break;
+        case 1024: c = &selectCoefficients<1024>(); break;
+        default: throw std::invalid_argument("unsupported N");
+        }
+        if (count) *count = (int)c->size();
+        for (int i = 0; i < (int)c->size() && i < capacity; i++) out[i] = (*c)[i];
+    })
+}
+
 #endif
 
 } // extern "C"

@@ -148,6 +148,14 @@ def doubled_sinc_coefficients(n):
     return buf[:cnt.value].copy()
 
 
+def sinc_coefficients(n):
+    L = load_sort()
+    buf = np.zeros(16384)
+    cnt = C.c_int()
+    _ck(L.fhesort_sinc_coefficients(n, _dp(buf), len(buf), C.byref(cnt)))
+    return buf[:cnt.value].copy()
+
+
 def shard_batches(n, rank, world, log_ring_dim=17):
     """(batches evaluated by `rank`, whether the sort is sharded at all) — host-only mirror of DirectSort::setShard."""
     L = load_sort()

@@ -42,6 +42,8 @@ int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity,
                       int *count);
 int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count);
+/* selectCoefficients<N>() (src/generated_coeffs.h, written by utils/generate_cheb_coeffs.cpp) */
+int fhesort_sinc_coefficients(int N, double *out, int capacity, int *count);
 
 #ifdef __cplusplus
 }

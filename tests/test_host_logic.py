@@ -70,3 +70,13 @@ def test_tables_equal_the_reference_generator_output():
         m = re.search(r"generatedDoubledSincCoefficients_%d = \{(.*?)\};" % n, txt, re.S)
         ref = np.array([float(v) for v in m.group(1).replace("\n", " ").split(",")])
         assert np.array_equal(ref, S.doubled_sinc_coefficients(n))
+
+
+def test_tables_equal_golden_reference_generator_output():
+    """tests/golden/chebyshev_tables.json: tables printed by the reference's own generators (tools/make_golden.py)."""
+    import json
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "chebyshev_tables.json")))
+    for n, want in gold["doubled_sinc"].items():
+        assert np.array_equal(np.array(want), S.doubled_sinc_coefficients(int(n)))
+    for n, want in gold["sinc"].items():
+        assert np.array_equal(np.array(want), S.sinc_coefficients(int(n)))
