@@ -1,0 +1,167 @@
+// baseconv.cu — fast base conversion (ModUp / ModDown of hybrid key switching) on the integer tensor cores.
+//
+//   out_t[k] = sum_j y_j[k] * C[j][t]  mod p_t          y_j = x_j * (Q/q_j)^-1 mod q_j  (already applied by the inverse NTT)
+//
+// is a small dense contraction per coefficient (14 sources x 37 targets at the N = 1024 parameters).  The scalar kernel
+// (keyswitch.cu: ks_modup / ks_moddown_conv) spends ~5000 integer instructions per coefficient and digit on it and sits on
+// the IMAD issue limit.  Here every 64-bit operand is cut into bytes: with y = sum_a y_a 2^(8a) and the constants
+// C'[j][a][t] = C[j][t] 2^(8a) mod p_t precomputed and cut into byte planes b,
+//
+//   out_t = sum_b 2^(8b) * ( sum_(j,a) y_(j,a) * byte_b(C'[j][a][t]) )  mod p_t
+//
+// and the inner sums are u8 x u8 -> s32 matrix products (mma.sync.m16n8k32, < 2^23 each, exact).  M = 16 coefficients,
+// K = (source, byte) in groups of 32 = 4 sources x 8 bytes, N = 8 targets; one accumulator tile per byte plane.  The A
+// fragments are simply the 32-bit halves of the u64 coefficients as they lie in HBM (no byte shuffling); the B fragments
+// are precomputed per lane (engine_ctx.cu: make_conv_table) and stay L1 resident.  The planes of one output sit in one
+// lane, so the recombination is lane-local: 6 planes fit a u64 (one single-word Barrett), 8 planes take the 128-bit path.
+// Measured on B200 (tools/ubench_mma.cu): 572 TMAC/s for this MMA shape, i.e. ~25 us for the 14 GMAC of one ModUp at 41
+// limbs; the kernel is bound by the epilogue and the 160 MB it moves instead.
+#include <stdexcept>
+
+#include "kernels.h"
+#include "modarith.cuh"
+
+namespace fheb200 {
+
+constexpr int BC_WARPS = 4; // 128 threads, 32 coefficients per warp
+
+__device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], const uint2 b) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+
+// sum_b s[b] 2^(8b), s[b] < 2^23: planes 0..5 -> one u64 (< 2^64 whenever the true value is, i.e. 6-plane targets)
+__device__ __forceinline__ u64 combine6(int s0, int s1, int s2, int s3, int s4, int s5) {
+    const u64 lo = (u64)(uint32_t)s0 + ((u64)(uint32_t)s1 << 8) + ((u64)(uint32_t)s2 << 16) + ((u64)(uint32_t)s3 << 24);
+    const u64 hi = (u64)(uint32_t)s4 + ((u64)(uint32_t)s5 << 8);
+    return lo + (hi << 32);
+}
+
+template <int KS>
+__global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, ConvArgs A) {
+    const ConvInstance I = A.inst[blockIdx.y];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, tq = lane & 3, n = T.n;
+    const int coef0 = (blockIdx.x * BC_WARPS + warp) * 32;
+    if (coef0 >= n) return;
+    const ConvTable &C = I.tab;
+
+    // A fragments: lane (g, tq) holds the (tq & 1) half of sources 4 ks + (tq >> 1) and + 2, rows g and g + 8 of each M tile
+    uint32_t a[2][KS][4];
+    {
+        const uint32_t *s32 = reinterpret_cast<const uint32_t *>(I.src);
+        const int half = tq & 1;
+#pragma unroll
+        for (int ks = 0; ks < KS; ks++) {
+            const int s0 = 4 * ks + (tq >> 1), s1 = s0 + 2;
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                const size_t r0 = (size_t)(coef0 + 16 * mt + g), r1 = r0 + 8;
+                a[mt][ks][0] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r0) + half] : 0u;
+                a[mt][ks][1] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r1) + half] : 0u;
+                a[mt][ks][2] = s1 < C.nsrc ? s32[2 * ((size_t)s1 * n + r0) + half] : 0u;
+                a[mt][ks][3] = s1 < C.nsrc ? s32[2 * ((size_t)s1 * n + r1) + half] : 0u;
+            }
+        }
+    }
+
+    for (int nt = 0; nt < C.NT; nt++) {
+        int acc[8][2][4];
+#pragma unroll
+        for (int b = 0; b < 8; b++)
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
+        const int np = C.planes[nt];
+#pragma unroll
+        for (int ks = 0; ks < KS; ks++) {
+            const uint2 *bp = C.B + ((size_t)(ks * C.NT + nt) * 8) * 32 + lane;
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                if (b < 6 || np > 6) { // planes 6, 7 only exist for targets above 48 bits (uniform branch)
+                    const uint2 bf = __ldg(bp + b * 32);
+                    imma_16832(acc[b][0], a[0][ks], bf);
+                    imma_16832(acc[b][1], a[1][ks], bf);
+                }
+            }
+        }
+        // epilogue: this lane owns targets 8 nt + 2 tq + {0, 1}, rows g and g + 8 of both M tiles
+#pragma unroll
+        for (int cpar = 0; cpar < 2; cpar++) {
+            const int tp = 8 * nt + 2 * tq + cpar;
+            const int slot = __ldg(C.tslot + tp);
+            if (slot < 0) continue;
+            const ModConst m = T.mc[__ldg(C.tqp + tp)];
+            u64 *o = I.dst + (size_t)slot * n + coef0 + g;
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                for (int rh = 0; rh < 2; rh++) {
+                    const int i = 2 * rh + cpar;
+                    const u64 lo = combine6(acc[0][mt][i], acc[1][mt][i], acc[2][mt][i], acc[3][mt][i], acc[4][mt][i], acc[5][mt][i]);
+                    u64 r;
+                    if (np > 6) { // + (s6 2^48 + s7 2^56): up to ~2^80
+                        const u64 top = (u64)(uint32_t)acc[6][mt][i] + ((u64)(uint32_t)acc[7][mt][i] << 8); // * 2^48
+                        const u64 add = top << 48;
+                        const u64 l2 = lo + add;
+                        const u64 h2 = (top >> 16) + (l2 < add);
+                        r = reduce128(h2, l2, m);
+                    } else {
+                        r = reduce64(lo, m);
+                    }
+                    o[16 * mt + 8 * rh] = r;
+                }
+        }
+    }
+
+    // ModUp: the digit's own limbs are the evaluation-domain input itself
+    if (I.copy_limbs > 0) {
+        for (int t = 0; t < I.copy_limbs; t++) I.copy_dst[(size_t)t * n + coef0 + lane] = I.copy_src[(size_t)t * n + coef0 + lane];
+    }
+}
+
+void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
+    const dim3 grid((T.n + BC_WARPS * 32 - 1) / (BC_WARPS * 32), count);
+    switch (KS) {
+#define CASE(k) case k: g_launches++, bc_convert<k><<<grid, BC_WARPS * 32, 0, st>>>(T, A); break;
+        CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6)
+#undef CASE
+        default: throw std::invalid_argument("fheb200: more than 24 limbs per digit unsupported");
+    }
+}
+
+
+// coef: ModUp's inverse-NTT output scaled by DevicePlan::up_scale; c_eval: the evaluation-domain input (own-digit copy)
+void k_modup_tc(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits, cudaStream_t st) {
+    const size_t n = T.n;
+    for (int j = 0; j < P.beta;) { // one launch per run of digits with the same number of K steps
+        ConvArgs A;
+        int cnt = 0;
+        const int KS = P.up[j].KS;
+        while (j + cnt < P.beta && P.up[j + cnt].KS == KS) {
+            const int d = j + cnt;
+            ConvInstance &I = A.inst[cnt++];
+            I.tab = P.up[d];
+            I.src = coef + (size_t)P.dstart[d] * n;
+            I.dst = digits + (size_t)d * P.width * n;
+            I.copy_src = c_eval + (size_t)P.dstart[d] * n;
+            I.copy_dst = digits + ((size_t)d * P.width + P.dstart[d]) * n;
+            I.copy_limbs = P.dsize[d];
+        }
+        k_base_convert(T, A, cnt, KS, st);
+        j += cnt;
+    }
+}
+// acc: [2][width][n] with the P limbs already through the inverse NTT scaled by DevicePlan::down_scale
+void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st) {
+    const size_t n = T.n;
+    ConvArgs A;
+    for (int b = 0; b < 2; b++) {
+        ConvInstance &I = A.inst[b];
+        I.tab = P.down;
+        I.src = acc + ((size_t)b * P.width + P.ell) * n;
+        I.dst = conv + (size_t)b * P.ell * n;
+    }
+    k_base_convert(T, A, 2, P.down.KS, st);
+}
+
+} // namespace fheb200

@@ -219,7 +219,7 @@ int fheb200_bench_rotations(fheb200_ctx *ctx, fheb200_ct *ct, const int *indices
 }
 
 // isolated kernels on scratch data at `ell` active limbs: "ntt_fwd", "ntt_inv", "inner_product", "modup_conv",
-// "moddown_conv", "automorphism", "tensor", "add"
+// "moddown_conv", "automorphism", "tensor", "add", and the CUDA-core conversions "modup_conv_scalar", "moddown_conv_scalar"
 int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, float *ms, double *algo_bytes) {
     GUARD({
         LOCKCTX(ctx);
@@ -236,8 +236,10 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
             if (k == "ntt_fwd") { k_ntt_fwd(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
             else if (k == "ntt_inv") { k_ntt_inv(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
             else if (k == "inner_product") { k_inner_product(C.T, D, a->p, C.evk_mult, b->p, C.stream); bytes = (3.0 * D.beta + 2.0) * D.width * limb; }
-            else if (k == "modup_conv") { k_modup(C.T, D, b->p, b->p, a->p, C.stream); bytes = (double)(ell + D.beta * D.width) * limb; }
-            else if (k == "moddown_conv") { k_moddown_conv(C.T, D, b->p, a->p, C.stream); bytes = 2.0 * (D.K + ell) * limb; }
+            else if (k == "modup_conv_scalar") { k_modup(C.T, D, b->p, b->p, a->p, C.stream); bytes = (double)(ell + D.beta * D.width) * limb; }
+            else if (k == "moddown_conv_scalar") { k_moddown_conv(C.T, D, b->p, a->p, C.stream); bytes = 2.0 * (D.K + ell) * limb; }
+            else if (k == "modup_conv") { k_modup_tc(C.T, D, b->p, b->p, a->p, C.stream); bytes = (double)(ell + D.beta * D.width) * limb; }
+            else if (k == "moddown_conv") { k_moddown_conv_tc(C.T, D, b->p, a->p, C.stream); bytes = 2.0 * (D.K + ell) * limb; }
             else if (k == "automorphism") { k_automorphism(C.T, 5, ell, a->p, b->p, C.stream); bytes = 2.0 * ell * limb; }
             else if (k == "tensor") { k_tensor(C.T, ell, a->p, a->p + (size_t)ell * n, a->p, a->p + (size_t)ell * n, b->p, b->p + (size_t)ell * n, b->p + (size_t)2 * ell * n, C.stream); bytes = 7.0 * ell * limb; }
             else if (k == "add") { k_binary(C.T, OP_ADD, ell, a->p, a->p + (size_t)ell * n, b->p, C.stream); bytes = 3.0 * ell * limb; }

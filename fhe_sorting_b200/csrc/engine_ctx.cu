@@ -3,6 +3,8 @@
 #include <random>
 #include <stdexcept>
 
+#include <algorithm>
+
 #include "engine.h"
 
 namespace fheb200 {
@@ -152,6 +154,78 @@ const DevicePlan &Context::plan(int ell) {
     for (int b = 0; b < 2; b++) {
         for (int k = 0; k < P->K; k++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
         for (int i = 0; i < ell; i++) dq2.push_back(((uint32_t)(b * ell + i) << 8) | (uint32_t)i);
+    }
+    // ---- tensor-core base conversion tables (baseconv.cu)
+    typedef unsigned __int128 u128;
+    auto bits_of = [&](int qp) { return P->mc[qp].bits; };
+    // C[src * cstride + tgt_pos]; targets = (output slot, modulus index) pairs
+    auto make_conv_table = [&](const std::vector<u64> &C, int cstride, int nsrc, std::vector<std::pair<int, int>> tg,
+                               const std::vector<int> &tpos) {
+        // targets needing 8 byte planes first, so that as few column groups as possible carry them
+        std::vector<int> order(tg.size());
+        for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return (bits_of(tg[a].second) > 48) > (bits_of(tg[b].second) > 48); });
+        ConvTable t;
+        t.nsrc = nsrc, t.KS = (nsrc + 3) / 4, t.NT = ((int)tg.size() + 7) / 8;
+        std::vector<int> tslot(t.NT * 8, -1), tqp(t.NT * 8, 0);
+        std::vector<unsigned char> planes(t.NT, 6);
+        std::vector<uint32_t> B((size_t)t.KS * t.NT * 8 * 32 * 2, 0);
+        for (size_t c = 0; c < order.size(); c++) {
+            tslot[c] = tg[order[c]].first, tqp[c] = tg[order[c]].second;
+            if (bits_of(tqp[c]) > 48) planes[c / 8] = 8;
+        }
+        for (int ks = 0; ks < t.KS; ks++)
+            for (int nt = 0; nt < t.NT; nt++)
+                for (int lane = 0; lane < 32; lane++) {
+                    const int g = lane >> 2, tq = lane & 3, col = 8 * nt + g;
+                    if (col >= (int)order.size()) continue;
+                    const u64 p = P->moduli[tqp[col]];
+                    for (int reg = 0; reg < 2; reg++) {
+                        const int j = 4 * ks + 2 * reg + (tq >> 1);
+                        if (j >= nsrc) continue;
+                        const u64 c0 = C[(size_t)j * cstride + tpos[order[col]]] % p;
+                        for (int i = 0; i < 4; i++) {
+                            const int a = 4 * (tq & 1) + i;
+                            const u64 cp = (u64)(((u128)c0 << (8 * a)) % p);
+                            for (int b = 0; b < 8; b++)
+                                B[(((size_t)(ks * t.NT + nt) * 8 + b) * 32 + lane) * 2 + reg] |= (uint32_t)((cp >> (8 * b)) & 0xff) << (8 * i);
+                        }
+                    }
+                }
+        t.B = (const uint2 *)owned_alloc(sizeof(uint32_t) * B.size(), B.data());
+        t.tslot = (const int *)owned_alloc(sizeof(int) * tslot.size(), tslot.data());
+        t.tqp = (const int *)owned_alloc(sizeof(int) * tqp.size(), tqp.data());
+        t.planes = (const unsigned char *)owned_alloc(planes.size(), planes.data());
+        return t;
+    };
+    auto shoup_of = [&](u64 v, u64 q) { return (u64)(((u128)v << 64) / q); };
+    auto mulmod = [&](u64 a, u64 b, u64 q) { return (u64)((u128)a * b % q); };
+    {
+        std::vector<u64> up(2 * (size_t)ell, 0), down(4 * (size_t)P->K, 0);
+        for (int j = 0; j < H.beta; j++) {
+            std::vector<std::pair<int, int>> tg;
+            std::vector<int> tpos;
+            for (int t = 0; t < H.width; t++)
+                if (t < H.dstart[j] || t >= H.dstart[j] + H.dsize[j]) tg.push_back({t, H.qp[t]}), tpos.push_back(t);
+            D.up[j] = make_conv_table(H.hat[j], H.width, H.dsize[j], tg, tpos);
+            for (int i = 0; i < H.dsize[j]; i++) {
+                const int limb = H.dstart[j] + i;
+                const u64 q = P->moduli[limb];
+                up[limb] = mulmod(P->n_inv[limb], H.hat_inv[j][i], q), up[ell + limb] = shoup_of(up[limb], q);
+            }
+        }
+        std::vector<std::pair<int, int>> tg;
+        std::vector<int> tpos;
+        for (int i = 0; i < ell; i++) tg.push_back({i, i}), tpos.push_back(i);
+        D.down = make_conv_table(H.p_hat, ell, P->K, tg, tpos);
+        for (int b = 0; b < 2; b++)
+            for (int k = 0; k < P->K; k++) {
+                const u64 q = P->moduli[P->L + k];
+                const u64 v = mulmod(P->n_inv[P->L + k], H.p_hat_inv[k], q);
+                down[b * P->K + k] = v, down[2 * P->K + b * P->K + k] = shoup_of(v, q);
+            }
+        D.up_scale = (u64 *)owned_alloc(sizeof(u64) * up.size(), up.data());
+        D.down_scale = (u64 *)owned_alloc(sizeof(u64) * down.size(), down.data());
     }
     D.desc_q = (uint32_t *)desc(dq);
     D.desc_modup = (uint32_t *)desc(dm);

@@ -29,12 +29,25 @@ Ct Context::clone(const Ct &a) {
 }
 
 // ------------------------------------------------------------------ key switching pipeline
+// FHEB200_CONV=scalar keeps the CUDA-core base conversion (keyswitch.cu) for A/B measurements; both are exact
+static bool tensor_core_conv() {
+    static const bool on = [] {
+        const char *e = getenv("FHEB200_CONV");
+        return !(e && std::string(e) == "scalar");
+    }();
+    return on;
+}
 void Context::modup(int ell, const u64 *c, u64 *digits) {
     const DevicePlan &D = plan(ell);
     const int n = P->n;
     Mem coef = alloc((size_t)ell * n);
-    k_ntt_inv(T, c, coef->p, D.desc_q, ell, stream);
-    k_modup(T, D, coef->p, c, digits, stream);
+    if (tensor_core_conv()) { // (Q_j/q_i)^-1 rides on the inverse NTT's final scaling; contraction on the integer tensor cores
+        k_ntt_inv(T, c, coef->p, D.desc_q, ell, stream, D.up_scale);
+        k_modup_tc(T, D, coef->p, c, digits, stream);
+    } else {
+        k_ntt_inv(T, c, coef->p, D.desc_q, ell, stream);
+        k_modup(T, D, coef->p, c, digits, stream);
+    }
     k_ntt_fwd(T, digits, D.desc_modup, D.n_modup, stream);
 }
 void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const u64 *add0, const u64 *add1, u64 *out0,
@@ -43,8 +56,13 @@ void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const
     const int n = P->n;
     Mem acc = alloc((size_t)2 * D.width * n), conv = alloc((size_t)2 * ell * n);
     k_inner_product(T, D, digits, evk, acc->p, stream);
-    k_ntt_inv(T, acc->p, D.desc_p2, 2 * D.K, stream);
-    k_moddown_conv(T, D, acc->p, conv->p, stream);
+    if (tensor_core_conv()) {
+        k_ntt_inv(T, acc->p, acc->p, D.desc_p2, 2 * D.K, stream, D.down_scale);
+        k_moddown_conv_tc(T, D, acc->p, conv->p, stream);
+    } else {
+        k_ntt_inv(T, acc->p, D.desc_p2, 2 * D.K, stream);
+        k_moddown_conv(T, D, acc->p, conv->p, stream);
+    }
     k_ntt_fwd(T, conv->p, D.desc_q2, 2 * ell, stream);
     k_moddown_finish(T, D, acc->p, conv->p, add0, add1, out0, out1, galois, stream);
 }

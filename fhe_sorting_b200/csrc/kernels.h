@@ -30,7 +30,8 @@ struct LimbScalars {             // per-limb scalar + Shoup companion, passed by
 // ---- NTT (batched over limbs) ----
 // src and dst share the slot layout of the descriptors; src == dst transforms in place
 void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
-void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
+void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st,
+               const u64 *custom_scale = nullptr);
 inline void k_ntt_fwd(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, int count, cudaStream_t st) {
     k_ntt_fwd(T, buf, buf, d_desc, count, st);
 }
@@ -68,6 +69,27 @@ void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *
                       u64 *out, cudaStream_t st);
 
 // ---- hybrid key switching ----
+// ---- base conversion on the integer tensor cores (baseconv.cu) ----
+struct ConvTable {
+    const uint2 *B = nullptr;    // [KS][NT][8 planes][32 lanes] per-lane B fragments (bytes of C[j][t] 2^(8a) mod p_t)
+    const int *tslot = nullptr;  // [NT * 8] output limb slot of each target column, -1 = padding
+    const int *tqp = nullptr;    // [NT * 8] modulus index of each target column
+    const unsigned char *planes = nullptr; // [NT] 6 or 8 byte planes
+    int nsrc = 0, KS = 0, NT = 0;
+};
+struct ConvInstance {
+    ConvTable tab;
+    const u64 *src = nullptr;    // nsrc source limbs [nsrc][n], coefficient domain, already times (Q/q_j)^-1
+    u64 *dst = nullptr;          // target limb of column c is dst + tslot[c] * n
+    const u64 *copy_src = nullptr; // copy_limbs limbs copied verbatim (ModUp: the digit's own limbs)
+    u64 *copy_dst = nullptr;
+    int copy_limbs = 0;
+};
+struct ConvArgs {
+    ConvInstance inst[8];
+};
+void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
+
 struct DevicePlan {              // device copy of a LevelPlan
     int ell = 0, beta = 0, width = 0, K = 0;
     int *qp = nullptr;           // [width]
@@ -81,11 +103,17 @@ struct DevicePlan {              // device copy of a LevelPlan
     int n_modup = 0;
     uint32_t *desc_p2 = nullptr;       // iNTT batch: P limbs of two stacked accumulators [2][width]
     uint32_t *desc_q2 = nullptr;       // NTT batch: Q limbs of two stacked [2][ell] buffers
+    ConvTable up[8], down;             // tensor-core base conversion tables per digit / for ModDown
+    u64 *up_scale = nullptr;           // [ell] + [ell] Shoup: n^-1 (Q_j/q_i)^-1 mod q_i, final scaling of ModUp's inverse NTT
+    u64 *down_scale = nullptr;         // [2K] + [2K] Shoup: n^-1 (P/p_k)^-1 mod p_k for the desc_p2 batch
 };
 // digits[j][t][k] for t outside digit j <- base conversion of coef (coefficient domain, ell limbs);
 // own-digit limbs <- copy of c_eval.
 void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits,
              cudaStream_t st);
+// tensor-core variants (baseconv.cu): inputs pre-scaled by the inverse NTT (DevicePlan::up_scale / down_scale)
+void k_modup_tc(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits, cudaStream_t st);
+void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st);
 // acc[2][width][n] = sum_j digits[j] * evk[j][{b,a}]   (evk stored at full chain: [digit][2][F][n])
 void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc,
                      cudaStream_t st);

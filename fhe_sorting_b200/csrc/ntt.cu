@@ -315,7 +315,8 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
 }
 
 __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu) {
+                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu,
+                                                 const u64 *__restrict__ custom) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -378,7 +379,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
     else fp_inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, qinv);
     const uint32_t st = g_step(G, p);
     if (last) {
-        const double ni = (double)T.ninv[qp];
+        const double ni = (double)(custom ? custom[blockIdx.y] : T.ninv[qp]);
 #pragma unroll
         for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = fp_to_u64(fp_mulmod(v[k], ni, qinv, q), q, qinv);
     } else {
@@ -402,7 +403,8 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass(DeviceTab
 // scale: multiply by n^-1 and reduce to [0,q) on the way out (last pass); otherwise values leave in [0,2q)
 template <bool LAZY>
 __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                              const uint32_t d, const PassGeom &G, int scale, u64 *sm) {
+                                              const uint32_t d, const PassGeom &G, int scale, u64 *sm,
+                                              const u64 *__restrict__ custom) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
@@ -444,7 +446,7 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
     else if (c_last == 2) inv_chunk<2, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     else inv_chunk<3, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     if (scale) {
-        const u64 ni = T.ninv[qp], nis = T.ninv[T.F + qp];
+        const u64 ni = custom ? custom[blockIdx.y] : T.ninv[qp], nis = custom ? custom[gridDim.y + blockIdx.y] : T.ninv[T.F + qp];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = shoup_mul(v[k], ni, nis, q);
     }
@@ -454,12 +456,13 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
 }
 
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                             const uint32_t *__restrict__ desc, PassGeom G, int first, int scale) {
+                                                             const uint32_t *__restrict__ desc, PassGeom G, int first, int scale,
+                                                             const u64 *__restrict__ custom) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom);
 }
 
 // Compile-time geometry for the production ring (n = 2^17): every shift, stride and loop trip count of the pass bodies
@@ -476,13 +479,14 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_c(DeviceT
 }
 template <int LOGN, int S, int S0, int LC, int PA>
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                                  const uint32_t *__restrict__ desc, int first, int scale) {
+                                                                  const uint32_t *__restrict__ desc, int first, int scale,
+                                                                  const u64 *__restrict__ custom) {
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom);
 }
 
 static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
@@ -517,7 +521,10 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     }
     g_launches++, ntt_fwd_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, A.S == 0, 1);
 }
-void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st) {
+// custom (optional): [count] scalars + [count] Shoup companions replacing n^-1 in the final scaling, one per batch entry
+// (ModUp / ModDown fold their (Q_j/q_i)^-1 factors into it)
+void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st,
+               const u64 *custom) {
     if (count <= 0) return;
     PassGeom A, B;
     int tile;
@@ -525,12 +532,12 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (T.logn == 17) {
-        g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
-        g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
+        g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0, custom);
+        g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1, custom);
         return;
     }
-    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0);
-    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1);
+    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0, custom);
+    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1, custom);
 }
 
 } // namespace fheb200

@@ -13,7 +13,7 @@ ctx.eval_mult_keygen(keys)
 import numpy as np  # noqa: E402
 ct = ctx.encrypt(keys, ctx.make_plaintext(np.linspace(-1, 1, 1024), 1, 0, 1024))
 out = {"tag": sys.argv[1] if len(sys.argv) > 1 else ""}
-for name in ("ntt_fwd", "ntt_inv", "inner_product", "modup_conv", "moddown_conv"):
+for name in ("ntt_fwd", "ntt_inv", "inner_product", "modup_conv", "moddown_conv", "modup_conv_scalar", "moddown_conv_scalar"):
     ctx.bench_kernel(name, 41, 5)
     ms, b = ctx.bench_kernel(name, 41, 50)
     out[name + "_us"] = round(1e3 * ms / 50, 2)
