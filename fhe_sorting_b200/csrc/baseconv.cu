@@ -13,7 +13,8 @@
 // K = (source, byte) in groups of 32 = 4 sources x 8 bytes, N = 8 targets; one accumulator tile per byte plane.  The A
 // fragments are simply the 32-bit halves of the u64 coefficients as they lie in HBM (no byte shuffling); the B fragments
 // are precomputed per lane (engine_ctx.cu: make_conv_table) and stay L1 resident.  The planes of one output sit in one
-// lane, so the recombination is lane-local: 6 planes fit a u64 (one single-word Barrett), 8 planes take the 128-bit path.
+// lane, so the recombination is lane-local, and because the quotient of the recombined value by p_t is below 2^16 the
+// reduction is one 32 x 32 multiplication for the quotient and one 17 x 64 for the remainder.
 // Measured on B200 (tools/ubench_mma.cu): 572 TMAC/s for this MMA shape, i.e. ~25 us for the 14 GMAC of one ModUp at 41
 // limbs; the kernel is bound by the epilogue and the 160 MB it moves instead.
 #include <stdexcept>
@@ -31,11 +32,32 @@ __device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], 
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 
-// sum_b s[b] 2^(8b), s[b] < 2^23: planes 0..5 -> one u64 (< 2^64 whenever the true value is, i.e. 6-plane targets)
-__device__ __forceinline__ u64 combine6(int s0, int s1, int s2, int s3, int s4, int s5) {
-    const u64 lo = (u64)(uint32_t)s0 + ((u64)(uint32_t)s1 << 8) + ((u64)(uint32_t)s2 << 16) + ((u64)(uint32_t)s3 << 24);
-    const u64 hi = (u64)(uint32_t)s4 + ((u64)(uint32_t)s5 << 8);
-    return lo + (hi << 32);
+// Recombination and reduction of one output.  The planes s[b] < 2^24 give V = sum_b s[b] 2^(8b) = sum over (source,
+// byte) terms of (byte < 2^8) * (constant < p), so V / p < 2^16 whatever the size of p: the quotient comes from one 32 x 32
+// multiplication of the top bits of V with mu = floor(2^(bits+31) / p) and is at most one short.
+//   tc = (p lo, p hi, mu, bits)
+__device__ __forceinline__ u64 planes_lo(const int (&s)[8]) { // s0 + s1 2^8 + s2 2^16 + s3 2^24 (< 2^49)
+    return mad_wide((uint32_t)s[3], 1u << 24, mad_wide((uint32_t)s[2], 1u << 16, mad_wide((uint32_t)s[1], 1u << 8, (u64)(uint32_t)s[0])));
+}
+__device__ __forceinline__ u64 finish6(const int (&s)[8], const uint4 tc) { // planes 0..5, p < 2^48: V < 2^64
+    const u64 hi = mad_wide((uint32_t)s[5], 1u << 8, (u64)(uint32_t)s[4]);
+    const u64 v = planes_lo(s) + (hi << 32);
+    const u64 p = ((u64)tc.y << 32) | tc.x;
+    const uint32_t top = (uint32_t)(v >> (tc.w - 16));
+    const uint32_t qe = (uint32_t)(((u64)top * tc.z) >> 47);
+    const u64 r = v - (u64)qe * p;
+    return r >= p ? r - p : r;
+}
+__device__ __forceinline__ u64 finish8(const int (&s)[8], const uint4 tc) { // planes 0..7, 2^48 < p < 2^63: V < 2^79
+    const u64 lo = planes_lo(s);
+    const u64 hi = mad_wide((uint32_t)s[7], 1u << 24, mad_wide((uint32_t)s[6], 1u << 16, mad_wide((uint32_t)s[5], 1u << 8, (u64)(uint32_t)s[4])));
+    const u64 p = ((u64)tc.y << 32) | tc.x;
+    const u64 v_hi32 = hi + (lo >> 32);                 // V >> 32
+    const u64 v_lo = lo + (hi << 32);                   // V mod 2^64
+    const uint32_t top = (uint32_t)(v_hi32 >> (tc.w - 48));
+    const uint32_t qe = (uint32_t)(((u64)top * tc.z) >> 47);
+    const u64 r = v_lo - (u64)qe * p;                   // V - qe p < 2 p < 2^64: the low words suffice
+    return r >= p ? r - p : r;
 }
 
 template <int KS>
@@ -90,25 +112,17 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
             const int tp = 8 * nt + 2 * tq + cpar;
             const int slot = __ldg(C.tslot + tp);
             if (slot < 0) continue;
-            const ModConst m = T.mc[__ldg(C.tqp + tp)];
+            const uint4 tc = __ldg(C.tconst + tp);
             u64 *o = I.dst + (size_t)slot * n + coef0 + g;
 #pragma unroll
             for (int mt = 0; mt < 2; mt++)
 #pragma unroll
                 for (int rh = 0; rh < 2; rh++) {
                     const int i = 2 * rh + cpar;
-                    const u64 lo = combine6(acc[0][mt][i], acc[1][mt][i], acc[2][mt][i], acc[3][mt][i], acc[4][mt][i], acc[5][mt][i]);
-                    u64 r;
-                    if (np > 6) { // + (s6 2^48 + s7 2^56): up to ~2^80
-                        const u64 top = (u64)(uint32_t)acc[6][mt][i] + ((u64)(uint32_t)acc[7][mt][i] << 8); // * 2^48
-                        const u64 add = top << 48;
-                        const u64 l2 = lo + add;
-                        const u64 h2 = (top >> 16) + (l2 < add);
-                        r = reduce128(h2, l2, m);
-                    } else {
-                        r = reduce64(lo, m);
-                    }
-                    o[16 * mt + 8 * rh] = r;
+                    int sv[8];
+#pragma unroll
+                    for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][i];
+                    o[16 * mt + 8 * rh] = tc.w > 48 ? finish8(sv, tc) : finish6(sv, tc); // a tile can mix both kinds
                 }
         }
     }

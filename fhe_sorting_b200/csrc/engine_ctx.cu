@@ -194,7 +194,15 @@ const DevicePlan &Context::plan(int ell) {
                 }
         t.B = (const uint2 *)owned_alloc(sizeof(uint32_t) * B.size(), B.data());
         t.tslot = (const int *)owned_alloc(sizeof(int) * tslot.size(), tslot.data());
-        t.tqp = (const int *)owned_alloc(sizeof(int) * tqp.size(), tqp.data());
+        std::vector<uint32_t> tconst(tqp.size() * 4, 0);
+        for (size_t c = 0; c < order.size(); c++) {
+            const u64 p = P->moduli[tqp[c]];
+            const int bits = bits_of(tqp[c]);
+            if (bits < 17 || bits > 62) throw std::runtime_error("fheb200: modulus size outside the base conversion's range");
+            tconst[4 * c] = (uint32_t)p, tconst[4 * c + 1] = (uint32_t)(p >> 32);
+            tconst[4 * c + 2] = (uint32_t)(((u128)1 << (bits + 31)) / p), tconst[4 * c + 3] = (uint32_t)bits;
+        }
+        t.tconst = (const uint4 *)owned_alloc(sizeof(uint32_t) * tconst.size(), tconst.data());
         t.planes = (const unsigned char *)owned_alloc(planes.size(), planes.data());
         return t;
     };

@@ -73,7 +73,7 @@ void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *
 struct ConvTable {
     const uint2 *B = nullptr;    // [KS][NT][8 planes][32 lanes] per-lane B fragments (bytes of C[j][t] 2^(8a) mod p_t)
     const int *tslot = nullptr;  // [NT * 8] output limb slot of each target column, -1 = padding
-    const int *tqp = nullptr;    // [NT * 8] modulus index of each target column
+    const uint4 *tconst = nullptr; // [NT * 8] (p lo, p hi, floor(2^(bits+31) / p), bits) of each target column
     const unsigned char *planes = nullptr; // [NT] 6 or 8 byte planes
     int nsrc = 0, KS = 0, NT = 0;
 };
