@@ -102,8 +102,22 @@ __global__ void __launch_bounds__(KS_THREADS) ks_inner(DeviceTables T, DevicePla
     if (k >= n) return;
     const int W = P.width, qp = P.qp[t], F = T.F;
     const ModConst m = T.mc[qp];
-    u64 sb[4] = {0, 0, 0, 0}, sa[4] = {0, 0, 0, 0}; // ll, lh, hl, hh
     const u64 *dp = digits + (size_t)t * n + k, *kp = evk + (size_t)qp * n + k;
+    if (fp_modulus_ok(m)) { // 40..42-bit scaling primes: 6 DP instructions per exact product instead of ~40 integer ones
+        const double2 qd = T.qd[qp];
+        double fb = 0.0, fa = 0.0;
+#pragma unroll 3
+        for (int j = 0; j < P.beta; j++) {
+            const double dv = fp_from_u64(dp[(size_t)j * W * n]);
+            const double kb = fp_from_u64(__ldcs(kp + (size_t)(2 * j) * F * n)), ka = fp_from_u64(__ldcs(kp + (size_t)(2 * j + 1) * F * n));
+            fb = __dadd_rn(fb, fp_mulmod(dv, kb, qd.y, qd.x));
+            fa = __dadd_rn(fa, fp_mulmod(dv, ka, qd.y, qd.x));
+        }
+        acc[((size_t)0 * W + t) * n + k] = fp_to_u64(fb, qd.x, qd.y);
+        acc[((size_t)1 * W + t) * n + k] = fp_to_u64(fa, qd.x, qd.y);
+        return;
+    }
+    u64 sb[4] = {0, 0, 0, 0}, sa[4] = {0, 0, 0, 0}; // ll, lh, hl, hh
 #pragma unroll 3
     for (int j = 0; j < P.beta; j++) {
         const u64 dv = dp[(size_t)j * W * n];

@@ -83,6 +83,32 @@ __device__ __forceinline__ u64 switch_modulus(u64 x, u64 q_from, u64 half, const
     return reduce64(x, to);
 }
 
+// ---- exact modular arithmetic in double precision for moduli of at most 42 bits (see ntt.cu, "FP64 path"): values are
+// exact signed integers held in doubles, a product is 6 DP instructions
+constexpr double FP_MAGIC = 6755399441055744.0; // 1.5 * 2^52: (x + M) - M rounds |x| < 2^51 to the nearest integer
+constexpr double FP_2P52 = 4503599627370496.0;
+__device__ __forceinline__ double fp_rint(double x) { return __dadd_rn(__dadd_rn(x, FP_MAGIC), -FP_MAGIC); }
+__device__ __forceinline__ double fp_mulmod(double y, double w, double qinv, double q) {
+    const double h = __dmul_rn(y, w);
+    const double l = __fma_rn(y, w, -h);
+    const double c = __dadd_rn(__fma_rn(h, qinv, FP_MAGIC), -FP_MAGIC); // rint(h / q), off by at most one from rint(y w / q)
+    const double d = __fma_rn(-c, q, h);
+    return __dadd_rn(d, l);
+}
+__device__ __forceinline__ double fp_center(double v, double q, double qinv) { // v - q*rint(v/q), |result| <= q/2 + 1
+    return __fma_rn(-fp_rint(__dmul_rn(v, qinv)), q, v);
+}
+__device__ __forceinline__ double fp_from_u64(u64 x) { // exact for x < 2^52
+    return __dadd_rn(__longlong_as_double((long long)(x | 0x4330000000000000ull)), -FP_2P52);
+}
+__device__ __forceinline__ u64 fp_to_u64(double v, double q, double qinv) { // any |v| < 2^51 -> [0, q)
+    double r = fp_center(v, q, qinv);
+    r = r < 0.0 ? __dadd_rn(r, q) : r;
+    r = r >= q ? __dadd_rn(r, -q) : r;
+    return (u64)__double_as_longlong(__dadd_rn(r, FP_2P52)) & 0x000fffffffffffffull;
+}
+__device__ __forceinline__ bool fp_modulus_ok(const ModConst &m) { return m.bits <= 42; }
+
 // counter-based generator shared with the oracle (spec: DESIGN.md "Randomness")
 __host__ __device__ __forceinline__ u64 mix64(u64 z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;

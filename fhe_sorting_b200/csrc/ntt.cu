@@ -183,28 +183,6 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
 // (6 DP instructions, no per-twiddle companion value to load or compute)
 // g == y*w (mod q) and |g| < 0.7 q for |y| < 2^50 (emulated exhaustively in tests/test_fp_modmul.py).  No conditional
 // corrections inside the butterflies: forward values grow by < q per stage, inverse sums are re-centred every <= 8 stages.
-constexpr double FP_MAGIC = 6755399441055744.0; // 1.5 * 2^52: (x + M) - M rounds |x| < 2^51 to the nearest integer
-constexpr double FP_2P52 = 4503599627370496.0;
-__device__ __forceinline__ double fp_rint(double x) { return __dadd_rn(__dadd_rn(x, FP_MAGIC), -FP_MAGIC); }
-__device__ __forceinline__ double fp_mulmod(double y, double w, double qinv, double q) {
-    const double h = __dmul_rn(y, w);
-    const double l = __fma_rn(y, w, -h);
-    const double c = __dadd_rn(__fma_rn(h, qinv, FP_MAGIC), -FP_MAGIC); // rint(h / q), off by at most one from rint(y w / q)
-    const double d = __fma_rn(-c, q, h);
-    return __dadd_rn(d, l);
-}
-__device__ __forceinline__ double fp_center(double v, double q, double qinv) { // v - q*rint(v/q), |result| <= q/2 + 1
-    return __fma_rn(-fp_rint(__dmul_rn(v, qinv)), q, v);
-}
-__device__ __forceinline__ double fp_from_u64(u64 x) { // exact for x < 2^52
-    return __dadd_rn(__longlong_as_double((long long)(x | 0x4330000000000000ull)), -FP_2P52);
-}
-__device__ __forceinline__ u64 fp_to_u64(double v, double q, double qinv) { // any |v| < 2^51 -> [0, q)
-    double r = fp_center(v, q, qinv);
-    r = r < 0.0 ? __dadd_rn(r, q) : r;
-    r = r >= q ? __dadd_rn(r, -q) : r;
-    return (u64)__double_as_longlong(__dadd_rn(r, FP_2P52)) & 0x000fffffffffffffull;
-}
 __device__ __forceinline__ void fp_ct(double &x, double &y, double w, double qinv, double q) {
     const double g = fp_mulmod(y, w, qinv, q);
     y = __dadd_rn(x, -g);
