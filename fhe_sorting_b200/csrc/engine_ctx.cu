@@ -147,14 +147,16 @@ const DevicePlan &Context::plan(int ell) {
     D.p_inv = up64(H.p_inv), D.p_inv_s = up64(H.p_inv_s);
     std::vector<uint32_t> dq, dm, dp2, dq2;
     for (int i = 0; i < ell; i++) dq.push_back(((uint32_t)i << 8) | (uint32_t)i);
-    for (int j = 0; j < H.beta; j++)
-        for (int t = 0; t < H.width; t++)
+    // batch order = launch order of the CTAs: limbs of equal modulus are adjacent so that their twiddles are read from
+    // HBM once and then hit in L2
+    for (int t = 0; t < H.width; t++)
+        for (int j = 0; j < H.beta; j++)
             if (t < H.dstart[j] || t >= H.dstart[j] + H.dsize[j])
                 dm.push_back(((uint32_t)(j * H.width + t) << 8) | (uint32_t)H.qp[t]);
-    for (int b = 0; b < 2; b++) {
-        for (int k = 0; k < P->K; k++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
-        for (int i = 0; i < ell; i++) dq2.push_back(((uint32_t)(b * ell + i) << 8) | (uint32_t)i);
-    }
+    for (int k = 0; k < P->K; k++) // (same order as DevicePlan::down_scale)
+        for (int b = 0; b < 2; b++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
+    for (int i = 0; i < ell; i++)
+        for (int b = 0; b < 2; b++) dq2.push_back(((uint32_t)(b * ell + i) << 8) | (uint32_t)i);
     // ---- tensor-core base conversion tables (baseconv.cu)
     typedef unsigned __int128 u128;
     auto bits_of = [&](int qp) { return P->mc[qp].bits; };
@@ -226,11 +228,11 @@ const DevicePlan &Context::plan(int ell) {
         std::vector<int> tpos;
         for (int i = 0; i < ell; i++) tg.push_back({i, i}), tpos.push_back(i);
         D.down = make_conv_table(H.p_hat, ell, P->K, tg, tpos);
-        for (int b = 0; b < 2; b++)
-            for (int k = 0; k < P->K; k++) {
+        for (int k = 0; k < P->K; k++)
+            for (int b = 0; b < 2; b++) { // entry order of desc_p2
                 const u64 q = P->moduli[P->L + k];
                 const u64 v = mulmod(P->n_inv[P->L + k], H.p_hat_inv[k], q);
-                down[b * P->K + k] = v, down[2 * P->K + b * P->K + k] = shoup_of(v, q);
+                down[2 * k + b] = v, down[2 * P->K + 2 * k + b] = shoup_of(v, q);
             }
         D.up_scale = (u64 *)owned_alloc(sizeof(u64) * up.size(), up.data());
         D.down_scale = (u64 *)owned_alloc(sizeof(u64) * down.size(), down.data());

@@ -115,10 +115,9 @@ void Context::rescale_poly(int ell, int npoly, const u64 *in, u64 *out) {
     // the dropped limb of poly p goes through the inverse NTT straight out of `in` (slot p * ell of both views)
     Mem last = alloc(((size_t)(npoly - 1) * ell + 1) * n), tmp = alloc((size_t)npoly * (ell - 1) * n);
     std::vector<uint32_t> dl, dt;
-    for (int p = 0; p < npoly; p++) {
-        dl.push_back(((uint32_t)(p * ell) << 8) | (uint32_t)(ell - 1));
-        for (int i = 0; i < ell - 1; i++) dt.push_back(((uint32_t)(p * (ell - 1) + i) << 8) | (uint32_t)i);
-    }
+    for (int p = 0; p < npoly; p++) dl.push_back(((uint32_t)(p * ell) << 8) | (uint32_t)(ell - 1));
+    for (int i = 0; i < ell - 1; i++) // limb-major: the polys' limbs of one modulus share their twiddles in L2
+        for (int p = 0; p < npoly; p++) dt.push_back(((uint32_t)(p * (ell - 1) + i) << 8) | (uint32_t)i);
     k_ntt_inv(T, in + (size_t)(ell - 1) * n, last->p, desc(dl), npoly, stream);
     k_rescale_lift(T, ell, npoly, last->p, (size_t)ell * n, tmp->p, stream);
     k_ntt_fwd(T, tmp->p, desc(dt), npoly * (ell - 1), stream);
