@@ -114,16 +114,28 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
             if (slot < 0) continue;
             const uint4 tc = __ldg(C.tconst + tp);
             u64 *o = I.dst + (size_t)slot * n + coef0 + g;
+            // a real branch (not a select): a tile is all-wide or all-narrow except for at most one mixed tile per table
+            if (tc.w > 48) {
 #pragma unroll
-            for (int mt = 0; mt < 2; mt++)
+                for (int mt = 0; mt < 2; mt++)
 #pragma unroll
-                for (int rh = 0; rh < 2; rh++) {
-                    const int i = 2 * rh + cpar;
-                    int sv[8];
+                    for (int rh = 0; rh < 2; rh++) {
+                        int sv[8];
 #pragma unroll
-                    for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][i];
-                    o[16 * mt + 8 * rh] = tc.w > 48 ? finish8(sv, tc) : finish6(sv, tc); // a tile can mix both kinds
-                }
+                        for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                        o[16 * mt + 8 * rh] = finish8(sv, tc);
+                    }
+            } else {
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int rh = 0; rh < 2; rh++) {
+                        int sv[8];
+#pragma unroll
+                        for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                        o[16 * mt + 8 * rh] = finish6(sv, tc);
+                    }
+            }
         }
     }
 

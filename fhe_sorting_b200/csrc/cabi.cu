@@ -53,7 +53,8 @@ struct OpTrace {
     }
     ~OpTrace() {
         if (!on) return;
-        cudaDeviceSynchronize();
+        static const bool host_only = [] { const char *e = getenv("FHEB200_TRACE"); return e && *e == '2'; }();
+        if (!host_only) cudaDeviceSynchronize(); // FHEB200_TRACE=2: time spent in the call by the launching thread only
         double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         std::lock_guard<std::mutex> g(g_trace_mu);
         TraceRow &r = g_trace[name];

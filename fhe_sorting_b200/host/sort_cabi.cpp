@@ -3,6 +3,8 @@
 // rotation / relinearisation keys resident in HBM, a DebugEncryption and a DirectSort<N>.
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -249,6 +251,12 @@ int fhesort_run(fhesort_session *s, int which, const double *input, const double
             if (!aux) throw std::invalid_argument("null argument: aux (ranks)");
             r = S.place(S.enc->encryptInput(std::vector<double>(aux, aux + S.len)), ct);
         } else throw std::invalid_argument("fhesort_run: unknown stage");
+        if (getenv("FHESORT_TIMING")) { // how far the launching thread runs ahead of the GPU
+            double host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            S.cc->Sync();
+            double gpu_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            fprintf(stderr, "fhesort_run: all work enqueued after %.1f ms, GPU done after %.1f ms\n", host_ms, gpu_ms);
+        }
         std::vector<double> v = S.enc->getPlaintext(r, 0.0); // decrypt synchronises the stream
         double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         for (int i = 0; i < S.len; i++) output[i] = i < (int)v.size() ? v[i] : 0.0;
