@@ -24,7 +24,14 @@
 
 namespace fheb200 {
 
-constexpr int BC_WARPS = 4; // 128 threads, 32 coefficients per warp
+#ifndef BC_MT_V
+#define BC_MT_V 2
+#endif
+#ifndef BC_WARPS_V
+#define BC_WARPS_V 4
+#endif
+constexpr int BC_WARPS = BC_WARPS_V; // warps per CTA
+constexpr int BC_MT = BC_MT_V;       // 16-coefficient M tiles per warp (B fragments are loaded once per BC_MT MMAs)
 
 __device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], const uint2 b) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -64,12 +71,12 @@ template <int KS>
 __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, ConvArgs A) {
     const ConvInstance I = A.inst[blockIdx.y];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, tq = lane & 3, n = T.n;
-    const int coef0 = (blockIdx.x * BC_WARPS + warp) * 32;
+    const int coef0 = (blockIdx.x * BC_WARPS + warp) * (16 * BC_MT);
     if (coef0 >= n) return;
     const ConvTable &C = I.tab;
 
     // A fragments: lane (g, tq) holds the (tq & 1) half of sources 4 ks + (tq >> 1) and + 2, rows g and g + 8 of each M tile
-    uint32_t a[2][KS][4];
+    uint32_t a[BC_MT][KS][4];
     {
         const uint32_t *s32 = reinterpret_cast<const uint32_t *>(I.src);
         const int half = tq & 1;
@@ -77,7 +84,7 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
         for (int ks = 0; ks < KS; ks++) {
             const int s0 = 4 * ks + (tq >> 1), s1 = s0 + 2;
 #pragma unroll
-            for (int mt = 0; mt < 2; mt++) {
+            for (int mt = 0; mt < BC_MT; mt++) {
                 const size_t r0 = (size_t)(coef0 + 16 * mt + g), r1 = r0 + 8;
                 a[mt][ks][0] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r0) + half] : 0u;
                 a[mt][ks][1] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r1) + half] : 0u;
@@ -88,11 +95,11 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
     }
 
     for (int nt = 0; nt < C.NT; nt++) {
-        int acc[8][2][4];
+        int acc[8][BC_MT][4];
 #pragma unroll
         for (int b = 0; b < 8; b++)
 #pragma unroll
-            for (int mt = 0; mt < 2; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
+            for (int mt = 0; mt < BC_MT; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
         const int np = C.planes[nt];
 #pragma unroll
         for (int ks = 0; ks < KS; ks++) {
@@ -101,8 +108,8 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
             for (int b = 0; b < 8; b++) {
                 if (b < 6 || np > 6) { // planes 6, 7 only exist for targets above 48 bits (uniform branch)
                     const uint2 bf = __ldg(bp + b * 32);
-                    imma_16832(acc[b][0], a[0][ks], bf);
-                    imma_16832(acc[b][1], a[1][ks], bf);
+#pragma unroll
+                    for (int mt = 0; mt < BC_MT; mt++) imma_16832(acc[b][mt], a[mt][ks], bf);
                 }
             }
         }
@@ -117,7 +124,7 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
             // a real branch (not a select): a tile is all-wide or all-narrow except for at most one mixed tile per table
             if (tc.w > 48) {
 #pragma unroll
-                for (int mt = 0; mt < 2; mt++)
+                for (int mt = 0; mt < BC_MT; mt++)
 #pragma unroll
                     for (int rh = 0; rh < 2; rh++) {
                         int sv[8];
@@ -127,7 +134,7 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
                     }
             } else {
 #pragma unroll
-                for (int mt = 0; mt < 2; mt++)
+                for (int mt = 0; mt < BC_MT; mt++)
 #pragma unroll
                     for (int rh = 0; rh < 2; rh++) {
                         int sv[8];
@@ -141,12 +148,13 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
 
     // ModUp: the digit's own limbs are the evaluation-domain input itself
     if (I.copy_limbs > 0) {
-        for (int t = 0; t < I.copy_limbs; t++) I.copy_dst[(size_t)t * n + coef0 + lane] = I.copy_src[(size_t)t * n + coef0 + lane];
+        if (lane < 16 * BC_MT)
+            for (int t = 0; t < I.copy_limbs; t++) I.copy_dst[(size_t)t * n + coef0 + lane] = I.copy_src[(size_t)t * n + coef0 + lane];
     }
 }
 
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
-    const dim3 grid((T.n + BC_WARPS * 32 - 1) / (BC_WARPS * 32), count);
+    const dim3 grid((T.n + BC_WARPS * 16 * BC_MT - 1) / (BC_WARPS * 16 * BC_MT), count);
     switch (KS) {
 #define CASE(k) case k: g_launches++, bc_convert<k><<<grid, BC_WARPS * 32, 0, st>>>(T, A); break;
         CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6)

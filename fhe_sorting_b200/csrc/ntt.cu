@@ -13,6 +13,9 @@
 // when limbs of equal modulus are adjacent in the batch).
 // Warp shuffles were considered for the 8x8 exchange between the last two radix-8 steps; 8 STS.64 + 8 LDS.64 per
 // thread is fewer issue slots than the 48 SHFL a 64-bit 8x8 lane transpose needs, so shared memory is used.
+#include <algorithm>
+#include <cstdlib>
+
 #include "kernels.h"
 #include "modarith.cuh"
 
@@ -294,7 +297,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
 
 __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu,
-                                                 const u64 *__restrict__ custom) {
+                                                 const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -382,7 +385,7 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass(DeviceTab
 template <bool LAZY>
 __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                               const uint32_t d, const PassGeom &G, int scale, u64 *sm,
-                                              const u64 *__restrict__ custom) {
+                                              const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
@@ -424,7 +427,7 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
     else if (c_last == 2) inv_chunk<2, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     else inv_chunk<3, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     if (scale) {
-        const u64 ni = custom ? custom[blockIdx.y] : T.ninv[qp], nis = custom ? custom[gridDim.y + blockIdx.y] : T.ninv[T.F + qp];
+        const u64 ni = custom ? custom[blockIdx.y] : T.ninv[qp], nis = custom ? custom_s[blockIdx.y] : T.ninv[T.F + qp];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = shoup_mul(v[k], ni, nis, q);
     }
@@ -435,12 +438,12 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
 
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                              const uint32_t *__restrict__ desc, PassGeom G, int first, int scale,
-                                                             const u64 *__restrict__ custom) {
+                                                             const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom, custom_s);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom, custom_s);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom, custom_s);
 }
 
 // Compile-time geometry for the production ring (n = 2^17): every shift, stride and loop trip count of the pass bodies
@@ -458,15 +461,23 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_c(DeviceT
 template <int LOGN, int S, int S0, int LC, int PA>
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                                   const uint32_t *__restrict__ desc, int first, int scale,
-                                                                  const u64 *__restrict__ custom) {
+                                                                  const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom, custom_s);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom, custom_s);
+    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom, custom_s);
 }
 
+static int ntt_group() { // limbs per launch pair at n = 2^17: everything unless FHEB200_NTT_GROUP says otherwise
+    static const int g = [] {
+        const char *e = getenv("FHEB200_NTT_GROUP");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? v : 1 << 20;
+    }();
+    return g;
+}
 static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
     const int logn = T.logn;
     if (logn <= NTT_TILE_LOG) {
@@ -489,8 +500,15 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (T.logn == 17) {
-        g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0);
-        g_launches++, ntt_fwd_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1);
+        // FHEB200_NTT_GROUP = g runs both passes over g limbs at a time so that the intermediate stays in L2.  Measured
+        // (profiles/r01/ntt_group_sweep.txt): slower for every g (41 limbs: 55.7 us ungrouped, 67.7 us at g = 24, 104 us at
+        // g = 8) - the passes are bound by the DP / issue pipes, not by HBM, and smaller launches only add tails.
+        const int group = ntt_group();
+        for (int c0 = 0; c0 < count; c0 += group) {
+            const dim3 gg(T.n / tile, std::min(group, count - c0));
+            g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0);
+            g_launches++, ntt_fwd_pass_c<17, 9, 8, 0, 0><<<gg, tile / 8, smem, st>>>(T, dst, dst, d_desc + c0, 0, 1);
+        }
         return;
     }
     if (A.S > 0) {
@@ -510,12 +528,21 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     if (T.logn == 17) {
-        g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, 1, 0, custom);
-        g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, 0, 1, custom);
+        const int group = ntt_group();
+        for (int c0 = 0; c0 < count; c0 += group) {
+            const int gc = std::min(group, count - c0);
+            const dim3 gg(T.n / tile, gc);
+            // custom scalars are indexed by blockIdx.y with the Shoup companions gridDim.y further on: hand each group its
+            // own window [c0, c0 + gc) + [count + c0, ...) through the two-pointer form
+            g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0, nullptr, nullptr);
+            g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<gg, tile / 8, smem, st>>>(
+                T, dst, dst, d_desc + c0, 0, 1, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
+        }
         return;
     }
-    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0, custom);
-    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1, custom);
+    const u64 *custom_s = custom ? custom + count : nullptr;
+    g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0, custom, custom_s);
+    if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1, custom, custom_s);
 }
 
 } // namespace fheb200
