@@ -105,6 +105,9 @@ int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *s) {
     })
 }
 int fheb200_ctx_sync(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->sync(); }) }
+int fheb200_ctx_fork(fheb200_ctx *ctx, int k) { GUARD({ need(ctx, "ctx"); ctx->c->fork(k); }) }
+int fheb200_ctx_use_stream(fheb200_ctx *ctx, int i) { GUARD({ need(ctx, "ctx"); ctx->c->use_stream(i); }) }
+int fheb200_ctx_join(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->join(); }) }
 int fheb200_ctx_info(fheb200_ctx *ctx, int *n, int *nq, int *np, int *alpha, int *batch) {
     GUARD({
         need(ctx, "ctx");

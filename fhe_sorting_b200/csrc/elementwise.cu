@@ -1,6 +1,8 @@
 // elementwise.cu — HBM-bound per-limb kernels: add/sub/mul, scalar ops, tensor product, plaintext product,
 // Galois automorphism gather, rescale lift/finish.  One thread handles two adjacent coefficients (128-bit
 // loads/stores); grid = (n / 2 / 256, limbs).  Algorithmic bytes per limb: 8n x (#inputs + #outputs).
+#include <stdexcept>
+
 #include "kernels.h"
 #include "modarith.cuh"
 
@@ -126,29 +128,45 @@ __global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, 
     st2(o, x, A);
 }
 
-// fused linear combination (Paterson-Stockmeyer leaves): each input coefficient is loaded once and feeds G accumulators
+// fused linear combination (Paterson-Stockmeyer leaves): each input coefficient is loaded once and feeds G accumulators.
+// The input pointer table and this limb's weights are staged in shared memory first, so the data loads of the main loop
+// do not hang off a pointer load each and can be issued eight at a time.
 template <int G>
 __global__ void __launch_bounds__(EW_THREADS) ew_lincomb(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
                                                          const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lsm[];
+    const u64 **ptr = reinterpret_cast<const u64 **>(lsm);
+    uint2 *wt = reinterpret_cast<uint2 *>(lsm + count); // [G][count]
     const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    for (int i = threadIdx.x; i < count; i += EW_THREADS) ptr[i] = in[i];
+    for (int i = threadIdx.x; i < G * count; i += EW_THREADS) wt[i] = __ldg(w + (size_t)i * ell + li);
+    __syncthreads();
     if (k >= n) return;
     const size_t idx = (size_t)blockIdx.y * n + k;
     u64 lo[G], hi[G];
 #pragma unroll
     for (int g = 0; g < G; g++) lo[g] = 0, hi[g] = 0;
-    for (int t0 = 0; t0 < count; t0 += 16) {
+    for (int t0 = 0; t0 < count; t0 += 16) { // 16 products of 30-bit halves fit a 64-bit partial sum
         u64 a0[G], a1[G], a2[G], a3[G];
 #pragma unroll
         for (int g = 0; g < G; g++) a0[g] = a1[g] = a2[g] = a3[g] = 0;
-        const int t1 = t0 + 16 < count ? t0 + 16 : count;
-        for (int t = t0; t < t1; t++) {
-            const u64 a = in[t][idx];
-            const uint32_t al = (uint32_t)a & 0x3fffffffu, ah = (uint32_t)(a >> 30);
 #pragma unroll
-            for (int g = 0; g < G; g++) {
-                const uint2 h = __ldg(w + ((size_t)g * count + t) * ell + li);
-                a0[g] = mad_wide(al, h.x, a0[g]), a1[g] = mad_wide(al, h.y, a1[g]);
-                a2[g] = mad_wide(ah, h.x, a2[g]), a3[g] = mad_wide(ah, h.y, a3[g]);
+        for (int h = 0; h < 16; h += 8) {
+            u64 a[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) a[u] = t0 + h + u < count ? ptr[t0 + h + u][idx] : 0;
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int t = t0 + h + u;
+                if (t < count) {
+                    const uint32_t al = (uint32_t)a[u] & 0x3fffffffu, ah = (uint32_t)(a[u] >> 30);
+#pragma unroll
+                    for (int g = 0; g < G; g++) {
+                        const uint2 hw = wt[g * count + t];
+                        a0[g] = mad_wide(al, hw.x, a0[g]), a1[g] = mad_wide(al, hw.y, a1[g]);
+                        a2[g] = mad_wide(ah, hw.x, a2[g]), a3[g] = mad_wide(ah, hw.y, a3[g]);
+                    }
+                }
             }
         }
 #pragma unroll
@@ -161,12 +179,14 @@ __global__ void __launch_bounds__(EW_THREADS) ew_lincomb(DeviceTables T, int ell
 void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
                u64 *const *out, cudaStream_t st) {
     dim3 grid((T.n + EW_THREADS - 1) / EW_THREADS, limbs2);
+    const size_t smem = sizeof(u64) * (size_t)count * (1 + G);
+    if (smem > 48 * 1024) throw std::invalid_argument("lincomb: too many inputs for one pass");
     g_launches++;
     switch (G) {
-    case 1: ew_lincomb<1><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
-    case 2: ew_lincomb<2><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
-    case 3: ew_lincomb<3><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
-    default: ew_lincomb<4><<<grid, EW_THREADS, 0, st>>>(T, ell, count, in, w, out); break;
+    case 1: ew_lincomb<1><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
+    case 2: ew_lincomb<2><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
+    case 3: ew_lincomb<3><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
+    default: ew_lincomb<4><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
     }
 }
 

@@ -25,6 +25,8 @@ struct DevMem { // stream-ordered device allocation owned by a context
     size_t words = 0;
     Context *ctx = nullptr;
     std::shared_ptr<Context> keep; // a buffer keeps its context (stream, memory pool) alive
+    cudaStream_t stream = nullptr; // the stream it was allocated on (and is freed on)
+    unsigned epoch = 0;            // Context::epoch at allocation (see Context::fork)
     ~DevMem();
 };
 typedef std::shared_ptr<DevMem> Mem;
@@ -137,6 +139,17 @@ class Context : public std::enable_shared_from_this<Context> {
     const uint32_t *desc(const std::vector<uint32_t> &d);
     Mem alloc(size_t words);
     void sync();
+    // ---- concurrent streams for independent sub-computations (the B batches of a DirectSort phase): fork(k) lets k
+    // side streams start from the main stream's current point, use_stream(i) directs every following call to side
+    // stream i, join() makes the main stream wait for all of them and goes back to it.  Rules the caller keeps:
+    // objects made inside the region are used on the stream that made them until join(); objects made before fork()
+    // are read-only inside.  Device-side caches hanging off shared objects are only trusted if usable().
+    void fork(int k);
+    void use_stream(int i);
+    void join();
+    bool forked() const { return forked_; }
+    bool usable(const Mem &m) const { return !forked_ || m->stream == stream || m->epoch < fork_epoch_; }
+    unsigned epoch = 1;
     u64 *evk_mult = nullptr;
     std::map<uint32_t, u64 *> evk_rot;
     size_t evk_words() const { return (size_t)P->beta(P->L) * 2 * (P->L + P->K) * P->n; }
@@ -159,6 +172,14 @@ class Context : public std::enable_shared_from_this<Context> {
     LimbScalars scalars_for(long double value, int ell, bool shoup) const;
 
   private:
+    friend struct DevMem;
+    cudaStream_t main_stream_ = nullptr;
+    std::vector<cudaStream_t> side_;
+    std::vector<cudaEvent_t> side_done_;
+    cudaEvent_t fork_ev_ = nullptr, free_ev_ = nullptr;
+    bool forked_ = false;
+    int fork_k_ = 0;
+    unsigned fork_epoch_ = 0;
     // pinned staging ring for host -> device uploads of slot values: the host never waits for the stream unless it is a
     // whole ring ahead of it (a pageable cudaMemcpyAsync would stall the launching thread at every plaintext)
     struct Stage { void *host = nullptr; cudaEvent_t done = nullptr; };

@@ -102,9 +102,9 @@ Ct Context::add_many(const std::vector<Ct> &v) {
 }
 
 Mem Context::encoding_for(const Pt &pt, int ell, double scale) {
-    if (pt->mem && pt->ell == ell && pt->scale == scale) return pt->mem;
+    if (pt->mem && pt->ell == ell && pt->scale == scale && usable(pt->mem)) return pt->mem;
     for (auto &e : pt->alt)
-        if (std::get<0>(e) == ell && std::get<1>(e) == scale) return std::get<2>(e);
+        if (std::get<0>(e) == ell && std::get<1>(e) == scale && usable(std::get<2>(e))) return std::get<2>(e);
     Mem m = encode_at(*pt, ell, scale);
     if (pt->alt.size() >= 4) pt->alt.erase(pt->alt.begin());
     pt->alt.emplace_back(ell, scale, m);

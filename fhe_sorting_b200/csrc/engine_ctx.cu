@@ -10,7 +10,13 @@
 namespace fheb200 {
 
 DevMem::~DevMem() {
-    if (p && ctx) cudaFreeAsync(p, ctx->stream);
+    if (!p || !ctx) return;
+    cudaStream_t s = stream ? stream : ctx->stream;
+    if (s != ctx->stream && ctx->free_ev_) { // last used on another stream than the one it lives on: free after that use
+        cudaEventRecord(ctx->free_ev_, ctx->stream);
+        cudaStreamWaitEvent(s, ctx->free_ev_, 0);
+    }
+    cudaFreeAsync(p, s);
 }
 
 Mem Context::alloc(size_t words) {
@@ -18,10 +24,52 @@ Mem Context::alloc(size_t words) {
     m->ctx = this;
     m->keep = weak_from_this().lock(); // null only while the context is being constructed or destroyed
     m->words = words;
+    m->stream = stream, m->epoch = epoch;
     FHE_CUDA(cudaMallocAsync((void **)&m->p, words * sizeof(u64), stream));
     return m;
 }
-void Context::sync() { FHE_CUDA(cudaStreamSynchronize(stream)); }
+void Context::sync() {
+    FHE_CUDA(cudaStreamSynchronize(stream));
+    if (forked_)
+        for (int i = 0; i < fork_k_; i++) FHE_CUDA(cudaStreamSynchronize(side_[i]));
+}
+
+void Context::fork(int k) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (forked_) throw std::runtime_error("fork: already forked");
+    if (k < 1 || k > 16) throw std::invalid_argument("fork: 1..16 streams");
+    FHE_CUDA(cudaSetDevice(device));
+    if (!fork_ev_) {
+        FHE_CUDA(cudaEventCreateWithFlags(&fork_ev_, cudaEventDisableTiming));
+        FHE_CUDA(cudaEventCreateWithFlags(&free_ev_, cudaEventDisableTiming));
+    }
+    while ((int)side_.size() < k) {
+        cudaStream_t s;
+        cudaEvent_t e;
+        FHE_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        FHE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        side_.push_back(s), side_done_.push_back(e);
+    }
+    main_stream_ = stream;
+    FHE_CUDA(cudaEventRecord(fork_ev_, main_stream_));
+    for (int i = 0; i < k; i++) FHE_CUDA(cudaStreamWaitEvent(side_[i], fork_ev_, 0));
+    fork_k_ = k, forked_ = true, fork_epoch_ = ++epoch;
+}
+void Context::use_stream(int i) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!forked_) throw std::runtime_error("use_stream: not forked");
+    stream = i < 0 ? main_stream_ : side_[i % fork_k_];
+}
+void Context::join() {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!forked_) return;
+    for (int i = 0; i < fork_k_; i++) {
+        FHE_CUDA(cudaEventRecord(side_done_[i], side_[i]));
+        FHE_CUDA(cudaStreamWaitEvent(main_stream_, side_done_[i], 0));
+    }
+    stream = main_stream_;
+    forked_ = false, ++epoch;
+}
 
 void *Context::owned_alloc(size_t bytes, const void *init) {
     void *d = nullptr;
@@ -94,7 +142,13 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
 }
 
 Context::~Context() {
+    if (forked_) stream = main_stream_;
+    for (auto s : side_) cudaStreamSynchronize(s);
     if (stream) cudaStreamSynchronize(stream);
+    for (auto s : side_) cudaStreamDestroy(s);
+    for (auto e : side_done_) cudaEventDestroy(e);
+    if (fork_ev_) cudaEventDestroy(fork_ev_);
+    if (free_ev_) cudaEventDestroy(free_ev_), free_ev_ = nullptr;
     if (evk_mult) cudaFree(evk_mult);
     for (auto &kv : evk_rot) cudaFree(kv.second);
     for (void *p : owned_) cudaFree(p);

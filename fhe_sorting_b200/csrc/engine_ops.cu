@@ -135,9 +135,14 @@ Ct Context::mod_reduce(const Ct &a) {
 Ct Context::rescale(const Ct &a) { return mod_reduce(a); }
 Ct Context::reduced(const Ct &a) {
     LOCK;
-    if (!a->reduced_cache) a->reduced_cache = mod_reduce(a);
-    a->reduced_cache->slots = a->slots; // SetSlots may have been called on the handle since
-    return a->reduced_cache;
+    Ct r = a->reduced_cache;
+    if (!r || !usable(r->mem)) { // (inside a forked region a copy made by another stream may not be complete yet)
+        r = mod_reduce(a);
+        // kept for later calls unless `a` is shared with the other streams of a forked region
+        if (!forked() || a->mem->stream == stream) a->reduced_cache = r;
+    }
+    r->slots = a->slots; // SetSlots may have been called on the handle since
+    return r;
 }
 Ct Context::level_reduce(const Ct &a, int levels) {
     LOCK;

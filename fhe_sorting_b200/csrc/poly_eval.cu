@@ -11,21 +11,38 @@
 
 #include "engine.h"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 namespace fheb200 {
 
 typedef std::vector<double> Poly; // true Chebyshev coefficients: p = sum p[i] T_i
+
+namespace {
+struct HostTimer { // FHEB200_PSTIME=1: where the launching thread spends its time inside one Paterson-Stockmeyer evaluation
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    double lap() {
+        auto t = std::chrono::steady_clock::now();
+        double ms = std::chrono::duration<double, std::milli>(t - t0).count();
+        t0 = t;
+        return ms;
+    }
+};
+double g_split_ms = 0;
+} // namespace
+
 
 static int degree_of(const Poly &p) {
     int d = (int)p.size() - 1;
     while (d > 0 && p[d] == 0.0) d--;
     return d;
 }
-// r += w * T_j * g  in the Chebyshev basis: T_j T_i = (T_{i+j} + T_{|i-j|}) / 2
-static void add_shifted(Poly &r, double w, int j, const Poly &g) {
-    int dg = degree_of(g);
+// r += w * T_j * g  in the Chebyshev basis: T_j T_i = (T_{i+j} + T_{|i-j|}) / 2 ; nz = indices of g's non-zero entries
+static void add_shifted(Poly &r, double w, int j, const Poly &g, const std::vector<int> &nz) {
+    const int dg = nz.empty() ? 0 : nz.back();
     if ((int)r.size() < dg + j + 1) r.resize(dg + j + 1, 0.0);
-    for (int i = 0; i <= dg; i++) {
-        if (g[i] == 0.0) continue;
+    for (int i : nz) {
         if (j == 0) {
             r[i] += w * g[i];
         } else {
@@ -34,9 +51,14 @@ static void add_shifted(Poly &r, double w, int j, const Poly &g) {
         }
     }
 }
-// f = q g + r, deg r < deg g
+// f = q g + r, deg r < deg g.  The divisors of the Paterson-Stockmeyer recursion are either a single T_j or met once per
+// node, so the work is linear in the number of non-zero terms (a dense scan of g per quotient term made the host side
+// of a degree-6510 evaluation cost more than its 5700 kernel launches).
 static void cheb_divide(const Poly &f, const Poly &g, Poly &q, Poly &r) {
     int n = degree_of(f), k = degree_of(g);
+    std::vector<int> nz;
+    for (int i = 0; i <= k; i++)
+        if (g[i] != 0.0) nz.push_back(i);
     r = f;
     r.resize(n + 1);
     q.assign(n >= k ? n - k + 1 : 1, 0.0);
@@ -48,7 +70,7 @@ static void cheb_divide(const Poly &f, const Poly &g, Poly &q, Poly &r) {
         }
         double lead = (n > k) ? 2.0 * r[n] / g[k] : r[n] / g[k];
         q[n - k] = lead;
-        add_shifted(r, -lead, n - k, g);
+        add_shifted(r, -lead, n - k, g, nz);
         r[n] = 0.0; // exact cancellation of the leading term
         n--;
         if (n < 0) break;
@@ -141,7 +163,11 @@ static Ct eval_inner(PSState &S, const Poly &f, int m) {
     const int k = S.k;
     if (m == 1) return eval_leaf(S, f);
     Poly q, c, s2;
-    ps_split(k, m, f, q, c, s2);
+    {
+        HostTimer ts;
+        ps_split(k, m, f, q, c, s2);
+        g_split_ms += ts.lap();
+    }
     Ct cu = weighted_sum(S, c, k - 1);
     Ct qu = eval_inner(S, q, m - 1);
     Ct su = eval_inner(S, s2, m - 1);
@@ -207,6 +233,9 @@ Ct Context::eval_chebyshev_linear(const Ct &x, const std::vector<double> &coeffs
 
 Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, double a, double b) {
     std::lock_guard<std::recursive_mutex> g(mu);
+    static const bool pstime = getenv("FHEB200_PSTIME") != nullptr;
+    HostTimer tm;
+    double t_basis = 0, t_giant = 0, t_collect = 0, t_lincomb = 0;
     int n = degree_of(coeffs);
     if (n < 5) return eval_chebyshev_linear(x, coeffs, a, b);
     PSState S;
@@ -220,12 +249,14 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
         adjust_pair(t, d);
         S.T[i] = t;
     }
+    t_basis = tm.lap();
     S.T2.resize(m);
     S.T2[0] = S.T[k - 1];
     for (int i = 1; i < m; i++) S.T2[i] = add_const(double_ct(this, mult(S.T2[i - 1], S.T2[i - 1])), -1.0);
     // T_{k(2^m - 1)} by T_{a+b} = 2 T_a T_b - T_{a-b} with a = k 2^i, b = k(2^i - 1), a - b = k
     Ct T2km1 = S.T2[0];
     for (int i = 1; i < m; i++) T2km1 = sub(double_ct(this, mult(T2km1, S.T2[i])), S.T2[0]);
+    t_giant = tm.lap();
     Poly f(coeffs.begin(), coeffs.begin() + n + 1);
     f[0] /= 2.0; // the series convention is c_0/2 + sum c_i T_i
     const int top = k * ((1 << m) - 1);
@@ -234,14 +265,20 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
     if (k > 2) { // every weighted sum of T_1..T_{k-1} the recursion needs, four outputs per pass over the baby steps
         std::vector<Poly> req;
         ps_collect(k, m, f, req);
+        t_collect = tm.lap();
         std::vector<Ct> in(k - 1);
         for (int i = 0; i + 1 < k; i++) in[i] = S.reduced(i);
         std::vector<std::vector<double>> w(req.size(), std::vector<double>(k - 1, 0.0));
         for (size_t r = 0; r < req.size(); r++)
             for (int i = 1; i < k && i < (int)req[r].size(); i++) w[r][i - 1] = req[r][i];
         S.ready = lincomb(in, w);
+        t_lincomb = tm.lap();
     }
+    g_split_ms = 0;
     Ct r = eval_inner(S, f, m);
+    if (pstime)
+        fprintf(stderr, "PS deg %d k %d m %d ell %d: basis %.2f giant %.2f collect %.2f lincomb %.2f inner %.2f (splits %.2f) ms host, ends at launch %llu\n",
+                n, k, m, x->ell, t_basis, t_giant, t_collect, t_lincomb, tm.lap(), g_split_ms, (unsigned long long)g_launches.load());
     return sub(r, T2km1);
 }
 

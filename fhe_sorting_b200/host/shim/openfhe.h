@@ -349,6 +349,10 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         return wrap(o);
     }
     void Sync() { fheb200_check(fheb200_ctx_sync(ctx)); }
+    // Engine extension (not an OpenFHE call): concurrent streams for independent sub-computations, see fheb200_ctx_fork
+    void ForkStreams(int k) { fheb200_check(fheb200_ctx_fork(ctx, k)); }
+    void UseStream(int i) { fheb200_check(fheb200_ctx_use_stream(ctx, i)); }
+    void JoinStreams() { fheb200_check(fheb200_ctx_join(ctx)); }
     // Multi-GPU extension (not an OpenFHE call): sum a partial ciphertext over the ranks that share this job.  `reduce`
     // sums the device buffer in place across ranks as 64-bit integers (NCCL all-reduce supplied by the launcher).
     std::function<void(void *device_ptr, size_t words)> allReduceWords;

@@ -8,6 +8,7 @@
 //   * the rotation-key list is derived from the schedule instead of being tabulated (same sets as the reference's
 //     tables up to indices that are multiples of the slot count, i.e. identity rotations).
 #pragma once
+#include <cstdlib>
 #include <algorithm>
 #include <cmath>
 #include <iostream>
@@ -68,6 +69,35 @@ inline std::vector<int> DirectSortBatchesOf(int B, int rank, int world) {
     return mine;
 }
 
+// The B batches of a phase are independent chains of small kernels (at N = 1024 the Paterson-Stockmeyer evaluations run on
+// 4..17 limbs): one CUDA stream cannot fill 148 SMs with them.  The first batch runs on the main stream (it fills the
+// caches that hang off the shared inputs: memoised rescales, plans), the others round-robin over k side streams; the
+// destructor joins.  The reference reaches the same concurrency with OpenMP threads (src/sort_algo.h:475, 713).
+class BatchStreams {
+    CryptoContext<DCRTPoly> cc;
+    int k, seen = 0;
+    bool forked = false;
+
+  public:
+    BatchStreams(CryptoContext<DCRTPoly> c, int streams) : cc(c), k(streams) {}
+    BatchStreams(const BatchStreams &) = delete;
+    void next() { // call at the top of every batch
+        if (k > 1 && seen >= 1) {
+            if (!forked) cc->ForkStreams(k), forked = true;
+            cc->UseStream((seen - 1) % k);
+        }
+        seen++;
+    }
+    ~BatchStreams() {
+        if (forked) cc->JoinStreams();
+    }
+};
+inline int DirectSortDefaultStreams() {
+    const char *e = getenv("FHESORT_STREAMS");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? (v > 16 ? 16 : v) : 4;
+}
+
 template <int N> class DirectSort : public SortBase<N> {
     CryptoContext<DCRTPoly> m_cc;
     PublicKey<DCRTPoly> m_PublicKey;
@@ -78,6 +108,7 @@ template <int N> class DirectSort : public SortBase<N> {
 
     typedef Ciphertext<DCRTPoly> CT;
     int m_rank = 0, m_world = 1; // multi-GPU: this process evaluates the batches b with b % m_world == m_rank
+    int m_streams = DirectSortDefaultStreams(); // concurrent CUDA streams over this process's batches
 
     bool mine(int b, int B) const {
         for (int x : DirectSortBatchesOf(B, m_rank, m_world))
@@ -118,6 +149,7 @@ template <int N> class DirectSort : public SortBase<N> {
     // and output ciphertexts are summed with CryptoContextImpl::AllReduceSum.  Lengths with fewer batches than processes
     // (N <= 256 on ring 2^17: a single comparison ciphertext) run replicated.
     void setShard(int rank, int world) { m_rank = rank, m_world = world; }
+    void setStreams(int k) { m_streams = k < 1 ? 1 : k; }
 
     // multiplicative depth per array length (reference table sort_algo.h:94-198), scaling modulus 40 bits, batch N, and
     // the rotation indices the schedule below uses on a ring of dimension `ringDim`
@@ -206,16 +238,20 @@ template <int N> class DirectSort : public SortBase<N> {
     CT constructRank(const CT &input_array, SignFunc SignFunc, SignConfig &Cfg) {
         const DirectSortShape sh(N, max_batch);
         std::vector<CT> baby = babySteps(input_array, sh.np_rank, sh.S);
-        CT rank;
-        for (int b = 0; b < sh.B; b++) {
-            if (!mine(b, sh.B)) continue;
-            CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b);
-            CT dup = input_array->Clone();
-            dup->SetSlots(sh.S);
-            CT c = comp.compare(m_cc, dup, shifted, SignFunc, Cfg);
-            if (rank) m_cc->EvalAddInPlace(rank, c);
-            else rank = c;
+        std::vector<CT> parts;
+        {
+            BatchStreams streams(m_cc, m_streams);
+            for (int b = 0; b < sh.B; b++) {
+                if (!mine(b, sh.B)) continue;
+                streams.next();
+                CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b);
+                CT dup = input_array->Clone();
+                dup->SetSlots(sh.S);
+                parts.push_back(comp.compare(m_cc, dup, shifted, SignFunc, Cfg));
+            }
         }
+        CT rank = parts.size() == 1 ? parts[0] : m_cc->EvalAddMany(parts);
+        parts.clear();
         if (sharded(sh.B)) m_cc->AllReduceSum(rank);
         foldCopies(rank, sh.S, sh.P);
         rank->SetSlots(N);
@@ -251,9 +287,12 @@ template <int N> class DirectSort : public SortBase<N> {
         index_minus_rank->SetSlots(sh.S);
         input_array->SetSlots(sh.S);
         static const std::vector<double> &coeffs = selectDoubledSincCoefficients<N>();
-        CT output;
+        std::vector<CT> parts;
+        {
+            BatchStreams streams(m_cc, m_streams);
         for (int b = 0; b < sh.B; b++) {
             if (!mine(b, sh.B)) continue;
+            streams.next();
             auto chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(sh.S, b * sh.P), 1, index_minus_rank->GetLevel(),
                                                      nullptr, sh.S);
             CT r = m_cc->EvalSub(index_minus_rank, chk);
@@ -261,10 +300,11 @@ template <int N> class DirectSort : public SortBase<N> {
             r = m_cc->EvalChebyshevSeriesPS(r, coeffs, -1, 1);
             CT masked = m_cc->EvalMult(r, input_array);
             std::vector<CT> masked_inputs = babySteps(masked, sh.np_idx, sh.S);
-            CT placed = blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P);
-            if (output) m_cc->EvalAddInPlace(output, placed);
-            else output = placed;
+            parts.push_back(blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P));
         }
+        }
+        CT output = parts.size() == 1 ? parts[0] : m_cc->EvalAddMany(parts);
+        parts.clear();
         if (sharded(sh.B)) m_cc->AllReduceSum(output);
         foldCopies(output, sh.S, sh.P);
         output->SetSlots(N);

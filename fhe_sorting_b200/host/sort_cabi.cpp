@@ -42,6 +42,7 @@ struct SessionBase {
     virtual Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &rank, const Ciphertext<DCRTPoly> &in) = 0;
     virtual Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) = 0;
     virtual void shard(int rank, int world) = 0;
+    virtual void streams(int) {}
 };
 template <int N> struct Session : SessionBase {
     std::unique_ptr<DirectSort<N>> sorter;
@@ -62,6 +63,7 @@ template <int N> struct Session : SessionBase {
     }
 #else
     void shard(int rank, int world) override { sorter->setShard(rank, world); }
+    void streams(int k) override { sorter->setStreams(k); }
 #endif
 };
 
@@ -230,6 +232,13 @@ int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_a
                 if (fn(user, p, w) != 0) throw std::runtime_error("all-reduce callback failed");
             };
         else s->s->cc->allReduceWords = nullptr;
+    })
+}
+
+int fhesort_session_set_streams(fhesort_session *s, int k) {
+    GUARD({
+        if (!s) throw std::invalid_argument("null argument: session");
+        s->s->streams(k);
     })
 }
 

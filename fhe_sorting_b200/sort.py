@@ -70,6 +70,10 @@ class DirectSortSession:
         except Exception:
             pass
 
+    def set_streams(self, k):
+        """Concurrent CUDA streams over the independent batches of a phase (default 4)."""
+        _ck(self.L.fhesort_session_set_streams(self.h, int(k)), self.L)
+
     def set_shard(self, rank, world):
         """Shard the sort's batches over `world` ranks of an initialised torch.distributed NCCL group (one GPU each)."""
         if world <= 1:

@@ -48,6 +48,14 @@ int fheb200_ctx_release(fheb200_ctx *ctx);
 /* run every later operation of this context on an existing CUDA stream (cudaStream_t passed as void*) */
 int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *cuda_stream);
 int fheb200_ctx_sync(fheb200_ctx *ctx);
+/* Concurrent streams for independent sub-computations (the B batches of a DirectSort phase; not in OpenFHE, whose callers
+ * use OpenMP threads instead - src/sort_algo.h:475, 713).  fork(k): k side streams continue from the main stream's
+ * current point; use_stream(i): every following call runs on side stream i (i < 0: the main stream); join(): the main
+ * stream waits for all of them.  Objects made inside the region stay on the stream that made them until join(); objects
+ * made before fork() are read-only inside. */
+int fheb200_ctx_fork(fheb200_ctx *ctx, int k);
+int fheb200_ctx_use_stream(fheb200_ctx *ctx, int i);
+int fheb200_ctx_join(fheb200_ctx *ctx);
 /* GetRingDimension / GetCyclotomicOrder (src/rotation.h:262, src/sort_algo.h:80) and chain geometry */
 int fheb200_ctx_info(fheb200_ctx *ctx, int *ring_dim, int *num_q, int *num_p, int *digit_size, int *batch);
 int fheb200_ctx_modulus(fheb200_ctx *ctx, int qp_index, uint64_t *q, uint64_t *psi);

@@ -34,6 +34,8 @@ int fhesort_run(fhesort_session *s, int stage, const double *input, const double
  * all-reduce, SUM, int64) and return 0 after the result is visible to other streams. */
 typedef int (*fhesort_allreduce_fn)(void *user, void *device_ptr, size_t words);
 int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_allreduce_fn fn, void *user);
+/* Concurrent CUDA streams over the batches this process evaluates (default 4, or FHESORT_STREAMS; 1 = one stream). */
+int fhesort_session_set_streams(fhesort_session *s, int k);
 /* RotationComposer<N>::rotate (src/rotation.h:215-233) */
 int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output);
 /* host-only (no GPU needed) */

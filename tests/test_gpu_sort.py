@@ -82,3 +82,21 @@ def test_reference_drivers_unmodified_on_the_engine():
         assert level == level_ref
         assert np.abs(out - out_ref).max() < 1e-3
         assert np.abs(ranks - ranks_ref).max() < 1e-3
+
+
+def test_batches_on_concurrent_streams_match_one_stream():
+    """N = 128 on ring 2^13 has 4 independent batches per phase: running them on 4 CUDA streams (fork / join in the
+    engine) must give what one stream gives, up to the fresh encryption noise."""
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input
+    s = DirectSortSession(128, 13, seed=31)
+    x = uniform_gap_input(128, seed=8)
+    outs = {}
+    for k in (1, 4, 2, 4):
+        s.set_streams(k)
+        for rep in range(2):
+            out, _, level = s.sort(x)
+            assert np.abs(out - np.sort(x)).max() < 0.01 and level == s.mult_depth
+            outs.setdefault(k, []).append(out)
+    assert np.abs(outs[4][0] - outs[1][0]).max() < 1e-4
+    assert np.abs(outs[4][3] - outs[1][1]).max() < 1e-4
+    s.close()
