@@ -168,12 +168,25 @@ int fheb200_make_packed_plaintext(fheb200_ctx *ctx, const double *v, size_t coun
         *out = new fheb200_pt{ctx->c->make_plaintext_real(v, count, nsd, level, slots)};
     })
 }
+int fheb200_pt_rotate(fheb200_ctx *ctx, fheb200_pt *pt, int index, fheb200_pt **out) {
+    GUARD({ need(ctx, "ctx"); need(pt, "pt"); need(out, "out"); *out = new fheb200_pt{ctx->c->rotate_plaintext(pt->p, index)}; })
+}
 int fheb200_pt_release(fheb200_pt *pt) { GUARD({ delete pt; }) }
 int fheb200_pt_values(fheb200_pt *pt, double *out, size_t cap, size_t *count) {
     GUARD({
         need(pt, "pt");
-        const Plaintext &P = *pt->p;
-        size_t nv = std::min(P.length, P.real_only ? P.re.size() : P.vals.size());
+        const Plaintext &P = pt->p->base ? *pt->p->base : *pt->p;
+        const size_t have = P.real_only ? P.re.size() : P.vals.size();
+        if (pt->p->base) { // rotated view: slot i = slot (i + rot) mod slots of the base (missing entries are zero)
+            const long S = P.slots;
+            if (count) *count = (size_t)S;
+            for (long i = 0; i < S && (size_t)i < cap; i++) {
+                const size_t j = (size_t)((((i + pt->p->rot) % S) + S) % S);
+                out[i] = j < have ? (P.real_only ? P.re[j] : P.vals[j].real()) : 0.0;
+            }
+            return 0;
+        }
+        size_t nv = std::min(P.length, have);
         if (count) *count = nv;
         for (size_t i = 0; i < nv && i < cap; i++) out[i] = P.real_only ? P.re[i] : P.vals[i].real();
     })

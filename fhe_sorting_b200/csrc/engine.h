@@ -59,6 +59,8 @@ struct Plaintext {
     std::vector<std::complex<double>> vals; // slot values (kept so the plaintext can be re-encoded at any level)
     std::vector<double> re;                 // ... or just their real parts (MakeCKKSPackedPlaintext of a real vector)
     bool real_only = false;
+    std::shared_ptr<Plaintext> base;        // ... or "base rotated left by rot slots": encoded as a Galois permutation
+    int rot = 0;                            //     of base's encoding instead of a transform of its own
     int slots = 0;
     int level = 0, nsd = 1;
     double scale = 0;
@@ -107,6 +109,7 @@ class Context : public std::enable_shared_from_this<Context> {
     // ---- encode / encrypt / decrypt
     Pt make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots);
     Pt make_plaintext_real(const double *vals, size_t count, int nsd, int level, int slots);
+    Pt rotate_plaintext(const Pt &base, int index); // slot i of the result = slot i + index of base
     Mem encode_at(const Plaintext &pt, int ell, double scale); // (re-)encode at a given limb count and scale
     Mem encoding_for(const Pt &pt, int ell, double scale);     // cached variant
     Ct encrypt(const Keys &k, const Pt &pt);

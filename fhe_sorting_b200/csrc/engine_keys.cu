@@ -218,6 +218,13 @@ Mem Context::encode_at(const Plaintext &pt, int ell, double scale) {
     std::lock_guard<std::recursive_mutex> g(mu);
     FHE_CUDA(cudaSetDevice(device));
     const int n = P->n, slots = pt.slots;
+    if (pt.base) { // rotation of an encoded plaintext = the automorphism X -> X^(5^rot) of its polynomial: one permutation
+        Mem src = encoding_for(pt.base, ell, scale), out = alloc((size_t)ell * n);
+        const uint32_t gal = P->galois_for_rotation(pt.rot);
+        if (gal == 1) return src;
+        k_automorphism(T, gal, ell, src->p, out->p, stream);
+        return out;
+    }
     Mem vbuf = alloc((size_t)2 * slots), rbuf;
     size_t nv;
     if (pt.real_only) {
@@ -261,6 +268,15 @@ Pt Context::new_plaintext(size_t count, int nsd, int level, int slots) {
 Pt Context::make_plaintext(const std::vector<std::complex<double>> &vals, int nsd, int level, int slots) {
     Pt p = new_plaintext(vals.size(), nsd, level, slots);
     p->vals = vals;
+    return p;
+}
+Pt Context::rotate_plaintext(const Pt &base, int index) {
+    if (!base) throw std::invalid_argument("rotate_plaintext: null plaintext");
+    if (base->base) return rotate_plaintext(base->base, base->rot + index);
+    auto p = std::make_shared<Plaintext>();
+    p->slots = base->slots, p->level = base->level, p->nsd = base->nsd, p->scale = base->scale, p->ell = base->ell;
+    p->length = base->slots, p->log_precision = base->log_precision;
+    p->base = base, p->rot = index;
     return p;
 }
 Pt Context::make_plaintext_real(const double *vals, size_t count, int nsd, int level, int slots) {

@@ -247,6 +247,12 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         fheb200_check(fheb200_make_packed_plaintext(ctx, v.data(), v.size(), (int)noiseScaleDeg, (int)level, (int)slots, &p->h));
         return p;
     }
+    // Engine extension (not an OpenFHE call): pt with its slots rotated left by `index`, encoded by a Galois permutation
+    Plaintext RotatePlaintext(const Plaintext &pt, int index) {
+        auto p = std::make_shared<PlaintextImpl>();
+        fheb200_check(fheb200_pt_rotate(ctx, pt->h, index, &p->h));
+        return p;
+    }
     CT Encrypt(const PublicKey<DCRTPoly> &pk, const Plaintext &pt) {
         fheb200_ct *o = nullptr;
         fheb200_check(fheb200_encrypt(ctx, pk.k->h, pt->h, &o));

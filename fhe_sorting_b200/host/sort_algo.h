@@ -219,12 +219,15 @@ template <int N> class DirectSort : public SortBase<N> {
     // pre-rotated right by the giant step so that one rotation by is*P + j*np puts everything in place).
     CT vecRotsOpt(const std::vector<CT> &preRotatedArrays, int num_partition, int num_slots, int np, int is) {
         std::vector<CT> groups(num_partition / np);
+        // every mask is the N-wide block of ones moved somewhere else: encode the block once, then each mask is a Galois
+        // permutation of that encoding (RotatePlaintext) instead of a 65536-point FFT and one NTT per limb
+        auto block0 = m_cc->MakeCKKSPackedPlaintext(generateMaskVector(num_slots, 0), 1, 0, nullptr, num_slots);
         for (int j = 0; j < num_partition / np; j++) {
             const int giant = is * num_partition + j * np;
             CT T;
             for (int i = 0; i < np; i++) {
-                auto msk = vectorRotate(generateMaskVector(num_slots, np * j + i), -giant);
-                auto pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, 0, nullptr, num_slots);
+                // = vectorRotate(generateMaskVector(num_slots, np * j + i), -giant)
+                auto pmsk = m_cc->RotatePlaintext(block0, -((np * j + i) * N + giant));
                 CT term = m_cc->EvalMult(preRotatedArrays[i], pmsk);
                 if (T) m_cc->EvalAddInPlace(T, term);
                 else T = term;
@@ -262,11 +265,12 @@ template <int N> class DirectSort : public SortBase<N> {
     // rank says "move left by ib*P + c"; group i collects copies np*i .. np*i+np-1 and rotates them by ib*P + i*np.
     CT blindRotationOptN(const std::vector<CT> &masked_inputs, int num_slots, int np, int ib, int num_partition) {
         CT result;
+        auto block0 = m_cc->MakeCKKSPackedPlaintext(generateMaskVectorN(num_slots, 0), 1, masked_inputs[0]->GetLevel(), nullptr, num_slots);
         for (int i = 0; i < (num_slots / N) / np; i++) {
             CT tmp;
             for (int j = 0; j < np; j++) {
-                auto msk = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j);
-                auto pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, masked_inputs[j]->GetLevel(), nullptr, num_slots);
+                // = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j), see vecRotsOpt
+                auto pmsk = m_cc->RotatePlaintext(block0, j - (np * i + j) * N);
                 CT term = m_cc->EvalMult(masked_inputs[j], pmsk);
                 if (tmp) m_cc->EvalAddInPlace(tmp, term);
                 else tmp = term;

@@ -198,6 +198,12 @@ class Context(_Handle):
                                                slots, C.byref(h)))
         return Plaintext(h)
 
+    def rotate_plaintext(self, pt, index):
+        """pt with its slots rotated left by index; encoded as a Galois permutation of pt's encoding."""
+        h = C.c_void_p()
+        _ck(_lib.fheb200_pt_rotate(self.h, pt.h, int(index), C.byref(h)))
+        return Plaintext(h)
+
     def encrypt(self, keys, pt):
         h = C.c_void_p()
         _ck(_lib.fheb200_encrypt(self.h, keys.h, pt.h, C.byref(h)))

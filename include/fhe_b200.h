@@ -75,6 +75,10 @@ int fheb200_eval_rotate_keygen(fheb200_ctx *ctx, fheb200_keys *k, const int *ind
 /* MakeCKKSPackedPlaintext(values, noiseScaleDeg, level, nullptr, slots) (src/sort_algo.h:317,341,609,706) */
 int fheb200_make_packed_plaintext(fheb200_ctx *ctx, const double *values, size_t count, int noise_scale_deg, int level,
                                   int slots, fheb200_pt **out);
+/* Engine extension: the plaintext whose slot i is slot i + index of `pt` (same level, scale and slot count).  Its
+ * encoding is the Galois automorphism X -> X^(5^index) of pt's encoding - one permutation kernel instead of an FFT and
+ * one NTT per limb.  The sort drivers build their N-wide block masks (src/sort_algo.h:339-342, 571-574) this way. */
+int fheb200_pt_rotate(fheb200_ctx *ctx, fheb200_pt *pt, int index, fheb200_pt **out);
 int fheb200_pt_release(fheb200_pt *pt);
 /* GetRealPackedValue / SetLength / GetLogPrecision (src/encryption.cpp:20, src/encryption.h:41) */
 int fheb200_pt_values(fheb200_pt *pt, double *out, size_t capacity, size_t *count);

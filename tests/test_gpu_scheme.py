@@ -191,3 +191,29 @@ def test_chebyshev_on_interval_and_poly(env):
     z = ctx.poly(enc(ctx, keys, w), p)
     assert np.abs(ctx.decrypt(keys, z, 8) - f3(w)).max() < 1e-7
     assert z.level == 4
+
+
+def test_rotated_plaintext_is_a_galois_permutation_of_the_encoding(env):
+    """fheb200_pt_rotate: slot i of the result is slot i + r of the plaintext, for sparse (8 of 2048) and full packing,
+    positive and negative r; used as a mask it equals the directly encoded rotated vector."""
+    import fhe_sorting_b200 as F
+    ctx, keys = env
+    v = np.array([0.5, -0.25, 0.125, 1.0, -1.0, 0.0, 0.75, -0.6])
+    x = np.array([1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0]) / 8
+    ct = enc(ctx, keys, x)
+    base = ctx.make_plaintext(v, 1, 0, 8)
+    for r in (1, 3, -2, 8, 13):
+        rp = ctx.rotate_plaintext(base, r)
+        want = np.roll(v, -r)
+        assert np.abs(ctx.decrypt(keys, ctx.encrypt(keys, rp), 8) - want).max() < 1e-9
+        direct = ctx.mult(ct, ctx.make_plaintext(want, 1, 0, 8))
+        via = ctx.mult(ct, rp)
+        assert np.abs(ctx.decrypt(keys, via, 8) - x * want).max() < 1e-9
+        assert np.abs(ctx.decrypt(keys, via, 8) - ctx.decrypt(keys, direct, 8)).max() < 1e-9
+    full = F.Context(12, 4, 40, 60, batch=2048)
+    k2 = full.keygen(3)
+    w = np.random.default_rng(2).uniform(-1, 1, 2048)
+    b2 = full.make_plaintext(w, 1, 0, 2048)
+    for r in (5, -700):
+        got = full.decrypt(k2, full.encrypt(k2, full.rotate_plaintext(b2, r)), 2048)
+        assert np.abs(got - np.roll(w, -r)).max() < 1e-7
