@@ -123,6 +123,9 @@ class Context : public std::enable_shared_from_this<Context> {
     Ct add_const(const Ct &a, double c);
     Ct negate(const Ct &a);
     Ct mult(const Ct &a, const Ct &b);       // EvalMult / EvalMultAndRelinearize / EvalSquare (a.get()==b.get())
+    Ct mult_lazy(const Ct &a, const Ct &b);  // tensor product only: 3 polynomials, relinearise() later
+    Ct relinearize(const Ct &a);             // 3 -> 2 polynomials (no-op on 2)
+    Ct add_lazy(const Ct &a, const Ct &b);   // EvalAdd where either side may still carry its s^2 polynomial
     Ct mult_pt(const Ct &a, const Pt &p);
     Ct mult_const(const Ct &a, double c);
     Ct rotate(const Ct &a, int index);

@@ -139,25 +139,56 @@ Ct Context::mult_pt(const Ct &a0, const Pt &p) {
     return r;
 }
 // ct * ct with relinearisation (EvalMult, EvalMultAndRelinearize, EvalSquare)
-Ct Context::mult(const Ct &a0, const Ct &b0) {
+Ct Context::mult(const Ct &a0, const Ct &b0) { return relinearize(mult_lazy(a0, b0)); }
+
+// The tensor product alone.  Paterson-Stockmeyer adds half of its products to another product before anything is
+// multiplied by them again, so those can share one relinearisation (poly_eval.cu: eval_inner).
+Ct Context::mult_lazy(const Ct &a0, const Ct &b0) {
     LOCK;
     check_pair(a0, b0);
-    if (!evk_mult) throw std::runtime_error("EvalMult: relinearisation key missing (call EvalMultKeyGen)");
     Ct a = a0, b = b0;
     adjust_pair_to_one(a, b);
     const int n = P->n, ell = a->ell;
-    const DevicePlan &D = plan(ell);
-    Mem d = alloc((size_t)3 * ell * n);
-    u64 *d0 = d->p, *d1 = d->p + (size_t)ell * n, *d2 = d->p + (size_t)2 * ell * n;
-    k_tensor(T, ell, a->poly(0, n), a->poly(1, n), b->poly(0, n), b->poly(1, n), d0, d1, d2, stream);
-    Mem digits = alloc((size_t)D.beta * D.width * n);
-    modup(ell, d2, digits->p);
     auto r = std::make_shared<Ciphertext>(*a);
-    r->mem = alloc((size_t)2 * ell * n);
+    r->npoly = 3;
+    r->mem = alloc((size_t)3 * ell * n);
     r->slots = std::max(a->slots, b->slots);
-    keyswitch_digits(ell, digits->p, evk_mult, d0, d1, r->poly(0, n), r->poly(1, n), 1u);
+    k_tensor(T, ell, a->poly(0, n), a->poly(1, n), b->poly(0, n), b->poly(1, n), r->poly(0, n), r->poly(1, n), r->poly(2, n), stream);
     r->nsd = a->nsd + b->nsd;
     r->scale = a->scale * b->scale;
+    return r;
+}
+Ct Context::relinearize(const Ct &a) {
+    LOCK;
+    if (!a) throw std::invalid_argument("fheb200: null ciphertext");
+    if (a->npoly == 2) return a;
+    if (a->npoly != 3) throw std::runtime_error("relinearize: expected 3 polynomials");
+    if (!evk_mult) throw std::runtime_error("EvalMult: relinearisation key missing (call EvalMultKeyGen)");
+    const int n = P->n, ell = a->ell;
+    const DevicePlan &D = plan(ell);
+    Mem digits = alloc((size_t)D.beta * D.width * n);
+    modup(ell, a->poly(2, n), digits->p);
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->npoly = 2;
+    r->mem = alloc((size_t)2 * ell * n);
+    keyswitch_digits(ell, digits->p, evk_mult, a->poly(0, n), a->poly(1, n), r->poly(0, n), r->poly(1, n), 1u);
+    return r;
+}
+Ct Context::add_lazy(const Ct &a0, const Ct &b0) {
+    LOCK;
+    if (!a0 || !b0) throw std::invalid_argument("fheb200: null ciphertext");
+    if (a0->npoly == 2 && b0->npoly == 2) return add(a0, b0);
+    Ct a = a0, b = b0;
+    adjust_pair(a, b); // the alignment helpers work on any number of polynomials
+    if (a->npoly < b->npoly) std::swap(a, b);
+    const int n = P->n;
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)a->npoly * a->ell * n);
+    r->slots = std::max(a->slots, b->slots);
+    for (int p = 0; p < a->npoly; p++) {
+        if (p < b->npoly) k_binary(T, OP_ADD, a->ell, a->poly(p, n), b->poly(p, n), r->poly(p, n), stream);
+        else FHE_CUDA(cudaMemcpyAsync(r->poly(p, n), a->poly(p, n), (size_t)a->ell * n * sizeof(u64), cudaMemcpyDeviceToDevice, stream));
+    }
     return r;
 }
 

@@ -169,12 +169,15 @@ static Ct eval_inner(PSState &S, const Poly &f, int m) {
         g_split_ms += ts.lap();
     }
     Ct cu = weighted_sum(S, c, k - 1);
-    Ct qu = eval_inner(S, q, m - 1);
-    Ct su = eval_inner(S, s2, m - 1);
+    Ct qu = S.C->relinearize(eval_inner(S, q, m - 1)); // a multiplicand has to be relinearised ...
+    Ct su = eval_inner(S, s2, m - 1);                   // ... a summand not: it may keep its s^2 polynomial
     Ct left = cu ? S.C->add(S.T2[m - 1], cu) : S.T2[m - 1];
     if (c[0] != 0.0) left = S.C->add_const(left, c[0]);
-    Ct prod = S.C->mult(left, qu);
-    return S.C->add(prod, su);
+    // product and remainder share one key switch, done by whoever multiplies by (or returns) the sum: half of the
+    // products of the recursion never pay for a relinearisation of their own
+    static const bool lazy = [] { const char *e = getenv("FHEB200_PS_LAZY_RELIN"); return !(e && *e == '0'); }();
+    if (!lazy) return S.C->add(S.C->mult(left, qu), S.C->relinearize(su));
+    return S.C->add_lazy(S.C->mult_lazy(left, qu), su);
 }
 
 static void choose_km(int n, int &k, int &m) {
@@ -279,7 +282,7 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
     if (pstime)
         fprintf(stderr, "PS deg %d k %d m %d ell %d: basis %.2f giant %.2f collect %.2f lincomb %.2f inner %.2f (splits %.2f) ms host, ends at launch %llu\n",
                 n, k, m, x->ell, t_basis, t_giant, t_collect, t_lincomb, tm.lap(), g_split_ms, (unsigned long long)g_launches.load());
-    return sub(r, T2km1);
+    return sub(relinearize(r), T2km1);
 }
 
 // power-basis evaluation with binary powers, depth ceil(log2 deg) + 1
