@@ -307,8 +307,17 @@ def run_ours(args, rank, world, local_rank):
     top = max(kernels, key=lambda k: kernels[k]["share_of_rotate"])
     rot_ms = ms / (ROT_PER_STEP * args.steps)
     ab = algo_bytes_rotate(n, ell, K, alpha)
+    traffic, traffic_src = None, None
+    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", "ncu_traffic.json")))
+        t = tj.get(top, {})
+        traffic = t.get("dram_bytes_per_launch", t.get("dram_bytes_per_limb", 0) * ell) or None
+        traffic_src = tj["source"] + "; " + t.get("note", "")
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": kernels[top]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": kernels[top]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                "frac": kernels[top]["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src,
                 "kernels": kernels,
                 "whole_rotate": {"algo_bytes": ab, "ms": rot_ms, "gbs": ab / (rot_ms * 1e-3) / 1e9,
                                  "frac": ab / (rot_ms * 1e-3) / 1e9 / peak}}
