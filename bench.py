@@ -26,8 +26,14 @@ import time
 
 import numpy as np
 
-# stdout carries exactly one JSON line: NCCL's version / debug banner goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly one JSON line.  Native libraries (NCCL prints "NCCL version ..." on fd 1 at communicator
+# creation) write past sys.stdout, so fd 1 is pointed at stderr for the whole run and the line goes to the saved fd.
+_RESULT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj):
+    os.write(_RESULT_FD, (json.dumps(obj) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -155,14 +161,14 @@ def run_reference(args, rank, world):
     v = args.steps * per_step / dt
     sample = ("bounded sample: %d EvalRotate per step (not %d) at the full parameter set (41 limbs), OpenMP over "
               "limbs" % (per_step, ROT_PER_STEP))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": workload_config(),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)):
@@ -339,7 +345,7 @@ def run_ours(args, rank, world, local_rank):
                          "sample": "3 EvalRotate of the same ciphertext at the full parameter set (41 limbs)",
                          "bit_exact_vs_gpu": parity},
     }
-    print(json.dumps(out))
+    emit(out)
     if dist is not None:
         dist.destroy_process_group()
 
