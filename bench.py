@@ -9,8 +9,9 @@ rotation pattern of constructRank's baby steps, src/sort_algo.h:425-431).  Each 
 evaluation key, so the working set (5 GiB of keys) is far larger than the 126 MB L2.
 
 value      rotations/s over all ranks, ciphertext and keys resident in HBM, CUDA events on the engine's stream
-e2e        same step through the C ABI with HOST ciphertext buffers: fheb200_ct_import (pinned host -> HBM),
-           ROT_PER_STEP x fheb200_eval_rotate, fheb200_ct_export of the last result (HBM -> host)
+e2e        same step through the C ABI with HOST ciphertext buffers: fheb200_ct_import_async (pinned host -> HBM),
+           ROT_PER_STEP x fheb200_eval_rotate, fheb200_ct_export_async of the last result (HBM -> host); the copies of
+           neighbouring steps overlap the kernels, fheb200_ctx_sync closes the timed region
 roofline   dominant kernel of the step, algorithmic bytes / CUDA-event time, against MEASURED_PEAKS.json
 cpu_baseline  the CPU oracle (a port of the OpenFHE algorithm; OpenFHE itself is absent) on the host cores
 Multi-GPU: rotations of a sort are independent work items; keys are replicated, every rank rotates its own
@@ -262,25 +263,37 @@ def run_ours(args, rank, world, local_rank):
     ms = float(t.item())
     value = world * ROT_PER_STEP * args.steps / (ms * 1e-3)
 
-    # ---- end to end through the C ABI with host buffers (pinned)
-    pin = [torch.empty((ell, n), dtype=torch.int64).pin_memory() for _ in range(4)]
-    h_in0, h_in1, h_out0, h_out1 = [p.numpy().view(np.uint64) for p in pin]
+    # ---- end to end through the C ABI with host buffers (pinned): every step imports its input ciphertext from host
+    # memory and exports its result to host memory.  The copies run on the library's copy streams
+    # (fheb200_ct_import_async / _export_async), so the import of step s + 1 and the export of step s - 1 overlap the
+    # kernels of step s; the timed region ends with fheb200_ctx_sync, after the last export has landed.
+    pin = [torch.empty((ell, n), dtype=torch.int64).pin_memory() for _ in range(6)]
+    h_in0, h_in1, h_out0, h_out1, h_out2, h_out3 = [p.numpy().view(np.uint64) for p in pin]
+    outs = [(h_out0, h_out1), (h_out2, h_out3)]
     ctx.ct_export(ct, out=(h_in0, h_in1))
     info = ct.info()
 
-    def e2e_step():
-        c = ctx.ct_import(h_in0, h_in1, info["nsd"], info["scale"], info["slots"])
-        r = None
-        for i in INDICES:
-            r = ctx.rotate(c, i)
-        ctx.ct_export(r, out=(h_out0, h_out1))
+    def e2e_run(steps):
+        nxt = ctx.ct_import_async(h_in0, h_in1, info["nsd"], info["scale"], info["slots"])
+        for s in range(steps):
+            c = nxt
+            if s + 1 < steps:
+                nxt = ctx.ct_import_async(h_in0, h_in1, info["nsd"], info["scale"], info["slots"])
+            ctx.ct_ready(c)
+            r = None
+            for i in INDICES:
+                r = ctx.rotate(c, i)
+            ctx.ct_export_async(r, outs[s & 1])
+        ctx.sync()
 
-    for _ in range(max(3, args.warmup)):
-        e2e_step()
+    e2e_run(max(3, args.warmup))
+    want = ctx.ct_export(ctx.rotate(ct, INDICES[-1]))
+    if not (np.array_equal(outs[(max(3, args.warmup) - 1) & 1][0], want[0])
+            and np.array_equal(outs[(max(3, args.warmup) - 1) & 1][1], want[1])):
+        raise SystemExit("bench: the asynchronously exported ciphertext differs from the synchronous one")
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_run(args.steps)
     barrier()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
     if dist is not None:

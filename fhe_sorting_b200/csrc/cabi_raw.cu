@@ -73,6 +73,35 @@ int fheb200_ct_import(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, 
         *out = new fheb200_ct{c};
     })
 }
+// Asynchronous variants for pinned host buffers: the copies run on the context's copy stream and overlap the kernels of
+// neighbouring work items.  The host buffers must stay untouched (import) / are valid (export) only after fheb200_ctx_sync.
+int fheb200_ct_import_async(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int ell, int nsd, double scale, int slots,
+                            fheb200_ct **out) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(c0, "c0"); need(c1, "c1"); need(out, "out");
+        if (ell < 1 || ell > C.P->L) throw std::invalid_argument("ct_import: bad limb count");
+        auto c = std::make_shared<Ciphertext>();
+        c->npoly = 2, c->ell = ell, c->level = C.P->L - ell, c->nsd = nsd, c->scale = scale, c->slots = slots > 0 ? slots : C.batch;
+        c->mem = C.alloc((size_t)2 * ell * n);
+        C.copy_in(c->poly(0, n), c0, (size_t)ell * n * 8, c->mem);
+        C.copy_in(c->poly(1, n), c1, (size_t)ell * n * 8, c->mem);
+        *out = new fheb200_ct{c};
+    })
+}
+int fheb200_ct_ready(fheb200_ctx *ctx, fheb200_ct *ct) {
+    GUARD({ LOCKCTX(ctx); need(ct, "ct"); C.wait_copy_in(ct->c->mem); })
+}
+int fheb200_ct_export_async(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(ct, "ct");
+        size_t w = (size_t)ct->c->ell * n;
+        if (words < w) throw std::invalid_argument("ct_export: buffer too small");
+        if (c0) C.copy_out(c0, ct->c->poly(0, n), w * 8, ct->c->mem);
+        if (c1) C.copy_out(c1, ct->c->poly(1, n), w * 8, ct->c->mem);
+    })
+}
 int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t words) {
     GUARD({
         LOCKCTX(ctx);

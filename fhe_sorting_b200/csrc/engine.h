@@ -13,6 +13,8 @@
 #include <tuple>
 #include <vector>
 
+#include <deque>
+
 #include "kernels.h"
 #include "params.h"
 
@@ -156,6 +158,12 @@ class Context : public std::enable_shared_from_this<Context> {
     bool forked() const { return forked_; }
     bool usable(const Mem &m) const { return !forked_ || m->stream == stream || m->epoch < fork_epoch_; }
     unsigned epoch = 1;
+    // ---- asynchronous host <-> device transfers on a copy stream of their own (pinned host buffers), so that the copies
+    // of one work item overlap the kernels of its neighbours; buffers a pending copy reads are kept alive until it is done
+    void copy_in(void *dst, const void *src, size_t bytes, const Mem &owner);   // H2D; wait_copy_in(owner) before first use
+    void wait_copy_in(const Mem &owner);                                         // current stream waits for owner's H2D copies
+    void copy_out(void *dst, const void *src, size_t bytes, const Mem &owner);  // D2H after everything queued so far
+    void drain_copies(bool wait);
     u64 *evk_mult = nullptr;
     std::map<uint32_t, u64 *> evk_rot;
     size_t evk_words() const { return (size_t)P->beta(P->L) * 2 * (P->L + P->K) * P->n; }
@@ -185,6 +193,12 @@ class Context : public std::enable_shared_from_this<Context> {
     cudaEvent_t fork_ev_ = nullptr, free_ev_ = nullptr;
     bool forked_ = false;
     int fork_k_ = 0;
+    cudaStream_t copy_stream_ = nullptr, out_stream_ = nullptr; // H2D and D2H copies (one DMA engine per direction)
+    struct PendingCopy { cudaEvent_t done; Mem keep; };
+    std::deque<PendingCopy> pending_;
+    std::map<const DevMem *, cudaEvent_t> inbound_; // last H2D copy into a buffer that nobody has waited for yet
+    std::vector<cudaEvent_t> free_events_;
+    cudaEvent_t take_event();
     unsigned fork_epoch_ = 0;
     // pinned staging ring for host -> device uploads of slot values: the host never waits for the stream unless it is a
     // whole ring ahead of it (a pageable cudaMemcpyAsync would stall the launching thread at every plaintext)

@@ -30,8 +30,74 @@ Mem Context::alloc(size_t words) {
 }
 void Context::sync() {
     FHE_CUDA(cudaStreamSynchronize(stream));
+    if (copy_stream_) {
+        FHE_CUDA(cudaStreamSynchronize(copy_stream_));
+        FHE_CUDA(cudaStreamSynchronize(out_stream_));
+        std::lock_guard<std::recursive_mutex> g(mu);
+        drain_copies(true);
+    }
     if (forked_)
         for (int i = 0; i < fork_k_; i++) FHE_CUDA(cudaStreamSynchronize(side_[i]));
+}
+
+cudaEvent_t Context::take_event() {
+    if (!free_events_.empty()) {
+        cudaEvent_t e = free_events_.back();
+        free_events_.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    FHE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return e;
+}
+void Context::drain_copies(bool wait) {
+    while (!pending_.empty()) {
+        PendingCopy &c = pending_.front();
+        if (wait) FHE_CUDA(cudaEventSynchronize(c.done));
+        else if (cudaEventQuery(c.done) != cudaSuccess) break;
+        auto it = inbound_.find(c.keep.get());
+        if (it != inbound_.end() && it->second == c.done) inbound_.erase(it); // complete: nothing left to wait for
+        free_events_.push_back(c.done);
+        pending_.pop_front(); // releases the buffer (stream-ordered free on the stream it lives on)
+    }
+}
+void Context::copy_in(void *dst, const void *src, size_t bytes, const Mem &owner) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!copy_stream_) {
+        FHE_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+        FHE_CUDA(cudaStreamCreateWithFlags(&out_stream_, cudaStreamNonBlocking));
+    }
+    drain_copies(false);
+    cudaEvent_t ready = take_event(), done = take_event();
+    FHE_CUDA(cudaEventRecord(ready, stream)); // the allocation (and whatever used the memory before) is ordered on `stream`
+    FHE_CUDA(cudaStreamWaitEvent(copy_stream_, ready, 0));
+    FHE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, copy_stream_));
+    FHE_CUDA(cudaEventRecord(done, copy_stream_));
+    free_events_.push_back(ready);
+    pending_.push_back(PendingCopy{done, owner});
+    inbound_[owner.get()] = done;
+}
+void Context::wait_copy_in(const Mem &owner) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = inbound_.find(owner.get());
+    if (it == inbound_.end()) return;
+    FHE_CUDA(cudaStreamWaitEvent(stream, it->second, 0));
+    inbound_.erase(it);
+}
+void Context::copy_out(void *dst, const void *src, size_t bytes, const Mem &owner) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!copy_stream_) {
+        FHE_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+        FHE_CUDA(cudaStreamCreateWithFlags(&out_stream_, cudaStreamNonBlocking));
+    }
+    drain_copies(false);
+    cudaEvent_t ready = take_event(), done = take_event();
+    FHE_CUDA(cudaEventRecord(ready, stream));
+    FHE_CUDA(cudaStreamWaitEvent(out_stream_, ready, 0));
+    FHE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, out_stream_));
+    FHE_CUDA(cudaEventRecord(done, out_stream_));
+    free_events_.push_back(ready);
+    pending_.push_back(PendingCopy{done, owner}); // the source stays allocated until the copy has run
 }
 
 void Context::fork(int k) {
@@ -143,6 +209,12 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
 
 Context::~Context() {
     if (forked_) stream = main_stream_;
+    if (copy_stream_) cudaStreamSynchronize(copy_stream_), cudaStreamSynchronize(out_stream_);
+    for (auto &c : pending_) cudaEventDestroy(c.done);
+    pending_.clear();
+    inbound_.clear();
+    for (auto e : free_events_) cudaEventDestroy(e);
+    if (copy_stream_) cudaStreamDestroy(copy_stream_), cudaStreamDestroy(out_stream_);
     for (auto s : side_) cudaStreamSynchronize(s);
     if (stream) cudaStreamSynchronize(stream);
     for (auto s : side_) cudaStreamDestroy(s);

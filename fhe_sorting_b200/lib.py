@@ -302,6 +302,27 @@ class Context(_Handle):
                                    nsd, C.c_double(scale), slots, C.byref(h)))
         return Ciphertext(h)
 
+    def ct_import_async(self, c0, c1, nsd, scale, slots):
+        """H2D on the copy stream from PINNED uint64 [limbs][n] arrays; call ct_ready(ct) before the first use of the
+        result, and leave c0/c1 untouched until the next sync()."""
+        assert c0.dtype == np.uint64 and c0.flags.c_contiguous and c1.dtype == np.uint64 and c1.flags.c_contiguous
+        h = C.c_void_p()
+        _ck(_lib.fheb200_ct_import_async(self.h, c0.ctypes.data_as(C.c_void_p), c1.ctypes.data_as(C.c_void_p), c0.shape[0],
+                                         nsd, C.c_double(scale), slots, C.byref(h)))
+        return Ciphertext(h)
+
+    def ct_ready(self, ct):
+        _ck(_lib.fheb200_ct_ready(self.h, ct.h))
+
+    def ct_export_async(self, ct, out):
+        """D2H on the copy stream into PINNED (c0, c1); the arrays are valid after the next sync()."""
+        c0, c1 = out
+        ell = ct.limbs
+        assert c0.dtype == np.uint64 and c0.shape == (ell, self.n) and c0.flags.c_contiguous
+        assert c1.dtype == np.uint64 and c1.shape == (ell, self.n) and c1.flags.c_contiguous
+        _ck(_lib.fheb200_ct_export_async(self.h, ct.h, c0.ctypes.data_as(C.c_void_p), c1.ctypes.data_as(C.c_void_p),
+                                         C.c_size_t(c0.size)))
+
     def pt_export(self, pt, ell):
         out = np.zeros((ell, self.n), dtype=np.uint64)
         _ck(_lib.fheb200_pt_export(self.h, pt.h, out.ctypes.data_as(C.c_void_p), C.c_size_t(out.size)))

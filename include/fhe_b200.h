@@ -145,6 +145,14 @@ int fheb200_ct_reduce_partial_sums(fheb200_ctx *ctx, fheb200_ct *ct);
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words_each);
 int fheb200_ct_import(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int num_limbs, int noise_scale_deg,
                       double scale, int slots, fheb200_ct **out);
+/* Asynchronous variants for pinned host buffers (cudaHostAlloc / torch pin_memory): the copies run on a copy stream of
+ * the context and overlap the kernels of neighbouring work items (issue the import of item s+1 before the work of item
+ * s); the import buffers must stay untouched, and the export buffers are valid, only after the next fheb200_ctx_sync. */
+int fheb200_ct_import_async(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int limbs, int noise_scale_deg,
+                            double scale, int slots, fheb200_ct **out);
+/* makes the engine's stream wait for the copies of an fheb200_ct_import_async; call it before the first use of `ct` */
+int fheb200_ct_ready(fheb200_ctx *ctx, fheb200_ct *ct);
+int fheb200_ct_export_async(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words_each);
 int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t words);
 /* keys: which = 0 secret [L+K][n] ; 1 public b [L][n] ; 2 public a [L][n] */
 int fheb200_keys_export(fheb200_ctx *ctx, fheb200_keys *k, int which, uint64_t *out, size_t words);

@@ -130,3 +130,44 @@ def test_encode_encrypt_match_oracle(pair):
     assert np.abs(dec - vals).max() < 1e-9, "CKKS encode does not decode under the oracle"
     got = ctx.decrypt(keys, ctx.encrypt(keys, pt), 16)
     assert np.abs(got - vals).max() < 1e-9
+
+
+def test_async_import_export_pipeline(pair):
+    """fheb200_ct_import_async / _ready / _export_async: a pipelined sequence of work items over pinned host buffers
+    gives the limbs of the synchronous path (and so of the oracle), whatever overlaps."""
+    import torch
+    ctx, orc, keys, s = pair
+    rng = np.random.default_rng(11)
+    ell = orc.L
+    items = [_fresh(ctx, orc, s, rng, ell) for _ in range(4)]
+    pins = [torch.empty((ell, orc.n), dtype=torch.int64).pin_memory() for _ in range(4 * len(items))]
+    bufs = [p.numpy().view(np.uint64) for p in pins]
+    h_in = [(bufs[4 * k], bufs[4 * k + 1]) for k in range(len(items))]
+    h_out = [(bufs[4 * k + 2], bufs[4 * k + 3]) for k in range(len(items))]
+    for (vals, scale, c0, c1), (i0, i1) in zip(items, h_in):
+        i0[:], i1[:] = c0, c1
+    want = []
+    for vals, scale, c0, c1 in items:
+        ct = ctx.ct_import(c0, c1, 2, scale, 8)
+        want.append(ctx.ct_export(ctx.rotate(ctx.rotate(ct, 1), 3)))
+    g1, g3 = orc.galois(1), orc.galois(3)
+    e = orc.rotate(g1, items[0][2], items[0][3], orc.keygen_rot(SEED, g1, s))
+    e = orc.rotate(g3, e[0], e[1], orc.keygen_rot(SEED, g3, s))
+    assert np.array_equal(want[0][0], e[0]) and np.array_equal(want[0][1], e[1])
+    nxt = ctx.ct_import_async(h_in[0][0], h_in[0][1], 2, items[0][1], 8)
+    for k in range(len(items)):
+        cur = nxt
+        if k + 1 < len(items):
+            nxt = ctx.ct_import_async(h_in[k + 1][0], h_in[k + 1][1], 2, items[k + 1][1], 8)
+        ctx.ct_ready(cur)
+        r = ctx.rotate(ctx.rotate(cur, 1), 3)
+        ctx.ct_export_async(r, h_out[k])
+        del cur, r  # the engine keeps the buffers alive until the copies have run
+    ctx.sync()
+    for k in range(len(items)):
+        assert np.array_equal(h_out[k][0], want[k][0]) and np.array_equal(h_out[k][1], want[k][1]), "item %d" % k
+    # an import that is never waited for explicitly is still complete after sync()
+    lone = ctx.ct_import_async(h_in[1][0], h_in[1][1], 2, items[1][1], 8)
+    ctx.sync()
+    back = ctx.ct_export(lone)
+    assert np.array_equal(back[0], items[1][2]) and np.array_equal(back[1], items[1][3])
