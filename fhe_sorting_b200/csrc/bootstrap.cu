@@ -1,0 +1,192 @@
+// bootstrap.cu — CKKS bootstrapping on the engine's own operations (plan: bootstrap_plan.cpp).
+//
+//   1. bring the ciphertext to its last two limbs, multiply by round(msg_scale q_1 / scale) and rescale: one limb q_0,
+//      message polynomial msg_scale * m with msg_scale = q_0 2^-correction (so that sin(2 pi t / q_0) is linear in it)
+//   2. ModRaise: the two polynomials as centred integers on the limbs of level 1; decrypts to msg_scale m + q_0 I, |I| < K
+//   3. SubSum: log2(n / 2s) rotate-and-adds project I onto the subring of the s-slot packing (and multiply by n / 2s)
+//   4. CoeffsToSlots (grouped FFT factors, hoisted rotations), + conjugate: 2s real slots t_k / (q_0 K)
+//   5. EvalMod: Chebyshev series of cos(2 pi (K u - 1/4) / 2^r) by Paterson-Stockmeyer, then r double-angle steps
+//   6. SlotsToCoeffs, + rotate by s
+// Reference call sites: src/k-way/EvalUtils.cpp:57-86 (checkLevelAndBoot), src/sign.cpp:163-170 (lazyBootstrap).
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+
+#include "engine.h"
+
+namespace fheb200 {
+
+#define LOCK                                           \
+    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    FHE_CUDA(cudaSetDevice(device))
+
+static const int RAISE_LEVEL = 1; // the raised ciphertext lives at level 1 (the FLEXIBLEAUTOEXT extra limb stays unused)
+
+static int env_int(const char *name, int dflt) {
+    const char *e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+
+void Context::bootstrap_setup(int budget_enc, int budget_dec, int slots) {
+    LOCK;
+    if (slots <= 0) slots = batch;
+    auto B = std::make_shared<BootState>();
+    B->plan = make_boot_plan(P->n, slots, budget_enc, budget_dec, (double)P->moduli[0], P->sf[RAISE_LEVEL],
+                             env_int("FHEB200_BOOT_CORRECTION", 12));
+    if (RAISE_LEVEL + B->plan.depth() > P->depth)
+        throw std::invalid_argument("EvalBootstrapSetup: multiplicative depth " + std::to_string(P->depth) +
+                                    " is below the bootstrapping depth " + std::to_string(RAISE_LEVEL + B->plan.depth()));
+    int level = RAISE_LEVEL;
+    for (auto &st : B->plan.cts) {
+        std::vector<Pt> v;
+        for (auto &d : st.diag) v.push_back(make_plaintext(d, 1, level, 2 * slots));
+        B->cts_pt.push_back(std::move(v));
+        level++;
+    }
+    level += B->plan.cheb_depth() + B->plan.r;
+    for (auto &st : B->plan.stc) {
+        std::vector<Pt> v;
+        for (auto &d : st.diag) v.push_back(make_plaintext(d, 1, std::min(level, P->L - 1), 2 * slots));
+        B->stc_pt.push_back(std::move(v));
+        level++;
+    }
+    boot[slots] = B;
+}
+int Context::bootstrap_depth(int slots) const {
+    auto it = boot.find(slots > 0 ? slots : batch);
+    if (it == boot.end()) throw std::runtime_error("EvalBootstrap: call EvalBootstrapSetup for this slot count first");
+    return RAISE_LEVEL + it->second->plan.depth();
+}
+
+void Context::gen_galois_keys(const Keys &k, const std::vector<uint32_t> &galois) {
+    LOCK;
+    if (!k || !k->s) throw std::runtime_error("key generation: secret key required");
+    const int n = P->n, F = P->L + P->K;
+    Mem sp = alloc((size_t)F * n);
+    for (uint32_t gal : galois) {
+        if (gal == 1 || evk_rot.count(gal)) continue;
+        k_automorphism(T, P->galois_inverse(gal), F, k->s->p, sp->p, stream);
+        evk_rot[gal] = gen_switch_key(gal, k->s->p, sp->p);
+    }
+    sync();
+}
+void Context::bootstrap_keygen(const Keys &k, int slots) {
+    LOCK;
+    if (slots <= 0) slots = batch;
+    auto it = boot.find(slots);
+    if (it == boot.end()) throw std::runtime_error("EvalBootstrapKeyGen: call EvalBootstrapSetup for this slot count first");
+    gen_rot_keys(k, it->second->plan.rotations());
+    gen_galois_keys(k, {(uint32_t)(2 * P->n - 1)});
+}
+
+Ct Context::rotate_galois(const Ct &a, uint32_t g) {
+    LOCK;
+    if (a->npoly != 2) throw std::runtime_error("automorphism: relinearise first");
+    if (g == 1) return clone(a);
+    auto it = evk_rot.find(g);
+    if (it == evk_rot.end()) throw std::runtime_error("automorphism: no evaluation key for Galois element " + std::to_string(g));
+    const int n = P->n, ell = a->ell;
+    const DevicePlan &D = plan(ell);
+    Mem digits = alloc((size_t)D.beta * D.width * n);
+    modup(ell, a->poly(1, n), digits->p);
+    auto r = std::make_shared<Ciphertext>(*a);
+    r->mem = alloc((size_t)2 * ell * n);
+    keyswitch_digits(ell, digits->p, it->second, a->poly(0, n), nullptr, r->poly(0, n), r->poly(1, n), g);
+    return r;
+}
+Ct Context::conjugate(const Ct &a) { return rotate_galois(a, (uint32_t)(2 * P->n - 1)); }
+
+Ct Context::mod_raise(const Ct &a, int ell_out, double scale_label) {
+    LOCK;
+    if (a->ell != 1 || a->npoly != 2) throw std::runtime_error("ModRaise: expected a two-element ciphertext on one limb");
+    const int n = P->n;
+    Mem coef = alloc((size_t)2 * n);
+    std::vector<uint32_t> d1 = {(0u << 8) | 0u, (1u << 8) | 0u}, dall;
+    k_ntt_inv(T, a->mem->p, coef->p, desc(d1), 2, stream);
+    auto r = std::make_shared<Ciphertext>();
+    r->npoly = 2, r->ell = ell_out, r->level = P->L - ell_out, r->nsd = 1, r->scale = scale_label, r->slots = a->slots;
+    r->mem = alloc((size_t)2 * ell_out * n);
+    k_modraise_lift(T, ell_out, 2, coef->p, (size_t)n, r->mem->p, stream);
+    for (int i = 0; i < ell_out; i++)
+        for (int p = 0; p < 2; p++) dall.push_back(((uint32_t)(p * ell_out + i) << 8) | (uint32_t)i);
+    k_ntt_fwd(T, r->mem->p, desc(dall), 2 * ell_out, stream);
+    return r;
+}
+
+// out = sum_i diag_i (.) rotate(x, rot_i): the rotations of one stage share a hoisted ModUp; the products stay at degree 2
+// and are rescaled once by whoever multiplies next
+Ct Context::linear_stage(const Ct &x0, const BootStage &st, const std::vector<Pt> &diag) {
+    LOCK;
+    Ct x = x0->nsd == 2 ? reduced(x0) : x0;
+    std::shared_ptr<Precomp> pre;
+    Ct acc;
+    for (size_t i = 0; i < st.rot.size(); i++) {
+        Ct r = x;
+        if (st.rot[i] != 0) {
+            if (!pre) pre = fast_rotation_precompute(x);
+            r = fast_rotation(x, st.rot[i], pre);
+        }
+        Ct t = mult_pt(r, diag[i]);
+        acc = acc ? add(acc, t) : t;
+    }
+    return acc;
+}
+
+Ct Context::bootstrap(const Ct &a, int stop_after) {
+    LOCK;
+    if (!a || a->npoly != 2) throw std::runtime_error("EvalBootstrap: expected a relinearised ciphertext");
+    const int slots = a->slots > 0 ? a->slots : batch;
+    auto it = boot.find(slots);
+    if (it == boot.end())
+        throw std::runtime_error("EvalBootstrap: no EvalBootstrapSetup for " + std::to_string(slots) + " slots");
+    const BootState &B = *it->second;
+    const BootPlan &bp = B.plan;
+    const int n = P->n;
+    static const bool verbose = getenv("FHEB200_BOOT_VERBOSE") != nullptr;
+
+    // 1. last two limbs -> one limb carrying msg_scale * m
+    Ct x = a->nsd == 2 ? reduced(a) : a;
+    if (x->ell < 2) throw std::runtime_error("EvalBootstrap: the ciphertext has no level left (bootstrap one level earlier)");
+    if (x->ell > 2) x = level_reduce(x, x->ell - 2);
+    {
+        const long double mult = (long double)bp.msg_scale * (long double)P->moduli[1] / (long double)x->scale;
+        if (mult < 2.0L) throw std::runtime_error("EvalBootstrap: scale too large for the correction factor");
+        LimbScalars s = scalars_for(mult, 2, true);
+        auto y = std::make_shared<Ciphertext>(*x);
+        y->mem = alloc((size_t)2 * 2 * n);
+        for (int p = 0; p < 2; p++) k_mul_scalar(T, 2, x->poly(p, n), s, y->poly(p, n), stream);
+        y->nsd = 2;
+        y->scale = x->scale * (double)roundl(mult);
+        x = mod_reduce(y); // scale == msg_scale up to 2^-40 relative
+    }
+    if (stop_after == 1) return x;
+    // 2. ModRaise
+    Ct r = mod_raise(x, P->L - RAISE_LEVEL, bp.raise_scale);
+    r->slots = 2 * slots;
+    // 3. SubSum
+    for (int step = slots; step < n / 2; step <<= 1) r = add(r, rotate(r, step));
+    if (stop_after == 2) return r;
+    // 4. CoeffsToSlots + conjugate
+    for (size_t i = 0; i < bp.cts.size(); i++) r = linear_stage(r, bp.cts[i], B.cts_pt[i]);
+    r = reduced(r);
+    r = add(r, conjugate(r));
+    if (verbose) fprintf(stderr, "bootstrap: after CoeffsToSlots level %d\n", r->level);
+    if (stop_after == 3) return r;
+    // 5. EvalMod
+    r = eval_chebyshev(r, bp.cheb, -1.0, 1.0);
+    for (int i = 0; i < bp.r; i++) {
+        Ct sq = mult(r, r);
+        r = add_const(add(sq, sq), -1.0);
+    }
+    if (verbose) fprintf(stderr, "bootstrap: after EvalMod level %d nsd %d\n", r->level, r->nsd);
+    if (stop_after == 4) return r;
+    // 6. SlotsToCoeffs + fold of the two halves
+    for (size_t i = 0; i < bp.stc.size(); i++) r = linear_stage(r, bp.stc[i], B.stc_pt[i]);
+    r = add(r, rotate(r, slots));
+    if (r.use_count() > 1) r = std::make_shared<Ciphertext>(*r);
+    r->slots = slots;
+    if (verbose) fprintf(stderr, "bootstrap: done at level %d nsd %d\n", r->level, r->nsd);
+    return r;
+}
+
+} // namespace fheb200

@@ -286,4 +286,56 @@ int fheb200_chebyshev_coefficients(double (*f)(double, void *), void *user, doub
     })
 }
 
+// ---- bootstrapping
+int fheb200_eval_bootstrap_setup(fheb200_ctx *ctx, int budget_enc, int budget_dec, int slots) {
+    GUARD({ need(ctx, "ctx"); ctx->c->bootstrap_setup(budget_enc, budget_dec, slots); })
+}
+int fheb200_eval_bootstrap_keygen(fheb200_ctx *ctx, fheb200_keys *k, int slots) {
+    GUARD({ need(ctx, "ctx"); need(k, "keys"); ctx->c->bootstrap_keygen(k->k, slots); })
+}
+int fheb200_eval_bootstrap(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "ct"); need(out, "out"); *out = wrap(ctx->c->bootstrap(a->c)); })
+}
+int fheb200_eval_bootstrap_partial(fheb200_ctx *ctx, fheb200_ct *a, int stop_after, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "ct"); need(out, "out"); *out = wrap(ctx->c->bootstrap(a->c, stop_after)); })
+}
+int fheb200_bootstrap_depth(fheb200_ctx *ctx, int slots, int *levels) {
+    GUARD({ need(ctx, "ctx"); need(levels, "levels"); *levels = ctx->c->bootstrap_depth(slots); })
+}
+int fheb200_eval_conjugate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(a, "ct"); need(out, "out"); *out = wrap(ctx->c->conjugate(a->c)); })
+}
+int fheb200_bootstrap_plan_info(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
+                                int correction, int *depth, int *k_range, int *double_angles, int *rotations, int capacity,
+                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb) {
+    GUARD({
+        BootPlan P = make_boot_plan(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale, correction);
+        if (depth) *depth = P.depth();
+        if (k_range) *k_range = P.K;
+        if (double_angles) *double_angles = P.r;
+        auto R = P.rotations();
+        if (num_rotations) *num_rotations = (int)R.size();
+        if (rotations) for (int i = 0; i < (int)R.size() && i < capacity; i++) rotations[i] = R[i];
+        if (num_cheb) *num_cheb = (int)P.cheb.size();
+        if (cheb) for (int i = 0; i < (int)P.cheb.size() && i < cheb_capacity; i++) cheb[i] = P.cheb[i];
+    })
+}
+int fheb200_bootstrap_plan_apply(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
+                                 int correction, int which, const double *in_re_im, double *out_re_im) {
+    GUARD({
+        need(in_re_im, "in"); need(out_re_im, "out");
+        BootPlan P = make_boot_plan(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale, correction);
+        const int m = 2 * slots;
+        std::vector<std::complex<double>> v(m), w(m);
+        for (int j = 0; j < m; j++) v[j] = std::complex<double>(in_re_im[2 * j], in_re_im[2 * j + 1]);
+        for (auto &st : which == 0 ? P.cts : P.stc) {
+            std::fill(w.begin(), w.end(), std::complex<double>(0, 0));
+            for (size_t t = 0; t < st.rot.size(); t++)
+                for (int j = 0; j < m; j++) w[j] += st.diag[t][j] * v[(j + st.rot[t]) % m];
+            v = w;
+        }
+        for (int j = 0; j < m; j++) out_re_im[2 * j] = v[j].real(), out_re_im[2 * j + 1] = v[j].imag();
+    })
+}
+
 } // extern "C"

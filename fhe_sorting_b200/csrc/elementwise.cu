@@ -115,6 +115,19 @@ __global__ void __launch_bounds__(EW_THREADS) ew_rescale_lift(DeviceTables T, in
     R.x = switch_modulus(V.x, ql, half, m), R.y = switch_modulus(V.y, ql, half, m);
     st2(tmp, (size_t)blockIdx.y * T.n + j, R);
 }
+// ModRaise (bootstrapping): coefficient-domain limb 0 of poly p at src + p * src_stride, taken as a centred integer in
+// (-q_0/2, q_0/2], re-expressed on limbs 0..ell_out-1.  blockIdx.y = poly * ell_out + limb
+__global__ void __launch_bounds__(EW_THREADS) ew_modraise_lift(DeviceTables T, int ell_out, const u64 *src, size_t src_stride, u64 *out) {
+    const int poly = blockIdx.y / ell_out, limb = blockIdx.y - poly * ell_out;
+    const int j = (blockIdx.x * EW_THREADS + threadIdx.x) * 2;
+    if (j >= T.n) return;
+    const ModConst m = T.mc[limb];
+    const u64 q0 = T.mc[0].q, half = q0 >> 1;
+    v2 V = ld2(src + poly * src_stride, j), R;
+    if (limb == 0) R = V;
+    else R.x = switch_modulus(V.x, q0, half, m), R.y = switch_modulus(V.y, q0, half, m);
+    st2(out, (size_t)blockIdx.y * T.n + j, R);
+}
 // blockIdx.y = poly * ell_out + limb; in has ell_out + 1 limbs per poly, tmp and o have ell_out
 __global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, int ell_out, const u64 *in, const u64 *tmp,
                                                                 LimbScalars s, u64 *o) {
@@ -229,6 +242,9 @@ void k_automorphism(const DeviceTables &T, uint32_t g, int limbs, const u64 *in,
 }
 void k_rescale_lift(const DeviceTables &T, int ell, int npoly, const u64 *last, size_t last_stride, u64 *tmp, cudaStream_t st) {
     g_launches++, ew_rescale_lift<<<ew_grid(T, npoly * (ell - 1)), EW_THREADS, 0, st>>>(T, ell, last, last_stride, tmp);
+}
+void k_modraise_lift(const DeviceTables &T, int ell_out, int npoly, const u64 *src, size_t src_stride, u64 *out, cudaStream_t st) {
+    g_launches++, ew_modraise_lift<<<ew_grid(T, npoly * ell_out), EW_THREADS, 0, st>>>(T, ell_out, src, src_stride, out);
 }
 void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *in, const u64 *tmp, const LimbScalars &s, u64 *out,
                       cudaStream_t st) {

@@ -15,6 +15,7 @@
 
 #include <deque>
 
+#include "bootstrap_plan.h"
 #include "kernels.h"
 #include "params.h"
 
@@ -80,6 +81,11 @@ struct KeySet {
 };
 typedef std::shared_ptr<KeySet> Keys;
 
+struct BootState { // EvalBootstrapSetup result for one slot count: the plan and its diagonals as (lazily encoded) plaintexts
+    BootPlan plan;
+    std::vector<std::vector<Pt>> cts_pt, stc_pt;
+};
+
 struct Precomp { // EvalFastRotationPrecompute result: ModUp'ed digits of c1
     Mem digits;
     int ell = 0;
@@ -136,6 +142,19 @@ class Context : public std::enable_shared_from_this<Context> {
     Ct add_many(const std::vector<Ct> &v);
     Ct rescale(const Ct &a);                 // explicit ModReduce (one level)
     Ct level_reduce(const Ct &a, int levels);
+
+    // ---- bootstrapping (bootstrap.cu): EvalBootstrapSetup / EvalBootstrapKeyGen / EvalBootstrap for sparsely packed
+    // ciphertexts (src/k-way/EvalUtils.cpp:76, tests/k-way/KWaySort2Test.cpp:42-44)
+    void bootstrap_setup(int budget_enc, int budget_dec, int slots);
+    void bootstrap_keygen(const Keys &k, int slots);
+    Ct bootstrap(const Ct &a, int stop_after = 0);      // stop_after 1..4: the intermediate ciphertext of that step (tests)
+    int bootstrap_depth(int slots) const;               // levels one EvalBootstrap consumes (after the raise to level 1)
+    Ct conjugate(const Ct &a);                          // slot-wise complex conjugation (Galois element 2n - 1)
+    void gen_galois_keys(const Keys &k, const std::vector<uint32_t> &galois);
+    Ct rotate_galois(const Ct &a, uint32_t g);
+    Ct mod_raise(const Ct &a, int ell_out, double scale_label); // a: one limb; result on limbs 0..ell_out-1
+    Ct linear_stage(const Ct &x, const BootStage &st, const std::vector<Pt> &diag);
+    std::map<int, std::shared_ptr<BootState>> boot;
 
     // ---- polynomial evaluation (poly_eval.cpp)
     Ct eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, double a, double b);

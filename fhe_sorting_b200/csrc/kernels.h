@@ -68,6 +68,11 @@ void k_rescale_lift(const DeviceTables &T, int ell, int npoly, const u64 *last_c
 void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *in, const u64 *tmp, const LimbScalars &qlinv,
                       u64 *out, cudaStream_t st);
 
+// ---- bootstrapping: ModRaise ----
+// src: coefficient-domain limb 0 of each poly (poly p at src + p * src_stride); out[p][ell_out][n] <- the centred integer
+// on limbs 0..ell_out-1 (coefficient domain; NTT it afterwards)
+void k_modraise_lift(const DeviceTables &T, int ell_out, int npoly, const u64 *src, size_t src_stride, u64 *out, cudaStream_t st);
+
 // ---- hybrid key switching ----
 // ---- base conversion on the integer tensor cores (baseconv.cu) ----
 struct ConvTable {

@@ -229,14 +229,26 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         fheb200_check(fheb200_eval_rotate_keygen(ctx, sk.k->h, idx.data(), idx.size()));
         evalKeys = sk.k;
     }
-    void EvalBootstrapSetup(const std::vector<uint32_t> &, const std::vector<uint32_t> & = {0, 0}, uint32_t = 0) {
-        throw std::runtime_error("EvalBootstrapSetup: CKKS bootstrapping is not built yet (DESIGN.md, out of scope this round)");
+    // ---- bootstrapping (tests/k-way/KWaySort2Test.cpp:42-44 ; src/k-way/EvalUtils.cpp:76 ; src/sign.cpp:168)
+    // levelBudget = levels for CoeffsToSlots / SlotsToCoeffs; bsgsDim is unused (each group's few diagonals share one
+    // hoisted ModUp); slots = 0 means the batch size.  Sparse packings only (2 * slots <= ring_dim / 2).
+    void EvalBootstrapSetup(const std::vector<uint32_t> &levelBudget = {5, 4}, const std::vector<uint32_t> & = {0, 0},
+                            uint32_t slots = 0, uint32_t = 0, bool = true) {
+        if (levelBudget.size() != 2) throw std::invalid_argument("EvalBootstrapSetup: levelBudget needs two entries");
+        if (!(features & FHE)) throw std::runtime_error("EvalBootstrapSetup: Enable(FHE) first");
+        fheb200_check(fheb200_eval_bootstrap_setup(ctx, (int)levelBudget[0], (int)levelBudget[1], (int)slots));
     }
-    void EvalBootstrapKeyGen(const PrivateKey<DCRTPoly> &, uint32_t) {
-        throw std::runtime_error("EvalBootstrapKeyGen: CKKS bootstrapping is not built yet");
+    void EvalBootstrapKeyGen(const PrivateKey<DCRTPoly> &sk, uint32_t slots) {
+        fheb200_check(fheb200_eval_bootstrap_keygen(ctx, sk.k->h, (int)slots));
+        evalKeys = sk.k;
     }
-    CT EvalBootstrap(const CT &, uint32_t = 1, uint32_t = 0) {
-        throw std::runtime_error("EvalBootstrap: CKKS bootstrapping is not built yet");
+    // numIterations > 1 (Meta-BTS) runs the single-iteration bootstrapping: its precision at 59-bit scaling already
+    // exceeds what the sorts need
+    CT EvalBootstrap(const CT &c, uint32_t numIterations = 1, uint32_t precision = 0) {
+        (void)numIterations, (void)precision;
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_bootstrap(ctx, c->h, &o));
+        return wrap(o);
     }
 
     // ---- encode / encrypt / decrypt (src/encryption.cpp:5-27)

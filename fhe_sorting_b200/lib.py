@@ -69,6 +69,30 @@ def params_chain(logn, depth, scale_bits=40, first_bits=60, dnum=3):
     return [int(x) for x in mod[:F]], [int(x) for x in psi[:F]], nq.value, npp.value, al.value
 
 
+def bootstrap_plan_info(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale, correction=12):
+    """Host-only: depth, K, double-angle count, rotation indices and Chebyshev series of the bootstrapping plan."""
+    L = load()
+    depth, K, r, nrot, ncheb = (C.c_int() for _ in range(5))
+    rots = (C.c_int * 4096)()
+    cheb = (C.c_double * 1024)()
+    _ck(L.fheb200_bootstrap_plan_info(ring_dim, slots, budget_enc, budget_dec, C.c_double(q0), C.c_double(raise_scale),
+                                      correction, C.byref(depth), C.byref(K), C.byref(r), rots, 4096, C.byref(nrot), cheb,
+                                      1024, C.byref(ncheb)))
+    return dict(depth=depth.value, K=K.value, r=r.value, rotations=list(rots[:nrot.value]),
+                cheb=np.array(cheb[:ncheb.value]))
+
+
+def bootstrap_plan_apply(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale, which, values, correction=12):
+    """Host-only: the plan's CoeffsToSlots (which=0) / SlotsToCoeffs (which=1) on 2*slots complex values, in the clear."""
+    L = load()
+    v = np.ascontiguousarray(np.asarray(values, dtype=np.complex128))
+    assert v.shape == (2 * slots,)
+    out = np.zeros_like(v)
+    _ck(L.fheb200_bootstrap_plan_apply(ring_dim, slots, budget_enc, budget_dec, C.c_double(q0), C.c_double(raise_scale),
+                                       correction, which, v.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
 class _Handle:
     _release = None
 
@@ -278,6 +302,26 @@ class Context(_Handle):
     def poly(self, x, coeffs):
         v = np.ascontiguousarray(np.asarray(coeffs, dtype=np.float64))
         return self._un("fheb200_eval_poly", x, v.ctypes.data_as(C.c_void_p), C.c_size_t(len(v)))
+
+    # -- bootstrapping
+    def bootstrap_setup(self, budget=(4, 4), slots=0):
+        _ck(_lib.fheb200_eval_bootstrap_setup(self.h, int(budget[0]), int(budget[1]), int(slots)))
+
+    def bootstrap_keygen(self, keys, slots=0):
+        _ck(_lib.fheb200_eval_bootstrap_keygen(self.h, keys.h, int(slots)))
+
+    def bootstrap(self, a, stop_after=0):
+        if stop_after:
+            return self._un("fheb200_eval_bootstrap_partial", a, C.c_int(stop_after))
+        return self._un("fheb200_eval_bootstrap", a)
+
+    def bootstrap_depth(self, slots=0):
+        d = C.c_int()
+        _ck(_lib.fheb200_bootstrap_depth(self.h, int(slots), C.byref(d)))
+        return d.value
+
+    def conjugate(self, a):
+        return self._un("fheb200_eval_conjugate", a)
 
     # -- raw RNS access (parity tests)
     def ct_export(self, ct, out=None):

@@ -134,6 +134,32 @@ int fheb200_eval_poly(fheb200_ctx *ctx, fheb200_ct *x, const double *coeffs, siz
 /* lbcrypto::EvalChebyshevCoefficients(f, a, b, degree) (utils/generate_cheb_coeffs.cpp:17); host only */
 int fheb200_chebyshev_coefficients(double (*f)(double, void *), void *user, double a, double b, int degree, double *out);
 
+/* ---- bootstrapping (sparsely packed ciphertexts, 2 * slots <= ring_dim / 2; uniform ternary secret) ---- */
+/* EvalBootstrapSetup(levelBudget, bsgsDim, slots) (tests/k-way/KWaySort2Test.cpp:42-43): budgets are the levels spent on
+ * CoeffsToSlots / SlotsToCoeffs (clamped to log2 slots); bsgsDim is not needed (every group has <= 2^(stages+1) diagonals,
+ * evaluated with one hoisted ModUp).  slots = 0 selects the context's batch size. */
+int fheb200_eval_bootstrap_setup(fheb200_ctx *ctx, int budget_enc, int budget_dec, int slots);
+/* EvalBootstrapKeyGen(secretKey, slots) (tests/k-way/KWaySort2Test.cpp:44): rotation keys of the plan + the conjugation key */
+int fheb200_eval_bootstrap_keygen(fheb200_ctx *ctx, fheb200_keys *k, int slots);
+/* EvalBootstrap(ct) (src/k-way/EvalUtils.cpp:76 ; src/sign.cpp:168 ; src/sort_algo.h:1111).  The input needs one level
+ * left (GetLevel() < multiplicative depth, or a pending rescale); the output is at level fheb200_bootstrap_depth - 1 with
+ * noise scale degree 2. */
+int fheb200_eval_bootstrap(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
+int fheb200_bootstrap_depth(fheb200_ctx *ctx, int slots, int *levels);
+/* test hook: the intermediate ciphertext after step 1 (scale-down to q_0), 2 (ModRaise + SubSum), 3 (CoeffsToSlots +
+ * conjugate), 4 (EvalMod); 0 = the whole bootstrapping */
+int fheb200_eval_bootstrap_partial(fheb200_ctx *ctx, fheb200_ct *a, int stop_after, fheb200_ct **out);
+/* slot-wise complex conjugation (Galois element 2 * ring_dim - 1; key made by fheb200_eval_bootstrap_keygen) */
+int fheb200_eval_conjugate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
+/* host only (no GPU): the bootstrapping plan for a parameter set - depth, the range K of the overflow polynomial, the
+ * number of double-angle steps, the rotation indices and the Chebyshev series; and the plan's CoeffsToSlots (which = 0)
+ * or SlotsToCoeffs (which = 1) applied to 2 * slots complex values in the clear (re, im interleaved) */
+int fheb200_bootstrap_plan_info(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
+                                int correction, int *depth, int *k_range, int *double_angles, int *rotations, int capacity,
+                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb);
+int fheb200_bootstrap_plan_apply(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
+                                 int correction, int which, const double *in_re_im, double *out_re_im);
+
 /* ---- multi-GPU combine of partial ciphertexts: the device buffer [2][limbs][n] of a ciphertext, to be
  * summed element-wise across ranks as 64-bit integers (NCCL all-reduce; <= 16 summands of < 2^60 cannot wrap), then
  * brought back to [0, q_limb) by fheb200_ct_reduce_partial_sums.  The caller orders the streams (fheb200_ctx_sync). */

@@ -1,0 +1,103 @@
+"""CKKS bootstrapping on the B200 engine, checked step by step against what each step must hold in the clear
+(EvalBootstrapSetup / EvalBootstrapKeyGen / EvalBootstrap, reference call sites tests/k-way/KWaySort2Test.cpp:42-44,
+src/k-way/EvalUtils.cpp:57-86).  Parameters as the k-way fixture: first modulus 60 bits, scaling 59 bits."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from test_bootstrap_plan import bitrev, special_matrix  # noqa: E402
+
+CORRECTION = 12  # BootPlan::correction default (FHEB200_BOOT_CORRECTION)
+
+
+def make(logn, depth, slots, budget, seed=5):
+    import fhe_sorting_b200 as F
+    ctx = F.Context(logn, depth, 59, 60, batch=slots)
+    keys = ctx.keygen(seed)
+    ctx.eval_mult_keygen(keys)
+    ctx.bootstrap_setup(budget, slots)
+    ctx.bootstrap_keygen(keys, slots)
+    return ctx, keys
+
+
+@pytest.fixture(scope="module")
+def env():
+    return make(12, 26, 8, (2, 2))
+
+
+def deep(ctx, keys, v, slots, levels):
+    """an encryption of v pushed down to `levels` consumed levels by multiplications with 1.0"""
+    c = ctx.encrypt(keys, ctx.make_plaintext(v, 1, 0, slots))
+    while c.level < levels:
+        c = ctx.mult(c, 1.0)
+    return c
+
+
+def test_bootstrap_steps(env):
+    ctx, keys = env
+    s, K = 8, 512
+    z = np.array([0.5, -0.25, 0.125, 0.9, -0.7, 0.0, 0.33, -0.6])
+    c = deep(ctx, keys, z, s, ctx.depth - 1)
+    assert ctx.bootstrap_depth(s) == 1 + 2 + 7 + 6 + 2
+    # step 1: one limb, message intact under the small scale q0 2^-c
+    c1 = ctx.bootstrap(c, 1)
+    i1 = c1.info()
+    assert i1["limbs"] == 1 and abs(i1["scale"] / (ctx.moduli[0] * 2.0 ** -CORRECTION) - 1) < 1e-9
+    assert np.abs(ctx.decrypt(keys, c1, s) - z).max() < 1e-6
+    # step 3: slots = t / (q0 K) with t = msg_scale m + q0 I: the fractional part of K x carries the coefficients
+    w = np.linalg.solve(special_matrix(s), z.astype(complex))
+    br = bitrev(s)
+    coef = np.concatenate([w.real[br], w.imag[br]])
+    c3 = ctx.bootstrap(c, 3)
+    assert c3.info()["slots"] == 2 * s
+    x = ctx.decrypt(keys, c3, 2 * s)
+    assert np.abs(x).max() < 1.0
+    frac = K * x - np.round(K * x)
+    assert np.abs(frac * 2.0 ** CORRECTION - coef).max() < 1e-4
+    # step 4: sin(2 pi t / q0) ~ 2 pi 2^-c m
+    y = ctx.decrypt(keys, ctx.bootstrap(c, 4), 2 * s)
+    assert np.abs(y / (2 * np.pi * 2.0 ** -CORRECTION) - coef).max() < 1e-4
+    # whole thing
+    out = ctx.bootstrap(c)
+    io = out.info()
+    assert io["slots"] == s and io["level"] + io["nsd"] - 1 == ctx.bootstrap_depth(s)
+    err = np.abs(ctx.decrypt(keys, out, s) - z).max()
+    print("bootstrap max error 2^%.1f, output level %d" % (np.log2(err), io["level"]))
+    assert err < 2.0 ** -16
+
+
+def test_bootstrap_then_compute(env):
+    ctx, keys = env
+    s = 8
+    z = np.linspace(0.05, 0.95, s)
+    c = deep(ctx, keys, z, s, ctx.depth - 1)
+    b = ctx.bootstrap(c)
+    sq = ctx.mult(ctx.mult(b, b), b)
+    assert np.abs(ctx.decrypt(keys, sq, s) - z ** 3).max() < 1e-4
+    # a second bootstrapping of a bootstrapped value
+    d = b
+    while d.level < ctx.depth - 1:
+        d = ctx.mult(d, 1.0)
+    b2 = ctx.bootstrap(d)
+    assert np.abs(ctx.decrypt(keys, b2, s) - z).max() < 1e-4
+
+
+def test_bootstrap_refuses_without_spare_level(env):
+    import fhe_sorting_b200 as F
+    ctx, keys = env
+    c = deep(ctx, keys, np.zeros(8), 8, ctx.depth)   # last level with a pending rescale: nothing left to scale down with
+    assert c.info()["nsd"] == 2 and c.info()["limbs"] == 2
+    with pytest.raises(F.FheError):
+        ctx.bootstrap(c)
+
+
+@pytest.mark.parametrize("logn,slots,budget", [(13, 64, (3, 3)), (14, 1024, (5, 5))])
+def test_bootstrap_sizes(logn, slots, budget):
+    ctx, keys = make(logn, 1 + budget[0] + 13 + budget[1] + 3, slots, budget, seed=9)
+    z = np.random.default_rng(slots).uniform(0, 1, slots)
+    c = deep(ctx, keys, z, slots, ctx.depth - 1)
+    out = ctx.bootstrap(c)
+    err = np.abs(ctx.decrypt(keys, out, slots) - z).max()
+    print("slots %d: bootstrap max error 2^%.1f" % (slots, np.log2(err)))
+    assert err < 2.0 ** -13
