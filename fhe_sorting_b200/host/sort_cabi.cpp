@@ -21,9 +21,11 @@
 #ifdef REFERENCE_DRIVERS
 #include <sort_algo.h>
 #include <mehp24/mehp24_sort.h>
+#include <kway_adapter.h>
 #else
 #include "sort_algo.h"
 #include "mehp24.h"
+#include "kway_adapter.h"
 #endif
 
 namespace {
@@ -43,6 +45,8 @@ struct SessionBase {
     virtual Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) = 0;
     virtual void shard(int rank, int world) = 0;
     virtual void streams(int) {}
+    virtual bool own_sign_config(int, int, int, SignConfig &) { return false; }
+    virtual int bootstraps() const { return 0; }
 };
 template <int N> struct Session : SessionBase {
     std::unique_ptr<DirectSort<N>> sorter;
@@ -128,6 +132,83 @@ SessionBase *make_mehp24_session(int N, int log_ring_dim, int depth_override, ui
     return s.release();
 }
 
+// HKC+21 k-way sorting network (reference fixture: tests/k-way/KWaySort2Test.cpp:14-58, KWaySort3Test.cpp): ring 2^17,
+// depth 40, first modulus 60, scaling 59, rotation keys +-2^i, EvalBootstrapSetup(levelBudget, {0,0}, slots) + KeyGen
+template <int N> struct KWaySession : SessionBase {
+    std::unique_ptr<KWayAdapter<N>> sorter;
+    int k = 2, M = 1;
+    Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        return sorter->sort(in, SignFunc::CompositeSign, cfg);
+    }
+    Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("k-way: sort only"); }
+    Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &, const Ciphertext<DCRTPoly> &) override {
+        throw std::runtime_error("k-way: sort only");
+    }
+    Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &, int) override { throw std::runtime_error("k-way: sort only"); }
+    void shard(int, int world) override {
+        if (world > 1) throw std::runtime_error("k-way: the stages of the network are sequential (replicas only)");
+    }
+    // The reference tests build CompositeSignConfig(3, d_f, d_g) for a constructor that reads (n, dg, df)
+    // (tests/k-way/KWaySort2Test.cpp:149 vs src/sign.h:17): the network really runs dg = 2 and df = the table's d_g.
+    bool own_sign_config(int n, int dg, int df, SignConfig &out) override {
+        if (n == 0) {
+            const int table = k == 2 ? (N <= 16 ? 2 : N <= 128 ? 3 : N <= 512 ? 4 : 5)
+                            : k == 3 ? (N <= 9 ? 2 : N <= 81 ? 3 : N <= 243 ? 4 : 5) : (N <= 125 ? 3 : 4);
+            n = 3, dg = 2, df = table;
+        }
+        out = SignConfig(CompositeSignConfig(n, dg, df), depth);
+        return true;
+    }
+#ifndef REFERENCE_DRIVERS
+    int bootstraps() const override { return sorter->bootstraps(); }
+#endif
+};
+template <int N> SessionBase *make_kway_session(int k, int M, int log_ring_dim, int depth_override, uint64_t seed, int device) {
+    auto t0 = std::chrono::steady_clock::now();
+    auto s = std::make_unique<KWaySession<N>>();
+    s->k = k, s->M = M;
+    CCParams<CryptoContextCKKSRNS> p;
+    std::vector<uint32_t> levelBudget;
+    KWayAdapter<N>::getSizeParameters(p, s->rotations, levelBudget);
+    p.SetRingDim(1u << log_ring_dim);
+    if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
+    p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
+    if (seed) CryptoContextImpl::SetKeySeed(seed);
+#ifdef REFERENCE_DRIVERS
+    setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
+    s->cc = GenCryptoContext(p);
+#else
+    s->cc = GenCryptoContext(p, device);
+#endif
+    s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE), s->cc->Enable(FHE);
+    const uint32_t slots = s->cc->GetEncodingParams()->GetBatchSize();
+    s->keys = s->cc->KeyGen();
+    s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
+    s->cc->EvalMultKeyGen(s->keys.secretKey);
+    s->cc->EvalBootstrapSetup(levelBudget, {0, 0}, slots);
+    s->cc->EvalBootstrapKeyGen(s->keys.secretKey, slots);
+    s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);
+    s->sorter = std::make_unique<KWayAdapter<N>>(s->cc, s->keys.publicKey, s->keys.secretKey, s->enc, k, M);
+    s->len = N, s->depth = (int)p.GetMultiplicativeDepth();
+    s->cc->Sync();
+    s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s.release();
+}
+SessionBase *make_kway_session_for(int k, int M, int log_ring_dim, int depth_override, uint64_t seed, int device) {
+    long N = 1;
+    for (int i = 0; i < M; i++) N *= k;
+#define KWAY_CASE(n) case n: return make_kway_session<n>(k, M, log_ring_dim, depth_override, seed, device);
+    switch (N) {
+        KWAY_CASE(4) KWAY_CASE(8) KWAY_CASE(16) KWAY_CASE(32) KWAY_CASE(64) KWAY_CASE(128) KWAY_CASE(256) KWAY_CASE(512) KWAY_CASE(1024)
+        KWAY_CASE(9) KWAY_CASE(27) KWAY_CASE(81) KWAY_CASE(243) KWAY_CASE(729)
+#ifdef REFERENCE_DRIVERS
+        KWAY_CASE(25) KWAY_CASE(125) KWAY_CASE(625)
+#endif
+    default: throw std::invalid_argument("k-way: array length k^M must be one of 4..1024 (k = 2), 9..729 (k = 3)");
+    }
+#undef KWAY_CASE
+}
+
 template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
     auto t0 = std::chrono::steady_clock::now();
     auto s = std::make_unique<Session<N>>();
@@ -209,6 +290,20 @@ int fhesort_mehp24_session_create(int N, int log_ring_dim, int mult_depth, uint6
         *out = new fhesort_session{std::unique_ptr<SessionBase>(make_mehp24_session(N, log_ring_dim, mult_depth, seed, device))};
     })
 }
+int fhesort_kway_session_create(int k, int M, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out) throw std::invalid_argument("null argument: out");
+        if (k != 2 && k != 3 && k != 5) throw std::invalid_argument("k-way: k must be 2, 3 or 5");
+        if (M < 1 || M > 10) throw std::invalid_argument("k-way: M out of range");
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(make_kway_session_for(k, M, log_ring_dim, mult_depth, seed, device))};
+    })
+}
+int fhesort_session_bootstraps(fhesort_session *s, int *count) {
+    GUARD({
+        if (!s || !count) throw std::invalid_argument("null argument");
+        *count = s->s->bootstraps();
+    })
+}
 int fhesort_session_free(fhesort_session *s) {
     GUARD({ delete s; })
 }
@@ -250,6 +345,7 @@ int fhesort_run(fhesort_session *s, int which, const double *input, const double
         SessionBase &S = *s->s;
         std::vector<double> in(input, input + S.len);
         SignConfig cfg = sign_config(sign_n, dg, df, S.len);
+        S.own_sign_config(sign_n, dg, df, cfg);
         S.cc->Sync();
         auto t0 = std::chrono::steady_clock::now();
         auto ct = S.enc->encryptInput(in);
@@ -316,6 +412,21 @@ int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out
     })
 }
 #endif
+// host-only: the network geometry of one k-way stage (kwaySort::sortType / genIndices / getRotateDistance); built from
+// this repository's kway.h in libfhesort.so and from the reference's src/k-way/Masking.cpp in oracle/_ref/libref_sort.so
+int fhesort_kway_stage(int k, int M, int stage, int num_slots, int *geometry4, int *indices0, int *indices1) {
+    GUARD({
+        if (!geometry4) throw std::invalid_argument("null argument: geometry");
+        auto t = kwaySort::sortType(k, M, stage);
+        const int m = std::get<0>(t), logDist = std::get<1>(t), slope = std::get<2>(t);
+        geometry4[0] = m, geometry4[1] = logDist, geometry4[2] = slope;
+        geometry4[3] = (int)kwaySort::getRotateDistance(k, logDist, slope);
+        if (indices0 && indices1) {
+            auto idx = kwaySort::genIndices(num_slots, k, M, m, logDist, slope);
+            for (int i = 0; i < num_slots; i++) indices0[i] = idx[0][i], indices1[i] = idx[1][i];
+        }
+    })
+}
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity, int *count) {
     GUARD({
         Decomposer<1024> d(std::vector<int>(key_indices, key_indices + num_keys));

@@ -185,3 +185,36 @@ class Mehp24SortSession(DirectSortSession):
     """tests/mehp24/Mehp24SortTest.cpp's fixture: N values in the first row of an N x N slot matrix, mehp24::sortFG
     (sortLargeArrayFG above 256 values).  Only sort() applies."""
     _create = "fhesort_mehp24_session_create"
+
+
+class KWaySortSession(DirectSortSession):
+    """tests/k-way/KWaySort2Test.cpp's fixture: the HKC+21 k-way sorting network on N = k^M values with bootstrapping
+    (depth 40, first modulus 60, scaling 59 bits, EvalBootstrapSetup + KeyGen).  Only sort() applies."""
+
+    def __init__(self, k, m, log_ring_dim=17, mult_depth=0, seed=1, device=0, drivers="ours"):
+        L = self.L = load_sort(drivers)
+        h = C.c_void_p()
+        _ck(L.fhesort_kway_session_create(k, m, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
+        self.h, self.n, self.k, self.m = h, k ** m, k, m
+        d, nk, ms = C.c_int(), C.c_int(), C.c_double()
+        _ck(L.fhesort_session_info(h, C.byref(d), C.byref(nk), C.byref(ms)), L)
+        self.mult_depth, self.num_rotation_keys, self.setup_ms = d.value, nk.value, ms.value
+
+    def bootstraps(self):
+        c = C.c_int()
+        _ck(self.L.fhesort_session_bootstraps(self.h, C.byref(c)), self.L)
+        return c.value
+
+
+def kway_stage(k, m_total, stage, num_slots, drivers="ours"):
+    """(m, logDist, slope, rotate distance), indices[2][num_slots] of one stage of the k-way network (host only)."""
+    L = load_sort(drivers)
+    geo = (C.c_int * 4)()
+    i0 = np.zeros(num_slots, dtype=np.int32)
+    i1 = np.zeros(num_slots, dtype=np.int32)
+    _ck(L.fhesort_kway_stage(k, m_total, stage, num_slots, geo, i0.ctypes.data_as(C.c_void_p), i1.ctypes.data_as(C.c_void_p)), L)
+    return tuple(geo), np.stack([i0, i1])
+
+
+def kway_num_stages(k, m_total):
+    return m_total + m_total * (m_total - 1) // 2 * ((k + 1) // 2)

@@ -22,6 +22,14 @@ int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t see
  * rotation keys of mehp24::utils::getRotationIndices(N)); fhesort_run stage 0 runs mehp24::sortFG (N <= 256) or
  * sortLargeArrayFG (src/mehp24/mehp24_sort.cpp:246, 609) with dg_i = (log2 N + 1) / 2, df_i = 2. */
 int fhesort_mehp24_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
+/* HKC+21 k-way sorting network session (tests/k-way/KWaySort2Test.cpp:14-58): N = k^M values, batch = next power of two,
+ * ring 2^log_ring_dim, depth 40 (mult_depth = 0), first modulus 60 / scaling 59 bits, rotation keys +-2^i < N,
+ * EvalBootstrapSetup({4,4} or {5,5}) + EvalBootstrapKeyGen; fhesort_run stage 0 runs KWayAdapter<N>::sort
+ * (src/kway_adapter.h:66) with bootstrapping enabled (SignConfig(compos, depth)); sign_n = 0 selects the configuration
+ * the reference tests really run (dg = 2, df = the test table's d_g).  k = 2 or 3 (k = 5: not built). */
+int fhesort_kway_session_create(int k, int M, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
+/* EvalBootstrap calls made by the network's level guards so far (the sign's own lazy bootstraps are not counted) */
+int fhesort_session_bootstraps(fhesort_session *s, int *count);
 int fhesort_session_free(fhesort_session *s);
 int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_keys, double *setup_ms);
 /* encrypt(input[N]) -> stage -> decrypt(output[N]).  stage 0: DirectSort<N>::sort (src/sort_algo.h:752) ;
@@ -41,6 +49,9 @@ int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, 
 /* host-only (no GPU needed) */
 int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count);
 int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out, int capacity, int *count, int *sharded);
+/* k-way network geometry of one stage: geometry4 = (m, logDist, slope, rotate distance); indices0/1[num_slots] = sorter size
+ * and 1-based position of every slot (src/k-way/Masking.cpp:26-167) */
+int fhesort_kway_stage(int k, int M, int stage, int num_slots, int *geometry4, int *indices0, int *indices1);
 int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wrap, int algo, int *steps, int capacity,
                       int *count);
 int fhesort_doubled_sinc_coefficients(int N, double *out, int capacity, int *count);

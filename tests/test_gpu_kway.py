@@ -1,0 +1,58 @@
+"""HKC+21 k-way sorting network with bootstrapping on the B200 engine (reference fixture and pass criterion:
+tests/k-way/KWaySort2Test.cpp:14-58, 137-190 and KWaySort3Test.cpp — max error < 0.01 against std::sort)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from fhe_sorting_b200 import sort as S  # noqa: E402
+
+
+def gap_input(n, seed):
+    """tests/k-way/KWaySort2Test.cpp:137 getVectorWithMinDiff(N, 0, 1, (1 - 1e-8) / N), seeded"""
+    rng = np.random.default_rng(seed)
+    return rng.permutation(n).astype(np.float64) * ((1 - 1e-8) / n)
+
+
+@pytest.mark.parametrize("k,m", [(2, 2), (2, 3), (2, 4), (3, 2)])
+def test_kway_sort_small_ring(k, m):
+    s = S.KWaySortSession(k, m, log_ring_dim=12, seed=3)
+    assert s.mult_depth == 40
+    x = gap_input(k ** m, 7)
+    out, ms, level = s.sort(x)
+    err = np.abs(out - np.sort(x)).max()
+    print("k=%d M=%d: %.0f ms, %d guard bootstraps, level %d, max error 2^%.1f" % (k, m, ms, s.bootstraps(), level, np.log2(err)))
+    assert err < 0.01
+    s.close()
+
+
+def test_kway_reference_drivers_unmodified_on_the_engine():
+    """the reference's own src/k-way/*.cpp + kway_adapter.h (oracle/_ref/libref_sort.so) against this repository's kway.h"""
+    if not os.path.exists(S.REFERENCE_DRIVERS_PATH):
+        pytest.skip("oracle/_ref/libref_sort.so not built (needs /root/reference at build time)")
+    x = gap_input(8, 11)
+    outs = {}
+    for drivers in ("ours", "reference"):
+        s = S.KWaySortSession(2, 3, log_ring_dim=12, seed=3, drivers=drivers)
+        outs[drivers] = s.sort(x)[0]
+        s.close()
+    assert np.abs(outs["reference"] - np.sort(x)).max() < 0.01
+    assert np.abs(outs["ours"] - outs["reference"]).max() < 1e-3
+    # k = 5 exists only in the reference's drivers; it must run on the engine too
+    s = S.KWaySortSession(5, 2, log_ring_dim=12, seed=3, drivers="reference")
+    x = gap_input(25, 5)
+    assert np.abs(s.sort(x)[0] - np.sort(x)).max() < 0.01
+    s.close()
+
+
+def test_kway_full_parameters():
+    """BASELINE config 5 parameter set (ring 2^17, 128-bit, depth 40, 59-bit scaling) at N = 16"""
+    s = S.KWaySortSession(2, 4, log_ring_dim=17, seed=5)
+    x = gap_input(16, 3)
+    out, ms, level = s.sort(x)
+    err = np.abs(out - np.sort(x)).max()
+    print("ring 2^17 N=16: %.0f ms, max error 2^%.1f, level %d" % (ms, np.log2(err), level))
+    assert err < 0.01
+    s.close()
