@@ -218,7 +218,52 @@ def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)
                          "final_level": level, "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys,
                          "sharded_over_ranks": False}
     s.close()
+    # HKC+21 k-way sorting network with bootstrapping, k = 2, N = 1024 (BASELINE.json config 5; tests/k-way/KWaySort2Test.cpp:
+    # ring 2^17, depth 40, 59-bit scaling, 1024 slots, level budget {5,5}): 55 strictly sequential stages on one
+    # ciphertext -> "replicas only"; one warm-up sort (it encodes the bootstrapping diagonals), one timed sort
+    from fhe_sorting_b200.sort import KWaySortSession
+    s = KWaySortSession(2, 10, 17, seed=SEED + 2, device=local_rank)
+    x = np.random.default_rng(1024).permutation(1024) * ((1 - 1e-8) / 1024)  # KWaySort2Test.cpp:137
+    s.sort(x)
+    barrier()
+    t0 = time.perf_counter()
+    res, _, level = s.sort(x)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    out["kway2_1024"] = {"seconds": float(dt.item()), "runs": [float(dt.item())],
+                         "max_abs_err": float(np.abs(res - np.sort(x)).max()), "final_level": level,
+                         "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys, "sharded_over_ranks": False,
+                         "guard_bootstraps_per_sort": s.bootstraps() // 2,
+                         "reference_cpu_seconds_published": 5732.0}
+    s.close()
+    out["bootstrap_1024_slots"] = bootstrap_latency(local_rank)
     return out
+
+
+def bootstrap_latency(device):
+    """EvalBootstrap at the k-way parameter set (ring 2^17, depth 40, 59-bit scaling, 1024 slots, budget {5,5}): mean
+    latency of 5 calls on a ciphertext at the second-to-last level, and the error against the encrypted values."""
+    import fhe_sorting_b200 as F
+    ctx = F.Context(17, 40, 59, 60, batch=1024, device=device)
+    keys = ctx.keygen(SEED)
+    ctx.eval_mult_keygen(keys)
+    ctx.bootstrap_setup((5, 5), 1024)
+    ctx.bootstrap_keygen(keys, 1024)
+    z = np.random.default_rng(1).uniform(0, 1, 1024)
+    ct = ctx.encrypt(keys, ctx.make_plaintext(z, 1, 0, 1024))
+    while ct.level < ctx.depth - 1:
+        ct = ctx.mult(ct, 1.0)
+    o = ctx.bootstrap(ct)
+    ctx.sync()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        o = ctx.bootstrap(ct)
+    ctx.sync()
+    ms = (time.perf_counter() - t0) / 5 * 1e3
+    err = float(np.abs(ctx.decrypt(keys, o, 1024) - z).max())
+    return {"ms": ms, "max_abs_err": err, "levels_consumed": ctx.bootstrap_depth(1024), "output_level": o.level,
+            "key_bytes_resident": ctx.key_bytes()}
 
 
 def run_ours(args, rank, world, local_rank):

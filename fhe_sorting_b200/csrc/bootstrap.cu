@@ -8,7 +8,9 @@
 //   5. EvalMod: Chebyshev series of cos(2 pi (K u - 1/4) / 2^r) by Paterson-Stockmeyer, then r double-angle steps
 //   6. SlotsToCoeffs, + rotate by s
 // Reference call sites: src/k-way/EvalUtils.cpp:57-86 (checkLevelAndBoot), src/sign.cpp:163-170 (lazyBootstrap).
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <stdexcept>
 
@@ -32,7 +34,7 @@ void Context::bootstrap_setup(int budget_enc, int budget_dec, int slots) {
     if (slots <= 0) slots = batch;
     auto B = std::make_shared<BootState>();
     B->plan = make_boot_plan(P->n, slots, budget_enc, budget_dec, (double)P->moduli[0], P->sf[RAISE_LEVEL],
-                             env_int("FHEB200_BOOT_CORRECTION", 12));
+                             env_int("FHEB200_BOOT_CORRECTION", 10));
     if (RAISE_LEVEL + B->plan.depth() > P->depth)
         throw std::invalid_argument("EvalBootstrapSetup: multiplicative depth " + std::to_string(P->depth) +
                                     " is below the bootstrapping depth " + std::to_string(RAISE_LEVEL + B->plan.depth()));
@@ -143,6 +145,18 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
     const BootPlan &bp = B.plan;
     const int n = P->n;
     static const bool verbose = getenv("FHEB200_BOOT_VERBOSE") != nullptr;
+    // FHEB200_BOOT_VERBOSE: synchronised wall time and kernel launches of every phase
+    auto t_last = std::chrono::steady_clock::now();
+    unsigned long long l_last = g_launches.load();
+    auto phase = [&](const char *name, const Ct &c) {
+        if (!verbose) return;
+        sync();
+        auto now = std::chrono::steady_clock::now();
+        unsigned long long l = g_launches.load();
+        fprintf(stderr, "bootstrap %-14s %8.2f ms %6llu launches -> level %d nsd %d limbs %d\n", name,
+                std::chrono::duration<double, std::milli>(now - t_last).count(), l - l_last, c->level, c->nsd, c->ell);
+        t_last = now, l_last = l;
+    };
 
     // 1. last two limbs -> one limb carrying msg_scale * m
     Ct x = a->nsd == 2 ? reduced(a) : a;
@@ -159,33 +173,37 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
         y->scale = x->scale * (double)roundl(mult);
         x = mod_reduce(y); // scale == msg_scale up to 2^-40 relative
     }
+    phase("scale-down", x);
     if (stop_after == 1) return x;
     // 2. ModRaise
     Ct r = mod_raise(x, P->L - RAISE_LEVEL, bp.raise_scale);
     r->slots = 2 * slots;
+    phase("ModRaise", r);
     // 3. SubSum
     for (int step = slots; step < n / 2; step <<= 1) r = add(r, rotate(r, step));
+    phase("SubSum", r);
     if (stop_after == 2) return r;
     // 4. CoeffsToSlots + conjugate
     for (size_t i = 0; i < bp.cts.size(); i++) r = linear_stage(r, bp.cts[i], B.cts_pt[i]);
     r = reduced(r);
     r = add(r, conjugate(r));
-    if (verbose) fprintf(stderr, "bootstrap: after CoeffsToSlots level %d\n", r->level);
+    phase("CoeffsToSlots", r);
     if (stop_after == 3) return r;
     // 5. EvalMod
     r = eval_chebyshev(r, bp.cheb, -1.0, 1.0);
+    phase("Chebyshev", r);
     for (int i = 0; i < bp.r; i++) {
         Ct sq = mult(r, r);
         r = add_const(add(sq, sq), -1.0);
     }
-    if (verbose) fprintf(stderr, "bootstrap: after EvalMod level %d nsd %d\n", r->level, r->nsd);
+    phase("double-angle", r);
     if (stop_after == 4) return r;
     // 6. SlotsToCoeffs + fold of the two halves
     for (size_t i = 0; i < bp.stc.size(); i++) r = linear_stage(r, bp.stc[i], B.stc_pt[i]);
     r = add(r, rotate(r, slots));
     if (r.use_count() > 1) r = std::make_shared<Ciphertext>(*r);
     r->slots = slots;
-    if (verbose) fprintf(stderr, "bootstrap: done at level %d nsd %d\n", r->level, r->nsd);
+    phase("SlotsToCoeffs", r);
     return r;
 }
 

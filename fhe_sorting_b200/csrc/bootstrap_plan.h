@@ -23,7 +23,7 @@ struct BootPlan {
     int K = 512;          // |I| < K for the overflow polynomial of a uniform ternary secret at ring_dim <= 2^17
     int r = 6;            // double-angle iterations
     int degree = 88;      // Chebyshev degree of cos(2 pi (K u - 1/4) / 2^r) on [-1, 1]
-    int correction = 12;  // the message is brought to q0 * 2^-correction before ModRaise
+    int correction = 10;  // the message is brought to q0 * 2^-correction before ModRaise
     double q0 = 0;        // first modulus
     double msg_scale = 0; // q0 * 2^-correction
     double raise_scale = 0; // scale label the raised ciphertext carries (sf of the level it is raised to)

@@ -8,7 +8,7 @@ pytestmark = pytest.mark.gpu
 
 from test_bootstrap_plan import bitrev, special_matrix  # noqa: E402
 
-CORRECTION = 12  # BootPlan::correction default (FHEB200_BOOT_CORRECTION)
+CORRECTION = 10  # BootPlan::correction default (FHEB200_BOOT_CORRECTION)
 
 
 def make(logn, depth, slots, budget, seed=5):
