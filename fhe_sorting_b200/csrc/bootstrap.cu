@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
+#include <string>
 
 #include "engine.h"
 
@@ -52,6 +53,7 @@ void Context::bootstrap_setup(int budget_enc, int budget_dec, int slots) {
         B->stc_pt.push_back(std::move(v));
         level++;
     }
+    B->cts_qp.resize(B->plan.cts.size()), B->stc_qp.resize(B->plan.stc.size());
     boot[slots] = B;
 }
 int Context::bootstrap_depth(int slots) const {
@@ -115,23 +117,85 @@ Ct Context::mod_raise(const Ct &a, int ell_out, double scale_label) {
     return r;
 }
 
-// out = sum_i diag_i (.) rotate(x, rot_i): the rotations of one stage share a hoisted ModUp; the products stay at degree 2
-// and are rescaled once by whoever multiplies next
-Ct Context::linear_stage(const Ct &x0, const BootStage &st, const std::vector<Pt> &diag) {
+Mem Context::encode_qp(const Plaintext &pt, int ell, double scale) {
+    LOCK;
+    if (pt.base || pt.real_only) throw std::logic_error("encode_qp: complex slot values expected");
+    const int n = P->n, slots = pt.slots, W = ell + P->K;
+    Mem vbuf = alloc((size_t)2 * slots);
+    const size_t nv = std::min((size_t)slots, pt.vals.size());
+    if (nv < (size_t)slots) FHE_CUDA(cudaMemsetAsync(vbuf->p, 0, sizeof(double2) * slots, stream));
+    if (nv) upload(vbuf->p, pt.vals.data(), sizeof(double2) * nv);
+    auto tabs = fft_device_tables(slots);
+    Mem out = alloc((size_t)W * n);
+    k_encode(T, (double2 *)vbuf->p, nullptr, (int)nv, slots, scale, tabs.first, tabs.second, ell, out->p, stream, P->L, P->K);
+    std::vector<uint32_t> d;
+    for (int t = 0; t < W; t++) d.push_back(((uint32_t)t << 8) | (uint32_t)(t < ell ? t : P->L + t - ell));
+    k_ntt_fwd(T, out->p, desc(d), W, stream);
+    return out;
+}
+
+// out = sum_i diag_i (.) rotate(x, rot_i).  The rotations of one stage share a hoisted ModUp.  With a QP cache (double
+// hoisting) the products are formed and summed in the extended basis - diag_i encoded on the P limbs too, the unrotated
+// c_b entering as P * c_b - and the stage pays for ONE ModDown instead of one per rotation.  The result stays at degree
+// 2 and is rescaled once by whoever multiplies next.
+Ct Context::linear_stage(const Ct &x0, const BootStage &st, const std::vector<Pt> &diag,
+                         std::vector<std::tuple<int, double, Mem>> *qp_cache) {
     LOCK;
     Ct x = x0->nsd == 2 ? reduced(x0) : x0;
-    std::shared_ptr<Precomp> pre;
-    Ct acc;
-    for (size_t i = 0; i < st.rot.size(); i++) {
-        Ct r = x;
-        if (st.rot[i] != 0) {
-            if (!pre) pre = fast_rotation_precompute(x);
-            r = fast_rotation(x, st.rot[i], pre);
+    static const bool single = [] { const char *e = getenv("FHEB200_BOOT_HOIST"); return e && std::string(e) == "single"; }();
+    if (single || !qp_cache || forked()) {
+        std::shared_ptr<Precomp> pre;
+        Ct acc;
+        for (size_t i = 0; i < st.rot.size(); i++) {
+            Ct r = x;
+            if (st.rot[i] != 0) {
+                if (!pre) pre = fast_rotation_precompute(x);
+                r = fast_rotation(x, st.rot[i], pre);
+            }
+            Ct t = mult_pt(r, diag[i]);
+            acc = acc ? add(acc, t) : t;
         }
-        Ct t = mult_pt(r, diag[i]);
-        acc = acc ? add(acc, t) : t;
+        return acc;
     }
-    return acc;
+    const int n = P->n, ell = x->ell, L = P->L, K = P->K;
+    const DevicePlan &D = plan(ell);
+    const int W = D.width;
+    const double ps = P->sf[x->level];
+    if (qp_cache->size() != diag.size()) qp_cache->assign(diag.size(), std::make_tuple(0, 0.0, Mem()));
+    // P * c_b on the Q limbs
+    LimbScalars pm;
+    memset(&pm, 0, sizeof(pm));
+    for (int i = 0; i < ell; i++) {
+        u64 q = P->moduli[i], v = 1;
+        for (int k = 0; k < K; k++) v = mulmod_h(v, P->moduli[L + k] % q, q);
+        pm.v[i] = v, pm.s[i] = shoup_h(v, q);
+    }
+    Mem cP = alloc((size_t)2 * ell * n), S = alloc((size_t)2 * W * n), acc = alloc((size_t)2 * W * n);
+    for (int b = 0; b < 2; b++) k_mul_scalar(T, ell, x->poly(b, n), pm, cP->p + (size_t)b * ell * n, stream);
+    FHE_CUDA(cudaMemsetAsync(S->p, 0, (size_t)2 * W * n * sizeof(u64), stream));
+    std::shared_ptr<Precomp> pre;
+    for (size_t i = 0; i < st.rot.size(); i++) {
+        auto &slot = (*qp_cache)[i];
+        if (!std::get<2>(slot) || std::get<0>(slot) != ell || std::get<1>(slot) != ps)
+            slot = std::make_tuple(ell, ps, encode_qp(*diag[i], ell, ps));
+        const u64 *pt = std::get<2>(slot)->p;
+        const uint32_t g = P->galois_for_rotation(st.rot[i]);
+        if (g == 1u) {
+            k_dh_accumulate(T, D, nullptr, cP->p, pt, S->p, 1u, stream);
+            continue;
+        }
+        auto it = evk_rot.find(g);
+        if (it == evk_rot.end()) throw std::runtime_error("EvalBootstrap: no evaluation key for rotation index " + std::to_string(st.rot[i]));
+        if (!pre) pre = fast_rotation_precompute(x);
+        k_inner_product(T, D, pre->digits->p, it->second, acc->p, stream);
+        k_dh_accumulate(T, D, acc->p, cP->p, pt, S->p, g, stream);
+    }
+    auto r = std::make_shared<Ciphertext>(*x);
+    r->mem = alloc((size_t)2 * ell * n);
+    moddown(ell, S->p, nullptr, nullptr, r->poly(0, n), r->poly(1, n), 1u);
+    r->nsd = x->nsd + 1;
+    r->scale = x->scale * ps;
+    return r;
 }
 
 Ct Context::bootstrap(const Ct &a, int stop_after) {
@@ -141,7 +205,7 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
     auto it = boot.find(slots);
     if (it == boot.end())
         throw std::runtime_error("EvalBootstrap: no EvalBootstrapSetup for " + std::to_string(slots) + " slots");
-    const BootState &B = *it->second;
+    BootState &B = *it->second;
     const BootPlan &bp = B.plan;
     const int n = P->n;
     static const bool verbose = getenv("FHEB200_BOOT_VERBOSE") != nullptr;
@@ -179,12 +243,13 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
     Ct r = mod_raise(x, P->L - RAISE_LEVEL, bp.raise_scale);
     r->slots = 2 * slots;
     phase("ModRaise", r);
+    if (stop_after == 5) return r;
     // 3. SubSum
     for (int step = slots; step < n / 2; step <<= 1) r = add(r, rotate(r, step));
     phase("SubSum", r);
     if (stop_after == 2) return r;
     // 4. CoeffsToSlots + conjugate
-    for (size_t i = 0; i < bp.cts.size(); i++) r = linear_stage(r, bp.cts[i], B.cts_pt[i]);
+    for (size_t i = 0; i < bp.cts.size(); i++) r = linear_stage(r, bp.cts[i], B.cts_pt[i], &B.cts_qp[i]);
     r = reduced(r);
     r = add(r, conjugate(r));
     phase("CoeffsToSlots", r);
@@ -199,7 +264,7 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
     phase("double-angle", r);
     if (stop_after == 4) return r;
     // 6. SlotsToCoeffs + fold of the two halves
-    for (size_t i = 0; i < bp.stc.size(); i++) r = linear_stage(r, bp.stc[i], B.stc_pt[i]);
+    for (size_t i = 0; i < bp.stc.size(); i++) r = linear_stage(r, bp.stc[i], B.stc_pt[i], &B.stc_qp[i]);
     r = add(r, rotate(r, slots));
     if (r.use_count() > 1) r = std::make_shared<Ciphertext>(*r);
     r->slots = slots;

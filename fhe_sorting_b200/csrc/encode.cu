@@ -78,7 +78,8 @@ __device__ __forceinline__ void double_to_i128(double x, u64 &lo, u64 &hi) {
 // coefficient j of the plaintext polynomial, on every limb: j = i * gap carries round(scale/size * Re or Im of slot
 // bitrev(i mod size)) (real parts first, then imaginary parts), every other coefficient is zero
 __global__ void __launch_bounds__(ENC_THREADS) enc_round_expand(DeviceTables T, const double2 *__restrict__ v, int logsize,
-                                                                double scale, int loggap, int ell, u64 *__restrict__ out) {
+                                                                double scale, int loggap, int ell, u64 *__restrict__ out,
+                                                                int extra_qp0, int extra) {
     const int j = blockIdx.x * ENC_THREADS + threadIdx.x;
     if (j >= T.n) return;
     const int size = 1 << logsize;
@@ -99,10 +100,10 @@ __global__ void __launch_bounds__(ENC_THREADS) enc_round_expand(DeviceTables T, 
         }
         live = (lo | hi) != 0;
     }
-    for (int limb = 0; limb < ell; limb++) {
+    for (int limb = 0; limb < ell + extra; limb++) { // limbs past ell: moduli extra_qp0.. (the P primes of a QP encoding)
         u64 r = 0;
         if (live) {
-            const ModConst m = T.mc[limb];
+            const ModConst m = T.mc[limb < ell ? limb : extra_qp0 + limb - ell];
             r = reduce128(hi, lo, m);
             if (neg) r = neg_mod(r, m.q);
         }
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(ENC_THREADS) enc_round_expand(DeviceTables T, 
 
 // v: device buffer of `size` double2 (work space; holds the complex slot values unless real_in is given)
 void k_encode(const DeviceTables &T, double2 *v, const double *real_in, int nv, int size, double scale, const double2 *ksi,
-              const int *rot, int ell, u64 *out, cudaStream_t st) {
+              const int *rot, int ell, u64 *out, cudaStream_t st, int extra_qp0, int extra) {
     int logsize = 0;
     while ((1 << logsize) < size) logsize++;
     int loggap = 0;
@@ -130,7 +131,7 @@ void k_encode(const DeviceTables &T, double2 *v, const double *real_in, int nv, 
     } else if (real_in) { // a single slot: no butterflies, just widen the value
         g_launches++, enc_fft_pass<<<1, ENC_THREADS, 0, st>>>(v, real_in, nv, 0, 0, 0, 0, 0, 0, ksi, rot);
     }
-    g_launches++, enc_round_expand<<<(T.n + ENC_THREADS - 1) / ENC_THREADS, ENC_THREADS, 0, st>>>(T, v, logsize, scale, loggap, ell, out);
+    g_launches++, enc_round_expand<<<(T.n + ENC_THREADS - 1) / ENC_THREADS, ENC_THREADS, 0, st>>>(T, v, logsize, scale, loggap, ell, out, extra_qp0, extra);
 }
 
 } // namespace fheb200

@@ -84,6 +84,9 @@ typedef std::shared_ptr<KeySet> Keys;
 struct BootState { // EvalBootstrapSetup result for one slot count: the plan and its diagonals as (lazily encoded) plaintexts
     BootPlan plan;
     std::vector<std::vector<Pt>> cts_pt, stc_pt;
+    // encodings of the diagonals over the extended basis (Q limbs of the level they are used at, then all P), filled on
+    // first use: [stage][diagonal] -> (limbs, scale, memory)
+    std::vector<std::vector<std::tuple<int, double, Mem>>> cts_qp, stc_qp;
 };
 
 struct Precomp { // EvalFastRotationPrecompute result: ModUp'ed digits of c1
@@ -153,7 +156,10 @@ class Context : public std::enable_shared_from_this<Context> {
     void gen_galois_keys(const Keys &k, const std::vector<uint32_t> &galois);
     Ct rotate_galois(const Ct &a, uint32_t g);
     Ct mod_raise(const Ct &a, int ell_out, double scale_label); // a: one limb; result on limbs 0..ell_out-1
-    Ct linear_stage(const Ct &x, const BootStage &st, const std::vector<Pt> &diag);
+    Ct linear_stage(const Ct &x, const BootStage &st, const std::vector<Pt> &diag,
+                    std::vector<std::tuple<int, double, Mem>> *qp_cache = nullptr);
+    Mem encode_qp(const Plaintext &pt, int ell, double scale);   // [ell + K][n]: Q limbs 0..ell-1, then the P limbs
+    void moddown(int ell, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois);
     std::map<int, std::shared_ptr<BootState>> boot;
 
     // ---- polynomial evaluation (poly_eval.cpp)

@@ -53,18 +53,24 @@ void Context::modup(int ell, const u64 *c, u64 *digits) {
 void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const u64 *add0, const u64 *add1, u64 *out0,
                                u64 *out1, uint32_t galois) {
     const DevicePlan &D = plan(ell);
-    const int n = P->n;
-    Mem acc = alloc((size_t)2 * D.width * n), conv = alloc((size_t)2 * ell * n);
+    Mem acc = alloc((size_t)2 * D.width * P->n);
     k_inner_product(T, D, digits, evk, acc->p, stream);
+    moddown(ell, acc->p, add0, add1, out0, out1, galois);
+}
+// acc[2][ell + K][n] (evaluation domain, overwritten) -> out_b = sigma_g(round(acc_b / P) + add_b) on the ell Q limbs
+void Context::moddown(int ell, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois) {
+    const DevicePlan &D = plan(ell);
+    const int n = P->n;
+    Mem conv = alloc((size_t)2 * ell * n);
     if (tensor_core_conv()) {
-        k_ntt_inv(T, acc->p, acc->p, D.desc_p2, 2 * D.K, stream, D.down_scale);
-        k_moddown_conv_tc(T, D, acc->p, conv->p, stream);
+        k_ntt_inv(T, acc, acc, D.desc_p2, 2 * D.K, stream, D.down_scale);
+        k_moddown_conv_tc(T, D, acc, conv->p, stream);
     } else {
-        k_ntt_inv(T, acc->p, D.desc_p2, 2 * D.K, stream);
-        k_moddown_conv(T, D, acc->p, conv->p, stream);
+        k_ntt_inv(T, acc, D.desc_p2, 2 * D.K, stream);
+        k_moddown_conv(T, D, acc, conv->p, stream);
     }
     k_ntt_fwd(T, conv->p, D.desc_q2, 2 * ell, stream);
-    k_moddown_finish(T, D, acc->p, conv->p, add0, add1, out0, out1, galois, stream);
+    k_moddown_finish(T, D, acc, conv->p, add0, add1, out0, out1, galois, stream);
 }
 
 Ct Context::rotate(const Ct &a, int index) {

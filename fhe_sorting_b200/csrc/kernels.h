@@ -128,6 +128,12 @@ void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, 
 void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *conv, const u64 *add0,
                       const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st);
 
+// double hoisting (bootstrapping's linear transforms): S_b[t][p] += pt[t][p] * v_b[t][sigma_g(p)] over the level limbs t of
+// the extended basis (Q 0..ell-1, then P), with v_0 = acc_0 + cP_0, v_1 = acc_1 (acc = an evk inner product) or, when acc
+// is null, v_b = cP_b; cP = P * c_b on the Q limbs ([2][ell][n]).  The sum is brought back to Q by one ModDown per stage.
+void k_dh_accumulate(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *cP, const u64 *pt, u64 *S,
+                     uint32_t galois, cudaStream_t st);
+
 // ---- samplers / encode helpers ----
 void k_sample_uniform(const DeviceTables &T, u64 seed, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st);
 enum SmallKind { SMALL_TERNARY = 0, SMALL_GAUSS = 1 };
@@ -141,7 +147,8 @@ void k_expand_i128(const DeviceTables &T, const u64 *coef_lohi, int ncoef, int g
 // device CKKS encode: in-place special inverse FFT of v[size], then words (lo,hi pairs) <- round(v * scale / size) in the
 // layout k_expand_i128 consumes (real parts first, imaginary parts after); ksi = exp(2 pi i k / 4 size), rot = 5^j mod 4 size
 void k_encode(const DeviceTables &T, double2 *v, const double *real_in, int nv, int size, double scale, const double2 *ksi,
-              const int *rot, int ell, u64 *out, cudaStream_t st);
+              const int *rot, int ell, u64 *out, cudaStream_t st, int extra_qp0 = 0, int extra = 0);
+// (extra > 0: `extra` further limbs after the ell Q limbs, reduced modulo moduli extra_qp0, extra_qp0 + 1, ...)
 // b = e - a*s_new + [limb in digit] * pmod * s_old   over F limbs (one digit of a switching key)
 void k_evk_finish(const DeviceTables &T, int F, const u64 *a, const u64 *e, const u64 *s_new, const u64 *s_old,
                   const LimbScalars &pmod, u64 *b, cudaStream_t st);

@@ -158,6 +158,32 @@ __global__ void __launch_bounds__(KS_THREADS) ks_moddown_finish(DeviceTables T, 
     (b ? out1 : out0)[(size_t)i * n + p] = r;
 }
 
+// S_b[t][p] += pt[t][p] * v_b[t][src(p)] (see kernels.h: k_dh_accumulate); one thread = one coefficient of one level limb
+__global__ void __launch_bounds__(KS_THREADS) ks_dh_accumulate(DeviceTables T, DevicePlan P, const u64 *__restrict__ acc,
+                                                               const u64 *__restrict__ cP, const u64 *__restrict__ pt,
+                                                               u64 *__restrict__ S, uint32_t g) {
+    const int t = blockIdx.y, n = T.n, W = P.width, ell = P.ell;
+    const uint32_t p = blockIdx.x * KS_THREADS + threadIdx.x;
+    if (p >= (uint32_t)n) return;
+    uint32_t src = p;
+    if (g != 1u) {
+        const int sh = 32 - T.logn;
+        uint32_t j = __brev(p) >> sh;
+        uint32_t idx = (((2u * j + 1u) * g) & (2u * n - 1u)) >> 1;
+        src = __brev(idx) >> sh;
+    }
+    if (!acc && t >= ell) return; // the unrotated term lives on the Q limbs only
+    const ModConst m = T.mc[P.qp[t]];
+    const u64 pv = pt[(size_t)t * n + p];
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+        u64 v = acc ? acc[((size_t)b * W + t) * n + src] : 0;
+        if (t < ell && (b == 0 || !acc)) v = add_mod(v, cP[((size_t)b * ell + t) * n + src], m.q);
+        const size_t o = ((size_t)b * W + t) * n + p;
+        S[o] = add_mod(S[o], mul_mod(v, pv, m), m.q);
+    }
+}
+
 #define DS_SWITCH(ds, CALL)                                                                                              \
     switch (ds) {                                                                                                        \
         case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break; case 4: CALL(4); break;                 \
@@ -200,6 +226,10 @@ void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc
                       const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st) {
     g_launches++, ks_moddown_finish<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.ell, 2), KS_THREADS, 0, st>>>(T, P, acc, conv, add0, add1,
                                                                                                   out0, out1, galois);
+}
+void k_dh_accumulate(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *cP, const u64 *pt, u64 *S,
+                     uint32_t galois, cudaStream_t st) {
+    g_launches++, ks_dh_accumulate<<<dim3((T.n + KS_THREADS - 1) / KS_THREADS, P.width), KS_THREADS, 0, st>>>(T, P, acc, cP, pt, S, galois);
 }
 
 } // namespace fheb200

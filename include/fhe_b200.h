@@ -147,7 +147,7 @@ int fheb200_eval_bootstrap_keygen(fheb200_ctx *ctx, fheb200_keys *k, int slots);
 int fheb200_eval_bootstrap(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
 int fheb200_bootstrap_depth(fheb200_ctx *ctx, int slots, int *levels);
 /* test hook: the intermediate ciphertext after step 1 (scale-down to q_0), 2 (ModRaise + SubSum), 3 (CoeffsToSlots +
- * conjugate), 4 (EvalMod); 0 = the whole bootstrapping */
+ * conjugate), 4 (EvalMod), 5 (ModRaise alone, before SubSum); 0 = the whole bootstrapping */
 int fheb200_eval_bootstrap_partial(fheb200_ctx *ctx, fheb200_ct *a, int stop_after, fheb200_ct **out);
 /* slot-wise complex conjugation (Galois element 2 * ring_dim - 1; key made by fheb200_eval_bootstrap_keygen) */
 int fheb200_eval_conjugate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);

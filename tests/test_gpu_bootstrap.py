@@ -67,6 +67,49 @@ def test_bootstrap_steps(env):
     assert err < 2.0 ** -16
 
 
+def test_modraise_is_the_centred_lift_bit_for_bit(env):
+    """ModRaise against its integer definition: inverse NTT of the one-limb ciphertext, centred representative in
+    (-q0/2, q0/2], residues modulo every limb of level 1, forward NTT (the engine's own NTT is bit-exact vs the oracle,
+    tests/test_gpu_primitives.py)."""
+    ctx, keys = env
+    c = deep(ctx, keys, np.linspace(-0.8, 0.8, 8), 8, ctx.depth - 1)
+    small = ctx.ct_export(ctx.bootstrap(c, 1))
+    raised = ctx.ct_export(ctx.bootstrap(c, 5))
+    q0 = ctx.moduli[0]
+    assert raised[0].shape[0] == ctx.L - 1
+    for poly in range(2):
+        coef = [int(v) for v in ctx.raw_ntt(0, small[poly][0], inverse=True)]
+        cent = [v - q0 if v > q0 // 2 else v for v in coef]
+        for limb in (0, 1, 7, ctx.L - 2):
+            q = ctx.moduli[limb]
+            want = ctx.raw_ntt(limb, np.array([v % q for v in cent], dtype=np.uint64))
+            assert np.array_equal(raised[poly][limb], want), (poly, limb)
+
+
+def test_double_hoisted_stages_match_single_hoisting():
+    """FHEB200_BOOT_HOIST=single evaluates every rotation of a linear-transform stage with its own ModDown; the default
+    sums the stage in the extended basis and pays for one.  Both must decrypt to the same values."""
+    import os
+    import subprocess
+    import sys
+    code = ("import numpy as np, sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+            "from test_gpu_bootstrap import make, deep\n"
+            "ctx, keys = make(13, 26, 64, (3, 3))\n"
+            "z = np.random.default_rng(2).uniform(0, 1, 64)\n"
+            "out = ctx.bootstrap(deep(ctx, keys, z, 64, ctx.depth - 1))\n"
+            "print(' '.join('%%.9f' %% v for v in ctx.decrypt(keys, out, 64)))\n") % (
+                os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for mode in ("double", "single"):
+        env2 = dict(os.environ, FHEB200_BOOT_HOIST=mode)
+        o = subprocess.run([sys.executable, "-c", code], env=env2, capture_output=True, text=True, timeout=300)
+        assert o.returncode == 0, o.stderr[-2000:]
+        res[mode] = np.array([float(v) for v in o.stdout.split()])
+    z = np.random.default_rng(2).uniform(0, 1, 64)
+    assert np.abs(res["double"] - z).max() < 2.0 ** -16 and np.abs(res["single"] - z).max() < 2.0 ** -16
+    assert np.abs(res["double"] - res["single"]).max() < 2.0 ** -16
+
+
 def test_bootstrap_then_compute(env):
     ctx, keys = env
     s = 8

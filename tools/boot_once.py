@@ -21,8 +21,9 @@ for c in [int(a) for a in sys.argv[1:]] or [12]:
         ct = ctx.mult(ct, 1.0)
     out = ctx.bootstrap(ct)  # first call encodes the diagonals
     ctx.sync()
+    print("launches before the timed bootstraps: %d" % F.launch_count(), file=sys.stderr, flush=True)
     t0 = time.time()
-    reps = 5
+    reps = int(os.environ.get("REPS", "5"))
     for _ in range(reps):
         out = ctx.bootstrap(ct)
     ctx.sync()
