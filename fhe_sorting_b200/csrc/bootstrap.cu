@@ -255,7 +255,12 @@ Ct Context::bootstrap(const Ct &a, int stop_after) {
     phase("CoeffsToSlots", r);
     if (stop_after == 3) return r;
     // 5. EvalMod
-    r = eval_chebyshev(r, bp.cheb, -1.0, 1.0);
+    if (bp.even) {
+        r = add_const(r, -bp.shift);                  // u = (x - delta) / (1 + delta)
+        Ct sq = mult(r, r);
+        r = add_const(add(sq, sq), -1.0);             // y = T_2(u)
+    }
+    r = eval_chebyshev(r, bp.cheb, -1.0, 1.0);        // sum_j c_2j T_j(y) = cos(w u)
     phase("Chebyshev", r);
     for (int i = 0; i < bp.r; i++) {
         Ct sq = mult(r, r);

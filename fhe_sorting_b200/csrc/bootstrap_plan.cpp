@@ -12,6 +12,7 @@
 #include "bootstrap_plan.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <functional>
 #include <map>
 #include <set>
@@ -109,8 +110,14 @@ BootPlan make_boot_plan(int n, int slots, int b_enc, int b_dec, double q0, doubl
     for (int len = s; len >= 2; len >>= 1) down.push_back(len);
     for (int len = 2; len <= s; len <<= 1) up.push_back(len);
 
-    // CoeffsToSlots: slots of the raised ciphertext = U w g / raise_scale; wanted: [Re w ; Im w] / (q0 K); conj-add doubles
-    const double k_enc = std::pow(raise_scale / (2.0 * g * q0 * (double)P.K), 1.0 / b_enc);
+    // CoeffsToSlots: slots of the raised ciphertext = U w g / raise_scale; wanted: x / (1 + delta) with x = [Re w ; Im w] /
+    // (q0 K) in [-1, 1] and delta = 1 / 4K (see EvalMod below); conj-add doubles
+    {
+        const char *e = getenv("FHEB200_BOOT_EVEN");
+        P.even = !(e && *e == '0');
+    }
+    const double delta = P.even ? 1.0 / (4.0 * (double)P.K) : 0.0;
+    const double k_enc = std::pow(raise_scale / (2.0 * g * q0 * (double)P.K * (1.0 + delta)), 1.0 / b_enc);
     auto ge = split(down, b_enc);
     for (size_t i = 0; i < ge.size(); i++) {
         Diags D;
@@ -134,8 +141,21 @@ BootPlan make_boot_plan(int n, int slots, int b_enc, int b_dec, double q0, doubl
                     if ((j + st.rot[t]) % (2 * s) >= s) st.diag[t][j] *= cd(0, 1);
         P.stc.push_back(std::move(st));
     }
-    const int K = P.K, r = P.r;
-    P.cheb = chebyshev_coefficients([K, r](double u) { return std::cos(2.0 * M_PI * ((double)K * u - 0.25) / (double)(1 << r)); }, -1.0, 1.0, P.degree);
+    // EvalMod: cos(2 pi (K x - 1/4) / 2^r) = cos(w u) with u = (x - delta) / (1 + delta) in [-1, 1) and
+    // w = 2 pi K (1 + delta) / 2^r.  Even in u, so it is a series in T_2j(u) = T_j(y), y = 2 u^2 - 1: half the degree for one
+    // extra square.  cos(w sqrt((y + 1) / 2)) is entire in y, so plain Chebyshev interpolation in y converges as fast.
+    // The conditioning in y is worse near u = 0 (|dH/dy| up to w^2 / 4 against |dh/du| <= w): about one bit of precision
+    // for 5 of 21 multiplications; FHEB200_BOOT_EVEN=0 evaluates the degree-88 series in u = x instead.
+    P.shift = delta / (1.0 + delta);
+    const double w = 2.0 * M_PI * (double)P.K * (1.0 + delta) / (double)(1 << P.r);
+    if (P.even) {
+        P.degree = 44;
+        P.cheb = chebyshev_coefficients([w](double y) { return std::cos(w * std::sqrt(std::max(0.0, (y + 1.0) / 2.0))); }, -1.0, 1.0, P.degree);
+    } else {
+        P.degree = 88;
+        const double quarter = M_PI / 2.0 / (double)(1 << P.r);
+        P.cheb = chebyshev_coefficients([w, quarter](double u) { return std::cos(w * u - quarter); }, -1.0, 1.0, P.degree);
+    }
     return P;
 }
 

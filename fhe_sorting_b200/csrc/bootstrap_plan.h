@@ -22,7 +22,9 @@ struct BootPlan {
     int n = 0, slots = 0;
     int K = 512;          // |I| < K for the overflow polynomial of a uniform ternary secret at ring_dim <= 2^17
     int r = 6;            // double-angle iterations
-    int degree = 88;      // Chebyshev degree of cos(2 pi (K u - 1/4) / 2^r) on [-1, 1]
+    int degree = 44;      // Chebyshev degree IN y = 2u^2 - 1 of the even function cos(w u), w = 2 pi K (1 + shift') / 2^r
+    double shift = 0;     // u = slot value - shift: the -1/4 of cos(2 pi (K x - 1/4) / 2^r) moved into the argument so
+                          // that the function is even in u and only every other Chebyshev term has to be evaluated
     int correction = 10;  // the message is brought to q0 * 2^-correction before ModRaise
     double q0 = 0;        // first modulus
     double msg_scale = 0; // q0 * 2^-correction
@@ -30,7 +32,8 @@ struct BootPlan {
     std::vector<BootStage> cts, stc;
     std::vector<double> cheb; // series convention c_0 / 2 + sum c_i T_i
     std::vector<int> rotations() const; // every rotation index the evaluation needs (SubSum, stages, final fold)
-    int cheb_depth() const { int d = 0; while ((1 << d) < degree + 1) d++; return d; }
+    bool even = true;     // FHEB200_BOOT_EVEN=0: the plain degree-88 series in u (one bit more precise, 6 ms slower)
+    int cheb_depth() const { int d = 0; while ((1 << d) < degree + 1) d++; return d + (even ? 1 : 0); } // + the square for y
     int depth() const { return (int)cts.size() + cheb_depth() + r + (int)stc.size(); }
 };
 

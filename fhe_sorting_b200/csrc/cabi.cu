@@ -307,7 +307,7 @@ int fheb200_eval_conjugate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) {
 }
 int fheb200_bootstrap_plan_info(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
                                 int correction, int *depth, int *k_range, int *double_angles, int *rotations, int capacity,
-                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb) {
+                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb, double *shift) {
     GUARD({
         BootPlan P = make_boot_plan(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale, correction);
         if (depth) *depth = P.depth();
@@ -316,6 +316,7 @@ int fheb200_bootstrap_plan_info(int ring_dim, int slots, int budget_enc, int bud
         auto R = P.rotations();
         if (num_rotations) *num_rotations = (int)R.size();
         if (rotations) for (int i = 0; i < (int)R.size() && i < capacity; i++) rotations[i] = R[i];
+        if (shift) *shift = P.shift;
         if (num_cheb) *num_cheb = (int)P.cheb.size();
         if (cheb) for (int i = 0; i < (int)P.cheb.size() && i < cheb_capacity; i++) cheb[i] = P.cheb[i];
     })

@@ -73,12 +73,13 @@ def bootstrap_plan_info(ring_dim, slots, budget_enc, budget_dec, q0, raise_scale
     """Host-only: depth, K, double-angle count, rotation indices and Chebyshev series of the bootstrapping plan."""
     L = load()
     depth, K, r, nrot, ncheb = (C.c_int() for _ in range(5))
+    shift = C.c_double()
     rots = (C.c_int * 4096)()
     cheb = (C.c_double * 1024)()
     _ck(L.fheb200_bootstrap_plan_info(ring_dim, slots, budget_enc, budget_dec, C.c_double(q0), C.c_double(raise_scale),
                                       correction, C.byref(depth), C.byref(K), C.byref(r), rots, 4096, C.byref(nrot), cheb,
-                                      1024, C.byref(ncheb)))
-    return dict(depth=depth.value, K=K.value, r=r.value, rotations=list(rots[:nrot.value]),
+                                      1024, C.byref(ncheb), C.byref(shift)))
+    return dict(depth=depth.value, K=K.value, r=r.value, shift=shift.value, rotations=list(rots[:nrot.value]),
                 cheb=np.array(cheb[:ncheb.value]))
 
 

@@ -152,11 +152,12 @@ int fheb200_eval_bootstrap_partial(fheb200_ctx *ctx, fheb200_ct *a, int stop_aft
 /* slot-wise complex conjugation (Galois element 2 * ring_dim - 1; key made by fheb200_eval_bootstrap_keygen) */
 int fheb200_eval_conjugate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
 /* host only (no GPU): the bootstrapping plan for a parameter set - depth, the range K of the overflow polynomial, the
- * number of double-angle steps, the rotation indices and the Chebyshev series; and the plan's CoeffsToSlots (which = 0)
+ * number of double-angle steps, the rotation indices, the Chebyshev series (in y = 2 u^2 - 1, u = slot - shift) of the
+ * even scaled cosine and that shift; and the plan's CoeffsToSlots (which = 0)
  * or SlotsToCoeffs (which = 1) applied to 2 * slots complex values in the clear (re, im interleaved) */
 int fheb200_bootstrap_plan_info(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
                                 int correction, int *depth, int *k_range, int *double_angles, int *rotations, int capacity,
-                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb);
+                                int *num_rotations, double *cheb, int cheb_capacity, int *num_cheb, double *shift);
 int fheb200_bootstrap_plan_apply(int ring_dim, int slots, int budget_enc, int budget_dec, double q0, double raise_scale,
                                  int correction, int which, const double *in_re_im, double *out_re_im);
 

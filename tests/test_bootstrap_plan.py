@@ -44,12 +44,16 @@ def test_cleartext_bootstrap(s, budget, n):
     x = F.bootstrap_plan_apply(n, s, budget[0], budget[1], q0, sf1, 0, np.concatenate([x0, x0]), c)
     x = x + np.conj(x)
     br = bitrev(s)
+    delta = 1.0 / (4 * K)
     want = np.concatenate([t[:s][br], t[s:][br]]) / (q0 * K)
-    assert np.abs(x - want).max() < 1e-9
-    y = Cheb.chebval(x.real, np.concatenate([[info["cheb"][0] / 2], info["cheb"][1:]]))
+    assert np.abs(x * (1 + delta) - want).max() < 1e-9
+    # EvalMod as the engine runs it: u = x - shift, y = 2 u^2 - 1, even-part series in y, r double angles
+    assert abs(info["shift"] - delta / (1 + delta)) < 1e-15 and len(info["cheb"]) == 45
+    u = x.real - info["shift"]
+    y = Cheb.chebval(2 * u * u - 1, np.concatenate([[info["cheb"][0] / 2], info["cheb"][1:]]))
     for _ in range(r):
         y = 2 * y * y - 1
-    assert np.abs(y - np.sin(2 * np.pi * K * x.real)).max() < 1e-8
+    assert np.abs(y - np.sin(2 * np.pi * K * want.real)).max() < 1e-8
     v = F.bootstrap_plan_apply(n, s, budget[0], budget[1], q0, sf1, 1, y.astype(complex), c)
     v = v + np.roll(v, -s)
     # the sine's own error (2 pi 2^-c m)^2 / 6 and, at many slots, double-precision noise of EvalMod times q0 / (2 pi T) sqrt(s)

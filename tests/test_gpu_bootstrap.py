@@ -53,6 +53,7 @@ def test_bootstrap_steps(env):
     assert c3.info()["slots"] == 2 * s
     x = ctx.decrypt(keys, c3, 2 * s)
     assert np.abs(x).max() < 1.0
+    x = x * (1 + 1.0 / (4 * K))                     # the plan folds 1 / (1 + delta) into CoeffsToSlots
     frac = K * x - np.round(K * x)
     assert np.abs(frac * 2.0 ** CORRECTION - coef).max() < 1e-4
     # step 4: sin(2 pi t / q0) ~ 2 pi 2^-c m
