@@ -7,10 +7,12 @@
 //   SortUtils fcnL, compareMax/Min, two/threeSorter (SortUtils.cpp:5-78), slotMatching2/3 (:202-237), slotAssemble (:425)
 //   Sorter    rightRotateForSort (Sorter.cpp:180-249), comparisonForSort (:251-262), runTwo/ThreeSorter (:8-69),
 //             sorter (:284-404)
-// Built here: k = 2 and k = 3 (the networks the reference publishes timings for, comparison/experimental_results/
-// kway_k2, kway_k3).  k = 5 needs the four/five-sorters and their slot matching (SortUtils.cpp:80-200, 239-423) and
-// reports "not built".  One ciphertext, strictly sequential stages: nothing to shard across GPUs (replicas only).
+//   k = 5     four/fiveSorter (SortUtils.cpp:80-200), slotMatching4/5/2345 (:239-423), runFour/Five/2345Sorter
+//             (Sorter.cpp:70-178), comparisonForSort2 (:264-282).  Here the pairwise bits of every sorter size come from one
+//             rule (pairBit below) instead of one hand-written table per size.
+// One ciphertext, strictly sequential stages: nothing to shard across GPUs (replicas only).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <memory>
 #include <stdexcept>
@@ -180,8 +182,47 @@ class SortUtils : public EvalUtils {
         auto sum = m_cc->EvalAdd(m_cc->EvalAdd(ctxt[0], ctxt[1]), ctxt[2]);
         out[1] = m_cc->EvalSub(m_cc->EvalSub(sum, out[0]), out[2]);
     }
-    void fourSorter(Ciphertext<DCRTPoly> *, Ciphertext<DCRTPoly> *, Ciphertext<DCRTPoly> *) { notBuilt("fourSorter"); }
-    void fiveSorter(Ciphertext<DCRTPoly> *, Ciphertext<DCRTPoly> *, Ciphertext<DCRTPoly> *) { notBuilt("fiveSorter"); }
+    // [a, b, c, d], comp = [(a>b), (a>c), (a>d), (b>c), (b>d), (c>d)] -> ascending.  Sort the halves {a,b}, {c,d}; the
+    // bits between the halves' extremes are selected from the input bits by the same two-sorters (a bit vector sorted by
+    // (a>b) is [bit of min(a,b), bit of max(a,b)]); then merge.
+    void fourSorter(Ciphertext<DCRTPoly> *ctxt, Ciphertext<DCRTPoly> *comp, Ciphertext<DCRTPoly> *out) {
+        Ciphertext<DCRTPoly> lo[2], hi[2], loVsC[2], loVsD[2], bigVsHi[2], smallVsHi[2];
+        twoSorter(ctxt[0], ctxt[1], comp[0], lo);            // lo = [min(a,b), max(a,b)]
+        twoSorter(ctxt[2], ctxt[3], comp[5], hi);            // hi = [min(c,d), max(c,d)]
+        twoSorter(comp[1], comp[3], comp[0], loVsC);         // [(lo0 > c), (lo1 > c)]
+        twoSorter(comp[2], comp[4], comp[0], loVsD);         // [(lo0 > d), (lo1 > d)]
+        twoSorter(loVsC[1], loVsD[1], comp[5], bigVsHi);     // [(lo1 > hi0), (lo1 > hi1)]
+        twoSorter(loVsC[0], loVsD[0], comp[5], smallVsHi);   // [(lo0 > hi0), (lo0 > hi1)]
+        compareMax(lo[1], hi[1], bigVsHi[1], out[3]);
+        Ciphertext<DCRTPoly> ifLoWins, ifHiWins;             // runner-up: max(lo0, hi1) if lo1 is the maximum, else max(lo1, hi0)
+        compareMax(lo[0], hi[1], smallVsHi[1], ifLoWins);
+        compareMax(lo[1], hi[0], bigVsHi[0], ifHiWins);
+        compareMax(ifLoWins, ifHiWins, bigVsHi[1], out[2]);
+        compareMin(lo[0], hi[0], smallVsHi[0], out[0]);
+        restByTotal(ctxt, 4, out, 1);
+    }
+    // [a..e], comp = [a>b a>c a>d a>e b>c b>d b>e c>d c>e d>e] -> ascending: 3-sorter on {a,b,c}, 2-sorter on {d,e}, the
+    // bits of the sorted triple against d and e by the same 3-sorter applied to the bit vectors, then merge
+    void fiveSorter(Ciphertext<DCRTPoly> *ctxt, Ciphertext<DCRTPoly> *comp, Ciphertext<DCRTPoly> *out) {
+        Ciphertext<DCRTPoly> tripleBits[3] = {comp[0], comp[1], comp[4]}, triple[3], pair[2];
+        threeSorter(ctxt, tripleBits, triple);
+        twoSorter(ctxt[3], ctxt[4], comp[9], pair);
+        Ciphertext<DCRTPoly> vsD[3] = {comp[2], comp[5], comp[7]}, vsE[3] = {comp[3], comp[6], comp[8]}, tVsD[3], tVsE[3];
+        threeSorter(vsD, tripleBits, tVsD);                  // (triple[i] > d)
+        threeSorter(vsE, tripleBits, tVsE);                  // (triple[i] > e)
+        Ciphertext<DCRTPoly> vsPair[3][2];                   // [(triple[i] > pair[0]), (triple[i] > pair[1])]
+        for (int i = 0; i < 3; i++) twoSorter(tVsD[i], tVsE[i], comp[9], vsPair[i]);
+        compareMax(triple[2], pair[1], vsPair[2][1], out[4]);
+        compareMin(triple[0], pair[0], vsPair[0][0], out[0]);
+        Ciphertext<DCRTPoly> x, y;
+        compareMax(triple[1], pair[1], vsPair[1][1], x);     // fourth: max(triple1, pair1) if triple2 is the maximum ...
+        compareMax(triple[2], pair[0], vsPair[2][0], y);     // ... else max(triple2, pair0)
+        compareMax(x, y, vsPair[2][1], out[3]);
+        compareMin(triple[1], pair[0], vsPair[1][0], x);     // second: min(triple1, pair0) if pair0 is not the minimum ...
+        compareMin(triple[0], pair[1], vsPair[0][1], y);     // ... else min(triple0, pair1)
+        compareMin(x, y, vsPair[0][0], out[1]);
+        restByTotal(ctxt, 5, out, 2);
+    }
 
     // bring partner p of every sorter onto the slot of its first element (rotation left by p * shift)
     void slotMatching2(Ciphertext<DCRTPoly> &ctxt, Ciphertext<DCRTPoly> &comp, std::vector<std::vector<int>> &indices, long shift,
@@ -205,6 +246,73 @@ class SortUtils : public EvalUtils {
         flipCtxt(comp_out[0], firstPlain);
         flipCtxt(comp_out[2], firstPlain);
     }
+    // The comparison ciphertexts hold, at member p of a cyclic s-sorter, comp1 = (x_p > x_{p-1}) and comp2 = (x_p > x_{p-2})
+    // (indices mod s; Sorter::comparisonForSort2).  The bit (x_i > x_j), i < j, on the sorter's first slot is therefore
+    //   comp_{s-D} rotated left by i * shift              if s - D is 1 or 2 (member i looks back onto j), D = j - i
+    //   mask - (comp_D rotated left by j * shift)         otherwise (member j looks back onto i: flipped)
+    // masked = true multiplies by `mask` (first slots of the sorters the bit is meant for) instead of leaving stray values
+    Ciphertext<DCRTPoly> pairBit(int s, int i, int j, Ciphertext<DCRTPoly> &comp1, Ciphertext<DCRTPoly> &comp2, long shift,
+                                 const Plaintext &mask, bool masked) {
+        const int D = j - i, back = s - D;
+        const bool direct = back == 1 || back == 2;
+        Ciphertext<DCRTPoly> bit;
+        leftRotate((direct ? back : D) == 1 ? comp1 : comp2, (direct ? i : j) * shift, bit);
+        if (masked) bit = m_cc->EvalMult(bit, mask);
+        if (!direct) flipCtxt(bit, mask);
+        return bit;
+    }
+    void slotMatching4(Ciphertext<DCRTPoly> &ctxt, Ciphertext<DCRTPoly> &comp1, Ciphertext<DCRTPoly> &comp2,
+                       std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> *arr, Ciphertext<DCRTPoly> *comp_arr) {
+        std::vector<double> first;
+        genMask(indices, 4, 1, first);
+        auto firstPlain = m_cc->MakeCKKSPackedPlaintext(first);
+        int at = 0;
+        for (int i = 0; i < 4; i++)
+            for (int j = i + 1; j < 4; j++) comp_arr[at++] = pairBit(4, i, j, comp1, comp2, shift, firstPlain, false);
+        for (int p = 0; p < 4; p++) { // the four-sorter's outputs are not masked afterwards: mask its inputs
+            leftRotate(ctxt, p * shift, arr[p]);
+            arr[p] = m_cc->EvalMult(arr[p], firstPlain);
+        }
+    }
+    void slotMatching5(Ciphertext<DCRTPoly> &ctxt, Ciphertext<DCRTPoly> &comp1, Ciphertext<DCRTPoly> &comp2,
+                       std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> *arr, Ciphertext<DCRTPoly> *comp_arr) {
+        std::vector<double> first;
+        genMask(indices, 5, 1, first);
+        auto firstPlain = m_cc->MakeCKKSPackedPlaintext(first);
+        for (int p = 0; p < 5; p++) leftRotate(ctxt, p * shift, arr[p]);
+        int at = 0;
+        for (int i = 0; i < 5; i++)
+            for (int j = i + 1; j < 5; j++) comp_arr[at++] = pairBit(5, i, j, comp1, comp2, shift, firstPlain, false);
+    }
+    // sorters of 2, 3, 4 and 5 members in one stage, all run through the five-sorter: a bit involving a member the sorter
+    // does not have is 0 ("the missing member is larger"), so the real members come out in the low positions
+    void slotMatching2345(Ciphertext<DCRTPoly> &ctxt, Ciphertext<DCRTPoly> &comp1, Ciphertext<DCRTPoly> &comp2,
+                          std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> *arr, Ciphertext<DCRTPoly> *comp_arr) {
+        for (int p = 0; p < 5; p++) leftRotate(ctxt, p * shift, arr[p]);
+        std::vector<std::vector<double>> first(6);
+        for (int s = 2; s <= 5; s++) genMask(indices, s, 1, first[s]);
+        int at = 0;
+        for (int i = 0; i < 5; i++)
+            for (int j = i + 1; j < 5; j++, at++) {
+                // sizes that have member j, grouped by where their bit comes from (the rule of pairBit)
+                Ciphertext<DCRTPoly> sum;
+                bool done[6] = {false, false, false, false, false, false};
+                for (int s = j + 1; s <= 5; s++) {
+                    if (done[s]) continue;
+                    const int D = j - i;
+                    auto source = [&](int size) { const int back = size - D; return (back == 1 || back == 2) ? back : -D; };
+                    std::vector<double> group((size_t)m_numSlots, 0.0);
+                    for (int t = s; t <= 5; t++)
+                        if (!done[t] && source(t) == source(s)) {
+                            done[t] = true;
+                            for (long x = 0; x < m_numSlots; x++) group[x] += first[t][x];
+                        }
+                    Ciphertext<DCRTPoly> term = pairBit(s, i, j, comp1, comp2, shift, m_cc->MakeCKKSPackedPlaintext(group), true);
+                    sum = sum ? m_cc->EvalAdd(sum, term) : term;
+                }
+                comp_arr[at] = sum;
+            }
+    }
     // sorted element i goes back i * shift slots to the right
     void slotAssemble(Ciphertext<DCRTPoly> *sorted, long num, long shift, Ciphertext<DCRTPoly> &out) {
         out = sorted[0];
@@ -216,8 +324,13 @@ class SortUtils : public EvalUtils {
     }
 
   protected:
-    [[noreturn]] static void notBuilt(const char *what) {
-        throw std::runtime_error(std::string("kwaySort::") + what + ": the 4- and 5-sorters of the k = 5 network are not built (k = 2, 3 are)");
+    // out[which] = sum of the inputs - sum of the other outputs (the one element the merge did not have to select)
+    void restByTotal(Ciphertext<DCRTPoly> *ctxt, int count, Ciphertext<DCRTPoly> *out, int which) {
+        Ciphertext<DCRTPoly> acc = ctxt[0];
+        for (int i = 1; i < count; i++) acc = m_cc->EvalAdd(acc, ctxt[i]);
+        for (int i = 0; i < count; i++)
+            if (i != which) acc = m_cc->EvalSub(acc, out[i]);
+        out[which] = acc;
     }
     long m_numSlots, m_k, m_M;
 };
@@ -273,9 +386,15 @@ class Sorter : public SortUtils {
         rightRotateForSort(ctxt, indices, logDist, slope, ctxt_rot, ctxt_fix);
         ctxt_comp = comp.compare(m_cc, ctxt, ctxt_rot, SignFunc::CompositeSign, Cfg);
     }
-    void comparisonForSort2(Ciphertext<DCRTPoly> &, std::vector<std::vector<int>> &, long, long, Ciphertext<DCRTPoly> &,
-                            Ciphertext<DCRTPoly> &, Ciphertext<DCRTPoly> &, SignConfig &) {
-        notBuilt("comparisonForSort2");
+    // comp1 = (x_p > x_{p-1}), comp2 = (x_p > x_{p-2}) inside every cyclic sorter: the shifted copy shifted once more
+    void comparisonForSort2(Ciphertext<DCRTPoly> &ctxt, std::vector<std::vector<int>> &indices, long logDist, long slope,
+                            Ciphertext<DCRTPoly> &ctxt_comp1, Ciphertext<DCRTPoly> &ctxt_comp2, Ciphertext<DCRTPoly> &ctxt_fix,
+                            SignConfig &Cfg) {
+        Ciphertext<DCRTPoly> once, twice, unused;
+        rightRotateForSort(ctxt, indices, logDist, slope, once, ctxt_fix);
+        rightRotateForSort(once, indices, logDist, slope, twice, unused);
+        ctxt_comp1 = comp.compare(m_cc, ctxt, once, SignFunc::CompositeSign, Cfg);
+        ctxt_comp2 = comp.compare(m_cc, ctxt, twice, SignFunc::CompositeSign, Cfg);
     }
 
     void runTwoSorter(Ciphertext<DCRTPoly> &ctxt, std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> &ctxt_comp,
@@ -300,17 +419,43 @@ class Sorter : public SortUtils {
         for (auto &c : sorted) c = m_cc->EvalMult(c, firstPlain);
         slotAssemble(sorted, 3, shift, ctxt_out);
     }
-    void runFourSorter(Ciphertext<DCRTPoly> &, std::vector<std::vector<int>> &, long, Ciphertext<DCRTPoly> &, Ciphertext<DCRTPoly> &,
-                       Ciphertext<DCRTPoly> &) { notBuilt("runFourSorter"); }
-    void runFiveSorter(Ciphertext<DCRTPoly> &, std::vector<std::vector<int>> &, long, Ciphertext<DCRTPoly> &, Ciphertext<DCRTPoly> &,
-                       Ciphertext<DCRTPoly> &) { notBuilt("runFiveSorter"); }
-    void run2345Sorter(Ciphertext<DCRTPoly> &, std::vector<std::vector<int>> &, long, Ciphertext<DCRTPoly> &, Ciphertext<DCRTPoly> &,
-                       Ciphertext<DCRTPoly> &) { notBuilt("run2345Sorter"); }
+    void runFourSorter(Ciphertext<DCRTPoly> &ctxt, std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> &ctxt_comp1,
+                       Ciphertext<DCRTPoly> &ctxt_comp2, Ciphertext<DCRTPoly> &ctxt_out) {
+        Ciphertext<DCRTPoly> aligned[4], bits[6], sorted[4];
+        slotMatching4(ctxt, ctxt_comp1, ctxt_comp2, indices, shift, aligned, bits);
+        fourSorter(aligned, bits, sorted);
+        slotAssemble(sorted, 4, shift, ctxt_out);
+    }
+    void runFiveSorter(Ciphertext<DCRTPoly> &ctxt, std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> &ctxt_comp1,
+                       Ciphertext<DCRTPoly> &ctxt_comp2, Ciphertext<DCRTPoly> &ctxt_out) {
+        std::vector<double> first;
+        genMask(indices, 5, 1, first);
+        auto firstPlain = m_cc->MakeCKKSPackedPlaintext(first);
+        Ciphertext<DCRTPoly> aligned[5], bits[10], sorted[5];
+        slotMatching5(ctxt, ctxt_comp1, ctxt_comp2, indices, shift, aligned, bits);
+        fiveSorter(aligned, bits, sorted);
+        for (auto &c : sorted) c = m_cc->EvalMult(c, firstPlain);
+        slotAssemble(sorted, 5, shift, ctxt_out);
+    }
+    // mixed sizes: output position i is kept on the first slots of the sorters that have more than i members
+    void run2345Sorter(Ciphertext<DCRTPoly> &ctxt, std::vector<std::vector<int>> &indices, long shift, Ciphertext<DCRTPoly> &ctxt_comp1,
+                       Ciphertext<DCRTPoly> &ctxt_comp2, Ciphertext<DCRTPoly> &ctxt_out) {
+        Ciphertext<DCRTPoly> aligned[5], bits[10], sorted[5];
+        slotMatching2345(ctxt, ctxt_comp1, ctxt_comp2, indices, shift, aligned, bits);
+        fiveSorter(aligned, bits, sorted);
+        for (int i = 0; i < 5; i++) {
+            std::vector<double> keep((size_t)m_numSlots, 0.0);
+            for (long x = 0; x < m_numSlots; x++)
+                if (indices[1][x] == 1 && indices[0][x] > std::max(i, 1)) keep[x] = 1.0;
+            sorted[i] = m_cc->EvalMult(sorted[i], m_cc->MakeCKKSPackedPlaintext(keep));
+        }
+        slotAssemble(sorted, 5, shift, ctxt_out);
+    }
 
     // M + M(M-1)/2 * ceil(k/2) stages; before each compare and each sorter the operands are bootstrapped if fewer levels
     // remain than the step needs (m_level, src/k-way/Sorter.h:85-93)
     void sorter(Ciphertext<DCRTPoly> &ctxt, Ciphertext<DCRTPoly> &ctxt_out, SignConfig &Cfg) {
-        if (m_k != 2 && m_k != 3) notBuilt("sorter (k = 5)");
+        if (m_k != 2 && m_k != 3 && m_k != 5) throw std::invalid_argument("kwaySort::Sorter: k must be 2, 3 or 5");
         static const int need[6] = {0, 1, 3, 5, 6, 7};
         const int depth = Cfg.multDepth, k = (int)m_k, M = (int)m_M;
         const int stages = M + M * (M - 1) / 2 * ((k + 1) / 2);
@@ -319,8 +464,37 @@ class Sorter : public SortUtils {
             std::tie(m, logDist, slope) = sortType(k, M, stage);
             const long shift = getRotateDistance(k, logDist, slope);
             auto indices = genIndices(m_numSlots, k, M, m, logDist, slope);
-            Ciphertext<DCRTPoly> bits, rest;
-            if (slope == 0) { // k-sorters
+            Ciphertext<DCRTPoly> bits, bits2, rest;
+            if (k == 5) { // two comparison ciphertexts per stage (neighbours at distance 1 and 2)
+                if (slope == 0) {
+                    checkLevelAndBoot(ctxt, need[5], depth);
+                    comparisonForSort2(ctxt, indices, logDist, slope, bits, bits2, rest, Cfg);
+                    checkLevelAndBoot2(bits, bits2, need[5], depth);
+                    runFiveSorter(ctxt, indices, shift, bits, bits2, ctxt);
+                } else if (slope == 3) { // middle slope: 4-sorters
+                    checkLevelAndBoot(ctxt, need[4], depth);
+                    comparisonForSort2(ctxt, indices, logDist, slope, bits, bits2, rest, Cfg);
+                    checkLevelAndBoot(ctxt, need[4], depth);
+                    checkLevelAndBoot2(bits, bits2, need[4], depth);
+                    runFourSorter(ctxt, indices, shift, bits, bits2, ctxt);
+                    ctxt = m_cc->EvalAdd(ctxt, rest);
+                } else if (slope == 1) { // diagonals of 2..5 members
+                    checkLevelAndBoot(ctxt, need[5], depth);
+                    comparisonForSort2(ctxt, indices, logDist, slope, bits, bits2, rest, Cfg);
+                    checkLevelAndBoot2(bits, bits2, need[5], depth);
+                    run2345Sorter(ctxt, indices, shift, bits, bits2, ctxt);
+                    ctxt = m_cc->EvalAdd(ctxt, rest);
+                } else { // slope 2: diagonals of 2 and 3 members
+                    Ciphertext<DCRTPoly> twos, threes;
+                    checkLevelAndBoot(ctxt, need[3], depth);
+                    comparisonForSort(ctxt, indices, logDist, slope, bits, rest, Cfg);
+                    checkLevelAndBoot(bits, need[2], depth);
+                    runTwoSorter(ctxt, indices, shift, bits, twos);
+                    checkLevelAndBoot(bits, need[3], depth);
+                    runThreeSorter(ctxt, indices, shift, bits, threes);
+                    ctxt = m_cc->EvalAdd(m_cc->EvalAdd(twos, rest), threes);
+                }
+            } else if (slope == 0) { // k-sorters
                 checkLevelAndBoot(ctxt, need[k], depth);
                 comparisonForSort(ctxt, indices, logDist, slope, bits, rest, Cfg);
                 checkLevelAndBoot(bits, need[k], depth);

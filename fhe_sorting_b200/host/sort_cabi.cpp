@@ -201,10 +201,8 @@ SessionBase *make_kway_session_for(int k, int M, int log_ring_dim, int depth_ove
     switch (N) {
         KWAY_CASE(4) KWAY_CASE(8) KWAY_CASE(16) KWAY_CASE(32) KWAY_CASE(64) KWAY_CASE(128) KWAY_CASE(256) KWAY_CASE(512) KWAY_CASE(1024)
         KWAY_CASE(9) KWAY_CASE(27) KWAY_CASE(81) KWAY_CASE(243) KWAY_CASE(729)
-#ifdef REFERENCE_DRIVERS
         KWAY_CASE(25) KWAY_CASE(125) KWAY_CASE(625)
-#endif
-    default: throw std::invalid_argument("k-way: array length k^M must be one of 4..1024 (k = 2), 9..729 (k = 3)");
+    default: throw std::invalid_argument("k-way: array length k^M must be one of 4..1024 (k = 2), 9..729 (k = 3), 25..625 (k = 5)");
     }
 #undef KWAY_CASE
 }

@@ -26,7 +26,7 @@ int fhesort_mehp24_session_create(int N, int log_ring_dim, int mult_depth, uint6
  * ring 2^log_ring_dim, depth 40 (mult_depth = 0), first modulus 60 / scaling 59 bits, rotation keys +-2^i < N,
  * EvalBootstrapSetup({4,4} or {5,5}) + EvalBootstrapKeyGen; fhesort_run stage 0 runs KWayAdapter<N>::sort
  * (src/kway_adapter.h:66) with bootstrapping enabled (SignConfig(compos, depth)); sign_n = 0 selects the configuration
- * the reference tests really run (dg = 2, df = the test table's d_g).  k = 2 or 3 (k = 5: not built). */
+ * the reference tests really run (dg = 2, df = the test table's d_g).  k = 2, 3 or 5. */
 int fhesort_kway_session_create(int k, int M, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
 /* EvalBootstrap calls made by the network's level guards so far (the sign's own lazy bootstraps are not counted) */
 int fhesort_session_bootstraps(fhesort_session *s, int *count);

@@ -16,7 +16,7 @@ def gap_input(n, seed):
     return rng.permutation(n).astype(np.float64) * ((1 - 1e-8) / n)
 
 
-@pytest.mark.parametrize("k,m", [(2, 2), (2, 3), (2, 4), (3, 2)])
+@pytest.mark.parametrize("k,m", [(2, 2), (2, 3), (2, 4), (3, 2), (3, 3), (5, 2), (5, 3)])
 def test_kway_sort_small_ring(k, m):
     s = S.KWaySortSession(k, m, log_ring_dim=12, seed=3)
     assert s.mult_depth == 40
@@ -40,11 +40,14 @@ def test_kway_reference_drivers_unmodified_on_the_engine():
         s.close()
     assert np.abs(outs["reference"] - np.sort(x)).max() < 0.01
     assert np.abs(outs["ours"] - outs["reference"]).max() < 1e-3
-    # k = 5 exists only in the reference's drivers; it must run on the engine too
-    s = S.KWaySortSession(5, 2, log_ring_dim=12, seed=3, drivers="reference")
+    # k = 5: four/five-sorters and the mixed 2..5 stage, reference's hand-written bit tables against the one-rule pairBit
     x = gap_input(25, 5)
-    assert np.abs(s.sort(x)[0] - np.sort(x)).max() < 0.01
-    s.close()
+    for drivers in ("ours", "reference"):
+        s = S.KWaySortSession(5, 2, log_ring_dim=12, seed=3, drivers=drivers)
+        outs[drivers] = s.sort(x)[0]
+        s.close()
+    assert np.abs(outs["reference"] - np.sort(x)).max() < 0.01
+    assert np.abs(outs["ours"] - outs["reference"]).max() < 1e-3
 
 
 def test_kway_full_parameters():
