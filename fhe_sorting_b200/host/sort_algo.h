@@ -324,3 +324,55 @@ template <int N> class DirectSort : public SortBase<N> {
         return output_array;
     }
 };
+
+// Bitonic sorting network on one ciphertext (interface and behaviour of the reference's BitonicSort<N>,
+// src/sort_algo.h:1066-1160): inputs in [0, 255] are normalised by 1/255; stage (k, j) pairs slot i with i ^ j, ascending
+// where (i & k) == 0; the ciphertext is bootstrapped whenever its level exceeds 29.  Per stage: four masks split the slots
+// into lower/upper members of ascending/descending pairs, four rotations by -+j bring every member's partner onto its
+// slot, one comparison (partner > own) selects between "what to keep if the partner is greater" and "... if it is not".
+template <int N> class BitonicSort : public SortBase<N> {
+    typedef Ciphertext<DCRTPoly> CT;
+    CryptoContext<DCRTPoly> m_cc;
+    PublicKey<DCRTPoly> m_PublicKey;
+    Comparison comp;
+    RotationComposer<N> rot;
+
+  public:
+    std::shared_ptr<Encryption> m_enc;
+    int bootstraps = 0;
+
+    BitonicSort(CryptoContext<DCRTPoly> cc, PublicKey<DCRTPoly> publicKey, std::vector<int> rotIndices, std::shared_ptr<Encryption> enc)
+        : SortBase<N>(enc), m_cc(cc), m_PublicKey(publicKey), comp(enc), rot(cc, enc, rotIndices), m_enc(enc) {}
+
+    CT sort(const CT &input_array, SignFunc SignFunc, SignConfig &Cfg) override {
+        CT result = m_cc->EvalMult(input_array, 1.0 / 255);
+        for (size_t k = 2; k <= (size_t)N; k *= 2)
+            for (size_t j = k / 2; j > 0; j /= 2) {
+                if (result->GetLevel() > 29) {
+                    result = m_cc->EvalBootstrap(result, 2, 20);
+                    bootstraps++;
+                }
+                // member kinds: 0 lower of an ascending pair, 1 its upper, 2 lower of a descending pair, 3 its upper
+                std::vector<std::vector<double>> mask(4, std::vector<double>(N, 0.0));
+                for (size_t i = 0; i < (size_t)N; i++) {
+                    const size_t l = i ^ j;
+                    if (i >= l) continue;
+                    const int kind = (i & k) == 0 ? 0 : 2;
+                    mask[kind][i] = 1, mask[kind + 1][l] = 1;
+                }
+                CT part[4], moved[4];
+                for (int t = 0; t < 4; t++) {
+                    part[t] = m_cc->EvalMult(result, m_cc->MakeCKKSPackedPlaintext(mask[t]));
+                    moved[t] = rot.rotate(part[t], (t & 1) ? (int)j : -(int)j); // lowers go up to their partner's slot, uppers down
+                }
+                CT partner = m_cc->EvalAdd(m_cc->EvalAdd(moved[0], moved[2]), m_cc->EvalAdd(moved[1], moved[3]));
+                // if the partner is greater, an ascending pair's lower slot keeps its own value and its upper slot takes the
+                // partner's (descending pairs the other way round); if it is not, the roles swap
+                CT ifGreater = m_cc->EvalAdd(m_cc->EvalAdd(moved[0], part[0]), m_cc->EvalAdd(moved[3], part[3]));
+                CT ifNot = m_cc->EvalAdd(m_cc->EvalAdd(moved[2], part[2]), m_cc->EvalAdd(moved[1], part[1]));
+                CT greater = comp.compare(m_cc, partner, result, SignFunc, Cfg);
+                result = m_cc->EvalAdd(m_cc->EvalMult(greater, ifGreater), m_cc->EvalMult(m_cc->EvalSub(1, greater), ifNot));
+            }
+        return m_cc->EvalMult(result, 255.0);
+    }
+};

@@ -207,6 +207,60 @@ SessionBase *make_kway_session_for(int k, int M, int log_ring_dim, int depth_ove
 #undef KWAY_CASE
 }
 
+// Bitonic sorting network (reference fixture: tests/BitonicSortTest.cpp:12-55): depth 58, 59-bit scaling, batch N, rotation
+// keys +-2^i, bootstrapping with level budget {3,3}; inputs in [0, 255], CompositeSign(4, 3, 3)
+template <int N> struct BitonicSession : SessionBase {
+    std::unique_ptr<BitonicSort<N>> sorter;
+    Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        return sorter->sort(in, SignFunc::CompositeSign, cfg);
+    }
+    Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("bitonic: sort only"); }
+    Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &, const Ciphertext<DCRTPoly> &) override {
+        throw std::runtime_error("bitonic: sort only");
+    }
+    Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &, int) override { throw std::runtime_error("bitonic: sort only"); }
+    void shard(int, int world) override {
+        if (world > 1) throw std::runtime_error("bitonic: the stages of the network are sequential (replicas only)");
+    }
+    bool own_sign_config(int n, int dg, int df, SignConfig &out) override {
+        out = n == 0 ? SignConfig(CompositeSignConfig(4, 3, 3)) : SignConfig(CompositeSignConfig(n, dg, df));
+        return true;
+    }
+#ifndef REFERENCE_DRIVERS
+    int bootstraps() const override { return sorter->bootstraps; }
+#endif
+};
+template <int N> SessionBase *make_bitonic_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
+    auto t0 = std::chrono::steady_clock::now();
+    auto s = std::make_unique<BitonicSession<N>>();
+    CCParams<CryptoContextCKKSRNS> p;
+    p.SetMultiplicativeDepth(depth_override > 0 ? depth_override : 58);
+    p.SetScalingModSize(59);
+    p.SetBatchSize(N);
+    p.SetRingDim(1u << log_ring_dim);
+    p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
+    if (seed) CryptoContextImpl::SetKeySeed(seed);
+#ifdef REFERENCE_DRIVERS
+    setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
+    s->cc = GenCryptoContext(p);
+#else
+    s->cc = GenCryptoContext(p, device);
+#endif
+    s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE), s->cc->Enable(FHE);
+    s->keys = s->cc->KeyGen();
+    for (int i = 1; i < N; i *= 2) s->rotations.push_back(i), s->rotations.push_back(-i);
+    s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
+    s->cc->EvalMultKeyGen(s->keys.secretKey);
+    s->cc->EvalBootstrapSetup({3, 3}, {0, 0}, N);
+    s->cc->EvalBootstrapKeyGen(s->keys.secretKey, N);
+    s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);
+    s->sorter = std::make_unique<BitonicSort<N>>(s->cc, s->keys.publicKey, s->rotations, s->enc);
+    s->len = N, s->depth = (int)p.GetMultiplicativeDepth();
+    s->cc->Sync();
+    s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s.release();
+}
+
 template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
     auto t0 = std::chrono::steady_clock::now();
     auto s = std::make_unique<Session<N>>();
@@ -294,6 +348,22 @@ int fhesort_kway_session_create(int k, int M, int log_ring_dim, int mult_depth, 
         if (k != 2 && k != 3 && k != 5) throw std::invalid_argument("k-way: k must be 2, 3 or 5");
         if (M < 1 || M > 10) throw std::invalid_argument("k-way: M out of range");
         *out = new fhesort_session{std::unique_ptr<SessionBase>(make_kway_session_for(k, M, log_ring_dim, mult_depth, seed, device))};
+    })
+}
+int fhesort_bitonic_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out) throw std::invalid_argument("null argument: out");
+        SessionBase *b = nullptr;
+        switch (N) {
+        case 4: b = make_bitonic_session<4>(log_ring_dim, mult_depth, seed, device); break;
+        case 8: b = make_bitonic_session<8>(log_ring_dim, mult_depth, seed, device); break;
+        case 16: b = make_bitonic_session<16>(log_ring_dim, mult_depth, seed, device); break;
+        case 32: b = make_bitonic_session<32>(log_ring_dim, mult_depth, seed, device); break;
+        case 64: b = make_bitonic_session<64>(log_ring_dim, mult_depth, seed, device); break;
+        case 128: b = make_bitonic_session<128>(log_ring_dim, mult_depth, seed, device); break;
+        default: throw std::invalid_argument("BitonicSort: array length must be a power of two in 4..128");
+        }
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(b)};
     })
 }
 int fhesort_session_bootstraps(fhesort_session *s, int *count) {

@@ -206,6 +206,16 @@ class KWaySortSession(DirectSortSession):
         return c.value
 
 
+class BitonicSortSession(DirectSortSession):
+    """tests/BitonicSortTest.cpp's fixture: BitonicSort<N> on values in [0, 255], depth 58, bootstrapping above level 29."""
+    _create = "fhesort_bitonic_session_create"
+
+    def bootstraps(self):
+        c = C.c_int()
+        _ck(self.L.fhesort_session_bootstraps(self.h, C.byref(c)), self.L)
+        return c.value
+
+
 def kway_stage(k, m_total, stage, num_slots, drivers="ours"):
     """(m, logDist, slope, rotate distance), indices[2][num_slots] of one stage of the k-way network (host only)."""
     L = load_sort(drivers)

@@ -28,6 +28,9 @@ int fhesort_mehp24_session_create(int N, int log_ring_dim, int mult_depth, uint6
  * (src/kway_adapter.h:66) with bootstrapping enabled (SignConfig(compos, depth)); sign_n = 0 selects the configuration
  * the reference tests really run (dg = 2, df = the test table's d_g).  k = 2, 3 or 5. */
 int fhesort_kway_session_create(int k, int M, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
+/* BitonicSort<N> session (tests/BitonicSortTest.cpp:12-55): depth 58 (mult_depth = 0), 59-bit scaling, batch N, rotation keys
+ * +-2^i, EvalBootstrapSetup({3,3}); inputs in [0, 255]; sign_n = 0 selects CompositeSign(4, 3, 3) as the reference test does */
+int fhesort_bitonic_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
 /* EvalBootstrap calls made by the network's level guards so far (the sign's own lazy bootstraps are not counted) */
 int fhesort_session_bootstraps(fhesort_session *s, int *count);
 int fhesort_session_free(fhesort_session *s);

@@ -59,3 +59,19 @@ def test_kway_full_parameters():
     print("ring 2^17 N=16: %.0f ms, max error 2^%.1f, level %d" % (ms, np.log2(err), level))
     assert err < 0.01
     s.close()
+
+
+@pytest.mark.parametrize("n", [4, 8])
+def test_bitonic_sort_with_bootstrapping(n):
+    """tests/BitonicSortTest.cpp: ring 2^12, depth 58, 59-bit scaling, budget {3,3}, values in [0, 255], CompositeSign(4,3,3);
+    pass criterion of the reference: max error < 1, no error above 0.1"""
+    s = S.BitonicSortSession(n, log_ring_dim=12, seed=4)
+    assert s.mult_depth == 58
+    rng = np.random.default_rng(n)
+    x = rng.permutation(255)[:n].astype(np.float64) + 0.25
+    out, ms, level = s.sort(x)
+    err = np.abs(out - np.sort(x))
+    print("bitonic N=%d: %.0f ms, %d bootstraps, level %d, max error %.3g" % (n, ms, s.bootstraps(), level, err.max()))
+    assert err.max() < 0.1
+    assert s.bootstraps() >= 1
+    s.close()
