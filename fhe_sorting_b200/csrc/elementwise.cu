@@ -1,6 +1,7 @@
 // elementwise.cu — HBM-bound per-limb kernels: add/sub/mul, scalar ops, tensor product, plaintext product,
 // Galois automorphism gather, rescale lift/finish.  One thread handles two adjacent coefficients (128-bit
 // loads/stores); grid = (n / 2 / 256, limbs).  Algorithmic bytes per limb: 8n x (#inputs + #outputs).
+#include <cstdlib>
 #include <stdexcept>
 
 #include "kernels.h"
@@ -144,16 +145,22 @@ __global__ void __launch_bounds__(EW_THREADS) ew_rescale_finish(DeviceTables T, 
 // fused linear combination (Paterson-Stockmeyer leaves): each input coefficient is loaded once and feeds G accumulators.
 // The input pointer table and this limb's weights are staged in shared memory first, so the data loads of the main loop
 // do not hang off a pointer load each and can be issued eight at a time.
-template <int G>
+// CH chunks of EW_THREADS coefficients per CTA: the staging of the pointer table and of this limb's G * count weights
+// (a strided gather and a barrier) is paid once per CH * 256 coefficients instead of once per 256
+template <int G, int CH>
 __global__ void __launch_bounds__(EW_THREADS) ew_lincomb(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
                                                          const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
     extern __shared__ u64 lsm[];
     const u64 **ptr = reinterpret_cast<const u64 **>(lsm);
     uint2 *wt = reinterpret_cast<uint2 *>(lsm + count); // [G][count]
-    const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    const int n = T.n, li = blockIdx.y % ell;
     for (int i = threadIdx.x; i < count; i += EW_THREADS) ptr[i] = in[i];
     for (int i = threadIdx.x; i < G * count; i += EW_THREADS) wt[i] = __ldg(w + (size_t)i * ell + li);
     __syncthreads();
+    const ModConst m = T.mc[li];
+#pragma unroll 1
+    for (int chunk = 0; chunk < CH; chunk++) {
+    const int k = (blockIdx.x * CH + chunk) * EW_THREADS + threadIdx.x;
     if (k >= n) return;
     const size_t idx = (size_t)blockIdx.y * n + k;
     u64 lo[G], hi[G];
@@ -185,6 +192,172 @@ __global__ void __launch_bounds__(EW_THREADS) ew_lincomb(DeviceTables T, int ell
 #pragma unroll
         for (int g = 0; g < G; g++) acc_split30(lo[g], hi[g], a0[g], a1[g], a2[g], a3[g]);
     }
+#pragma unroll
+    for (int g = 0; g < G; g++) out[g][idx] = reduce128(hi[g], lo[g], m);
+    }
+}
+
+// Same sums with the loads of the next eight inputs issued before the products of the current eight (register double
+// buffer): twice the bytes in flight per thread.  Bit-identical to ew_lincomb (same partial sums in the same order).
+template <int G>
+__global__ void __launch_bounds__(EW_THREADS) ew_lincomb_pf(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
+                                                            const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lsm[];
+    const u64 **ptr = reinterpret_cast<const u64 **>(lsm);
+    uint2 *wt = reinterpret_cast<uint2 *>(lsm + count); // [G][count]
+    const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    for (int i = threadIdx.x; i < count; i += EW_THREADS) ptr[i] = in[i];
+    for (int i = threadIdx.x; i < G * count; i += EW_THREADS) wt[i] = __ldg(w + (size_t)i * ell + li);
+    __syncthreads();
+    if (k >= n) return;
+    const size_t idx = (size_t)blockIdx.y * n + k;
+    u64 lo[G], hi[G], a0[G], a1[G], a2[G], a3[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) lo[g] = hi[g] = a0[g] = a1[g] = a2[g] = a3[g] = 0;
+    u64 cur[8], nxt[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) cur[u] = u < count ? __ldcs(ptr[u] + idx) : 0;
+    for (int t0 = 0; t0 < count; t0 += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) nxt[u] = t0 + 8 + u < count ? __ldcs(ptr[t0 + 8 + u] + idx) : 0;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int t = t0 + u;
+            if (t < count) {
+                const uint32_t al = (uint32_t)cur[u] & 0x3fffffffu, ah = (uint32_t)(cur[u] >> 30);
+#pragma unroll
+                for (int g = 0; g < G; g++) {
+                    const uint2 hw = wt[g * count + t];
+                    a0[g] = mad_wide(al, hw.x, a0[g]), a1[g] = mad_wide(al, hw.y, a1[g]);
+                    a2[g] = mad_wide(ah, hw.x, a2[g]), a3[g] = mad_wide(ah, hw.y, a3[g]);
+                }
+            }
+        }
+        if ((t0 & 8) || t0 + 8 >= count) { // 16 products of 30-bit halves fit a 64-bit partial sum
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                acc_split30(lo[g], hi[g], a0[g], a1[g], a2[g], a3[g]);
+                a0[g] = a1[g] = a2[g] = a3[g] = 0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) cur[u] = nxt[u];
+    }
+    const ModConst m = T.mc[li];
+#pragma unroll
+    for (int g = 0; g < G; g++) out[g][idx] = reduce128(hi[g], lo[g], m);
+}
+
+// Same sums with the inputs streamed through a shared-memory ring by cp.async (LDGSTS): every thread keeps LC_STAGES - 1
+// eight-byte copies of its own coefficient in flight without holding registers for them, and only ever reads back what it
+// copied itself, so the ring needs no barrier.  The loads of ew_lincomb wait in registers, eight at a time, and the
+// kernel sits at a third of HBM peak on load latency; this one keeps 3 CTAs x LC_STAGES x 2 KB in flight per SM.
+constexpr int LC_STAGES = 12;
+template <int G>
+__global__ void __launch_bounds__(EW_THREADS) ew_lincomb_async(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
+                                                               const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lsm[];
+    const u64 **ptr = reinterpret_cast<const u64 **>(lsm);
+    uint2 *wt = reinterpret_cast<uint2 *>(lsm + count);            // [G][count]
+    u64 *ring = lsm + (size_t)count * (1 + G) + threadIdx.x;       // [LC_STAGES][EW_THREADS], this thread's column
+    const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    for (int i = threadIdx.x; i < count; i += EW_THREADS) ptr[i] = in[i];
+    for (int i = threadIdx.x; i < G * count; i += EW_THREADS) wt[i] = __ldg(w + (size_t)i * ell + li);
+    __syncthreads();
+    if (k >= n) return;
+    const size_t idx = (size_t)blockIdx.y * n + k;
+    auto fetch = [&](int t) {
+        if (t < count) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (size_t)(t % LC_STAGES) * EW_THREADS);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(ptr[t] + idx) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory"); // one group per input, empty past the end: the wait count stays fixed
+    };
+#pragma unroll
+    for (int t = 0; t < LC_STAGES - 1; t++) fetch(t);
+    u64 lo[G], hi[G], a0[G], a1[G], a2[G], a3[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) lo[g] = hi[g] = a0[g] = a1[g] = a2[g] = a3[g] = 0;
+    for (int t = 0; t < count; t++) {
+        fetch(t + LC_STAGES - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(LC_STAGES - 1) : "memory"); // input t has landed
+        const u64 a = ring[(size_t)(t % LC_STAGES) * EW_THREADS];
+        const uint32_t al = (uint32_t)a & 0x3fffffffu, ah = (uint32_t)(a >> 30);
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const uint2 hw = wt[g * count + t];
+            a0[g] = mad_wide(al, hw.x, a0[g]), a1[g] = mad_wide(al, hw.y, a1[g]);
+            a2[g] = mad_wide(ah, hw.x, a2[g]), a3[g] = mad_wide(ah, hw.y, a3[g]);
+        }
+        if ((t & 15) == 15 || t + 1 == count) { // 16 products of 30-bit halves fit a 64-bit partial sum
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                acc_split30(lo[g], hi[g], a0[g], a1[g], a2[g], a3[g]);
+                a0[g] = a1[g] = a2[g] = a3[g] = 0;
+            }
+        }
+    }
+    const ModConst m = T.mc[li];
+#pragma unroll
+    for (int g = 0; g < G; g++) out[g][idx] = reduce128(hi[g], lo[g], m);
+}
+
+// The leaf sums without a single data-dependent branch: pointer table and weights are padded to a multiple of 16 inputs
+// (pad weights are zero, pad pointers repeat input 0), so the body is straight-line code over groups of 16 inputs - the
+// per-input bounds checks of ew_lincomb cost it 3x the instructions (ncu: 5.9e8 warp instructions, ALU pipe 50 %, DRAM
+// 26 %).  Inputs arrive through a 16-deep cp.async ring (each thread reads back only its own copies: no barrier); ring
+// slots, weight and pointer offsets inside a group are compile-time constants.  Same partial sums in the same order as
+// ew_lincomb: bit-identical results.
+template <int G>
+__global__ void __launch_bounds__(EW_THREADS) ew_lincomb_ring(DeviceTables T, int ell, int count, const u64 *const *__restrict__ in,
+                                                              const uint2 *__restrict__ w, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lsm[];
+    const int cpad = (count + 15) & ~15;
+    const u64 **ptr = reinterpret_cast<const u64 **>(lsm);          // [cpad]
+    uint2 *wt = reinterpret_cast<uint2 *>(lsm + cpad);              // [G][cpad]
+    u64 *ring = lsm + (size_t)cpad * (1 + G) + threadIdx.x;         // [16][EW_THREADS], this thread's column
+    const int n = T.n, k = blockIdx.x * EW_THREADS + threadIdx.x, li = blockIdx.y % ell;
+    for (int i = threadIdx.x; i < cpad; i += EW_THREADS) ptr[i] = in[i < count ? i : 0];
+    for (int i = threadIdx.x; i < G * cpad; i += EW_THREADS) {
+        const int g = i / cpad, t = i - g * cpad;
+        wt[i] = t < count ? __ldg(w + (size_t)(g * count + t) * ell + li) : make_uint2(0u, 0u);
+    }
+    __syncthreads();
+    if (k >= n) return;
+    const size_t idx = (size_t)blockIdx.y * n + k;
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);
+#pragma unroll
+    for (int u = 0; u < 15; u++) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + u * EW_THREADS * 8), "l"(ptr[u] + idx) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    u64 lo[G], hi[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) lo[g] = hi[g] = 0;
+    for (int t0 = 0; t0 < cpad; t0 += 16) {
+        u64 a0[G], a1[G], a2[G], a3[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) a0[g] = a1[g] = a2[g] = a3[g] = 0;
+        const u64 **pg = ptr + t0 + 15;
+        const uint2 *wg = wt + t0;
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            if (t0 + u + 15 < cpad)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + ((u + 15) & 15) * EW_THREADS * 8), "l"(pg[u] + idx) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory"); // one group per input (empty past the end)
+            asm volatile("cp.async.wait_group 15;" ::: "memory");  // input t0 + u has landed
+            const u64 a = ring[u * EW_THREADS];
+            const uint32_t al = (uint32_t)a & 0x3fffffffu, ah = (uint32_t)(a >> 30);
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const uint2 hw = wg[g * cpad + u];
+                a0[g] = mad_wide(al, hw.x, a0[g]), a1[g] = mad_wide(al, hw.y, a1[g]);
+                a2[g] = mad_wide(ah, hw.x, a2[g]), a3[g] = mad_wide(ah, hw.y, a3[g]);
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) acc_split30(lo[g], hi[g], a0[g], a1[g], a2[g], a3[g]); // 16 products fit 64 bits
+    }
     const ModConst m = T.mc[li];
 #pragma unroll
     for (int g = 0; g < G; g++) out[g][idx] = reduce128(hi[g], lo[g], m);
@@ -195,12 +368,37 @@ void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, con
     const size_t smem = sizeof(u64) * (size_t)count * (1 + G);
     if (smem > 48 * 1024) throw std::invalid_argument("lincomb: too many inputs for one pass");
     g_launches++;
-    switch (G) {
-    case 1: ew_lincomb<1><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
-    case 2: ew_lincomb<2><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
-    case 3: ew_lincomb<3><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
-    default: ew_lincomb<4><<<grid, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;
+    // FHEB200_LINCOMB: 1 = one chunk of 256 coefficients per CTA, 2 = register-prefetching variant, 3 = cp.async ring, 5 = branch-free padded groups of 16 through a cp.async ring,
+    // 4 / 8 = chunks per CTA
+    static const int variant = [] { const char *e = getenv("FHEB200_LINCOMB"); return e ? atoi(e) : 1; }();
+#define LC_LAUNCH(KERNEL, GRID)                                                                 \
+    switch (G) {                                                                                \
+    case 1: KERNEL(1)<<<GRID, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;        \
+    case 2: KERNEL(2)<<<GRID, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;        \
+    case 3: KERNEL(3)<<<GRID, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;        \
+    default: KERNEL(4)<<<GRID, EW_THREADS, smem, st>>>(T, ell, count, in, w, out); break;       \
     }
+#define LC_RG(g) ew_lincomb_ring<g>
+#define LC_AS(g) ew_lincomb_async<g>
+#define LC_PF(g) ew_lincomb_pf<g>
+#define LC_C1(g) ew_lincomb<g, 1>
+#define LC_C4(g) ew_lincomb<g, 4>
+#define LC_C8(g) ew_lincomb<g, 8>
+    const int blocks = (T.n + EW_THREADS - 1) / EW_THREADS;
+    if (variant == 5 && count >= 12) { // (short sums would mostly multiply padding)
+        const int cpad = (count + 15) & ~15;
+        const size_t smem = sizeof(u64) * ((size_t)cpad * (1 + G) + 16 * EW_THREADS);
+        LC_LAUNCH(LC_RG, grid)
+    } else if (variant == 3) {
+        const size_t smem0 = smem;
+        {
+            const size_t smem = smem0 + sizeof(u64) * LC_STAGES * EW_THREADS; // shadows the table-only size in LC_LAUNCH
+            LC_LAUNCH(LC_AS, grid)
+        }
+    } else if (variant == 2) { LC_LAUNCH(LC_PF, grid) }
+    else if (variant == 8) { dim3 g8((blocks + 7) / 8, limbs2); LC_LAUNCH(LC_C8, g8) }
+    else if (variant == 4) { dim3 g4((blocks + 3) / 4, limbs2); LC_LAUNCH(LC_C4, g4) }
+    else { LC_LAUNCH(LC_C1, grid) }
 }
 
 __global__ void __launch_bounds__(EW_THREADS) ew_reduce_words(DeviceTables T, u64 *__restrict__ a) {

@@ -171,3 +171,22 @@ def test_async_import_export_pipeline(pair):
     ctx.sync()
     back = ctx.ct_export(lone)
     assert np.array_equal(back[0], items[1][2]) and np.array_equal(back[1], items[1][3])
+
+
+def test_lincomb_kernel_variants_are_bit_identical():
+    """The Paterson-Stockmeyer leaf-sum kernel has two implementations (FHEB200_LINCOMB=1: bounds-checked register loads,
+    5: branch-free padded groups through a cp.async ring).  Same partial sums in the same order: identical output
+    checksums on 63 inputs -> 4 outputs at three limb counts (fheb200_bench_kernel("lincomb") prints them)."""
+    import os
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sums = {}
+    for v in ("1", "5"):
+        o = subprocess.run([sys.executable, os.path.join(root, "tools", "lincomb_bench.py")], capture_output=True, text=True,
+                           env=dict(os.environ, FHEB200_LINCOMB=v), timeout=300)
+        assert o.returncode == 0, o.stderr[-2000:]
+        sums[v] = re.findall(r"lincomb checksum ([0-9a-f]{16})", o.stderr)
+        assert len(sums[v]) == 3
+    assert sums["1"] == sums["5"]
