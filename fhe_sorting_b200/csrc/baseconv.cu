@@ -153,6 +153,124 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Weighted sums of many polynomials (the leaf sums of Paterson-Stockmeyer: up to 8 outputs = sum_t w[g][t] * in_t, 63
+// inputs at degree 6510) are the same contraction as a base conversion with all targets on one modulus: K = (input,
+// byte), N = 8 outputs, M = 16 coefficients.  The CUDA-core kernel (elementwise.cu: ew_lincomb) needs four 30 x 30-bit
+// products per (input, output) pair and sits on the integer issue limit at a third of HBM bandwidth; here the products
+// are u8 x u8 MMAs (5 byte planes for 40-bit moduli), 8 outputs per pass over the inputs instead of 4, and the kernel
+// streams its inputs once.  A fragments are loaded per K step (nothing to reuse: one N tile), the B fragments of a limb
+// (built on the device by lc_build_tables from the weight residues) are read by every warp of that limb and stay in L1/L2.
+// The recombined value can reach 2^17 q, so the epilogue reduces the full 128-bit value (reduce128) instead of the
+// 16-bit-quotient shortcut of the base conversion.  Bit-identical to ew_lincomb (exact integer sums either way).
+constexpr int LC_WARPS = 4, LC_MT = 2;
+
+// B[li][ks][b][lane] (uint2): lane (g, tq), reg r, byte i  <->  output g, input j = 4 ks + 2 r + (tq >> 1), input byte
+// a = 4 (tq & 1) + i; the entry is byte b of w[g][j] 2^(8a) mod q_li.  One thread per (lane, reg).
+__global__ void __launch_bounds__(64) lc_build_tables(DeviceTables T, int ell, int count, int G, int KS, const uint2 *__restrict__ w,
+                                                      uint32_t *__restrict__ B) {
+    const int ks = blockIdx.x, li = blockIdx.y, lane = threadIdx.x & 31, reg = threadIdx.x >> 5;
+    const int g = lane >> 2, tq = lane & 3, j = 4 * ks + 2 * reg + (tq >> 1);
+    const ModConst m = T.mc[li];
+    uint32_t word[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (g < G && j < count) {
+        const uint2 sp = __ldg(w + (size_t)(g * count + j) * ell + li); // (lo30, hi30) split residue
+        const u64 c0 = (u64)sp.x | ((u64)sp.y << 30);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int a = 4 * (tq & 1) + i;
+            const u64 cp = mul_mod(c0, reduce64(1ull << (8 * a), m), m);
+#pragma unroll
+            for (int b = 0; b < 8; b++) word[b] |= (uint32_t)((cp >> (8 * b)) & 0xff) << (8 * i);
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < 8; b++) B[((((size_t)li * KS + ks) * 8 + b) * 32 + lane) * 2 + reg] = word[b];
+}
+
+__global__ void __launch_bounds__(LC_WARPS * 32) lc_tc(DeviceTables T, int ell, int count, int G, int KS, const u64 *const *__restrict__ in,
+                                                       const uint2 *__restrict__ B, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lcsm[];
+    const u64 **ptr = reinterpret_cast<const u64 **>(lcsm); // [4 KS], padded with input 0 (its weights are zero)
+    for (int i = threadIdx.x; i < 4 * KS; i += LC_WARPS * 32) ptr[i] = in[i < count ? i : 0];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, tq = lane & 3, n = T.n;
+    const int coef0 = (blockIdx.x * LC_WARPS + warp) * (16 * LC_MT);
+    if (coef0 >= n) return;
+    const int li = blockIdx.y % ell, half = tq & 1;
+    const ModConst m = T.mc[li];
+    const int np = (int)(m.bits + 7) >> 3; // byte planes of a constant below q
+    const size_t base = (size_t)blockIdx.y * n;
+    const uint2 *Bl = B + (size_t)li * KS * 8 * 32 + lane;
+
+    int acc[8][LC_MT][4];
+#pragma unroll
+    for (int b = 0; b < 8; b++)
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
+
+    // A fragments of K step ks + 1 are requested before the MMAs of step ks (two steps of loads in flight per warp)
+    uint32_t a[2][LC_MT][4];
+    auto load_a = [&](int ks, uint32_t (&dst)[LC_MT][4]) {
+        const uint32_t *s0 = reinterpret_cast<const uint32_t *>(ptr[4 * ks + (tq >> 1)] + base);
+        const uint32_t *s1 = reinterpret_cast<const uint32_t *>(ptr[4 * ks + (tq >> 1) + 2] + base);
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++) {
+            const size_t r0 = 2 * (size_t)(coef0 + 16 * mt + g) + half, r1 = r0 + 16;
+            dst[mt][0] = __ldcs(s0 + r0), dst[mt][1] = __ldcs(s0 + r1), dst[mt][2] = __ldcs(s1 + r0), dst[mt][3] = __ldcs(s1 + r1);
+        }
+    };
+    auto mma_step = [&](int ks, const uint32_t (&src)[LC_MT][4]) {
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            if (b < np) { // uniform: one modulus per CTA
+                const uint2 bf = __ldg(Bl + (size_t)(ks * 8 + b) * 32);
+#pragma unroll
+                for (int mt = 0; mt < LC_MT; mt++) imma_16832(acc[b][mt], src[mt], bf);
+            }
+        }
+    };
+    load_a(0, a[0]);
+    for (int ks = 0; ks < KS; ks += 2) {
+        if (ks + 1 < KS) load_a(ks + 1, a[1]);
+        mma_step(ks, a[0]);
+        if (ks + 1 < KS) {
+            if (ks + 2 < KS) load_a(ks + 2, a[0]);
+            mma_step(ks + 1, a[1]);
+        }
+    }
+    // this lane owns outputs 2 tq + {0, 1}, rows g and g + 8 of both M tiles
+#pragma unroll
+    for (int cpar = 0; cpar < 2; cpar++) {
+        const int target = 2 * tq + cpar;
+        if (target >= G) continue;
+        u64 *o = out[target] + base + coef0 + g;
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++)
+#pragma unroll
+            for (int rh = 0; rh < 2; rh++) {
+                int sv[8];
+#pragma unroll
+                for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                const u64 lo4 = planes_lo(sv); // planes 0..3, < 2^57
+                const u64 hi4 = mad_wide((uint32_t)sv[7], 1u << 24, mad_wide((uint32_t)sv[6], 1u << 16, mad_wide((uint32_t)sv[5], 1u << 8, (u64)(uint32_t)sv[4])));
+                const u64 vlo = lo4 + (hi4 << 32), vhi = (hi4 >> 32) + (vlo < lo4); // V = lo4 + hi4 2^32
+                o[16 * mt + 8 * rh] = reduce128(vhi, vlo, m);
+            }
+    }
+}
+
+// in: `count` input pointers, out: G <= 8 output pointers (device arrays), w: split weights [(g * count + t) * ell + limb],
+// scratch: ell * ceil(count / 4) * 256 words for the B tables
+void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
+                  u64 *const *out, u64 *scratch, cudaStream_t st) {
+    if (G < 1 || G > 8) throw std::invalid_argument("lincomb (tensor cores): 1..8 outputs per pass");
+    const int KS = (count + 3) / 4;
+    g_launches++, lc_build_tables<<<dim3(KS, ell), 64, 0, st>>>(T, ell, count, G, KS, w, reinterpret_cast<uint32_t *>(scratch));
+    const dim3 grid((T.n + LC_WARPS * 16 * LC_MT - 1) / (LC_WARPS * 16 * LC_MT), limbs2);
+    g_launches++, lc_tc<<<grid, LC_WARPS * 32, sizeof(u64) * 4 * KS, st>>>(T, ell, count, G, KS, in, reinterpret_cast<const uint2 *>(scratch), out);
+}
+
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
     const dim3 grid((T.n + BC_WARPS * 16 * BC_MT - 1) / (BC_WARPS * 16 * BC_MT), count);
     switch (KS) {

@@ -263,8 +263,9 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
         double bytes = 0;
         // "lincomb": 4 weighted sums of 63 polynomials of 2 * ell limbs each (the Paterson-Stockmeyer leaf pass of a
         // degree-6510 evaluation, k = 64): pointer table and split weights as Context::lincomb lays them out
-        const int lc_count = 63, lc_G = 4;
-        Mem lc_in, lc_out, lc_tab;
+        const bool lc_tc = [] { const char *e = getenv("FHEB200_LINCOMB"); return e ? atoi(e) == 6 : true; }();
+        const int lc_count = 63, lc_G = lc_tc ? 8 : 4;
+        Mem lc_in, lc_out, lc_tab, lc_scratch;
         if (k == "lincomb") {
             lc_in = C.alloc((size_t)lc_count * 2 * ell * n), lc_out = C.alloc((size_t)lc_G * 2 * ell * n);
             k_sample_uniform(C.T, 7, 99, 0, 1, lc_in->p, C.stream); // one limb of noise, replicated below
@@ -274,10 +275,12 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
             for (int t = 0; t < lc_count; t++) blob[t] = (u64)(uintptr_t)(lc_in->p + (size_t)t * 2 * ell * n);
             for (int g = 0; g < lc_G; g++) blob[lc_count + g] = (u64)(uintptr_t)(lc_out->p + (size_t)g * 2 * ell * n);
             for (size_t i = (size_t)lc_count + lc_G; i < blob.size(); i++) {
-                u64 v = (0x9e3779b97f4a7c15ull * (i + 1)) % C.P->moduli[(i - lc_count - lc_G) % ell];
+                const size_t rel = i - lc_count - lc_G;
+                u64 v = (0x9e3779b97f4a7c15ull * (rel + 1)) % C.P->moduli[rel % ell];
                 blob[i] = (v & 0x3fffffffull) | ((v >> 30) << 32);
             }
             lc_tab = C.alloc(blob.size());
+            lc_scratch = C.alloc(lincomb_tc_scratch_words(ell, lc_count));
             FHE_CUDA(cudaMemcpyAsync(lc_tab->p, blob.data(), blob.size() * 8, cudaMemcpyHostToDevice, C.stream));
             FHE_CUDA(cudaStreamSynchronize(C.stream));
         }
@@ -293,8 +296,12 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
             else if (k == "tensor") { k_tensor(C.T, ell, a->p, a->p + (size_t)ell * n, a->p, a->p + (size_t)ell * n, b->p, b->p + (size_t)ell * n, b->p + (size_t)2 * ell * n, C.stream); bytes = 7.0 * ell * limb; }
             else if (k == "add") { k_binary(C.T, OP_ADD, ell, a->p, a->p + (size_t)ell * n, b->p, C.stream); bytes = 3.0 * ell * limb; }
             else if (k == "lincomb") {
-                k_lincomb(C.T, ell, 2 * ell, lc_count, lc_G, (const u64 *const *)lc_tab->p, (const uint2 *)(lc_tab->p + lc_count + lc_G),
-                          (u64 *const *)(lc_tab->p + lc_count), C.stream);
+                if (lc_tc)
+                    k_lincomb_tc(C.T, ell, 2 * ell, lc_count, lc_G, (const u64 *const *)lc_tab->p, (const uint2 *)(lc_tab->p + lc_count + lc_G),
+                                 (u64 *const *)(lc_tab->p + lc_count), lc_scratch->p, C.stream);
+                else
+                    k_lincomb(C.T, ell, 2 * ell, lc_count, lc_G, (const u64 *const *)lc_tab->p, (const uint2 *)(lc_tab->p + lc_count + lc_G),
+                              (u64 *const *)(lc_tab->p + lc_count), C.stream);
                 bytes = (double)(lc_count + lc_G) * 2 * ell * limb;
             }
             else throw std::invalid_argument("bench_kernel: unknown kernel " + k);
@@ -313,7 +320,7 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
         cudaEventDestroy(e1);
         if (algo_bytes) *algo_bytes = bytes;
         if (k == "lincomb") { // checksum of the outputs on stderr: identical across kernel variants (FHEB200_LINCOMB)
-            std::vector<u64> h(lc_out->words);
+            std::vector<u64> h((size_t)4 * 2 * ell * n); // the first four outputs: the same sums whatever the outputs per pass
             FHE_CUDA(cudaMemcpy(h.data(), lc_out->p, h.size() * 8, cudaMemcpyDeviceToHost));
             u64 x = 0;
             for (size_t i = 0; i < h.size(); i++) x = x * 1099511628211ull + h[i];

@@ -188,8 +188,12 @@ std::vector<Ct> Context::lincomb(const std::vector<Ct> &in, const std::vector<st
         for (double x : w[r]) any = any || x != 0.0;
         if (any) live.push_back((int)r);
     }
-    for (size_t g0 = 0; g0 < live.size(); g0 += 4) {
-        const int G = (int)std::min<size_t>(4, live.size() - g0);
+    // FHEB200_LINCOMB=6: the sums on the integer tensor cores, 8 outputs per pass over the inputs (baseconv.cu: lc_tc)
+    static const bool tc = [] { const char *e = getenv("FHEB200_LINCOMB"); return e ? atoi(e) == 6 : true; }();
+    const bool use_tc = tc && count >= 8;
+    const size_t per_pass = use_tc ? 8 : 4;
+    for (size_t g0 = 0; g0 < live.size(); g0 += per_pass) {
+        const int G = (int)std::min<size_t>(per_pass, live.size() - g0);
         // one blob: count input pointers, G output pointers, G*count*ell split weights
         std::vector<u64> blob((size_t)count + G + (size_t)G * count * ell);
         for (int t = 0; t < count; t++) blob[t] = (u64)(uintptr_t)in[t]->mem->p;
@@ -207,8 +211,14 @@ std::vector<Ct> Context::lincomb(const std::vector<Ct> &in, const std::vector<st
         }
         Mem d = alloc(blob.size());
         FHE_CUDA(cudaMemcpyAsync(d->p, blob.data(), blob.size() * sizeof(u64), cudaMemcpyHostToDevice, stream));
-        k_lincomb(T, ell, npoly * ell, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G),
-                  (u64 *const *)(d->p + count), stream);
+        if (use_tc) {
+            Mem tables = alloc(lincomb_tc_scratch_words(ell, count));
+            k_lincomb_tc(T, ell, npoly * ell, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G),
+                         (u64 *const *)(d->p + count), tables->p, stream);
+        } else {
+            k_lincomb(T, ell, npoly * ell, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G),
+                      (u64 *const *)(d->p + count), stream);
+        }
     }
     return out;
 }

@@ -56,6 +56,11 @@ void k_tensor_square(const DeviceTables &T, int ell, const u64 *a0, const u64 *a
 // over limbs2 = npoly * ell limbs; weights are residues pre-split as (lo30, hi30); all pointer tables live in HBM
 void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
                u64 *const *out, cudaStream_t st);
+// the same sums on the integer tensor cores (baseconv.cu): G <= 8 outputs per pass, bit-identical results; scratch holds the
+// per-limb B fragment tables (lincomb_tc_scratch_words of them), built on the device from w
+void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
+                  u64 *const *out, u64 *scratch, cudaStream_t st);
+inline size_t lincomb_tc_scratch_words(int ell, int count) { return (size_t)ell * ((count + 3) / 4) * 256; }
 // a[limb][k] <- a[limb][k] mod q_limb for arbitrary 64-bit words (sums of residues from several ranks)
 void k_reduce_words(const DeviceTables &T, int ell, u64 *a, cudaStream_t st);
 // Galois automorphism (eval domain, bit-reversed order) on `limbs` limbs

@@ -98,6 +98,12 @@ inline int DirectSortDefaultStreams() {
     return v > 0 ? (v > 16 ? 16 : v) : 4;
 }
 
+inline int ilog2(int v) {
+    int l = 0;
+    while ((1 << (l + 1)) <= v) l++;
+    return l;
+}
+
 template <int N> class DirectSort : public SortBase<N> {
     CryptoContext<DCRTPoly> m_cc;
     PublicKey<DCRTPoly> m_PublicKey;
@@ -322,6 +328,83 @@ template <int N> class DirectSort : public SortBase<N> {
         CT output_array = rotationIndexCheckN(ctx_Rank, input_array);
         PRINT_PT(m_enc, output_array);
         return output_array;
+    }
+
+    // ---- hybrid: the rank of this sort, the placement of MEHP24 (reference src/sort_algo.h:776-1064)
+    // row sums of an m x m slot matrix gathered on column `col`: log2 m rotate-adds, towards the right where col's bit is set
+    CT sumColumnsToTarget(CT c, size_t m, size_t col, bool maskOutput) {
+        c->SetSlots(m * m);
+        const int logm = ilog2((int)m);
+        size_t step = m >> 1;
+        for (int i = 0; i < logm; i++, step >>= 1) {
+            const bool right = (col >> (logm - 1 - i)) & 1;
+            c = m_cc->EvalAdd(c, rot.rotate(c, right ? -(int)step : (int)step));
+        }
+        if (maskOutput) {
+            std::vector<double> msk(m * m, 0.0);
+            for (size_t i = 0; i < m; i++) msk[m * i + col] = 1.0;
+            c = m_cc->EvalMult(c, m_cc->MakeCKKSPackedPlaintext(msk, 1, c->GetLevel(), nullptr, m * m));
+        }
+        return c;
+    }
+    // column `row` of the matrix laid onto row `row`: element (i, row) moves to (row, i) by steps m(m-1)/2, m(m-1)/4, ...
+    CT transposeColumnTarget(CT c, size_t m, size_t row, bool maskOutput) {
+        c->SetSlots(m * m);
+        const int logm = ilog2((int)m);
+        size_t step = m * (m - 1) / 2;
+        for (int i = 0; i < logm; i++, step >>= 1) {
+            const bool right = (row >> (logm - 1 - i)) & 1;
+            c = m_cc->EvalAdd(c, rot.rotate(c, right ? -(int)step : (int)step));
+        }
+        if (maskOutput) {
+            std::vector<double> msk(m * m, 0.0);
+            for (size_t i = 0; i < m; i++) msk[m * row + i] = 1.0;
+            c = m_cc->EvalMult(c, m_cc->MakeCKKSPackedPlaintext(msk, 1, c->GetLevel(), nullptr, m * m));
+        }
+        return c;
+    }
+    // Slot (i, j) of block b asks "is the rank of the element in column j equal to b m + i?": a one-hot indicator of
+    // (position - rank) / N (Chebyshev sinc below 256 values, the sign-based indicator from there on) times the input,
+    // summed along the rows and transposed, leaves sorted[b m + i] on slot b m + i.  Arrays above 256 values are cut into
+    // 256-value blocks on the full ring (every block sees every window of 256 elements through the shifts k * 256).
+    CT rotationIndexCheckHybrid(const CT &ctx_Rank, const CT &input_array, PrivateKey<DCRTPoly> = PrivateKey<DCRTPoly>()) {
+        const size_t m = std::min<size_t>(N, 256), batches = N / m;
+        const size_t num_slots = N > 256 ? (size_t)max_batch : (size_t)N * N;
+        if (num_slots > (size_t)max_batch) throw std::invalid_argument("sort_hybrid: N * N slots do not fit this ring");
+        ctx_Rank->SetSlots(num_slots);
+        input_array->SetSlots(num_slots);
+        CT r = m_cc->EvalMult(ctx_Rank, 1.0 / N);
+        std::vector<CT> shiftedRank(batches), shiftedInput(batches);
+        for (size_t k = 0; k < batches; k++) {
+            shiftedRank[k] = k ? rot.rotate(r, (int)(k * 256)) : r;
+            shiftedInput[k] = k ? rot.rotate(input_array, (int)(k * 256)) : input_array;
+        }
+        std::vector<CT> placed(batches);
+        for (size_t b = 0; b < batches; b++) {
+            std::vector<double> position(num_slots, 0.0);
+            for (size_t i = 0; i < m; i++)
+                for (size_t j = 0; j < m; j++) position[i * m + j] = (double)(b * m + i) / (double)N;
+            Plaintext positionPlain = m_cc->MakeCKKSPackedPlaintext(position, 1, ctx_Rank->GetLevel(), nullptr, num_slots);
+            CT acc;
+            for (size_t k = 0; k < batches; k++) {
+                CT hit = m_cc->EvalSub(positionPlain, shiftedRank[k]);
+                if (N < 256) {
+                    hit = m_cc->EvalChebyshevSeriesPS(hit, selectCoefficients<N>(), -1, 1);
+                } else {
+                    SignConfig Cfg = SignConfig(CompositeSignConfig(3, N < 512 ? 4 : 5, 2));
+                    hit = comp.indicator(m_cc, hit, 0.5 / N, SignFunc::CompositeSign, Cfg);
+                }
+                CT term = m_cc->EvalMult(shiftedInput[k], hit);
+                acc = k ? m_cc->EvalAdd(acc, term) : term;
+            }
+            acc = sumColumnsToTarget(acc, m, b, true);
+            placed[b] = transposeColumnTarget(acc, m, b, true);
+        }
+        return batches == 1 ? placed[0] : m_cc->EvalAddMany(placed);
+    }
+    CT sort_hybrid(const CT &input_array, SignFunc SignFunc, SignConfig &Cfg, PrivateKey<DCRTPoly> sk = PrivateKey<DCRTPoly>()) {
+        CT ctx_Rank = constructRank(input_array, SignFunc, Cfg);
+        return rotationIndexCheckHybrid(ctx_Rank, input_array, sk);
     }
 };
 

@@ -16,6 +16,7 @@
 #include <omp.h>
 
 #include "../../include/fhe_sort.h"
+#include "hybrid_params.h"
 // the reference's rotation.h has no include guard: reach it through sort_algo.h only.  Angle brackets in the reference
 // build: a quoted include would find this directory's own drivers first.
 #ifdef REFERENCE_DRIVERS
@@ -40,6 +41,7 @@ struct SessionBase {
     double setup_ms = 0;
     virtual ~SessionBase() = default;
     virtual Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
+    virtual Ciphertext<DCRTPoly> sort_hybrid(const Ciphertext<DCRTPoly> &, SignConfig &) { throw std::runtime_error("sort_hybrid: DirectSort sessions only"); }
     virtual Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
     virtual Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &rank, const Ciphertext<DCRTPoly> &in) = 0;
     virtual Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) = 0;
@@ -53,6 +55,9 @@ template <int N> struct Session : SessionBase {
     std::unique_ptr<RotationComposer<N>> composer;
     Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
         return sorter->sort(in, SignFunc::CompositeSign, cfg);
+    }
+    Ciphertext<DCRTPoly> sort_hybrid(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
+        return sorter->sort_hybrid(in, SignFunc::CompositeSign, cfg, keys.secretKey);
     }
     Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
         return sorter->constructRank(in, SignFunc::CompositeSign, cfg);
@@ -261,12 +266,17 @@ template <int N> SessionBase *make_bitonic_session(int log_ring_dim, int depth_o
     return s.release();
 }
 
-template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device) {
+template <int N> SessionBase *make_session(int log_ring_dim, int depth_override, uint64_t seed, int device, bool hybrid = false) {
     auto t0 = std::chrono::steady_clock::now();
     auto s = std::make_unique<Session<N>>();
     CCParams<CryptoContextCKKSRNS> p;
     p.SetRingDim(1u << log_ring_dim);
     DirectSort<N>::getSizeParameters(p, s->rotations);
+    if (hybrid) { // sort_hybrid: the deeper chain and the placement's rotation steps (tests/DirectSortHTest.cpp:22-110)
+        p.SetMultiplicativeDepth(DirectSortHybridDepth(N));
+        for (int r : DirectSortHybridExtraRotations(N))
+            if (std::find(s->rotations.begin(), s->rotations.end(), r) == s->rotations.end()) s->rotations.push_back(r);
+    }
     if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
     if (seed) CryptoContextImpl::SetKeySeed(seed);
@@ -331,6 +341,25 @@ int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t see
         case 256: b = make_session<256>(log_ring_dim, mult_depth, seed, device); break;
         case 512: b = make_session<512>(log_ring_dim, mult_depth, seed, device); break;
         case 1024: b = make_session<1024>(log_ring_dim, mult_depth, seed, device); break;
+        default: throw std::invalid_argument("DirectSort: array length must be a power of two in 4..1024");
+        }
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(b)};
+    })
+}
+int fhesort_hybrid_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out) throw std::invalid_argument("null argument: out");
+        SessionBase *b = nullptr;
+        switch (N) {
+        case 4: b = make_session<4>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 8: b = make_session<8>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 16: b = make_session<16>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 32: b = make_session<32>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 64: b = make_session<64>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 128: b = make_session<128>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 256: b = make_session<256>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 512: b = make_session<512>(log_ring_dim, mult_depth, seed, device, true); break;
+        case 1024: b = make_session<1024>(log_ring_dim, mult_depth, seed, device, true); break;
         default: throw std::invalid_argument("DirectSort: array length must be a power of two in 4..1024");
         }
         *out = new fhesort_session{std::unique_ptr<SessionBase>(b)};
@@ -420,6 +449,7 @@ int fhesort_run(fhesort_session *s, int which, const double *input, const double
         Ciphertext<DCRTPoly> r;
         if (which == 0) r = S.sort(ct, cfg);
         else if (which == 1) r = S.rank(ct, cfg);
+        else if (which == 3) r = S.sort_hybrid(ct, cfg);
         else if (which == 2) {
             if (!aux) throw std::invalid_argument("null argument: aux (ranks)");
             r = S.place(S.enc->encryptInput(std::vector<double>(aux, aux + S.len)), ct);

@@ -114,6 +114,10 @@ class DirectSortSession:
         """DirectSort<N>::sort; returns (sorted values, elapsed ms incl. encrypt/decrypt, final level)."""
         return self._run(0, values, None, sign)
 
+    def sort_hybrid(self, values, sign=(0, 0, 0)):
+        """DirectSort<N>::sort_hybrid (rank + MEHP24-style placement); needs a HybridSortSession."""
+        return self._run(3, values, None, sign)
+
     def rank(self, values, sign=(0, 0, 0)):
         return self._run(1, values, None, sign)
 
@@ -204,6 +208,11 @@ class KWaySortSession(DirectSortSession):
         c = C.c_int()
         _ck(self.L.fhesort_session_bootstraps(self.h, C.byref(c)), self.L)
         return c.value
+
+
+class HybridSortSession(DirectSortSession):
+    """tests/DirectSortHTest.cpp's fixture: DirectSort<N> with the depth and rotation keys sort_hybrid() needs."""
+    _create = "fhesort_hybrid_session_create"
 
 
 class BitonicSortSession(DirectSortSession):

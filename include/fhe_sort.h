@@ -18,6 +18,9 @@ const char *fhesort_last_error(void);
 /* CCParams via DirectSort<N>::getSizeParameters, GenCryptoContext, KeyGen, EvalRotateKeyGen, EvalMultKeyGen, DirectSort<N>
  * (tests/DirectSortTest.cpp:24-51, 96-100).  mult_depth = 0 keeps the per-N depth; seed = 0 draws one from the OS. */
 int fhesort_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
+/* The same fixture with the parameters of DirectSort<N>::sort_hybrid (tests/DirectSortHTest.cpp:22-110: deeper chain, the
+ * rotation steps of the MEHP24-style placement); run it with fhesort_run stage 3. */
+int fhesort_hybrid_session_create(int N, int log_ring_dim, int mult_depth, uint64_t seed, int device, fhesort_session **out);
 /* MEHP24 ranking sort session (tests/mehp24/Mehp24SortTest.cpp:22-93: batch = min(N^2, n/2), depth per N, scale 40,
  * rotation keys of mehp24::utils::getRotationIndices(N)); fhesort_run stage 0 runs mehp24::sortFG (N <= 256) or
  * sortLargeArrayFG (src/mehp24/mehp24_sort.cpp:246, 609) with dg_i = (log2 N + 1) / 2, df_i = 2. */
@@ -36,7 +39,7 @@ int fhesort_session_bootstraps(fhesort_session *s, int *count);
 int fhesort_session_free(fhesort_session *s);
 int fhesort_session_info(fhesort_session *s, int *mult_depth, int *num_rotation_keys, double *setup_ms);
 /* encrypt(input[N]) -> stage -> decrypt(output[N]).  stage 0: DirectSort<N>::sort (src/sort_algo.h:752) ;
- * 1: constructRank (:368) ; 2: rotationIndexCheckN (:658) on encrypted aux[N] ranks.  sign_n = 0 selects the
+ * 1: constructRank (:368) ; 2: rotationIndexCheckN (:658) on encrypted aux[N] ranks ; 3: sort_hybrid (:1050).  sign_n = 0 selects the
  * reference tests' CompositeSign configuration for N.  elapsed_ms covers encrypt + stage + decrypt (host clock). */
 int fhesort_run(fhesort_session *s, int stage, const double *input, const double *aux, int sign_n, int dg, int df,
                 double *output, double *elapsed_ms, int *out_level);

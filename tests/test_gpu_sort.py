@@ -100,3 +100,23 @@ def test_batches_on_concurrent_streams_match_one_stream():
     assert np.abs(outs[4][0] - outs[1][0]).max() < 1e-4
     assert np.abs(outs[4][3] - outs[1][1]).max() < 1e-4
     s.close()
+
+
+@pytest.mark.parametrize("n,logn", [(8, 12), (16, 13), (32, 13)])
+def test_sort_hybrid(n, logn):
+    """DirectSort<N>::sort_hybrid (src/sort_algo.h:1050: rank + MEHP24-style placement on an N x N slot matrix) with the
+    parameters of tests/DirectSortHTest.cpp; pass criterion of that test: max error < 0.01.  Ours and, where built, the
+    reference's own sort_hybrid on the same engine."""
+    import os
+    from fhe_sorting_b200 import sort as S
+    x = S.uniform_gap_input(n, seed=9)
+    drivers = ["ours"] + (["reference"] if os.path.exists(S.REFERENCE_DRIVERS_PATH) and n == 16 else [])
+    outs = {}
+    for d in drivers:
+        s = S.HybridSortSession(n, logn, seed=31 + n, drivers=d)
+        outs[d], ms, level = s.sort_hybrid(x)
+        assert level <= s.mult_depth
+        s.close()
+        assert np.abs(outs[d] - np.sort(x)).max() < 0.01, d
+    if "reference" in outs:
+        assert np.abs(outs["ours"] - outs["reference"]).max() < 1e-3
