@@ -17,6 +17,7 @@
 // reduction is one 32 x 32 multiplication for the quotient and one 17 x 64 for the remainder.
 // Measured on B200 (tools/ubench_mma.cu): 572 TMAC/s for this MMA shape, i.e. ~25 us for the 14 GMAC of one ModUp at 41
 // limbs; the kernel is bound by the epilogue and the 160 MB it moves instead.
+#include <cstdlib>
 #include <stdexcept>
 
 #include "kernels.h"
@@ -260,6 +261,89 @@ __global__ void __launch_bounds__(LC_WARPS * 32) lc_tc(DeviceTables T, int ell, 
     }
 }
 
+
+// lc_tc with the inputs streamed through warp-private cp.async rings: every warp stages its own 32 rows of the four sources
+// of a K step (1 KB, two 16-byte copies per lane) LC_RING - 1 steps ahead, so 7 KB per warp are in flight without holding
+// registers, and builds its A fragments from shared memory (source stride padded to 80 words: the two sources a warp reads
+// at once fall on disjoint banks).  Only the warp itself touches its ring: __syncwarp orders copies and reads.
+constexpr int LC_RING = 8, LC_SRC_WORDS = 80 /* 32 rows x 2 words + 16 pad */, LC_STAGE_WORDS = 4 * LC_SRC_WORDS;
+__global__ void __launch_bounds__(LC_WARPS * 32) lc_tc_ring(DeviceTables T, int ell, int count, int G, int KS, const u64 *const *__restrict__ in,
+                                                            const uint2 *__restrict__ B, u64 *const *__restrict__ out) {
+    extern __shared__ u64 lcsm[];
+    const u64 **ptr = reinterpret_cast<const u64 **>(lcsm); // [4 KS], padded with input 0 (its weights are zero)
+    for (int i = threadIdx.x; i < 4 * KS; i += LC_WARPS * 32) ptr[i] = in[i < count ? i : 0];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, tq = lane & 3, n = T.n;
+    const int coef0 = (blockIdx.x * LC_WARPS + warp) * (16 * LC_MT);
+    if (coef0 >= n) return;
+    const int li = blockIdx.y % ell, half = tq & 1;
+    const ModConst m = T.mc[li];
+    const int np = (int)(m.bits + 7) >> 3;
+    const size_t base = (size_t)blockIdx.y * n;
+    const uint2 *Bl = B + (size_t)li * KS * 8 * 32 + lane;
+    uint32_t *ring = reinterpret_cast<uint32_t *>(lcsm + 4 * KS) + (size_t)warp * LC_RING * LC_STAGE_WORDS;
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);
+
+    int acc[8][LC_MT][4];
+#pragma unroll
+    for (int b = 0; b < 8; b++)
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
+
+    // lane copies chunk (16 bytes = rows 2c, 2c + 1) c = lane & 15 of sources (lane >> 4) and (lane >> 4) + 2
+    const int csrc = lane >> 4, chunk = lane & 15;
+    const size_t goff = base + coef0 + 2 * chunk;
+    auto stage_in = [&](int ks) {
+        if (ks < KS) {
+            const unsigned dst = ring_s + (unsigned)(((ks % LC_RING) * LC_STAGE_WORDS + csrc * LC_SRC_WORDS + chunk * 4) * 4);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(ptr[4 * ks + csrc] + goff) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2 * LC_SRC_WORDS * 4), "l"(ptr[4 * ks + csrc + 2] + goff) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory"); // one group per K step (empty past the end)
+    };
+#pragma unroll
+    for (int ks = 0; ks < LC_RING - 1; ks++) stage_in(ks);
+    for (int ks = 0; ks < KS; ks++) {
+        stage_in(ks + LC_RING - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(LC_RING - 1) : "memory");
+        __syncwarp();
+        const uint32_t *st = ring + (ks % LC_RING) * LC_STAGE_WORDS + (tq >> 1) * LC_SRC_WORDS + half;
+        uint32_t a[LC_MT][4];
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++) {
+            const int r0 = 2 * (16 * mt + g);
+            a[mt][0] = st[r0], a[mt][1] = st[r0 + 16], a[mt][2] = st[2 * LC_SRC_WORDS + r0], a[mt][3] = st[2 * LC_SRC_WORDS + r0 + 16];
+        }
+        __syncwarp(); // every lane has its fragments before the slot is refilled by the next iteration's copies
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            if (b < np) {
+                const uint2 bf = __ldg(Bl + (size_t)(ks * 8 + b) * 32);
+#pragma unroll
+                for (int mt = 0; mt < LC_MT; mt++) imma_16832(acc[b][mt], a[mt], bf);
+            }
+        }
+    }
+#pragma unroll
+    for (int cpar = 0; cpar < 2; cpar++) {
+        const int target = 2 * tq + cpar;
+        if (target >= G) continue;
+        u64 *o = out[target] + base + coef0 + g;
+#pragma unroll
+        for (int mt = 0; mt < LC_MT; mt++)
+#pragma unroll
+            for (int rh = 0; rh < 2; rh++) {
+                int sv[8];
+#pragma unroll
+                for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                const u64 lo4 = planes_lo(sv);
+                const u64 hi4 = mad_wide((uint32_t)sv[7], 1u << 24, mad_wide((uint32_t)sv[6], 1u << 16, mad_wide((uint32_t)sv[5], 1u << 8, (u64)(uint32_t)sv[4])));
+                const u64 vlo = lo4 + (hi4 << 32), vhi = (hi4 >> 32) + (vlo < lo4);
+                o[16 * mt + 8 * rh] = reduce128(vhi, vlo, m);
+            }
+    }
+}
+
 // in: `count` input pointers, out: G <= 8 output pointers (device arrays), w: split weights [(g * count + t) * ell + limb],
 // scratch: ell * ceil(count / 4) * 256 words for the B tables
 void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
@@ -268,6 +352,13 @@ void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, 
     const int KS = (count + 3) / 4;
     g_launches++, lc_build_tables<<<dim3(KS, ell), 64, 0, st>>>(T, ell, count, G, KS, w, reinterpret_cast<uint32_t *>(scratch));
     const dim3 grid((T.n + LC_WARPS * 16 * LC_MT - 1) / (LC_WARPS * 16 * LC_MT), limbs2);
+    // FHEB200_LINCOMB_RING=0: A fragments straight from global memory (lc_tc) instead of through the cp.async rings
+    static const bool ring = [] { const char *e = getenv("FHEB200_LINCOMB_RING"); return !(e && *e == '0'); }();
+    if (ring) {
+        const size_t smem = sizeof(u64) * 4 * KS + sizeof(uint32_t) * LC_WARPS * LC_RING * LC_STAGE_WORDS;
+        g_launches++, lc_tc_ring<<<grid, LC_WARPS * 32, smem, st>>>(T, ell, count, G, KS, in, reinterpret_cast<const uint2 *>(scratch), out);
+        return;
+    }
     g_launches++, lc_tc<<<grid, LC_WARPS * 32, sizeof(u64) * 4 * KS, st>>>(T, ell, count, G, KS, in, reinterpret_cast<const uint2 *>(scratch), out);
 }
 
