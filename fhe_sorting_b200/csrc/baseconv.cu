@@ -17,6 +17,7 @@
 // reduction is one 32 x 32 multiplication for the quotient and one 17 x 64 for the remainder.
 // Measured on B200 (tools/ubench_mma.cu): 572 TMAC/s for this MMA shape, i.e. ~25 us for the 14 GMAC of one ModUp at 41
 // limbs; the kernel is bound by the epilogue and the 160 MB it moves instead.
+#include <algorithm>
 #include <cstdlib>
 #include <stdexcept>
 
@@ -152,6 +153,129 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
         if (lane < 16 * BC_MT)
             for (int t = 0; t < I.copy_limbs; t++) I.copy_dst[(size_t)t * n + coef0 + lane] = I.copy_src[(size_t)t * n + coef0 + lane];
     }
+}
+
+// Persistent form of bc_convert.  ncu on the kernel above: 56 % of the warp stalls are long-scoreboard waits - the B
+// fragments (48 KB per digit, three digits per SM) fall out of L1 and every MMA pair waits for an L2 round trip, and the A
+// loads of a 32-coefficient tile are only covered by the other warps.  Here a CTA of 8 warps stays on one conversion
+// instance: it copies that instance's B fragments and target constants into shared memory once, and every warp walks its
+// share of the 32-coefficient tiles, building the A fragments from a warp-private shared-memory stage that cp.async fills
+// with the next tile while the current one is in the MMAs (source stride padded to 80 words as in lc_tc_ring).
+constexpr int BCP_WARPS = 8, BCP_SRC_WORDS = 80;
+template <int KS>
+__global__ void __launch_bounds__(BCP_WARPS * 32, 2) bc_convert_p(DeviceTables T, ConvArgs A) {
+    extern __shared__ uint4 bcsm[];
+    const ConvInstance &I = A.inst[blockIdx.y];
+    const ConvTable &C = I.tab;
+    const int NT = C.NT, n = T.n;
+    uint2 *Bs = reinterpret_cast<uint2 *>(bcsm);                      // [KS][NT][8][32]
+    uint4 *tcs = reinterpret_cast<uint4 *>(Bs + (size_t)KS * NT * 256); // [NT * 8]
+    int *slots = reinterpret_cast<int *>(tcs + NT * 8);                // [NT * 8]
+    uint32_t *stage_all = reinterpret_cast<uint32_t *>(slots + NT * 8); // [BCP_WARPS][4 KS][BCP_SRC_WORDS]
+    {
+        const uint4 *Bg = reinterpret_cast<const uint4 *>(C.B);
+        uint4 *Bd = reinterpret_cast<uint4 *>(Bs);
+        for (int i = threadIdx.x; i < KS * NT * 128; i += BCP_WARPS * 32) Bd[i] = __ldg(Bg + i);
+        for (int i = threadIdx.x; i < NT * 8; i += BCP_WARPS * 32) tcs[i] = __ldg(C.tconst + i), slots[i] = __ldg(C.tslot + i);
+        for (int i = threadIdx.x; i < BCP_WARPS * 4 * KS * BCP_SRC_WORDS; i += BCP_WARPS * 32) stage_all[i] = 0u;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, tq = lane & 3, half = tq & 1;
+    uint32_t *stage = stage_all + (size_t)warp * 4 * KS * BCP_SRC_WORDS;
+    const unsigned stage_s = (unsigned)__cvta_generic_to_shared(stage);
+    const int ntiles = n / (16 * BC_MT), step = gridDim.x * BCP_WARPS;
+    // lane copies chunk c = lane & 15 (rows 2c, 2c + 1) of sources (lane >> 4) + 2 i
+    const int csrc = lane >> 4, chunk = lane & 15;
+    auto stage_in = [&](int tile) {
+        if (tile < ntiles) {
+            const u64 *gp = I.src + (size_t)tile * (16 * BC_MT) + 2 * chunk;
+#pragma unroll
+            for (int i = 0; i < 2 * KS; i++) {
+                const int sidx = csrc + 2 * i;
+                if (sidx < C.nsrc) {
+                    const unsigned dst = stage_s + (unsigned)((sidx * BCP_SRC_WORDS + chunk * 4) * 4);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(gp + (size_t)sidx * n) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int tile = blockIdx.x * BCP_WARPS + warp;
+    stage_in(tile);
+    for (; tile < ntiles; tile += step) {
+        const int coef0 = tile * (16 * BC_MT);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        uint32_t a[BC_MT][KS][4];
+#pragma unroll
+        for (int ks = 0; ks < KS; ks++) {
+            const uint32_t *s0 = stage + (4 * ks + (tq >> 1)) * BCP_SRC_WORDS + half, *s1 = s0 + 2 * BCP_SRC_WORDS;
+#pragma unroll
+            for (int mt = 0; mt < BC_MT; mt++) {
+                const int r0 = 16 * mt + g, r1 = r0 + 8;
+                a[mt][ks][0] = s0[2 * r0], a[mt][ks][1] = s0[2 * r1];
+                a[mt][ks][2] = s1[2 * r0], a[mt][ks][3] = s1[2 * r1];
+            }
+        }
+        __syncwarp();
+        stage_in(tile + step);
+
+        for (int nt = 0; nt < NT; nt++) {
+            int acc[8][BC_MT][4];
+#pragma unroll
+            for (int b = 0; b < 8; b++)
+#pragma unroll
+                for (int mt = 0; mt < BC_MT; mt++) acc[b][mt][0] = acc[b][mt][1] = acc[b][mt][2] = acc[b][mt][3] = 0;
+            const int np = C.planes[nt];
+#pragma unroll
+            for (int ks = 0; ks < KS; ks++) {
+                const uint2 *bp = Bs + ((size_t)(ks * NT + nt) * 8) * 32 + lane;
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    if (b < 6 || np > 6) {
+                        const uint2 bf = bp[b * 32];
+#pragma unroll
+                        for (int mt = 0; mt < BC_MT; mt++) imma_16832(acc[b][mt], a[mt][ks], bf);
+                    }
+                }
+            }
+#pragma unroll
+            for (int cpar = 0; cpar < 2; cpar++) {
+                const int tp = 8 * nt + 2 * tq + cpar;
+                const int slot = slots[tp];
+                if (slot < 0) continue;
+                const uint4 tc = tcs[tp];
+                u64 *o = I.dst + (size_t)slot * n + coef0 + g;
+                if (tc.w > 48) {
+#pragma unroll
+                    for (int mt = 0; mt < BC_MT; mt++)
+#pragma unroll
+                        for (int rh = 0; rh < 2; rh++) {
+                            int sv[8];
+#pragma unroll
+                            for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                            o[16 * mt + 8 * rh] = finish8(sv, tc);
+                        }
+                } else {
+#pragma unroll
+                    for (int mt = 0; mt < BC_MT; mt++)
+#pragma unroll
+                        for (int rh = 0; rh < 2; rh++) {
+                            int sv[8];
+#pragma unroll
+                            for (int b = 0; b < 8; b++) sv[b] = acc[b][mt][2 * rh + cpar];
+                            o[16 * mt + 8 * rh] = finish6(sv, tc);
+                        }
+                }
+            }
+        }
+        if (I.copy_limbs > 0 && lane < 16 * BC_MT)
+            for (int t = 0; t < I.copy_limbs; t++) I.copy_dst[(size_t)t * n + coef0 + lane] = I.copy_src[(size_t)t * n + coef0 + lane];
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+static size_t bcp_smem(int KS, int NT) {
+    return (size_t)KS * NT * 2048 + (size_t)NT * 8 * (sizeof(uint4) + sizeof(int)) + (size_t)BCP_WARPS * 4 * KS * BCP_SRC_WORDS * 4;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -363,6 +487,27 @@ void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, 
 }
 
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
+    // FHEB200_BC_PERSIST=1: persistent CTAs with the B fragments in shared memory (bc_convert_p); default: one
+    // 32-coefficient tile per warp, operands straight from global memory (bc_convert)
+    static const bool persist = [] { const char *e = getenv("FHEB200_BC_PERSIST"); return e && *e == '1'; }();
+    int NT = 0;
+    for (int i = 0; i < count; i++) NT = std::max(NT, A.inst[i].tab.NT);
+    const size_t smem = bcp_smem(KS, NT);
+    if (persist && BC_MT == 2 && T.n % (16 * BC_MT * BCP_WARPS) == 0 && smem <= 110 * 1024) {
+        static int sms = [] { int d = 0, v = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d); return v; }();
+        const int tiles = T.n / (16 * BC_MT * BCP_WARPS);
+        const dim3 grid(std::max(1, std::min(tiles, 2 * sms / count)), count);
+        switch (KS) {
+#define CASE(k) case k: { \
+            static bool attr = false; \
+            if (!attr) cudaFuncSetAttribute(bc_convert_p<k>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024), attr = true; \
+            g_launches++, bc_convert_p<k><<<grid, BCP_WARPS * 32, smem, st>>>(T, A); } break;
+            CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6)
+#undef CASE
+            default: throw std::invalid_argument("fheb200: more than 24 limbs per digit unsupported");
+        }
+        return;
+    }
     const dim3 grid((T.n + BC_WARPS * 16 * BC_MT - 1) / (BC_WARPS * 16 * BC_MT), count);
     switch (KS) {
 #define CASE(k) case k: g_launches++, bc_convert<k><<<grid, BC_WARPS * 32, 0, st>>>(T, A); break;
