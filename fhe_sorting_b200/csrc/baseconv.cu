@@ -161,6 +161,8 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
 // instance: it copies that instance's B fragments and target constants into shared memory once, and every warp walks its
 // share of the 32-coefficient tiles, building the A fragments from a warp-private shared-memory stage that cp.async fills
 // with the next tile while the current one is in the MMAs (source stride padded to 80 words as in lc_tc_ring).
+// Measured on B200 (profiles/r01/baseconv_tiling_sweep.txt): 92.1 / 50.0 us (ModUp / ModDown at 41 limbs) against 84.6 / 44.3 us
+// for bc_convert, bit-identical output - the waits were not the B fragments.  Kept behind FHEB200_BC_PERSIST=1 for the record.
 constexpr int BCP_WARPS = 8, BCP_SRC_WORDS = 80;
 template <int KS>
 __global__ void __launch_bounds__(BCP_WARPS * 32, 2) bc_convert_p(DeviceTables T, ConvArgs A) {
