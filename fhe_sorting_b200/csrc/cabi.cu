@@ -253,6 +253,9 @@ int fheb200_eval_add_many(fheb200_ctx *ctx, fheb200_ct *const *cts, size_t count
 int fheb200_eval_mult_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
     GUARD({ need(ctx, "ctx"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->mult_pt(a->c, p->p)); })
 }
+int fheb200_eval_mult_plain_add(fheb200_ctx *ctx, fheb200_ct *acc, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
+    GUARD({ need(ctx, "ctx"); need(acc, "acc"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->mult_pt_add(acc->c, a->c, p->p)); })
+}
 int fheb200_eval_mult_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out) {
     GUARD({ need(ctx, "ctx"); need(a, "a"); *out = wrap(ctx->c->mult_const(a->c, c)); })
 }

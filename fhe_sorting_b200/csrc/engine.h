@@ -138,6 +138,7 @@ class Context : public std::enable_shared_from_this<Context> {
     Ct relinearize(const Ct &a);             // 3 -> 2 polynomials (no-op on 2)
     Ct add_lazy(const Ct &a, const Ct &b);   // EvalAdd where either side may still carry its s^2 polynomial
     Ct mult_pt(const Ct &a, const Pt &p);
+    Ct mult_pt_add(const Ct &acc, const Ct &a, const Pt &p); // acc + a * p, one pass
     Ct mult_const(const Ct &a, double c);
     Ct rotate(const Ct &a, int index);
     std::shared_ptr<Precomp> fast_rotation_precompute(const Ct &a);

@@ -313,6 +313,18 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     CT EvalSquare(const CT &a) { return binary(fheb200_eval_mult, a, a); }
     CT EvalMult(const CT &a, const Plaintext &p) { return plain(fheb200_eval_mult_plain, a, p); }
     CT EvalMult(const Plaintext &p, const CT &a) { return plain(fheb200_eval_mult_plain, a, p); }
+    // extension (not lbcrypto): acc += a * p in one pass; acc may be empty
+    void EvalMultAddInPlace(CT &acc, const CT &a, const Plaintext &p) {
+        if (!acc) {
+            acc = EvalMult(a, p);
+            return;
+        }
+        need(a);
+        if (!p) throw std::runtime_error("null plaintext passed to the crypto context");
+        fheb200_ct *o = nullptr;
+        fheb200_check(fheb200_eval_mult_plain_add(ctx, acc->h, a->h, p->h, &o));
+        acc->replace(o);
+    }
     CT EvalMult(const CT &a, double c) { return constant(fheb200_eval_mult_const, a, c); }
     CT EvalMult(double c, const CT &a) { return constant(fheb200_eval_mult_const, a, c); }
     void EvalMultInPlace(CT &a, double c) { inplace(a, EvalMult(a, c)); }

@@ -234,9 +234,7 @@ template <int N> class DirectSort : public SortBase<N> {
             for (int i = 0; i < np; i++) {
                 // = vectorRotate(generateMaskVector(num_slots, np * j + i), -giant)
                 auto pmsk = m_cc->RotatePlaintext(block0, -((np * j + i) * N + giant));
-                CT term = m_cc->EvalMult(preRotatedArrays[i], pmsk);
-                if (T) m_cc->EvalAddInPlace(T, term);
-                else T = term;
+                m_cc->EvalMultAddInPlace(T, preRotatedArrays[i], pmsk);
             }
             groups[j] = rot.rotate(T, giant);
         }
@@ -277,9 +275,7 @@ template <int N> class DirectSort : public SortBase<N> {
             for (int j = 0; j < np; j++) {
                 // = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j), see vecRotsOpt
                 auto pmsk = m_cc->RotatePlaintext(block0, j - (np * i + j) * N);
-                CT term = m_cc->EvalMult(masked_inputs[j], pmsk);
-                if (tmp) m_cc->EvalAddInPlace(tmp, term);
-                else tmp = term;
+                m_cc->EvalMultAddInPlace(tmp, masked_inputs[j], pmsk);
             }
             tmp = rot.rotate(tmp, ib * num_partition + i * np);
             if (result) m_cc->EvalAddInPlace(result, tmp);

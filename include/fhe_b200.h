@@ -111,6 +111,9 @@ int fheb200_eval_add_many(fheb200_ctx *ctx, fheb200_ct *const *cts, size_t count
 int fheb200_eval_mult(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
 /* EvalMult(ct, pt) (src/sort_algo.h:319,344,359,576) */
 int fheb200_eval_mult_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
+/* acc + a * p in one pass: EvalMult(ct, pt) followed by EvalAddInPlace (src/sort_algo.h:269-276, 616-624), bit-identical to
+ * the two calls; acc may be modified in place and returned under the new handle - release acc afterwards, do not reuse it */
+int fheb200_eval_mult_plain_add(fheb200_ctx *ctx, fheb200_ct *acc, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
 /* EvalMult(ct, double) / EvalMultInPlace(ct, double) (src/sign.cpp:26-30 ; src/sort_algo.h:723) */
 int fheb200_eval_mult_const(fheb200_ctx *ctx, fheb200_ct *a, double c, fheb200_ct **out);
 /* explicit rescale (ModReduce) — a no-op at the OpenFHE API level in FLEXIBLEAUTOEXT, exposed for tests */
