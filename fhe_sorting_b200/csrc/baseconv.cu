@@ -473,13 +473,14 @@ __global__ void __launch_bounds__(LC_WARPS * 32) lc_tc_ring(DeviceTables T, int 
 // in: `count` input pointers, out: G <= 8 output pointers (device arrays), w: split weights [(g * count + t) * ell + limb],
 // scratch: ell * ceil(count / 4) * 256 words for the B tables
 void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
-                  u64 *const *out, u64 *scratch, cudaStream_t st) {
+                  u64 *const *out, u64 *scratch, cudaStream_t st, int force_ring) {
     if (G < 1 || G > 8) throw std::invalid_argument("lincomb (tensor cores): 1..8 outputs per pass");
     const int KS = (count + 3) / 4;
     g_launches++, lc_build_tables<<<dim3(KS, ell), 64, 0, st>>>(T, ell, count, G, KS, w, reinterpret_cast<uint32_t *>(scratch));
     const dim3 grid((T.n + LC_WARPS * 16 * LC_MT - 1) / (LC_WARPS * 16 * LC_MT), limbs2);
     // FHEB200_LINCOMB_RING=0: A fragments straight from global memory (lc_tc) instead of through the cp.async rings
-    static const bool ring = [] { const char *e = getenv("FHEB200_LINCOMB_RING"); return !(e && *e == '0'); }();
+    static const bool ring_env = [] { const char *e = getenv("FHEB200_LINCOMB_RING"); return !(e && *e == '0'); }();
+    const bool ring = force_ring < 0 ? ring_env : force_ring != 0;
     if (ring) {
         const size_t smem = sizeof(u64) * 4 * KS + sizeof(uint32_t) * LC_WARPS * LC_RING * LC_STAGE_WORDS;
         g_launches++, lc_tc_ring<<<grid, LC_WARPS * 32, smem, st>>>(T, ell, count, G, KS, in, reinterpret_cast<const uint2 *>(scratch), out);

@@ -183,6 +183,104 @@ int fheb200_raw_rescale(fheb200_ctx *ctx, int ell, const uint64_t *in, uint64_t 
     })
 }
 
+// ---- single-kernel entry points for the limb-level parity tests (tests/test_gpu_kernels_limb.py)
+// out[g][limbs2][n] = sum_t in[t][limbs2][n] * w[g][t][limb % ell]  (the Paterson-Stockmeyer leaf sums);
+// variant 0: integer tensor cores through the cp.async rings (lc_tc_ring), 1: tensor cores, operands from global memory
+// (lc_tc), 2: CUDA cores (ew_lincomb, G <= 4)
+int fheb200_raw_lincomb(fheb200_ctx *ctx, int ell, int limbs2, int count, int G, const uint64_t *in, const uint64_t *w, uint64_t *out,
+                        int variant) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(in, "in"); need(w, "w"); need(out, "out");
+        if (ell < 1 || ell > C.P->L || limbs2 % ell || count < 1 || G < 1 || G > (variant == 2 ? 4 : 8))
+            throw std::invalid_argument("raw_lincomb: bad shape");
+        const size_t poly = (size_t)limbs2 * n;
+        Mem din = C.alloc(poly * count), dout = C.alloc(poly * G);
+        h2d(C, din->p, in, poly * count * 8);
+        std::vector<u64> blob((size_t)count + G + (size_t)G * count * ell);
+        for (int t = 0; t < count; t++) blob[t] = (u64)(uintptr_t)(din->p + poly * t);
+        for (int g = 0; g < G; g++) blob[count + g] = (u64)(uintptr_t)(dout->p + poly * g);
+        for (size_t i = 0; i < (size_t)G * count * ell; i++) blob[(size_t)count + G + i] = (w[i] & 0x3fffffffull) | ((w[i] >> 30) << 32);
+        Mem d = C.alloc(blob.size());
+        h2d(C, d->p, blob.data(), blob.size() * 8);
+        if (variant == 2) {
+            k_lincomb(C.T, ell, limbs2, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G), (u64 *const *)(d->p + count), C.stream);
+        } else {
+            Mem tables = C.alloc(lincomb_tc_scratch_words(ell, count));
+            k_lincomb_tc(C.T, ell, limbs2, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G), (u64 *const *)(d->p + count),
+                         tables->p, C.stream, variant == 0 ? 1 : 0);
+        }
+        d2h(C, out, dout->p, poly * G * 8);
+    })
+}
+// o_b = (accumulate ? o_b : 0) + a_b * pt on ell limbs (ew_mul_pt)
+int fheb200_raw_mul_pt(fheb200_ctx *ctx, int ell, const uint64_t *a0, const uint64_t *a1, const uint64_t *pt, uint64_t *o0, uint64_t *o1,
+                       int accumulate) {
+    GUARD({
+        LOCKCTX(ctx);
+        const size_t w = (size_t)ell * n;
+        Mem d = C.alloc(5 * w);
+        h2d(C, d->p, a0, w * 8); h2d(C, d->p + w, a1, w * 8); h2d(C, d->p + 2 * w, pt, w * 8);
+        h2d(C, d->p + 3 * w, o0, w * 8); h2d(C, d->p + 4 * w, o1, w * 8);
+        k_mul_pt(C.T, ell, d->p, d->p + w, d->p + 2 * w, d->p + 3 * w, d->p + 4 * w, accumulate, C.stream);
+        d2h(C, o0, d->p + 3 * w, w * 8); d2h(C, o1, d->p + 4 * w, w * 8);
+    })
+}
+// (d0, d1, d2) = (a0 b0, a0 b1 + a1 b0, a1 b1) on ell limbs (ew_tensor; b == a: ew_tensor_square)
+int fheb200_raw_tensor(fheb200_ctx *ctx, int ell, const uint64_t *a0, const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                       uint64_t *d0, uint64_t *d1, uint64_t *d2) {
+    GUARD({
+        LOCKCTX(ctx);
+        const size_t w = (size_t)ell * n;
+        Mem d = C.alloc(7 * w);
+        h2d(C, d->p, a0, w * 8); h2d(C, d->p + w, a1, w * 8);
+        if (b0) { h2d(C, d->p + 2 * w, b0, w * 8); h2d(C, d->p + 3 * w, b1, w * 8); }
+        if (b0) k_tensor(C.T, ell, d->p, d->p + w, d->p + 2 * w, d->p + 3 * w, d->p + 4 * w, d->p + 5 * w, d->p + 6 * w, C.stream);
+        else k_tensor_square(C.T, ell, d->p, d->p + w, d->p + 4 * w, d->p + 5 * w, d->p + 6 * w, C.stream);
+        d2h(C, d0, d->p + 4 * w, w * 8); d2h(C, d1, d->p + 5 * w, w * 8); d2h(C, d2, d->p + 6 * w, w * 8);
+    })
+}
+// S[2][ell + K][n] += pt (.) sigma_g(v) in the extended basis (ks_dh_accumulate; acc may be null: the unrotated term)
+int fheb200_raw_dh_accumulate(fheb200_ctx *ctx, int ell, const uint64_t *acc, const uint64_t *cP, const uint64_t *pt, uint64_t *S,
+                              uint32_t galois) {
+    GUARD({
+        LOCKCTX(ctx);
+        const DevicePlan &D = C.plan(ell);
+        const size_t W = (size_t)D.width * n, Q = (size_t)ell * n;
+        Mem dacc = C.alloc(2 * W), dcp = C.alloc(2 * Q), dpt = C.alloc(W), dS = C.alloc(2 * W);
+        if (acc) h2d(C, dacc->p, acc, 2 * W * 8);
+        h2d(C, dcp->p, cP, 2 * Q * 8); h2d(C, dpt->p, pt, W * 8); h2d(C, dS->p, S, 2 * W * 8);
+        k_dh_accumulate(C.T, D, acc ? dacc->p : nullptr, dcp->p, dpt->p, dS->p, galois, C.stream);
+        d2h(C, S, dS->p, 2 * W * 8);
+    })
+}
+// evk inner product alone: acc[2][ell + K][n] = sum_j digits[j] (.) evk[j] with the key of Galois element g (0: relin key)
+int fheb200_raw_inner_product(fheb200_ctx *ctx, int ell, uint32_t galois, const uint64_t *digits, uint64_t *acc) {
+    GUARD({
+        LOCKCTX(ctx);
+        const DevicePlan &D = C.plan(ell);
+        const u64 *evk = galois == 0 ? C.evk_mult : (C.evk_rot.count(galois) ? C.evk_rot[galois] : nullptr);
+        if (!evk) throw std::runtime_error("raw_inner_product: key not present");
+        const size_t W = (size_t)D.width * n;
+        Mem dd = C.alloc(D.beta * W), da = C.alloc(2 * W);
+        h2d(C, dd->p, digits, D.beta * W * 8);
+        k_inner_product(C.T, D, dd->p, evk, da->p, C.stream);
+        d2h(C, acc, da->p, 2 * W * 8);
+    })
+}
+// ModDown alone: acc[2][ell + K][n] (evaluation domain) -> out_b = round(acc_b / P) on ell limbs
+int fheb200_raw_moddown(fheb200_ctx *ctx, int ell, const uint64_t *acc, uint64_t *out0, uint64_t *out1) {
+    GUARD({
+        LOCKCTX(ctx);
+        const DevicePlan &D = C.plan(ell);
+        const size_t W = (size_t)D.width * n, Q = (size_t)ell * n;
+        Mem da = C.alloc(2 * W), o = C.alloc(2 * Q);
+        h2d(C, da->p, acc, 2 * W * 8);
+        C.moddown(ell, da->p, nullptr, nullptr, o->p, o->p + Q, 1u);
+        d2h(C, out0, o->p, Q * 8); d2h(C, out1, o->p + Q, Q * 8);
+    })
+}
+
 int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words) {
     GUARD({
         need(ct, "ct");

@@ -238,6 +238,7 @@ const uint32_t *Context::desc(const std::vector<uint32_t> &d) {
     auto it = descs_.find(d);
     if (it != descs_.end()) return it->second;
     uint32_t *p = (uint32_t *)owned_alloc(sizeof(uint32_t) * d.size(), d.data());
+    ntt_register_desc(p, d.data(), d.size());
     descs_[d] = p;
     return p;
 }
@@ -275,10 +276,13 @@ const DevicePlan &Context::plan(int ell) {
     for (int i = 0; i < ell; i++) dq.push_back(((uint32_t)i << 8) | (uint32_t)i);
     // batch order = launch order of the CTAs: limbs of equal modulus are adjacent so that their twiddles are read from
     // HBM once and then hit in L2
-    for (int t = 0; t < H.width; t++)
+    // ... and the 60-bit P limbs (integer path, 1.6x the time of an FP64 limb) go first so that they do not form the tail
+    for (int tt = 0; tt < H.width; tt++) {
+        const int t = tt < P->K ? ell + tt : tt - P->K;
         for (int j = 0; j < H.beta; j++)
             if (t < H.dstart[j] || t >= H.dstart[j] + H.dsize[j])
                 dm.push_back(((uint32_t)(j * H.width + t) << 8) | (uint32_t)H.qp[t]);
+    }
     for (int k = 0; k < P->K; k++) // (same order as DevicePlan::down_scale)
         for (int b = 0; b < 2; b++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
     for (int i = 0; i < ell; i++)

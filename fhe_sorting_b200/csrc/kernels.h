@@ -28,6 +28,8 @@ struct LimbScalars {             // per-limb scalar + Shoup companion, passed by
 };
 
 // ---- NTT (batched over limbs) ----
+// host copy of a descriptor array that lives at `dev` (the fused n = 2^17 kernels take descriptors as kernel parameters)
+void ntt_register_desc(const uint32_t *dev, const uint32_t *host, size_t count);
 // src and dst share the slot layout of the descriptors; src == dst transforms in place
 void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
 void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st,
@@ -58,8 +60,9 @@ void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, con
                u64 *const *out, cudaStream_t st);
 // the same sums on the integer tensor cores (baseconv.cu): G <= 8 outputs per pass, bit-identical results; scratch holds the
 // per-limb B fragment tables (lincomb_tc_scratch_words of them), built on the device from w
+// (force_ring: -1 = FHEB200_LINCOMB_RING decides [default: ring], 0 = lc_tc, 1 = lc_tc_ring)
 void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
-                  u64 *const *out, u64 *scratch, cudaStream_t st);
+                  u64 *const *out, u64 *scratch, cudaStream_t st, int force_ring = -1);
 inline size_t lincomb_tc_scratch_words(int ell, int count) { return (size_t)ell * ((count + 3) / 4) * 256; }
 // a[limb][k] <- a[limb][k] mod q_limb for arbitrary 64-bit words (sums of residues from several ranks)
 void k_reduce_words(const DeviceTables &T, int ell, u64 *a, cudaStream_t st);

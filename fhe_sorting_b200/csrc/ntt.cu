@@ -15,6 +15,10 @@
 // thread is fewer issue slots than the 48 SHFL a 64-bit 8x8 lane transpose needs, so shared memory is used.
 #include <algorithm>
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <vector>
 
 #include "kernels.h"
 #include "modarith.cuh"
@@ -103,10 +107,16 @@ struct PassGeom {
     int logn, S, S0, lc, log_tile; // S stages starting at global stage S0; lc = 0 for pass B
     int pass_a;
 };
-__device__ __forceinline__ uint32_t tile_to_g(const PassGeom &G, int e) {
-    if (G.pass_a) return ((uint32_t)(e >> G.lc) << (G.logn - G.S)) + (blockIdx.x << G.lc) + (e & ((1 << G.lc) - 1));
-    return (blockIdx.x << G.log_tile) + e;
+__device__ __forceinline__ uint32_t tile_to_g(const PassGeom &G, int e, uint32_t tile) {
+    if (G.pass_a) return ((uint32_t)(e >> G.lc) << (G.logn - G.S)) + (tile << G.lc) + (e & ((1 << G.lc) - 1));
+    return (tile << G.log_tile) + e;
 }
+// CG: the word was written earlier in the same launch by another SM (fused two-phase kernels): read it from L2, never
+// from this SM's L1, which may still hold the line as phase 0 of an in-place transform saw it
+template <bool CG>
+__device__ __forceinline__ u64 ld_word(const u64 *p) { return CG ? __ldcg(p) : *p; }
+template <bool CG>
+__device__ __forceinline__ ulonglong2 ld_pair(const ulonglong2 *p) { return CG ? __ldcg(p) : *p; }
 __device__ __forceinline__ int triple_base(int tid, int p) { return ((tid >> p) << (p + 3)) | (tid & ((1 << p) - 1)); }
 
 __device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
@@ -115,9 +125,9 @@ __device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
 
 // ---------------------------------------------------------------- forward pass
 // final_reduce: bring values to [0,q) on the way out (last pass), otherwise they stay in [0,4q)
-template <bool LAZY>
+template <bool LAZY, bool CG>
 __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                              const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm) {
+                                              const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm, uint32_t tile) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const ModConst mc = T.mc[qp];
@@ -127,12 +137,12 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
     const int c_first = (G.S - 1) % 3 + 1;
     int p = G.S - 3 + lowbit; // low bit of the current triple
     int base = triple_base(tid, p);
-    uint32_t g0 = tile_to_g(G, base);
+    uint32_t g0 = tile_to_g(G, base, tile);
     u64 v[8];
     {
         const uint32_t st = g_step(G, p);
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
+        for (int k = 0; k < 8; k++) v[k] = ld_word<CG>(src + off + g0 + k * st);
     }
     int s = G.S0;
     if (c_first == 1) fwd_chunk<1, LAZY>(v, tw, s, G.logn, g0, nq, q2);
@@ -151,7 +161,7 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
         base = triple_base(tid, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
-        g0 = tile_to_g(G, base);
+        g0 = tile_to_g(G, base, tile);
         fwd_chunk<3, LAZY>(v, tw, s, G.logn, g0, nq, q2);
         s += 3;
     }
@@ -238,8 +248,9 @@ __device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__res
 }
 
 // first: the pass reads reduced u64 input (otherwise doubles left by the previous pass); last: writes reduced u64
+template <bool CG>
 __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu) {
+                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu, uint32_t tile) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -250,13 +261,13 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
     const int c_first = (G.S - 1) % 3 + 1;
     int p = G.S - 3 + lowbit;
     int base = triple_base(tid, p);
-    uint32_t g0 = tile_to_g(G, base);
+    uint32_t g0 = tile_to_g(G, base, tile);
     double v[8];
     {
         const uint32_t st = g_step(G, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const u64 x = src[off + g0 + k * st];
+            const u64 x = ld_word<CG>(src + off + g0 + k * st);
             v[k] = first ? fp_from_u64(x) : __longlong_as_double((long long)x);
         }
     }
@@ -277,7 +288,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
         base = triple_base(tid, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
-        g0 = tile_to_g(G, base);
+        g0 = tile_to_g(G, base, tile);
         fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
         s += 3;
     }
@@ -295,9 +306,11 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
     }
 }
 
+template <bool CG>
 __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu,
-                                                 const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
+                                                 const u64 *__restrict__ custom, const u64 *__restrict__ custom_s, uint32_t tile,
+                                                 uint32_t bidx) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -308,13 +321,13 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
     const int c_last = (G.S - 1) % 3 + 1, ptop = G.S - 3 + lowbit, m = (G.S - c_last) / 3;
     int p = m > 0 ? lowbit : ptop;
     int base = triple_base(tid, p);
-    uint32_t g0 = tile_to_g(G, base);
+    uint32_t g0 = tile_to_g(G, base, tile);
     double v[8];
     if (!G.pass_a && p == 0) {
         const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const ulonglong2 t = in[k];
+            const ulonglong2 t = ld_pair<CG>(in + k);
             v[2 * k] = first ? fp_from_u64(t.x) : __longlong_as_double((long long)t.x);
             v[2 * k + 1] = first ? fp_from_u64(t.y) : __longlong_as_double((long long)t.y);
         }
@@ -322,7 +335,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
         const uint32_t st = g_step(G, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const u64 x = src[off + g0 + k * st];
+            const u64 x = ld_word<CG>(src + off + g0 + k * st);
             v[k] = first ? fp_from_u64(x) : __longlong_as_double((long long)x);
         }
     }
@@ -349,7 +362,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
         base = triple_base(tid, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
-        g0 = tile_to_g(G, base);
+        g0 = tile_to_g(G, base, tile);
     }
     if (growth + c_last > 8) {
 #pragma unroll
@@ -360,7 +373,7 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
     else fp_inv_chunk<3>(v, tw, G.S0, G.logn, g0, q, qinv);
     const uint32_t st = g_step(G, p);
     if (last) {
-        const double ni = (double)(custom ? custom[blockIdx.y] : T.ninv[qp]);
+        const double ni = (double)(custom ? custom[bidx] : T.ninv[qp]);
 #pragma unroll
         for (int k = 0; k < 8; k++) dst[off + g0 + k * st] = fp_to_u64(fp_mulmod(v[k], ni, qinv, q), q, qinv);
     } else {
@@ -375,17 +388,18 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass(DeviceTab
                                                              const uint32_t *__restrict__ desc, PassGeom G, int first, int final_reduce) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body(T, src, dst, d, G, first, final_reduce, sm);
-    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true>(T, src, dst, d, G, final_reduce, sm);
-    else fwd_pass_body<false>(T, src, dst, d, G, final_reduce, sm);
+    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, blockIdx.x);
+    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
+    else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
 }
 
 // ---------------------------------------------------------------- inverse pass
 // scale: multiply by n^-1 and reduce to [0,q) on the way out (last pass); otherwise values leave in [0,2q)
-template <bool LAZY>
+template <bool LAZY, bool CG>
 __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                               const uint32_t d, const PassGeom &G, int scale, u64 *sm,
-                                              const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
+                                              const u64 *__restrict__ custom, const u64 *__restrict__ custom_s, uint32_t tile,
+                                              uint32_t bidx) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
@@ -394,19 +408,19 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
     const int c_last = (G.S - 1) % 3 + 1, ptop = G.S - 3 + lowbit, m = (G.S - c_last) / 3; // m full radix-8 steps first
     int p = m > 0 ? lowbit : ptop;
     int base = triple_base(tid, p);
-    uint32_t g0 = tile_to_g(G, base);
+    uint32_t g0 = tile_to_g(G, base, tile);
     u64 v[8];
     if (!G.pass_a && p == 0) {
         const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            ulonglong2 t = in[k];
+            ulonglong2 t = ld_pair<CG>(in + k);
             v[2 * k] = t.x, v[2 * k + 1] = t.y;
         }
     } else {
         const uint32_t st = g_step(G, p);
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = src[off + g0 + k * st];
+        for (int k = 0; k < 8; k++) v[k] = ld_word<CG>(src + off + g0 + k * st);
     }
 #pragma unroll
     for (int i = 0; i < m; i++) {
@@ -420,14 +434,14 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
         base = triple_base(tid, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
-        g0 = tile_to_g(G, base);
+        g0 = tile_to_g(G, base, tile);
     }
     // last (possibly partial) step on the top triple: stages S0 + c_last - 1 ... S0
     if (c_last == 1) inv_chunk<1, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     else if (c_last == 2) inv_chunk<2, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     else inv_chunk<3, LAZY>(v, tw, G.S0, G.logn, g0, q, nq, q2);
     if (scale) {
-        const u64 ni = custom ? custom[blockIdx.y] : T.ninv[qp], nis = custom ? custom_s[blockIdx.y] : T.ninv[T.F + qp];
+        const u64 ni = custom ? custom[bidx] : T.ninv[qp], nis = custom ? custom_s[bidx] : T.ninv[T.F + qp];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = shoup_mul(v[k], ni, nis, q);
     }
@@ -441,9 +455,9 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass(DeviceTab
                                                              const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
     extern __shared__ u64 sm[];
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom, custom_s);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom, custom_s);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom, custom_s);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body<false>(T, src, dst, d, G, first, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+    else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
 }
 
 // Compile-time geometry for the production ring (n = 2^17): every shift, stride and loop trip count of the pass bodies
@@ -454,9 +468,9 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_c(DeviceT
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body(T, src, dst, d, G, first, final_reduce, sm);
-    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true>(T, src, dst, d, G, final_reduce, sm);
-    else fwd_pass_body<false>(T, src, dst, d, G, final_reduce, sm);
+    if (fp_ok(T, d & 0xff)) fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, blockIdx.x);
+    else if (lazy_ok(T, d & 0xff)) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
+    else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
 }
 template <int LOGN, int S, int S0, int LC, int PA>
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_c(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
@@ -465,9 +479,145 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_c(DeviceT
     extern __shared__ u64 sm[];
     const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
     const uint32_t d = desc[blockIdx.y];
-    if (fp_ok(T, d & 0xff)) fp_inv_pass_body(T, src, dst, d, G, first, scale, sm, custom, custom_s);
-    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true>(T, src, dst, d, G, scale, sm, custom, custom_s);
-    else inv_pass_body<false>(T, src, dst, d, G, scale, sm, custom, custom_s);
+    if (fp_ok(T, d & 0xff)) fp_inv_pass_body<false>(T, src, dst, d, G, first, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+    else if (lazy_ok(T, d & 0xff)) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+    else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+}
+
+// ---------------------------------------------------------------- fused two-phase transform (n = 2^17)
+// One launch runs both passes of a whole batch.  Work items (one CTA each) are ordered by blockIdx.x so that phase 1 of
+// limb i is queued NTT_AHEAD limbs' worth of phase-0 items after phase 0 of limb i: by the time the hardware dispatches
+// it (CTAs start in blockIdx order; the same assumption CUB's decoupled look-back scan makes) its 64 producers have long
+// been running or are done, so the per-limb counter it polls is normally already complete, and the 1 MiB intermediate of
+// a limb is consumed out of L2 a few microseconds after it was written instead of making a round trip through HBM.
+// DRAM traffic per limb: 8n read + 8n written (the algorithmic 16n) + twiddles.  Phase-1 loads bypass L1 (ld.global.cg).
+// done[limb]: +1 per finished phase-0 tile (64 = ready), +1 per finished phase-1 tile; the CTA that brings it to 128
+// resets it to 0, so the scratch is clean for the next launch on the same stream without a memset.
+constexpr int NTT_AHEAD = 10;        // limbs of phase-0 work between a limb's two phases (>= resident CTAs / 64 = 9.25)
+constexpr int NTT_FUSED_MAX = 256;   // descriptors travel in the kernel parameters (constant bank)
+struct NttBatch {
+    uint32_t desc[NTT_FUSED_MAX];
+};
+__device__ __forceinline__ void fused_item(uint32_t b, int count, int &phase, int &limb) {
+    const int D = NTT_AHEAD;
+    if (count <= D) {
+        phase = (int)b >= count;
+        limb = phase ? (int)b - count : (int)b;
+    } else if ((int)b < D) {
+        phase = 0, limb = (int)b;
+    } else {
+        const int r = (int)b - D, pairs = count - D;
+        if (r < 2 * pairs) phase = !(r & 1), limb = (r & 1) ? D + (r >> 1) : (r >> 1);
+        else phase = 1, limb = pairs + (r - 2 * pairs);
+    }
+}
+__device__ __forceinline__ void fused_publish(unsigned *done, int limb, int tiles) { // after the CTA's last global store
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned v = atomicAdd(done + limb, 1u) + 1u;
+        if (v == 2u * (unsigned)tiles) atomicExch(done + limb, 0u);
+    }
+}
+__device__ __forceinline__ void fused_wait(unsigned *done, int limb, int tiles) {
+    if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        unsigned v;
+        for (;;) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done + limb) : "memory");
+            if (v >= (unsigned)tiles) break;
+            __nanosleep(64);
+            if (clock64() - t0 > 8000000000ll) __trap(); // seconds: the dispatch-order assumption failed - fail loudly, never hang
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+template <int LOGN>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_fused(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                 NttBatch B, int count, unsigned *done) {
+    extern __shared__ u64 sm[];
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - 9;
+    const uint32_t tile = blockIdx.x & (TILES - 1);
+    int phase, limb;
+    fused_item(blockIdx.x >> LT, count, phase, limb);
+    const uint32_t d = B.desc[limb];
+    const int qp = d & 0xff;
+    if (phase == 0) {
+        const PassGeom G{LOGN, SA, 0, NTT_TILE_LOG - SA, NTT_TILE_LOG, 1};
+        if (fp_ok(T, qp)) fp_fwd_pass_body<false>(T, src, dst, d, G, 1, 0, sm, tile);
+        else if (lazy_ok(T, qp)) fwd_pass_body<true, false>(T, src, dst, d, G, 0, sm, tile);
+        else fwd_pass_body<false, false>(T, src, dst, d, G, 0, sm, tile);
+        fused_publish(done, limb, TILES);
+    } else {
+        const PassGeom G{LOGN, 9, SA, 0, NTT_TILE_LOG, 0};
+        fused_wait(done, limb, TILES);
+        if (fp_ok(T, qp)) fp_fwd_pass_body<true>(T, dst, dst, d, G, 0, 1, sm, tile);
+        else if (lazy_ok(T, qp)) fwd_pass_body<true, true>(T, dst, dst, d, G, 1, sm, tile);
+        else fwd_pass_body<false, true>(T, dst, dst, d, G, 1, sm, tile);
+        fused_publish(done, limb, TILES);
+    }
+}
+template <int LOGN>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_fused(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                 NttBatch B, int count, unsigned *done, const u64 *__restrict__ custom,
+                                                                 const u64 *__restrict__ custom_s) {
+    extern __shared__ u64 sm[];
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - 9;
+    const uint32_t tile = blockIdx.x & (TILES - 1);
+    int phase, limb;
+    fused_item(blockIdx.x >> LT, count, phase, limb);
+    const uint32_t d = B.desc[limb];
+    const int qp = d & 0xff;
+    if (phase == 0) { // the 9 small-stride stages first
+        const PassGeom G{LOGN, 9, SA, 0, NTT_TILE_LOG, 0};
+        if (fp_ok(T, qp)) fp_inv_pass_body<false>(T, src, dst, d, G, 1, 0, sm, nullptr, nullptr, tile, limb);
+        else if (lazy_ok(T, qp)) inv_pass_body<true, false>(T, src, dst, d, G, 0, sm, nullptr, nullptr, tile, limb);
+        else inv_pass_body<false, false>(T, src, dst, d, G, 0, sm, nullptr, nullptr, tile, limb);
+        fused_publish(done, limb, TILES);
+    } else {
+        const PassGeom G{LOGN, SA, 0, NTT_TILE_LOG - SA, NTT_TILE_LOG, 1};
+        fused_wait(done, limb, TILES);
+        if (fp_ok(T, qp)) fp_inv_pass_body<true>(T, dst, dst, d, G, 0, 1, sm, custom, custom_s, tile, limb);
+        else if (lazy_ok(T, qp)) inv_pass_body<true, true>(T, dst, dst, d, G, 1, sm, custom, custom_s, tile, limb);
+        else inv_pass_body<false, true>(T, dst, dst, d, G, 1, sm, custom, custom_s, tile, limb);
+        fused_publish(done, limb, TILES);
+    }
+}
+// FHEB200_NTT_FUSED=0 keeps the two-launch form
+static bool ntt_fused() {
+    static const bool on = [] { const char *e = getenv("FHEB200_NTT_FUSED"); return !(e && *e == '0'); }();
+    return on;
+}
+// per (device, stream) counters: launches on one stream run in order, so one self-cleaning scratch per stream suffices
+static unsigned *fused_scratch(cudaStream_t st) {
+    static std::mutex mu;
+    static std::map<std::pair<int, cudaStream_t>, unsigned *> tab;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = tab.find({dev, st});
+    if (it != tab.end()) return it->second;
+    unsigned *p = nullptr;
+    if (cudaMalloc(&p, NTT_FUSED_MAX * sizeof(unsigned)) != cudaSuccess) throw std::runtime_error("fheb200: cudaMalloc failed (NTT counters)");
+    cudaMemset(p, 0, NTT_FUSED_MAX * sizeof(unsigned)); // synchronous, once per stream
+    tab[{dev, st}] = p;
+    return p;
+}
+
+// host copies of the descriptor arrays (Context::desc registers them): the fused kernels take descriptors by value
+static std::mutex g_desc_mu;
+static std::map<const uint32_t *, std::vector<uint32_t>> g_desc_host;
+void ntt_register_desc(const uint32_t *dev, const uint32_t *host, size_t count) {
+    std::lock_guard<std::mutex> lock(g_desc_mu);
+    g_desc_host[dev] = std::vector<uint32_t>(host, host + count);
+}
+static bool host_desc(const uint32_t *dev, int count, std::vector<uint32_t> &out) {
+    std::lock_guard<std::mutex> lock(g_desc_mu);
+    auto it = g_desc_host.find(dev);
+    if (it == g_desc_host.end() || (int)it->second.size() < count) return false;
+    out.assign(it->second.begin(), it->second.begin() + count);
+    return true;
 }
 
 static int ntt_group() { // limbs per launch pair at n = 2^17: everything unless FHEB200_NTT_GROUP says otherwise
@@ -499,6 +649,17 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     passes(T, A, B, tile);
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    std::vector<uint32_t> hd;
+    if (T.logn == 17 && ntt_fused() && host_desc(d_desc, count, hd)) {
+        unsigned *done = fused_scratch(st);
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            g_launches++, ntt_fwd_fused<17><<<2 * gc * (T.n / tile), tile / 8, smem, st>>>(T, src, dst, B, gc, done);
+        }
+        return;
+    }
     if (T.logn == 17) {
         // FHEB200_NTT_GROUP = g runs both passes over g limbs at a time so that the intermediate stays in L2.  Measured
         // (profiles/r01/ntt_group_sweep.txt): slower for every g (41 limbs: 55.7 us ungrouped, 67.7 us at g = 24, 104 us at
@@ -527,6 +688,18 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     passes(T, A, B, tile);
     dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    std::vector<uint32_t> hd;
+    if (T.logn == 17 && ntt_fused() && host_desc(d_desc, count, hd)) {
+        unsigned *done = fused_scratch(st);
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            g_launches++, ntt_inv_fused<17><<<2 * gc * (T.n / tile), tile / 8, smem, st>>>(
+                T, src, dst, B, gc, done, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
+        }
+        return;
+    }
     if (T.logn == 17) {
         const int group = ntt_group();
         for (int c0 = 0; c0 < count; c0 += group) {

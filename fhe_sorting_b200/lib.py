@@ -410,6 +410,56 @@ class Context(_Handle):
         _ck(_lib.fheb200_raw_rescale(self.h, a.shape[0], a.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def raw_lincomb(self, inputs, weights, variant=0):
+        """inputs [count][limbs2][n], weights [G][count][ell] residues -> [G][limbs2][n] (PS leaf sums, one kernel)."""
+        a = np.ascontiguousarray(inputs, dtype=np.uint64)
+        w = np.ascontiguousarray(weights, dtype=np.uint64)
+        count, limbs2 = a.shape[0], a.shape[1]
+        G, ell = w.shape[0], w.shape[2]
+        out = np.zeros((G, limbs2, self.n), dtype=np.uint64)
+        _ck(_lib.fheb200_raw_lincomb(self.h, ell, limbs2, count, G, a.ctypes.data_as(C.c_void_p), w.ctypes.data_as(C.c_void_p),
+                                     out.ctypes.data_as(C.c_void_p), variant))
+        return out
+
+    def raw_mul_pt(self, a0, a1, pt, acc=None):
+        a0, a1, pt = (np.ascontiguousarray(x, dtype=np.uint64) for x in (a0, a1, pt))
+        o0 = np.ascontiguousarray(acc[0], dtype=np.uint64).copy() if acc is not None else np.zeros_like(a0)
+        o1 = np.ascontiguousarray(acc[1], dtype=np.uint64).copy() if acc is not None else np.zeros_like(a0)
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _ck(_lib.fheb200_raw_mul_pt(self.h, a0.shape[0], vp(a0), vp(a1), vp(pt), vp(o0), vp(o1), 1 if acc is not None else 0))
+        return o0, o1
+
+    def raw_tensor(self, a0, a1, b0=None, b1=None):
+        vp = lambda x: x.ctypes.data_as(C.c_void_p) if x is not None else None  # noqa: E731
+        a0, a1 = np.ascontiguousarray(a0, dtype=np.uint64), np.ascontiguousarray(a1, dtype=np.uint64)
+        if b0 is not None:
+            b0, b1 = np.ascontiguousarray(b0, dtype=np.uint64), np.ascontiguousarray(b1, dtype=np.uint64)
+        d = [np.zeros_like(a0) for _ in range(3)]
+        _ck(_lib.fheb200_raw_tensor(self.h, a0.shape[0], vp(a0), vp(a1), vp(b0), vp(b1), vp(d[0]), vp(d[1]), vp(d[2])))
+        return d
+
+    def raw_dh_accumulate(self, ell, acc, cP, pt, S, galois):
+        vp = lambda x: x.ctypes.data_as(C.c_void_p) if x is not None else None  # noqa: E731
+        acc = np.ascontiguousarray(acc, dtype=np.uint64) if acc is not None else None
+        cP, pt = np.ascontiguousarray(cP, dtype=np.uint64), np.ascontiguousarray(pt, dtype=np.uint64)
+        S = np.ascontiguousarray(S, dtype=np.uint64).copy()
+        _ck(_lib.fheb200_raw_dh_accumulate(self.h, ell, vp(acc), vp(cP), vp(pt), vp(S), C.c_uint32(galois)))
+        return S
+
+    def raw_inner_product(self, ell, galois, digits):
+        d = np.ascontiguousarray(digits, dtype=np.uint64)
+        acc = np.zeros((2, ell + self.K, self.n), dtype=np.uint64)
+        _ck(_lib.fheb200_raw_inner_product(self.h, ell, C.c_uint32(galois), d.ctypes.data_as(C.c_void_p),
+                                           acc.ctypes.data_as(C.c_void_p)))
+        return acc
+
+    def raw_moddown(self, ell, acc):
+        a = np.ascontiguousarray(acc, dtype=np.uint64)
+        o0, o1 = np.zeros((ell, self.n), dtype=np.uint64), np.zeros((ell, self.n), dtype=np.uint64)
+        _ck(_lib.fheb200_raw_moddown(self.h, ell, a.ctypes.data_as(C.c_void_p), o0.ctypes.data_as(C.c_void_p),
+                                     o1.ctypes.data_as(C.c_void_p)))
+        return o0, o1
+
     # -- device timing loops
     def bench_rotate(self, ct, index, reps):
         ms = C.c_float()

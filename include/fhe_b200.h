@@ -194,6 +194,19 @@ int fheb200_raw_ntt(fheb200_ctx *ctx, int inverse, int qp_index, uint64_t *poly)
 int fheb200_raw_automorphism(fheb200_ctx *ctx, uint32_t galois, int limbs, const uint64_t *in, uint64_t *out);
 int fheb200_raw_modup(fheb200_ctx *ctx, int num_limbs, const uint64_t *c, uint64_t *digits, size_t digit_words);
 int fheb200_raw_rescale(fheb200_ctx *ctx, int num_limbs, const uint64_t *in, uint64_t *out);
+/* single kernels on host-supplied limbs (limb-level parity tests against the oracle; not on any hot path).
+ * raw_lincomb: out[g] = sum_t w[g][t][limb] * in[t] over limbs2 = npoly * num_limbs limbs (Paterson-Stockmeyer leaf sums inside
+ * EvalChebyshevSeriesPS, reference src/sort_algo.h:557); variant 0 = tensor cores + cp.async rings, 1 = tensor cores, 2 = CUDA cores */
+int fheb200_raw_lincomb(fheb200_ctx *ctx, int num_limbs, int limbs2, int count, int outputs, const uint64_t *in, const uint64_t *weights,
+                        uint64_t *out, int variant);
+int fheb200_raw_mul_pt(fheb200_ctx *ctx, int num_limbs, const uint64_t *a0, const uint64_t *a1, const uint64_t *pt, uint64_t *o0,
+                       uint64_t *o1, int accumulate);
+int fheb200_raw_tensor(fheb200_ctx *ctx, int num_limbs, const uint64_t *a0, const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                       uint64_t *d0, uint64_t *d1, uint64_t *d2);
+int fheb200_raw_dh_accumulate(fheb200_ctx *ctx, int num_limbs, const uint64_t *acc, const uint64_t *cP, const uint64_t *pt, uint64_t *S,
+                              uint32_t galois);
+int fheb200_raw_inner_product(fheb200_ctx *ctx, int num_limbs, uint32_t galois, const uint64_t *digits, uint64_t *acc);
+int fheb200_raw_moddown(fheb200_ctx *ctx, int num_limbs, const uint64_t *acc, uint64_t *out0, uint64_t *out1);
 /* timing loops for bench.py: `reps` back-to-back launches on the context stream with inputs resident in HBM;
  * returns the elapsed device time in milliseconds measured with CUDA events on that stream. */
 int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms);

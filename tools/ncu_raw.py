@@ -17,14 +17,20 @@ want = [('gpu__time_duration.sum', 'dur'), ('dram__bytes_read.sum', 'rd'), ('dra
         ('launch__registers_per_thread', 'regs'), ('smsp__inst_executed.sum', 'winst'),
         ('l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'bankconf'),
         ('lts__t_sector_hit_rate.pct', 'l2hit%'), ('launch__waves_per_multiprocessor', 'waves'),
-        ('smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio', 'st_long'),
-        ('smsp__average_warp_latency_issue_stalled_math_pipe_throttle.ratio', 'st_math'),
-        ('smsp__average_warp_latency_issue_stalled_short_scoreboard.ratio', 'st_short'),
-        ('smsp__average_warp_latency_issue_stalled_barrier.ratio', 'st_bar'),
-        ('smsp__average_warp_latency_issue_stalled_wait.ratio', 'st_wait'),
-        ('smsp__average_warp_latency_issue_stalled_not_selected.ratio', 'st_notsel'),
-        ('smsp__average_warp_latency_issue_stalled_lg_throttle.ratio', 'st_lg'),
-        ('smsp__average_warp_latency_issue_stalled_mio_throttle.ratio', 'st_mio')]
+        ('sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active', 'fp64%'),
+        ('sm__inst_executed_pipe_tensor_subpipe_imma.avg.pct_of_peak_sustained_active', 'imma%'),
+        ('lts__t_sectors_srcunit_tex_op_read.sum', 'l2rd_sectors'),
+        # warps stalled per issued instruction, by reason (sum + 1 ~ resident warps per scheduler / issue rate)
+        ('smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio', 'st_long'),
+        ('smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio', 'st_math'),
+        ('smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio', 'st_short'),
+        ('smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio', 'st_bar'),
+        ('smsp__average_warps_issue_stalled_wait_per_issue_active.ratio', 'st_wait'),
+        ('smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio', 'st_notsel'),
+        ('smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio', 'st_lg'),
+        ('smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio', 'st_mio'),
+        ('smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio', 'st_disp'),
+        ('smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio', 'st_noinst')]
 ki = H.index('Kernel Name')
 for r in rows[2:]:
     parts = []
