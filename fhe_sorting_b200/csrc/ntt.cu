@@ -584,9 +584,10 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_fused(DeviceTa
         fused_publish(done, limb, TILES);
     }
 }
-// FHEB200_NTT_FUSED=0 keeps the two-launch form
+// opt-in (FHEB200_NTT_FUSED=1).  Measured on B200 (profiles/r02/ntt_variants.txt): DRAM traffic per limb drops to the algorithmic
+// 16n bytes, but 41 limbs take 61.5 us against 55.8 us for the two launches - the passes are bound by latency / issue, not by HBM.
 static bool ntt_fused() {
-    static const bool on = [] { const char *e = getenv("FHEB200_NTT_FUSED"); return !(e && *e == '0'); }();
+    static const bool on = [] { const char *e = getenv("FHEB200_NTT_FUSED"); return e && *e == '1'; }();
     return on;
 }
 // per (device, stream) counters: launches on one stream run in order, so one self-cleaning scratch per stream suffices
