@@ -281,6 +281,28 @@ int fheb200_raw_moddown(fheb200_ctx *ctx, int ell, const uint64_t *acc, uint64_t
     })
 }
 
+// Forward NTT of `count` limbs that already lie in DEVICE memory ([count][n] u64, limb i reduced modulo modulus qp_indices[i]),
+// written to d_out ([count][n], may equal d_in), on the context's stream.  Allocates nothing: see k_ntt_fwd_static.  Returns
+// after the launch; fheb200_ctx_sync (or stream order) makes the result visible.
+int fheb200_ntt_forward_noalloc(fheb200_ctx *ctx, const int *qp_indices, int count, const uint64_t *d_in, uint64_t *d_out) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(qp_indices, "qp_indices"); need(d_in, "d_in"); need(d_out, "d_out");
+        if (count < 1 || count > ntt_static_max_limbs())
+            throw std::invalid_argument("ntt_forward_noalloc: count must be 1.." + std::to_string(ntt_static_max_limbs()) +
+                                        " limbs (size of the static scratch array)");
+        uint32_t desc[256];
+        static_assert(sizeof(desc) / sizeof(desc[0]) >= 256, "descriptor buffer");
+        if (ntt_static_max_limbs() > 256) throw std::logic_error("ntt_forward_noalloc: descriptor buffer too small");
+        for (int i = 0; i < count; i++) {
+            if (qp_indices[i] < 0 || qp_indices[i] >= C.T.F) throw std::out_of_range("ntt_forward_noalloc: modulus index");
+            desc[i] = ((uint32_t)i << 8) | (uint32_t)qp_indices[i];
+        }
+        k_ntt_fwd_static(C.T, d_in, d_out, desc, count, C.stream);
+    })
+}
+int fheb200_ntt_forward_noalloc_max_limbs(void) { return ntt_static_max_limbs(); }
+
 int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words) {
     GUARD({
         need(ct, "ct");

@@ -41,6 +41,11 @@ inline void k_ntt_inv(const DeviceTables &T, u64 *buf, const uint32_t *d_desc, i
     k_ntt_inv(T, buf, buf, d_desc, count, st);
 }
 
+// forward NTT at n = 2^17 with no allocation anywhere on the call path: the fused kernel's counters sit in a static device
+// array (ntt.cu); host_desc is a HOST array of `count` <= ntt_static_max_limbs() descriptors; src/dst are device pointers
+void k_ntt_fwd_static(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *host_desc, int count, cudaStream_t st);
+int ntt_static_max_limbs();
+
 // ---- elementwise over ell limbs; qp of limb i is qp0 + i ----
 enum BinOp { OP_ADD = 0, OP_SUB = 1, OP_MUL = 2 };
 void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 *b, u64 *out, cudaStream_t st);

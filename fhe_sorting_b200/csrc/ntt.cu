@@ -18,6 +18,7 @@
 #include <map>
 #include <mutex>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 #include "kernels.h"
@@ -717,6 +718,49 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
     const u64 *custom_s = custom ? custom + count : nullptr;
     g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, src, dst, d_desc, B, 1, A.S == 0, custom, custom_s);
     if (A.S > 0) g_launches++, ntt_inv_pass<<<grid, tile / 8, smem, st>>>(T, dst, dst, d_desc, A, 0, 1, custom, custom_s);
+}
+
+// ---------------------------------------------------------------- allocation-free forward NTT
+// Same fused two-phase kernel as k_ntt_fwd at n = 2^17, but the per-limb dependency counters live in a file-scope device
+// array instead of a cudaMalloc'd block, so the call path contains no cudaMalloc / cudaFree / pool allocation at all
+// (usable under CUDA graph capture or in harnesses that forbid allocation).  Limits and rules:
+//   * at most NTT_STATIC_MAX_LIMBS limbs per call (the array is 1 KiB; every GPU that loads the library holds it until exit);
+//   * every call shares the array: it is cleared on the stream before each launch, and two calls that overlap on the GPU
+//     (different streams, no ordering between them) race on it - callers must order such calls themselves.
+constexpr int NTT_STATIC_MAX_LIMBS = NTT_FUSED_MAX;
+static __device__ __align__(256) unsigned g_ntt_static_done[NTT_STATIC_MAX_LIMBS];
+int ntt_static_max_limbs() { return NTT_STATIC_MAX_LIMBS; }
+// the array's device address on the current device: in host code the symbol's name is only a host-side stand-in, never a
+// device pointer, so it is resolved once per device with that device current and cached
+static unsigned *ntt_static_scratch() {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static unsigned *addr[MAX_DEV] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) throw std::runtime_error("fheb200: no current CUDA device");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        unsigned *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_ntt_static_done);
+        if (e != cudaSuccess || !p) throw std::runtime_error(std::string("fheb200: cudaGetSymbolAddress(NTT counters): ") + cudaGetErrorString(e));
+        addr[dev] = p;
+    }
+    return addr[dev];
+}
+void k_ntt_fwd_static(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *host_desc, int count, cudaStream_t st) {
+    if (T.logn != 17) throw std::invalid_argument("ntt_forward_noalloc: only ring dimension 2^17 (the fused two-phase kernel) is supported");
+    if (count < 1 || count > NTT_STATIC_MAX_LIMBS)
+        throw std::invalid_argument("ntt_forward_noalloc: 1.." + std::to_string(NTT_STATIC_MAX_LIMBS) + " limbs per call");
+    unsigned *done = ntt_static_scratch();
+    NttBatch B;
+    std::copy(host_desc, host_desc + count, B.desc);
+    const int tile = NTT_TILE;
+    const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    // the counters must start at zero whatever an earlier (possibly aborted) call left behind
+    if (cudaMemsetAsync(done, 0, sizeof(unsigned) * count, st) != cudaSuccess) throw std::runtime_error("fheb200: cudaMemsetAsync failed (NTT counters)");
+    g_launches++, ntt_fwd_fused<17><<<2 * count * (T.n / tile), tile / 8, smem, st>>>(T, src, dst, B, count, done);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) throw std::runtime_error(std::string("fheb200: ntt_fwd_fused launch: ") + cudaGetErrorString(e));
 }
 
 } // namespace fheb200

@@ -207,6 +207,15 @@ int fheb200_raw_dh_accumulate(fheb200_ctx *ctx, int num_limbs, const uint64_t *a
                               uint32_t galois);
 int fheb200_raw_inner_product(fheb200_ctx *ctx, int num_limbs, uint32_t galois, const uint64_t *digits, uint64_t *acc);
 int fheb200_raw_moddown(fheb200_ctx *ctx, int num_limbs, const uint64_t *acc, uint64_t *out0, uint64_t *out1);
+/* Forward NTT with NO allocation on the call path.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * d_in / d_out are DEVICE pointers to [count][ring_dim] uint64 limbs (limb i modulo modulus qp_indices[i]; d_out may equal
+ * d_in); ring dimension 2^17 only; count <= fheb200_ntt_forward_noalloc_max_limbs() (= 256; beyond it the call fails with an
+ * error).  The kernel's scratch (per-limb dependency counters, 1 KiB) is a static device array that every GPU loading the
+ * library holds until exit and that ALL calls share: it is cleared before each launch, and calls that overlap on the GPU
+ * race on it - order them.  Runs on the context's stream; same limbs out as fheb200_raw_ntt. */
+int fheb200_ntt_forward_noalloc(fheb200_ctx *ctx, const int *qp_indices, int count, const uint64_t *d_in, uint64_t *d_out);
+int fheb200_ntt_forward_noalloc_max_limbs(void);
 /* timing loops for bench.py: `reps` back-to-back launches on the context stream with inputs resident in HBM;
  * returns the elapsed device time in milliseconds measured with CUDA events on that stream. */
 int fheb200_bench_rotate(fheb200_ctx *ctx, fheb200_ct *ct, int index, int reps, float *ms);
