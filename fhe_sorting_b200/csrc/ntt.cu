@@ -31,6 +31,9 @@ std::atomic<unsigned long long> g_launches{0};
 #ifndef NTT_TILE_LOG_V
 #define NTT_TILE_LOG_V 11
 #endif
+#ifndef NTT_PERSIST_DEFAULT
+#define NTT_PERSIST_DEFAULT 0
+#endif
 constexpr int NTT_TILE_LOG = NTT_TILE_LOG_V;
 constexpr int NTT_CTAS = 8192 / (1 << NTT_TILE_LOG_V); // resident CTAs per SM: 1024 threads of 64 registers
 constexpr int NTT_TILE = 1 << NTT_TILE_LOG;            // coefficients per CTA tile
@@ -126,9 +129,12 @@ __device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
 
 // ---------------------------------------------------------------- forward pass
 // final_reduce: bring values to [0,q) on the way out (last pass), otherwise they stay in [0,4q)
+// pre (optional): the 8 words of this thread's first access pattern, already loaded by the caller (persistent kernels
+// fetch them one tile ahead with tile_prefetch); src is then not read
 template <bool LAZY, bool CG>
 __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                              const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm, uint32_t tile) {
+                                              const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm, uint32_t tile,
+                                              const u64 *pre = nullptr) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const ModConst mc = T.mc[qp];
@@ -143,7 +149,7 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
     {
         const uint32_t st = g_step(G, p);
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = ld_word<CG>(src + off + g0 + k * st);
+        for (int k = 0; k < 8; k++) v[k] = pre ? pre[k] : ld_word<CG>(src + off + g0 + k * st);
     }
     int s = G.S0;
     if (c_first == 1) fwd_chunk<1, LAZY>(v, tw, s, G.logn, g0, nq, q2);
@@ -251,7 +257,8 @@ __device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__res
 // first: the pass reads reduced u64 input (otherwise doubles left by the previous pass); last: writes reduced u64
 template <bool CG>
 __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
-                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu, uint32_t tile) {
+                                                 const uint32_t d, const PassGeom &G, int first, int last, u64 *smu, uint32_t tile,
+                                                 const u64 *pre = nullptr) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -268,7 +275,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
         const uint32_t st = g_step(G, p);
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const u64 x = ld_word<CG>(src + off + g0 + k * st);
+            const u64 x = pre ? pre[k] : ld_word<CG>(src + off + g0 + k * st);
             v[k] = first ? fp_from_u64(x) : __longlong_as_double((long long)x);
         }
     }
@@ -311,7 +318,7 @@ template <bool CG>
 __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu,
                                                  const u64 *__restrict__ custom, const u64 *__restrict__ custom_s, uint32_t tile,
-                                                 uint32_t bidx) {
+                                                 uint32_t bidx, const u64 *pre = nullptr) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -324,7 +331,10 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
     int base = triple_base(tid, p);
     uint32_t g0 = tile_to_g(G, base, tile);
     double v[8];
-    if (!G.pass_a && p == 0) {
+    if (pre) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = first ? fp_from_u64(pre[k]) : __longlong_as_double((long long)pre[k]);
+    } else if (!G.pass_a && p == 0) {
         const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
@@ -400,7 +410,7 @@ template <bool LAZY, bool CG>
 __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                               const uint32_t d, const PassGeom &G, int scale, u64 *sm,
                                               const u64 *__restrict__ custom, const u64 *__restrict__ custom_s, uint32_t tile,
-                                              uint32_t bidx) {
+                                              uint32_t bidx, const u64 *pre = nullptr) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const u64 q = T.mc[qp].q, q2 = q << 1, nq = 0 - q;
@@ -411,7 +421,10 @@ __device__ __forceinline__ void inv_pass_body(const DeviceTables &T, const u64 *
     int base = triple_base(tid, p);
     uint32_t g0 = tile_to_g(G, base, tile);
     u64 v[8];
-    if (!G.pass_a && p == 0) {
+    if (pre) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = pre[k];
+    } else if (!G.pass_a && p == 0) {
         const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
@@ -607,6 +620,106 @@ static unsigned *fused_scratch(cudaStream_t st) {
     return p;
 }
 
+// ---------------------------------------------------------------- persistent passes with next-tile prefetch (n = 2^17)
+// ncu on the one-tile-per-CTA kernels: the largest stall is the long scoreboard (a CTA's first global load is on its
+// critical path; only the other three CTAs of the SM cover it).  Here a CTA walks a strided list of (limb, tile) items
+// and issues the 8 loads of its NEXT tile before it starts the butterflies of the current one, so the HBM / L2 latency
+// of a tile is covered by a whole tile of arithmetic of the same warp.  CTAS = resident CTAs per SM the kernel is
+// compiled for (4: 64 registers, 3: 85 registers - the 16 prefetch registers fit without spills).
+template <bool INV>
+__device__ __forceinline__ void tile_prefetch(const u64 *__restrict__ src, uint32_t d, const PassGeom &G, uint32_t tile, int n,
+                                              u64 (&r)[8]) {
+    const int tid = threadIdx.x, lowbit = G.pass_a ? G.lc : 0, ptop = G.S - 3 + lowbit;
+    int p = ptop;
+    if (INV) {
+        const int c_last = (G.S - 1) % 3 + 1, m = (G.S - c_last) / 3;
+        p = m > 0 ? lowbit : ptop;
+    }
+    const int base = triple_base(tid, p);
+    const uint32_t g0 = tile_to_g(G, base, tile);
+    const size_t off = (size_t)(d >> 8) * n;
+    if (!G.pass_a && p == 0) {
+        const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(src + off + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const ulonglong2 t = in[k];
+            r[2 * k] = t.x, r[2 * k + 1] = t.y;
+        }
+    } else {
+        const uint32_t st = g_step(G, p);
+#pragma unroll
+        for (int k = 0; k < 8; k++) r[k] = src[off + g0 + k * st];
+    }
+}
+template <int LOGN, int S, int S0, int LC, int PA, int CTAS>
+__global__ void __launch_bounds__(NTT_TILE / 8, CTAS) ntt_fwd_persist(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                      NttBatch B, int count, int first, int final_reduce) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG;
+    const int total = count * TILES;
+    int item = blockIdx.x;
+    if (item >= total) return;
+    u64 nxt[8];
+    tile_prefetch<false>(src, B.desc[item >> LT], G, item & (TILES - 1), T.n, nxt);
+    for (; item < total; item += gridDim.x) {
+        u64 cur[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) cur[k] = nxt[k];
+        const int ni = item + gridDim.x;
+        if (ni < total) tile_prefetch<false>(src, B.desc[ni >> LT], G, ni & (TILES - 1), T.n, nxt);
+        const uint32_t d = B.desc[item >> LT], tile = item & (TILES - 1);
+        const int qp = d & 0xff;
+        if (fp_ok(T, qp)) fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, tile, cur);
+        else if (lazy_ok(T, qp)) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, tile, cur);
+        else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, tile, cur);
+        __syncthreads(); // the tile's last shared-memory reads are done before the next tile's first writes
+    }
+}
+template <int LOGN, int S, int S0, int LC, int PA, int CTAS>
+__global__ void __launch_bounds__(NTT_TILE / 8, CTAS) ntt_inv_persist(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                      NttBatch B, int count, int first, int scale,
+                                                                      const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG;
+    const int total = count * TILES;
+    int item = blockIdx.x;
+    if (item >= total) return;
+    u64 nxt[8];
+    tile_prefetch<true>(src, B.desc[item >> LT], G, item & (TILES - 1), T.n, nxt);
+    for (; item < total; item += gridDim.x) {
+        u64 cur[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) cur[k] = nxt[k];
+        const int ni = item + gridDim.x;
+        if (ni < total) tile_prefetch<true>(src, B.desc[ni >> LT], G, ni & (TILES - 1), T.n, nxt);
+        const uint32_t d = B.desc[item >> LT], tile = item & (TILES - 1), bidx = item >> LT;
+        const int qp = d & 0xff;
+        if (fp_ok(T, qp)) fp_inv_pass_body<false>(T, src, dst, d, G, first, scale, sm, custom, custom_s, tile, bidx, cur);
+        else if (lazy_ok(T, qp)) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, tile, bidx, cur);
+        else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, tile, bidx, cur);
+        __syncthreads();
+    }
+}
+// FHEB200_NTT_PERSIST = 0 (one tile per CTA), 3 or 4 (persistent CTAs per SM)
+static int ntt_persist() {
+    static const int v = [] {
+        const char *e = getenv("FHEB200_NTT_PERSIST");
+        const int x = e ? atoi(e) : NTT_PERSIST_DEFAULT;
+        return (x == 3 || x == 4) ? x : 0;
+    }();
+    return v;
+}
+static int sm_count() {
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return 148;
+    if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    return sms[dev] > 0 ? sms[dev] : 148;
+}
+
 // host copies of the descriptor arrays (Context::desc registers them): the fused kernels take descriptors by value
 static std::mutex g_desc_mu;
 static std::map<const uint32_t *, std::vector<uint32_t>> g_desc_host;
@@ -662,6 +775,23 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
         }
         return;
     }
+    if (T.logn == 17 && ntt_persist() && host_desc(d_desc, count, hd)) {
+        const int pc = ntt_persist();
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            const int gridp = std::min(gc * (T.n / tile), pc * sm_count());
+            if (pc == 3) {
+                g_launches++, ntt_fwd_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
+                g_launches++, ntt_fwd_persist<17, 9, 8, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
+            } else {
+                g_launches++, ntt_fwd_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
+                g_launches++, ntt_fwd_persist<17, 9, 8, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
+            }
+        }
+        return;
+    }
     if (T.logn == 17) {
         // FHEB200_NTT_GROUP = g runs both passes over g limbs at a time so that the intermediate stays in L2.  Measured
         // (profiles/r01/ntt_group_sweep.txt): slower for every g (41 limbs: 55.7 us ungrouped, 67.7 us at g = 24, 104 us at
@@ -699,6 +829,24 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
             std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
             g_launches++, ntt_inv_fused<17><<<2 * gc * (T.n / tile), tile / 8, smem, st>>>(
                 T, src, dst, B, gc, done, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
+        }
+        return;
+    }
+    if (T.logn == 17 && ntt_persist() && host_desc(d_desc, count, hd)) {
+        const int pc = ntt_persist();
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            const int gridp = std::min(gc * (T.n / tile), pc * sm_count());
+            const u64 *cu = custom ? custom + c0 : nullptr, *cs = custom ? custom + count + c0 : nullptr;
+            if (pc == 3) {
+                g_launches++, ntt_inv_persist<17, 9, 8, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
+                g_launches++, ntt_inv_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
+            } else {
+                g_launches++, ntt_inv_persist<17, 9, 8, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
+                g_launches++, ntt_inv_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
+            }
         }
         return;
     }
