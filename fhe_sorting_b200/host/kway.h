@@ -125,6 +125,23 @@ class EvalUtils {
         checkLevelAndBoot(a, (int)level, (int)multDepth, verbose);
         checkLevelAndBoot(b, (int)level, (int)multDepth, verbose);
     }
+    // integer multiple without consuming a level: double-and-add over the bits of |coeff| (src/k-way/EvalUtils.cpp:18-44)
+    void multByInt(Ciphertext<DCRTPoly> &ctxt, long coeff, Ciphertext<DCRTPoly> &ctxt_out) {
+        if (coeff == 0) throw std::invalid_argument("kwaySort::multByInt: coefficient must be non-zero");
+        const Ciphertext<DCRTPoly> unit = coeff < 0 ? m_cc->EvalNegate(ctxt) : ctxt;
+        unsigned long mag = (unsigned long)(coeff < 0 ? -coeff : coeff);
+        int top = 0;
+        while ((mag >> (top + 1)) != 0) top++;
+        Ciphertext<DCRTPoly> acc = unit;
+        for (int bit = top - 1; bit >= 0; bit--) {
+            acc = m_cc->EvalAdd(acc, acc);
+            if ((mag >> bit) & 1ul) acc = m_cc->EvalAdd(acc, unit);
+        }
+        ctxt_out = acc;
+    }
+    // HEAAN's "kill imaginary part" products: the packing here is real, so they are the plain product and square
+    void multAndKillImage(Ciphertext<DCRTPoly> &a, Ciphertext<DCRTPoly> &b, Ciphertext<DCRTPoly> &out) { out = m_cc->EvalMult(a, b); }
+    void squareAndKillImage(Ciphertext<DCRTPoly> &a, Ciphertext<DCRTPoly> &out) { out = m_cc->EvalSquare(a); }
     void flipCtxt(Ciphertext<DCRTPoly> &ctxt) { ctxt = m_cc->EvalSub(1.0, ctxt); }
     void flipCtxt(Ciphertext<DCRTPoly> &ctxt, const Plaintext &mask) { ctxt = m_cc->EvalSub(mask, ctxt); }
 

@@ -40,29 +40,47 @@ template <int N> class Decomposer {
     }
     std::vector<int> getRotIndices() { return rotIndices; }
 
+    // Conventions of the reference (src/rotation.h:104-165): Step::stepSize is the SIGNED rotation amount of the digit,
+    // Step::value its digit (-1, 0, 1), and the steps come largest magnitude first.
+    // plain binary digits below N
     std::vector<Step> decomposeBinary(int rotation) const {
         std::vector<Step> s;
-        for (int bit = 1; rotation; bit <<= 1, rotation >>= 1)
-            if (rotation & 1) s.emplace_back((int8_t)1, bit);
-        return s;
-    }
-    // non-adjacent form: digits in {-1,0,1}, no two adjacent non-zero
-    std::vector<Step> decomposeNAF(int rotation) const {
-        std::vector<Step> s;
-        for (int bit = 1; rotation; bit <<= 1) {
-            if (rotation & 1) {
-                int d = 2 - (rotation & 3); // +1 or -1
-                s.emplace_back((int8_t)d, bit);
-                rotation -= d;
-            }
-            rotation >>= 1;
+        for (int bit = 30; bit >= 0; bit--) {
+            const int w = 1 << bit;
+            if (w < N && (rotation & w)) s.emplace_back((int8_t)1, w);
         }
         return s;
     }
-    // balanced variant: prefer the sign that keeps the partial sums inside [0, N)
-    std::vector<Step> decomposeBNAF(int rotation) const {
-        std::vector<Step> naf = decomposeNAF(rotation), bin = decomposeBinary(rotation);
-        return naf.size() < bin.size() ? naf : bin;
+    // non-adjacent form: digits in {-1, 0, 1}, no two adjacent non-zero (works on negative amounts too: two's complement
+    // bits and an arithmetic shift).  A digit worth -N/2 is emitted as +N/2: the two rotations coincide on N slots.
+    std::vector<Step> decomposeNAF(int rotation) const {
+        std::vector<Step> s;
+        for (int bit = 0; rotation != 0; bit++, rotation >>= 1) {
+            if (!(rotation & 1)) continue;
+            const int d = (rotation & 2) ? -1 : 1;
+            const int amount = d * (1 << bit);
+            if (amount == -N / 2) s.emplace_back((int8_t)-d, -amount);
+            else s.emplace_back((int8_t)d, amount);
+            rotation -= d;
+        }
+        std::reverse(s.begin(), s.end());
+        return s;
+    }
+    // balanced recoding in base 2: a digit above B/2 - or equal to B/2 with the next digit at least B/2 - borrows from
+    // the next position (src/rotation.h:138-165)
+    std::vector<Step> decomposeBNAF(int k) const {
+        const int B = 2;
+        std::vector<int> digit;
+        for (int rest = k; rest != 0;) {
+            int d = rest % B;
+            rest = (rest - d) / B;
+            if (d > B / 2 || (d == B / 2 && rest % B >= B / 2)) d -= B, rest += 1;
+            digit.push_back(d);
+        }
+        std::vector<Step> s;
+        for (size_t i = digit.size(); i-- > 0;)
+            if (digit[i] != 0) s.emplace_back((int8_t)digit[i], digit[i] * (1 << i));
+        return s;
     }
 
     std::vector<Step> decompose(int rotation, int wrapN, DecomposeAlgo algo) {
@@ -73,6 +91,7 @@ template <int N> class Decomposer {
             steps.emplace_back(largest);
             rotation -= largest;
         }
+        if (rotation == 0) return steps; // (as the reference: whole-key amounts are returned as they are, wrap steps included)
         while (rotation > maxDecomposed) { // then the largest key strictly below the remainder
             auto it = std::lower_bound(rotIndices.begin(), rotIndices.end(), rotation);
             if (it == rotIndices.begin()) break;
@@ -80,7 +99,8 @@ template <int N> class Decomposer {
             steps.emplace_back(legal);
             rotation -= legal;
         }
-        if (rotation) {
+        if (rotation == 0) return steps;
+        {
             std::vector<Step> rest = algo == DecomposeAlgo::NAF    ? decomposeNAF(rotation)
                                      : algo == DecomposeAlgo::BNAF ? decomposeBNAF(rotation)
                                                                    : decomposeBinary(rotation);
@@ -112,7 +132,7 @@ template <int N> class RotationComposer {
         if (available_indices.count(rotation)) return m_cc->EvalRotate(input, rotation);
         Ciphertext<DCRTPoly> r = input->Clone();
         for (const Step &s : m_decomposer.decompose(rotation, (int)input->GetSlots(), m_algo))
-            r = m_cc->EvalRotate(r, s.value < 0 ? -s.stepSize : s.stepSize);
+            r = m_cc->EvalRotate(r, s.stepSize);
         return r;
     }
     const std::set<int> &getRotationCalls() const { return rotation_calls; }
@@ -146,7 +166,7 @@ template <int N> class RotationTree {
     }
 
   public:
-    RotationTree(CryptoContext<DCRTPoly> cc, std::vector<int> rotIndices, DecomposeAlgo algo = DecomposeAlgo::BINARY)
+    RotationTree(CryptoContext<DCRTPoly> cc, std::vector<int> rotIndices, DecomposeAlgo algo = DecomposeAlgo::NAF)
         : m_cc(cc), m_decomposer(rotIndices), m_algo(algo), M(cc->GetCyclotomicOrder()) {}
 
     // register rotations start..end-1 (negative amounts rotate right)
@@ -155,8 +175,7 @@ template <int N> class RotationTree {
             if (r == 0) continue;
             std::vector<int> p;
             for (const Step &s : m_decomposer.decompose(std::abs(r), N * N, m_algo)) {
-                int v = (s.value < 0 ? -s.stepSize : s.stepSize) * (r < 0 ? -1 : 1);
-                p.push_back(v);
+                p.push_back(s.stepSize * (r < 0 ? -1 : 1));
             }
             std::sort(p.begin(), p.end(), [](int a, int b) { return std::abs(a) > std::abs(b); });
             paths[r] = p;

@@ -30,7 +30,10 @@
 namespace lbcrypto {
 
 typedef unsigned int usint;
-struct DCRTPoly {};                 // tag only: polynomials live in HBM behind the C ABI
+struct PrecompHandle;                // owner of a fheb200_pre (hoisted ModUp digits in HBM)
+struct DCRTPoly {                    // tag: polynomials live in HBM behind the C ABI.  The one place the reference holds
+    std::shared_ptr<PrecompHandle> pre; // DCRTPoly values is the result of EvalFastRotationPrecompute (src/rotation.h:247)
+};
 struct CryptoContextCKKSRNS {};
 enum SecurityLevel { HEStd_128_classic, HEStd_192_classic, HEStd_256_classic, HEStd_NotSet };
 enum PKESchemeFeature { PKE = 1, KEYSWITCH = 2, PRE = 4, LEVELEDSHE = 8, ADVANCEDSHE = 16, MULTIPARTY = 32, FHE = 64 };
@@ -173,12 +176,13 @@ struct EncodingParamsImpl {
     usint batch = 0;
     usint GetBatchSize() const { return batch; }
 };
-struct FastRotationPrecomp { // stands for std::shared_ptr<std::vector<DCRTPoly>>
+struct PrecompHandle {
     fheb200_pre *h = nullptr;
-    ~FastRotationPrecomp() {
+    ~PrecompHandle() {
         if (h) fheb200_pre_release(h);
     }
 };
+typedef std::vector<DCRTPoly> FastRotationPrecomp; // OpenFHE's type: std::shared_ptr<std::vector<DCRTPoly>>; element 0 owns the digits
 
 // ---- the crypto context
 class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl> {
@@ -339,14 +343,17 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     }
     std::shared_ptr<FastRotationPrecomp> EvalFastRotationPrecompute(const CT &a) {
         need(a);
-        auto p = std::make_shared<FastRotationPrecomp>();
-        fheb200_check(fheb200_fast_rotation_precompute(ctx, a->h, &p->h));
+        auto h = std::make_shared<PrecompHandle>();
+        fheb200_check(fheb200_fast_rotation_precompute(ctx, a->h, &h->h));
+        auto p = std::make_shared<FastRotationPrecomp>(1);
+        (*p)[0].pre = h;
         return p;
     }
     CT EvalFastRotation(const CT &a, usint index, usint /*cyclotomic order*/, const std::shared_ptr<FastRotationPrecomp> &pre) {
         need(a);
         fheb200_ct *o = nullptr;
-        fheb200_check(fheb200_eval_fast_rotation(ctx, a->h, (int)index, pre->h, &o));
+        if (!pre || pre->empty() || !(*pre)[0].pre) throw std::invalid_argument("EvalFastRotation: empty precomputation");
+        fheb200_check(fheb200_eval_fast_rotation(ctx, a->h, (int)index, (*pre)[0].pre->h, &o));
         return wrap(o);
     }
     bool HasRotationKey(int index) const {

@@ -2,6 +2,7 @@
 // Restates the evaluation schedule of the reference (src/sign.cpp:15-185, 610-651) so that level consumption is the
 // same: each g_3 / f_3 costs 3 levels (2 squarings, 3 relinearised products, 4 scalar products), g_4 / f_4 cost 4.
 #include "sign.h"
+#include "signum_polycircuit_table.h"
 
 #include <cstdlib>
 
@@ -96,13 +97,23 @@ Ciphertext<DCRTPoly> tanh(Ciphertext<DCRTPoly> a, CryptoContext<DCRTPoly> cc) {
     return cc->EvalChebyshevFunction([](double x) -> double { return std::tanh(x * RAND_MAX); }, a, -1, 1, 1006);
 }
 
+// Degree-1023 odd Chebyshev series of the polycircuit library (reference: src/sign.cpp:188-608, which evaluates T_0..T_1008
+// with EvalChebyshevSeries and adds T_1009..T_1023 through a hand-unrolled product tree).  Same polynomial here, in one
+// Paterson-Stockmeyer evaluation over the whole coefficient vector: 10 levels.
+Ciphertext<DCRTPoly> signum_polycircuit(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc) {
+    static const std::vector<double> coeffs = [] {
+        std::vector<double> c(1024, 0.0);
+        for (int i = 0; i < 512; i++) c[2 * i + 1] = kSignumOddChebyshev[i];
+        return c;
+    }();
+    return cc->EvalChebyshevSeries(x, coeffs, -1, 1);
+}
+
 Ciphertext<DCRTPoly> sign(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc, SignFunc func, const SignConfig &Cfg) {
     switch (func) {
     case SignFunc::Tanh: return tanh(x, cc);
     case SignFunc::NaiveDiscrete: return naive_discrete_sign(x, cc);
-    case SignFunc::SignumPolycircuit:
-        throw std::runtime_error("sign: SignumPolycircuit (degree-1023 table of src/sign.cpp:189-608) is not built; "
-                                 "use CompositeSign");
+    case SignFunc::SignumPolycircuit: return signum_polycircuit(x, cc);
     case SignFunc::CompositeSign:
     default:
         if (Cfg.compos.n == 3) return compositeSign<3>(x, cc, Cfg);

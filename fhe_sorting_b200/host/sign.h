@@ -22,5 +22,6 @@ struct SignConfig {
 template <int n>
 Ciphertext<DCRTPoly> compositeSign(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc, const SignConfig &Cfg);
 Ciphertext<DCRTPoly> sign(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc, SignFunc func, const SignConfig &Cfg);
+Ciphertext<DCRTPoly> signum_polycircuit(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc);
 Ciphertext<DCRTPoly> naive_discrete_sign(Ciphertext<DCRTPoly> a, CryptoContext<DCRTPoly> cc);
 Ciphertext<DCRTPoly> tanh(Ciphertext<DCRTPoly> a, CryptoContext<DCRTPoly> cc);

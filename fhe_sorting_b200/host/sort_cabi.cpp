@@ -298,6 +298,54 @@ template <int N> SessionBase *make_session(int log_ring_dim, int depth_override,
     s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return s.release();
 }
+// Fixture of the reference's primitive-level tests (tests/RotationTest.cpp:30-54, SignTest.cpp:22-39, SincTest.cpp,
+// utils/sign_characterizer.cpp:26-38): a context with caller-chosen depth / scaling size / batch and rotation keys, no sorter.
+struct ToolkitSession : SessionBase {
+    std::unique_ptr<RotationComposer<128>> composer; // RotationTest.cpp:51: array_length = 128, NAF
+    Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("toolkit session: no sorter"); }
+    Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("toolkit session: no sorter"); }
+    Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &, const Ciphertext<DCRTPoly> &) override {
+        throw std::runtime_error("toolkit session: no sorter");
+    }
+    Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &in, int r) override { return composer->rotate(in, r); }
+    void shard(int, int world) override {
+        if (world > 1) throw std::runtime_error("toolkit session: nothing to shard");
+    }
+};
+SessionBase *make_toolkit_session(int log_ring_dim, int depth, int scaling_bits, int batch, const int *keys, int num_keys, uint64_t seed,
+                                  int device, int boot_budget) {
+    auto t0 = std::chrono::steady_clock::now();
+    auto s = std::make_unique<ToolkitSession>();
+    CCParams<CryptoContextCKKSRNS> p;
+    p.SetRingDim(1u << log_ring_dim);
+    p.SetMultiplicativeDepth(depth);
+    p.SetScalingModSize(scaling_bits);
+    p.SetBatchSize(batch);
+    p.SetSecurityLevel(HEStd_NotSet);
+    if (seed) CryptoContextImpl::SetKeySeed(seed);
+#ifdef REFERENCE_DRIVERS
+    setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
+    s->cc = GenCryptoContext(p);
+#else
+    s->cc = GenCryptoContext(p, device);
+#endif
+    s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE);
+    if (boot_budget > 0) s->cc->Enable(FHE);
+    s->keys = s->cc->KeyGen();
+    if (boot_budget > 0) { // tests/k-way/SorterTest.cpp:40-43
+        s->cc->EvalBootstrapSetup({(uint32_t)boot_budget, (uint32_t)boot_budget}, {0, 0}, (uint32_t)batch);
+        s->cc->EvalBootstrapKeyGen(s->keys.secretKey, (uint32_t)batch);
+    }
+    s->rotations.assign(keys, keys + num_keys);
+    if (num_keys > 0) s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
+    s->cc->EvalMultKeyGen(s->keys.secretKey);
+    s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);
+    if (num_keys > 0) s->composer = std::make_unique<RotationComposer<128>>(s->cc, s->enc, s->rotations, DecomposeAlgo::NAF);
+    s->len = batch, s->depth = depth;
+    s->cc->Sync();
+    s->setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s.release();
+}
 SignConfig sign_config(int n, int dg, int df, int N) {
     if (n == 0) { // the reference tests' choice per array length (tests/DirectSortTest.cpp:103-111)
         n = 3, df = 2;
@@ -322,6 +370,19 @@ struct fhesort_session {
         g_err = "unknown error";    \
         return 1;                   \
     }
+
+// RotationTree<N>(cc, keys, algo).buildTree(start, end) then treeRotate(ct, r) for every r in `rotations`
+// (tests/RotationTest.cpp:77-109); N in {8, 128}; outputs [nrot][count]
+template <int N>
+void tree_rotate_all(SessionBase &S, int algo, int start, int end, const Ciphertext<DCRTPoly> &ct, const int *rotations, int nrot,
+                            int count, double *outputs) {
+    RotationTree<N> tree(S.cc, S.rotations, algo == 0 ? DecomposeAlgo::NAF : algo == 1 ? DecomposeAlgo::BNAF : DecomposeAlgo::BINARY);
+    tree.buildTree(start, end);
+    for (int i = 0; i < nrot; i++) {
+        auto v = S.enc->getPlaintext(tree.treeRotate(ct, rotations[i]), 0.0);
+        for (int k = 0; k < count; k++) outputs[(size_t)i * count + k] = v[k];
+    }
+}
 
 extern "C" {
 
@@ -468,6 +529,101 @@ int fhesort_run(fhesort_session *s, int which, const double *input, const double
     })
 }
 
+int fhesort_toolkit_session_create(int log_ring_dim, int mult_depth, int scaling_mod_size, int batch_size, const int *rotation_keys,
+                                   int num_keys, int bootstrap_budget, uint64_t seed, int device, fhesort_session **out) {
+    GUARD({
+        if (!out || (num_keys > 0 && !rotation_keys)) throw std::invalid_argument("null argument");
+        *out = new fhesort_session{std::unique_ptr<SessionBase>(
+            make_toolkit_session(log_ring_dim, mult_depth, scaling_mod_size, batch_size, rotation_keys, num_keys, seed, device, bootstrap_budget))};
+    })
+}
+// sign(x, cc, func, cfg) of src/sign.cpp:635-651 on a fresh encryption of `input`; func: 0 CompositeSign(n, dg, df),
+// 1 SignumPolycircuit, 2 Tanh, 3 NaiveDiscrete
+int fhesort_sign_eval(fhesort_session *s, int func, int n, int dg, int df, const double *input, int count, double *output, int *level,
+                      double *elapsed_ms) {
+    GUARD({
+        if (!s || !input || !output) throw std::invalid_argument("null argument");
+        if (func < 0 || func > 3) throw std::invalid_argument("sign: unknown function");
+        SessionBase &S = *s->s;
+        const SignFunc f = func == 0 ? SignFunc::CompositeSign : func == 1 ? SignFunc::SignumPolycircuit : func == 2 ? SignFunc::Tanh : SignFunc::NaiveDiscrete;
+        SignConfig cfg = func == 0 ? SignConfig(CompositeSignConfig(n, dg, df)) : SignConfig();
+        auto ct = S.enc->encryptInput(std::vector<double>(input, input + count));
+        S.cc->Sync();
+        auto t0 = std::chrono::steady_clock::now();
+        auto r = sign(ct, S.cc, f, cfg);
+        S.cc->Sync();
+        if (elapsed_ms) *elapsed_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (level) *level = (int)r->GetLevel();
+        auto v = S.enc->getPlaintext(r, 0.0);
+        for (int i = 0; i < count; i++) output[i] = v[i];
+    })
+}
+int fhesort_tree_rotate(fhesort_session *s, int N, int algo, int start, int end, const double *input, int count, const int *rotations,
+                        int nrot, double *outputs) {
+    GUARD({
+        if (!s || !input || !rotations || !outputs) throw std::invalid_argument("null argument");
+        SessionBase &S = *s->s;
+        auto ct = S.enc->encryptInput(std::vector<double>(input, input + count));
+        if (N == 8) tree_rotate_all<8>(S, algo, start, end, ct, rotations, nrot, count, outputs);
+        else if (N == 128) tree_rotate_all<128>(S, algo, start, end, ct, rotations, nrot, count, outputs);
+        else throw std::invalid_argument("tree_rotate: N must be 8 or 128");
+    })
+}
+
+// One call of a kwaySort::EvalUtils / SortUtils / Sorter method on fresh encryptions of the given slot vectors - what the
+// reference's tests/k-way/{EvalUtilsTest,SortUtilsTest,SorterTest}.cpp exercise.  op:
+//   1 multByInt(in0, param)         2 multAndKillImage(in0, in1)     3 squareAndKillImage(in0)
+//   4 leftRotate(in0, param)        5 rightRotate(in0, param)        6 checkLevelAndBoot(in0 encoded at level `aux`, param, depth)
+//   10 fcnL(in0, in1, comp = in2)   11 twoSorter({in0, in1}, comp = in2) -> out[0..count) min, out[count..2count) max
+//   22..25 run{Two,Three,Four,Five}Sorter(in0, indices, shift = param, comp1 = in1, comp2 = in2)
+// out: count values (2 * count for op 11); levels: level of in0 before / of the result after.
+int fhesort_kway_unit(fhesort_session *s, int op, long k, long M, long param, int aux, const double *in0, const double *in1,
+                      const double *in2, const int *idx0, const int *idx1, int count, double *out, int *level_before, int *level_after) {
+    GUARD({
+        if (!s || !in0 || !out) throw std::invalid_argument("null argument");
+        SessionBase &S = *s->s;
+        const long slots = (long)S.cc->GetEncodingParams()->GetBatchSize();
+        if (count < 1 || count > slots) throw std::invalid_argument("kway_unit: count must be 1..batch size");
+        auto enc = [&](const double *v, int level) {
+            if (!v) throw std::invalid_argument("kway_unit: missing input vector");
+            auto pt = level > 0 ? S.cc->MakeCKKSPackedPlaintext(std::vector<double>(v, v + count), 1, (uint32_t)level, nullptr, (uint32_t)slots)
+                                : S.cc->MakeCKKSPackedPlaintext(std::vector<double>(v, v + count));
+            return S.cc->Encrypt(S.keys.publicKey, pt);
+        };
+        auto put = [&](const Ciphertext<DCRTPoly> &c, double *dst) {
+            auto v = S.enc->getPlaintext(c, 0.0);
+            for (int i = 0; i < count; i++) dst[i] = v[i];
+        };
+        kwaySort::Sorter sorter(S.cc, S.enc, slots, k, M);
+        Ciphertext<DCRTPoly> a = enc(in0, op == 6 ? aux : 0), r;
+        if (level_before) *level_before = (int)a->GetLevel();
+        if (op == 1) sorter.multByInt(a, param, r);
+        else if (op == 2) { auto b = enc(in1, 0); sorter.multAndKillImage(a, b, r); }
+        else if (op == 3) sorter.squareAndKillImage(a, r);
+        else if (op == 4) sorter.leftRotate(a, param, r);
+        else if (op == 5) sorter.rightRotate(a, param, r);
+        else if (op == 6) { sorter.checkLevelAndBoot(a, (int)param, S.depth); r = a; }
+        else if (op == 10) { auto b = enc(in1, 0), c = enc(in2, 0); sorter.fcnL(a, b, c, r); }
+        else if (op == 11) {
+            Ciphertext<DCRTPoly> pair[2] = {a, enc(in1, 0)}, res[2];
+            auto c = enc(in2, 0);
+            sorter.twoSorter(pair, c, res);
+            put(res[1], out + count);
+            r = res[0];
+        } else if (op >= 22 && op <= 25) {
+            if (!idx0 || !idx1) throw std::invalid_argument("kway_unit: missing indices");
+            std::vector<std::vector<int>> indices(2, std::vector<int>((size_t)slots, 0));
+            for (int i = 0; i < count; i++) indices[0][i] = idx0[i], indices[1][i] = idx1[i];
+            auto c1 = enc(in1, 0);
+            if (op == 22) sorter.runTwoSorter(a, indices, param, c1, r);
+            else if (op == 23) sorter.runThreeSorter(a, indices, param, c1, r);
+            else { auto c2 = enc(in2, 0); op == 24 ? sorter.runFourSorter(a, indices, param, c1, c2, r) : sorter.runFiveSorter(a, indices, param, c1, c2, r); }
+        } else throw std::invalid_argument("kway_unit: unknown op");
+        if (level_after) *level_after = (int)r->GetLevel();
+        put(r, out);
+    })
+}
+
 // RotationComposer::rotate on a fresh encryption of `input` (count values, `slots` slots)
 int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output) {
     GUARD({
@@ -530,7 +686,7 @@ int fhesort_decompose(const int *key_indices, int num_keys, int rotation, int wr
         Decomposer<1024> d(std::vector<int>(key_indices, key_indices + num_keys));
         auto st = d.decompose(rotation, wrap, algo == 0 ? DecomposeAlgo::NAF : algo == 1 ? DecomposeAlgo::BNAF : DecomposeAlgo::BINARY);
         if (count) *count = (int)st.size();
-        for (int i = 0; i < (int)st.size() && i < capacity; i++) steps[i] = st[i].value * st[i].stepSize;
+        for (int i = 0; i < (int)st.size() && i < capacity; i++) steps[i] = st[i].stepSize; // signed amount (reference convention)
     })
 }
 #ifndef REFERENCE_DRIVERS

@@ -8,25 +8,19 @@ from .lib import FheError
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SORT_LIB_PATH = os.path.join(_HERE, "libfhesort.so")
-# the reference's own unmodified drivers compiled against the shim (oracle/Makefile `ref`; exists only where it was built)
-REFERENCE_DRIVERS_PATH = os.path.join(os.path.dirname(_HERE), "oracle", "_ref", "libref_sort.so")
-_libs = {}
 _lib = None
 
 
-def load_sort(drivers="ours"):
+def load_sort():
+    """dlopen libfhesort.so (this repository's host drivers); raises when it has not been built."""
     global _lib
-    if drivers not in _libs:
-        path = SORT_LIB_PATH if drivers == "ours" else REFERENCE_DRIVERS_PATH
-        if not os.path.exists(path):
-            raise FheError("%s is missing: build it with `make -C fhe_sorting_b200`%s"
-                           % (path, "" if drivers == "ours" else " and `make -C oracle ref` (needs /root/reference)"))
-        L = C.CDLL(path)
+    if _lib is None:
+        if not os.path.exists(SORT_LIB_PATH):
+            raise FheError("%s is missing: build it with `make -C fhe_sorting_b200`" % SORT_LIB_PATH)
+        L = C.CDLL(SORT_LIB_PATH)
         L.fhesort_last_error.restype = C.c_char_p
-        _libs[drivers] = L
-    if drivers == "ours":
-        _lib = _libs[drivers]
-    return _libs[drivers]
+        _lib = L
+    return _lib
 
 
 def _ck(rc, L=None):
@@ -49,9 +43,9 @@ class DirectSortSession:
 
     _create = "fhesort_session_create"
 
-    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0, drivers="ours"):
-        """drivers="reference" runs the reference's own sort_algo.h / sign.cpp ... (oracle/_ref) on the same engine."""
-        L = self.L = load_sort(drivers)
+    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0, lib=None):
+        """lib: another library with the same C ABI (tests pass the reference's own drivers built under oracle/_ref)."""
+        L = self.L = lib or load_sort()
         h = C.c_void_p()
         _ck(getattr(L, self._create)(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
         self.h, self.n = h, n
@@ -139,12 +133,13 @@ def rotation_indices(n, log_ring_dim=17):
     return list(out[:cnt.value])
 
 
-def decompose(keys, rotation, wrap, algo="BINARY"):
-    L = load_sort()
+def decompose(keys, rotation, wrap, algo="BINARY", lib=None):
+    """Decomposer<1024>::decompose: the signed rotation amounts, largest first (src/rotation.h:53-102)."""
+    L = lib or load_sort()
     k = (C.c_int * len(keys))(*keys)
     out = (C.c_int * 64)()
     cnt = C.c_int()
-    _ck(L.fhesort_decompose(k, len(keys), rotation, wrap, {"NAF": 0, "BNAF": 1, "BINARY": 2}[algo], out, 64, C.byref(cnt)))
+    _ck(L.fhesort_decompose(k, len(keys), rotation, wrap, {"NAF": 0, "BNAF": 1, "BINARY": 2}[algo], out, 64, C.byref(cnt)), L)
     return list(out[:cnt.value])
 
 
@@ -195,8 +190,8 @@ class KWaySortSession(DirectSortSession):
     """tests/k-way/KWaySort2Test.cpp's fixture: the HKC+21 k-way sorting network on N = k^M values with bootstrapping
     (depth 40, first modulus 60, scaling 59 bits, EvalBootstrapSetup + KeyGen).  Only sort() applies."""
 
-    def __init__(self, k, m, log_ring_dim=17, mult_depth=0, seed=1, device=0, drivers="ours"):
-        L = self.L = load_sort(drivers)
+    def __init__(self, k, m, log_ring_dim=17, mult_depth=0, seed=1, device=0, lib=None):
+        L = self.L = lib or load_sort()
         h = C.c_void_p()
         _ck(L.fhesort_kway_session_create(k, m, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
         self.h, self.n, self.k, self.m = h, k ** m, k, m
@@ -225,9 +220,9 @@ class BitonicSortSession(DirectSortSession):
         return c.value
 
 
-def kway_stage(k, m_total, stage, num_slots, drivers="ours"):
+def kway_stage(k, m_total, stage, num_slots, lib=None):
     """(m, logDist, slope, rotate distance), indices[2][num_slots] of one stage of the k-way network (host only)."""
-    L = load_sort(drivers)
+    L = lib or load_sort()
     geo = (C.c_int * 4)()
     i0 = np.zeros(num_slots, dtype=np.int32)
     i1 = np.zeros(num_slots, dtype=np.int32)
@@ -237,3 +232,54 @@ def kway_stage(k, m_total, stage, num_slots, drivers="ours"):
 
 def kway_num_stages(k, m_total):
     return m_total + m_total * (m_total - 1) // 2 * ((k + 1) // 2)
+
+
+SIGN_FUNCS = {"CompositeSign": 0, "SignumPolycircuit": 1, "Tanh": 2, "NaiveDiscrete": 3}
+_ALGOS = {"NAF": 0, "BNAF": 1, "BINARY": 2}
+
+
+class ToolkitSession(DirectSortSession):
+    """Fixture of the reference's primitive-level tests (tests/RotationTest.cpp, SignTest.cpp, tests/k-way/SorterTest.cpp,
+    utils/sign_characterizer.cpp): a context with the given depth / scaling size / batch / rotation keys and, optionally,
+    bootstrapping with level budget {b, b}; no sorter."""
+
+    def __init__(self, log_ring_dim, mult_depth, scaling_mod_size, batch, rotation_keys=(), bootstrap_budget=0, seed=1, device=0,
+                 lib=None):
+        L = self.L = lib or load_sort()
+        h = C.c_void_p()
+        keys = (C.c_int * max(1, len(rotation_keys)))(*rotation_keys)
+        _ck(L.fhesort_toolkit_session_create(log_ring_dim, mult_depth, scaling_mod_size, batch, keys, len(rotation_keys),
+                                             bootstrap_budget, C.c_uint64(seed), device, C.byref(h)), L)
+        self.h, self.n, self.mult_depth = h, batch, mult_depth
+
+    def sign(self, func, values, n=0, dg=0, df=0):
+        """sign(x, cc, func, cfg) of src/sign.cpp:635-651 -> (values, final level, milliseconds)"""
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        out = np.zeros(len(v))
+        lv, ms = C.c_int(), C.c_double()
+        _ck(self.L.fhesort_sign_eval(self.h, SIGN_FUNCS[func], n, dg, df, _dp(v), len(v), _dp(out), C.byref(lv), C.byref(ms)), self.L)
+        return out, lv.value, ms.value
+
+    def tree_rotate(self, n_template, values, start, end, rotations, algo="NAF"):
+        """RotationTree<N>::buildTree(start, end), then treeRotate for every requested rotation -> [len(rotations)][count]"""
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        rots = (C.c_int * len(rotations))(*rotations)
+        out = np.zeros((len(rotations), len(v)))
+        _ck(self.L.fhesort_tree_rotate(self.h, n_template, _ALGOS[algo], start, end, _dp(v), len(v), rots, len(rotations), _dp(out)), self.L)
+        return out
+
+    def kway_unit(self, op, k, m, in0, in1=None, in2=None, indices=None, param=0, aux=0):
+        """One kwaySort method on fresh encryptions (op codes: host/sort_cabi.cpp fhesort_kway_unit) -> (out, level before, after)"""
+        a = [None if x is None else np.ascontiguousarray(x, dtype=np.float64) for x in (in0, in1, in2)]
+        count = len(a[0])
+        out = np.zeros(2 * count)
+        i0 = i1 = None
+        if indices is not None:
+            i0 = np.ascontiguousarray(indices[0], dtype=np.int32)
+            i1 = np.ascontiguousarray(indices[1], dtype=np.int32)
+        lb, la = C.c_int(), C.c_int()
+        ip = lambda x: None if x is None else x.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _ck(self.L.fhesort_kway_unit(self.h, op, C.c_long(k), C.c_long(m), C.c_long(param), aux, _dp(a[0]),
+                                     None if a[1] is None else _dp(a[1]), None if a[2] is None else _dp(a[2]), ip(i0), ip(i1),
+                                     count, _dp(out), C.byref(lb), C.byref(la)), self.L)
+        return (out if op == 11 else out[:count]), lb.value, la.value

@@ -52,6 +52,21 @@ int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_a
 int fhesort_session_set_streams(fhesort_session *s, int k);
 /* RotationComposer<N>::rotate (src/rotation.h:215-233) */
 int fhesort_composed_rotate(fhesort_session *s, const double *input, int count, int rotation, double *output);
+/* Fixture of the reference's primitive-level tests (tests/RotationTest.cpp:30-54, tests/SignTest.cpp:22-39,
+ * utils/sign_characterizer.cpp:26-38): context + keys with the given depth / scaling size / batch size / rotation keys. */
+int fhesort_toolkit_session_create(int log_ring_dim, int mult_depth, int scaling_mod_size, int batch_size, const int *rotation_keys,
+                                   int num_keys, int bootstrap_budget, uint64_t seed, int device, fhesort_session **out);
+/* one kwaySort::EvalUtils / SortUtils / Sorter method on fresh encryptions (tests/k-way/EvalUtilsTest.cpp:62-158,
+ * SortUtilsTest.cpp:68-113, SorterTest.cpp:67-260); op codes: see host/sort_cabi.cpp */
+int fhesort_kway_unit(fhesort_session *s, int op, long k, long M, long param, int aux, const double *in0, const double *in1,
+                      const double *in2, const int *idx0, const int *idx1, int count, double *out, int *level_before, int *level_after);
+/* sign(x, cc, func, cfg) (src/sign.cpp:635-651): func 0 = CompositeSign(n, dg, df), 1 = SignumPolycircuit, 2 = Tanh, 3 = NaiveDiscrete */
+int fhesort_sign_eval(fhesort_session *s, int func, int n, int dg, int df, const double *input, int count, double *output, int *level,
+                      double *elapsed_ms);
+/* RotationTree<N>::buildTree(start, end) + treeRotate for each requested rotation (src/rotation.h:240-357); N = 8 or 128;
+ * algo 0 = NAF, 1 = BNAF, 2 = BINARY; outputs [nrot][count] */
+int fhesort_tree_rotate(fhesort_session *s, int N, int algo, int start, int end, const double *input, int count, const int *rotations,
+                        int nrot, double *outputs);
 /* host-only (no GPU needed) */
 int fhesort_rotation_indices(int N, int log_ring_dim, int *out, int capacity, int *count);
 int fhesort_shard_batches(int N, int log_ring_dim, int rank, int world, int *out, int capacity, int *count, int *sharded);

@@ -30,12 +30,12 @@ def test_kway_sort_small_ring(k, m):
 
 def test_kway_reference_drivers_unmodified_on_the_engine():
     """the reference's own src/k-way/*.cpp + kway_adapter.h (oracle/_ref/libref_sort.so) against this repository's kway.h"""
-    if not os.path.exists(S.REFERENCE_DRIVERS_PATH):
-        pytest.skip("oracle/_ref/libref_sort.so not built (needs /root/reference at build time)")
+    import refdrivers
+    libs = {"ours": None, "reference": refdrivers.library()}
     x = gap_input(8, 11)
     outs = {}
     for drivers in ("ours", "reference"):
-        s = S.KWaySortSession(2, 3, log_ring_dim=12, seed=3, drivers=drivers)
+        s = S.KWaySortSession(2, 3, log_ring_dim=12, seed=3, lib=libs[drivers])
         outs[drivers] = s.sort(x)[0]
         s.close()
     assert np.abs(outs["reference"] - np.sort(x)).max() < 0.01
@@ -43,7 +43,7 @@ def test_kway_reference_drivers_unmodified_on_the_engine():
     # k = 5: four/five-sorters and the mixed 2..5 stage, reference's hand-written bit tables against the one-rule pairBit
     x = gap_input(25, 5)
     for drivers in ("ours", "reference"):
-        s = S.KWaySortSession(5, 2, log_ring_dim=12, seed=3, drivers=drivers)
+        s = S.KWaySortSession(5, 2, log_ring_dim=12, seed=3, lib=libs[drivers])
         outs[drivers] = s.sort(x)[0]
         s.close()
     assert np.abs(outs["reference"] - np.sort(x)).max() < 0.01

@@ -33,12 +33,13 @@ def test_mehp24_n256_reference_parameters():
 
 def test_mehp24_reference_drivers_agree():
     """The reference's own src/mehp24/*.cpp compiled unmodified against the shim (oracle/_ref) and run on the engine."""
-    from fhe_sorting_b200.sort import Mehp24SortSession, uniform_gap_input, REFERENCE_DRIVERS_PATH
-    if not os.path.exists(REFERENCE_DRIVERS_PATH):
+    import refdrivers
+    from fhe_sorting_b200.sort import Mehp24SortSession, uniform_gap_input
+    if not refdrivers.available():
         pytest.skip("oracle/_ref/libref_sort.so not built (no reference checkout on the build machine)")
     n, logn = 16, 13
     x = uniform_gap_input(n, seed=4)
-    ref = Mehp24SortSession(n, logn, seed=5, drivers="reference")
+    ref = Mehp24SortSession(n, logn, seed=5, lib=refdrivers.library())
     out_ref, _, level_ref = ref.sort(x)
     ref.close()
     ours = Mehp24SortSession(n, logn, seed=5)

@@ -65,12 +65,13 @@ def test_reference_drivers_unmodified_on_the_engine():
     against the lbcrypto shim (oracle/_ref/libref_sort.so, built where /root/reference exists), sort on the B200 engine
     and agree with this repository's restated drivers."""
     import os
-    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input, REFERENCE_DRIVERS_PATH
-    if not os.path.exists(REFERENCE_DRIVERS_PATH):
+    import refdrivers
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input
+    if not refdrivers.available():
         pytest.skip("oracle/_ref/libref_sort.so not built (no reference checkout on the build machine)")
     for n, logn in ((16, 13), (64, 13), (16, 17)):
         x = uniform_gap_input(n, seed=99)
-        ref = DirectSortSession(n, logn, seed=5, drivers="reference")
+        ref = DirectSortSession(n, logn, seed=5, lib=refdrivers.library())
         out_ref, _, level_ref = ref.sort(x)
         ranks_ref, _, _ = ref.rank(x)
         ref.close()
@@ -110,10 +111,11 @@ def test_sort_hybrid(n, logn):
     import os
     from fhe_sorting_b200 import sort as S
     x = S.uniform_gap_input(n, seed=9)
-    drivers = ["ours"] + (["reference"] if os.path.exists(S.REFERENCE_DRIVERS_PATH) and n == 16 else [])
+    import refdrivers
+    drivers = ["ours"] + (["reference"] if refdrivers.available() and n == 16 else [])
     outs = {}
     for d in drivers:
-        s = S.HybridSortSession(n, logn, seed=31 + n, drivers=d)
+        s = S.HybridSortSession(n, logn, seed=31 + n, lib=refdrivers.library() if d == "reference" else None)
         outs[d], ms, level = s.sort_hybrid(x)
         assert level <= s.mult_depth
         s.close()

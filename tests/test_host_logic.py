@@ -36,13 +36,31 @@ def test_rotation_indices_match_reference_tables_up_to_128():
 
 
 def test_decompose_sums_to_rotation():
-    """tests/DecomposeTest.cpp:64-74: the signed steps always add up to the requested rotation."""
+    """tests/DecomposeTest.cpp:64-74: the signed steps always add up to the requested rotation (modulo N for the NAF form,
+    whose -N/2 digit is emitted as +N/2, src/rotation.h:124-128; Decomposer<1024> here)."""
     keys = [1, 2, 4, 8, 16, 32, 64, 512]
     for algo, rot in itertools.product(("NAF", "BNAF", "BINARY"), list(range(1, 130)) + [511, 513, 1000]):
         steps = S.decompose(keys, rot, 1 << 20, algo)
-        assert sum(steps) == rot, (algo, rot, steps)
-    assert S.decompose(keys, 5, 1 << 20, "BINARY") == [1, 4]
-    assert sorted(S.decompose(keys, 7, 1 << 20, "NAF")) == [-1, 8]
+        assert (sum(steps) - rot) % 1024 == 0, (algo, rot, steps)
+    assert S.decompose(keys, 5, 1 << 20, "BINARY") == [4, 1]          # largest step first
+    assert S.decompose(keys, 7, 1 << 20, "NAF") == [8, -1]
+    assert S.decompose(keys, 7, 1 << 20, "BNAF") == [8, -1]
+    assert S.decompose(keys, 3, 1 << 20, "BNAF") == [4, -1]           # balanced recoding: digit 1 followed by digit 1 borrows
+    assert S.decompose(keys, 5, 1 << 20, "BNAF") == [4, 1]
+    assert S.decompose(keys, 600, 1 << 20, "NAF")[0] == 512           # the largest key is peeled off first
+    assert S.decompose(keys, 96, 64, "BINARY") == [32]                 # steps that are multiples of the wrap length are dropped
+
+
+def test_decompose_equals_the_reference_decomposer():
+    """Every rotation 1..1100, the three digit forms, two key lists: same steps in the same order as the reference's own
+    Decomposer<1024> (src/rotation.h:29-165, compiled unmodified into oracle/_ref/libref_sort.so)."""
+    import refdrivers
+    ref = refdrivers.library()
+    for keys in ([1, 2, 4, 8, 16, 32, 64, 512], [-1, -2, -4, -8, 1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048]):
+        for algo in ("NAF", "BNAF", "BINARY"):
+            for rot in range(1, 1101):
+                for wrap in (128, 1 << 20):
+                    assert S.decompose(keys, rot, wrap, algo) == S.decompose(keys, rot, wrap, algo, lib=ref), (keys, algo, rot, wrap)
 
 
 def test_doubled_sinc_table_is_a_one_hot_at_rank_offsets():

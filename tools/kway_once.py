@@ -8,7 +8,12 @@ k, m = int(sys.argv[1]), int(sys.argv[2])
 logn = int(sys.argv[3]) if len(sys.argv) > 3 else 17
 drivers = sys.argv[4] if len(sys.argv) > 4 else "ours"
 t0 = time.time()
-s = S.KWaySortSession(k, m, log_ring_dim=logn, seed=5, drivers=drivers)
+lib = None
+if drivers == "reference":
+    sys.path.insert(0, "tests")
+    import refdrivers
+    lib = refdrivers.library()
+s = S.KWaySortSession(k, m, log_ring_dim=logn, seed=5, lib=lib)
 print("setup %.1f s (%d rotation keys requested by the network)" % (time.time() - t0, s.num_rotation_keys), flush=True)
 n = k ** m
 x = np.random.default_rng(n).permutation(n) * ((1 - 1e-8) / n)

@@ -23,13 +23,17 @@ print({k: {n: len(v) for n, v in t.items()} for k, t in out.items()})
 # k-way network geometry from the reference's own src/k-way/Masking.cpp (compiled into oracle/_ref/libref_sort.so)
 import sys
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 from fhe_sorting_b200 import sort as S  # noqa: E402
+import refdrivers  # noqa: E402
+
+REF = refdrivers.library()
 
 kw = {}
 for k, m in ((2, 2), (2, 3), (2, 5), (3, 2), (3, 3), (5, 2), (5, 3)):
     rows = []
     for st in range(S.kway_num_stages(k, m)):
-        geo, idx = S.kway_stage(k, m, st, k ** m, drivers="reference")
+        geo, idx = S.kway_stage(k, m, st, k ** m, lib=REF)
         rows.append({"geometry": list(geo), "indices": idx.tolist()})
     kw["%d^%d" % (k, m)] = rows
 json.dump(kw, open(os.path.join(ROOT, "tests", "golden", "kway_stages.json"), "w"), separators=(",", ":"))
