@@ -1,4 +1,5 @@
 // cabi.cu — extern "C" boundary (include/fhe_b200.h) over the engine.
+#include <cmath>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -298,6 +299,27 @@ int fheb200_eval_bootstrap_keygen(fheb200_ctx *ctx, fheb200_keys *k, int slots) 
 }
 int fheb200_eval_bootstrap(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out) {
     GUARD({ need(ctx, "ctx"); need(a, "ct"); need(out, "out"); *out = wrap(ctx->c->bootstrap(a->c)); })
+}
+// Meta-BTS (Bae, Cheon, Cho, Kim, Kim 2022; what OpenFHE's EvalBootstrap(ct, numIterations, precision) runs, reference
+// call site src/sort_algo.h:1110-1111): bootstrap, measure the error of that pass against the input at the input's level,
+// scale the error up by 2^p, bootstrap it, scale it back and subtract.  One more pass per extra iteration; each removes
+// ~p bits of the previous pass's error.  p is capped at 12: a single pass here is accurate to ~2^-16 for |m| <= 1 and the
+// scaled error must stay inside the bootstrapping's input range.
+static Ct bootstrap_iterated(Context &C, const Ct &a, int iterations, int precision) {
+    if (iterations <= 1) return C.bootstrap(a);
+    const int p = std::max(1, std::min(precision > 0 ? precision : 12, 12));
+    Ct first = bootstrap_iterated(C, a, iterations - 1, precision);
+    Ct err = C.sub(first, a);                       // aligned to the input's level: the error of the pass(es) so far
+    for (int i = 0; i < p; i++) err = C.add(err, err); // times 2^p without spending a level
+    Ct second = C.bootstrap(err);
+    return C.sub(first, C.mult_const(second, std::ldexp(1.0, -p)));
+}
+int fheb200_eval_bootstrap_iterated(fheb200_ctx *ctx, fheb200_ct *a, int iterations, int precision, fheb200_ct **out) {
+    GUARD({
+        need(ctx, "ctx"); need(a, "ct"); need(out, "out");
+        if (iterations < 1 || iterations > 4) throw std::invalid_argument("EvalBootstrap: numIterations must be 1..4");
+        *out = wrap(bootstrap_iterated(*ctx->c, a->c, iterations, precision));
+    })
 }
 int fheb200_eval_bootstrap_partial(fheb200_ctx *ctx, fheb200_ct *a, int stop_after, fheb200_ct **out) {
     GUARD({ need(ctx, "ctx"); need(a, "ct"); need(out, "out"); *out = wrap(ctx->c->bootstrap(a->c, stop_after)); })

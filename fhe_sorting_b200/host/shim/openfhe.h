@@ -246,12 +246,12 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         fheb200_check(fheb200_eval_bootstrap_keygen(ctx, sk.k->h, (int)slots));
         evalKeys = sk.k;
     }
-    // numIterations > 1 (Meta-BTS) runs the single-iteration bootstrapping: its precision at 59-bit scaling already
-    // exceeds what the sorts need
+    // numIterations > 1: Meta-BTS, one more bootstrapping of the scaled error per extra iteration (engine: cabi.cu)
     CT EvalBootstrap(const CT &c, uint32_t numIterations = 1, uint32_t precision = 0) {
-        (void)numIterations, (void)precision;
+        need(c);
         fheb200_ct *o = nullptr;
-        fheb200_check(fheb200_eval_bootstrap(ctx, c->h, &o));
+        if (numIterations <= 1) fheb200_check(fheb200_eval_bootstrap(ctx, c->h, &o));
+        else fheb200_check(fheb200_eval_bootstrap_iterated(ctx, c->h, (int)numIterations, (int)precision, &o));
         return wrap(o);
     }
 

@@ -311,7 +311,9 @@ class Context(_Handle):
     def bootstrap_keygen(self, keys, slots=0):
         _ck(_lib.fheb200_eval_bootstrap_keygen(self.h, keys.h, int(slots)))
 
-    def bootstrap(self, a, stop_after=0):
+    def bootstrap(self, a, stop_after=0, iterations=1, precision=0):
+        if iterations > 1:
+            return self._un("fheb200_eval_bootstrap_iterated", a, C.c_int(iterations), C.c_int(precision))
         if stop_after:
             return self._un("fheb200_eval_bootstrap_partial", a, C.c_int(stop_after))
         return self._un("fheb200_eval_bootstrap", a)

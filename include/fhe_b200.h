@@ -148,6 +148,9 @@ int fheb200_eval_bootstrap_keygen(fheb200_ctx *ctx, fheb200_keys *k, int slots);
  * left (GetLevel() < multiplicative depth, or a pending rescale); the output is at level fheb200_bootstrap_depth - 1 with
  * noise scale degree 2. */
 int fheb200_eval_bootstrap(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
+/* EvalBootstrap(ct, numIterations, precision) (src/sort_algo.h:1110-1111): Meta-BTS, one extra bootstrapping of the scaled
+ * error per extra iteration; precision (bits removed per extra pass) is capped at 12 */
+int fheb200_eval_bootstrap_iterated(fheb200_ctx *ctx, fheb200_ct *a, int iterations, int precision, fheb200_ct **out);
 int fheb200_bootstrap_depth(fheb200_ctx *ctx, int slots, int *levels);
 /* test hook: the intermediate ciphertext after step 1 (scale-down to q_0), 2 (ModRaise + SubSum), 3 (CoeffsToSlots +
  * conjugate), 4 (EvalMod), 5 (ModRaise alone, before SubSum); 0 = the whole bootstrapping */

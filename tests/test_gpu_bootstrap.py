@@ -145,3 +145,20 @@ def test_bootstrap_sizes(logn, slots, budget):
     err = np.abs(ctx.decrypt(keys, out, slots) - z).max()
     print("slots %d: bootstrap max error 2^%.1f" % (slots, np.log2(err)))
     assert err < 2.0 ** -13
+
+
+def test_meta_bts_second_iteration_removes_the_first_pass_error(env):
+    """EvalBootstrap(ct, 2, precision) (reference call: src/sort_algo.h:1110-1111 EvalBootstrap(result, 2, 20)): the second
+    pass bootstraps the scaled error of the first, so the output error drops by orders of magnitude; levels: one more than
+    the single pass (the 2^-p constant)."""
+    ctx, keys = env
+    z = np.array([0.5, -0.25, 0.125, 0.9, -0.7, 0.0, 0.33, -0.6])
+    c = deep(ctx, keys, z, 8, ctx.depth - 2)
+    one = ctx.bootstrap(c)
+    two = ctx.bootstrap(c, iterations=2, precision=20)
+    e1 = np.abs(ctx.decrypt(keys, one, 8) - z).max()
+    e2 = np.abs(ctx.decrypt(keys, two, 8) - z).max()
+    print("bootstrap error: one pass 2^%.1f, Meta-BTS 2^%.1f" % (np.log2(e1), np.log2(e2)))
+    assert e1 < 2.0 ** -12
+    assert e2 < e1 / 64
+    assert two.level <= one.level + 2
