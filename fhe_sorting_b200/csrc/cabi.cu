@@ -154,6 +154,15 @@ int fheb200_params_chain(const fheb200_params *p, uint64_t *moduli, uint64_t *ps
     })
 }
 
+int fheb200_ctx_allow_deterministic_keys(fheb200_ctx *ctx, int allow) {
+    GUARD({ need(ctx, "ctx"); ctx->c->allow_deterministic = allow != 0; })
+}
+int fheb200_ctx_get_rng_keys(fheb200_ctx *ctx, unsigned char *keys64) {
+    GUARD({ need(ctx, "ctx"); need(keys64, "keys64"); ctx->c->get_rng_keys(keys64); })
+}
+int fheb200_ctx_set_rng_keys(fheb200_ctx *ctx, const unsigned char *keys64) {
+    GUARD({ need(ctx, "ctx"); need(keys64, "keys64"); ctx->c->set_rng_keys(keys64); })
+}
 int fheb200_keygen(fheb200_ctx *ctx, uint64_t seed, fheb200_keys **out) {
     GUARD({ need(ctx, "ctx"); need(out, "out"); *out = new fheb200_keys{ctx->c->keygen(seed)}; })
 }

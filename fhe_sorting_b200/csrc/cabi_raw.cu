@@ -5,6 +5,7 @@
 
 #include "../../include/fhe_b200.h"
 #include "engine.h"
+#include "modarith.cuh"
 
 using namespace fheb200;
 
@@ -303,6 +304,18 @@ int fheb200_ntt_forward_noalloc(fheb200_ctx *ctx, const int *qp_indices, int cou
 }
 int fheb200_ntt_forward_noalloc_max_limbs(void) { return ntt_static_max_limbs(); }
 
+// host-side evaluation of the generator the sampling kernels use (known-answer test of the ChaCha20 block function)
+int fheb200_rng_block(const uint32_t *key8, uint64_t stream, uint64_t index, uint64_t *out2) {
+    GUARD({
+        need(key8, "key"); need(out2, "out");
+        uint32_t k[8];
+        for (int i = 0; i < 8; i++) k[i] = key8[i];
+        u64 w0, w1;
+        chacha20_128(k, stream, index, w0, w1);
+        out2[0] = w0, out2[1] = w1;
+    })
+}
+
 int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words) {
     GUARD({
         need(ct, "ct");
@@ -388,7 +401,11 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
         Mem lc_in, lc_out, lc_tab, lc_scratch;
         if (k == "lincomb") {
             lc_in = C.alloc((size_t)lc_count * 2 * ell * n), lc_out = C.alloc((size_t)lc_G * 2 * ell * n);
-            k_sample_uniform(C.T, 7, 99, 0, 1, lc_in->p, C.stream); // one limb of noise, replicated below
+            {
+                RngState bench_rng; // fixed test pattern (one limb of noise, replicated below)
+                bench_rng.seed = 7;
+                k_sample_uniform(C.T, bench_rng, 99, 0, 1, lc_in->p, C.stream);
+            }
             for (size_t off = (size_t)n; off < lc_in->words; off *= 2)
                 FHE_CUDA(cudaMemcpyAsync(lc_in->p + off, lc_in->p, std::min(off, lc_in->words - off) * 8, cudaMemcpyDeviceToDevice, C.stream));
             std::vector<u64> blob((size_t)lc_count + lc_G + (size_t)lc_G * lc_count * ell);

@@ -107,8 +107,16 @@ class Context : public std::enable_shared_from_this<Context> {
     cudaStream_t stream = nullptr;
     bool own_stream = true;
     std::recursive_mutex mu;
-    u64 seed = 0;
+    // generator state (modarith.cuh "randomness"): secret material and the public uniform polynomials draw from
+    // independent ChaCha20 keys (OS entropy); keygen(seed != 0) switches both to the TEST-ONLY deterministic generator and
+    // is refused unless allow_deterministic was set (fheb200_ctx_allow_deterministic_keys)
+    RngState rng_secret, rng_public;
+    bool allow_deterministic = false;
+    bool rng_pinned = false; // key material was installed by set_rng_keys (replicated keys): KeyGen must not redraw it
     std::atomic<u64> nonce{1};
+    void reseed_from_os();                       // fresh 2 x 256 bits of OS entropy (throws when none is available)
+    void set_rng_keys(const unsigned char *k64); // replicate key material on another rank (64 bytes from get_rng_keys)
+    void get_rng_keys(unsigned char *k64) const;
 
     // ---- keys
     Keys keygen(u64 seed);
@@ -182,6 +190,7 @@ class Context : public std::enable_shared_from_this<Context> {
     void use_stream(int i);
     void join();
     bool forked() const { return forked_; }
+    bool park_if_shared(u64 *p, unsigned buf_epoch); // DevMem release inside a forked region (see DevMem::~DevMem)
     bool usable(const Mem &m) const { return !forked_ || m->stream == stream || m->epoch < fork_epoch_; }
     unsigned epoch = 1;
     // ---- asynchronous host <-> device transfers on a copy stream of their own (pinned host buffers), so that the copies
@@ -217,6 +226,8 @@ class Context : public std::enable_shared_from_this<Context> {
     std::vector<cudaStream_t> side_;
     std::vector<cudaEvent_t> side_done_;
     cudaEvent_t fork_ev_ = nullptr, free_ev_ = nullptr;
+    std::mutex park_mu_;
+    std::vector<u64 *> parked_; // pre-fork buffers dropped inside the forked region, freed by join()
     bool forked_ = false;
     int fork_k_ = 0;
     cudaStream_t copy_stream_ = nullptr, out_stream_ = nullptr; // H2D and D2H copies (one DMA engine per direction)

@@ -107,7 +107,10 @@ Mem Context::encoding_for(const Pt &pt, int ell, double scale) {
     for (auto &e : pt->alt)
         if (std::get<0>(e) == ell && std::get<1>(e) == scale && usable(std::get<2>(e))) return std::get<2>(e);
     Mem m = encode_at(*pt, ell, scale);
-    if (pt->alt.size() >= 4) pt->alt.erase(pt->alt.begin());
+    // inside a forked region an encoding made by one stream is unusable by its siblings (usable()), so every stream keeps
+    // its own entries: room for 4 per stream, or they evict each other on every call
+    const size_t cap = forked_ ? 4 * (size_t)(fork_k_ + 1) : 4;
+    while (pt->alt.size() >= cap) pt->alt.erase(pt->alt.begin());
     pt->alt.emplace_back(ell, scale, m);
     return m;
 }

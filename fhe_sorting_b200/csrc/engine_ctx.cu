@@ -5,6 +5,11 @@
 
 #include <algorithm>
 
+#include <sys/random.h>
+
+#include <cstdio>
+#include <cstring>
+
 #include "engine.h"
 
 namespace fheb200 {
@@ -12,6 +17,9 @@ namespace fheb200 {
 DevMem::~DevMem() {
     if (!p || !ctx) return;
     cudaStream_t s = stream ? stream : ctx->stream;
+    // Inside a forked region a buffer that existed before the fork is readable by EVERY side stream, so no single event
+    // orders its release: park it; join() frees it on the main stream once all side streams have been joined.
+    if (ctx->park_if_shared(p, epoch)) return;
     if (s != ctx->stream && ctx->free_ev_) { // last used on another stream than the one it lives on: free after that use
         cudaEventRecord(ctx->free_ev_, ctx->stream);
         cudaStreamWaitEvent(s, ctx->free_ev_, 0);
@@ -135,6 +143,18 @@ void Context::join() {
     }
     stream = main_stream_;
     forked_ = false, ++epoch;
+    std::vector<u64 *> parked;
+    {
+        std::lock_guard<std::mutex> pg(park_mu_);
+        parked.swap(parked_);
+    }
+    for (u64 *q : parked) cudaFreeAsync(q, main_stream_); // ordered after every side stream's last kernel
+}
+bool Context::park_if_shared(u64 *q, unsigned buf_epoch) {
+    std::lock_guard<std::mutex> pg(park_mu_);
+    if (!forked_ || buf_epoch >= fork_epoch_) return false;
+    parked_.push_back(q);
+    return true;
 }
 
 void *Context::owned_alloc(size_t bytes, const void *init) {
@@ -166,7 +186,7 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
     FHE_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t keep = UINT64_MAX;
     FHE_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-    C->seed = ((u64)std::random_device{}() << 32) ^ std::random_device{}();
+    C->reseed_from_os();
 
     const int F = P.L + P.K, n = P.n;
     DeviceTables &T = C->T;
@@ -216,6 +236,8 @@ Context::~Context() {
     for (auto e : free_events_) cudaEventDestroy(e);
     if (copy_stream_) cudaStreamDestroy(copy_stream_), cudaStreamDestroy(out_stream_);
     for (auto s : side_) cudaStreamSynchronize(s);
+    for (u64 *q : parked_) cudaFree(q); // a forked region that was never joined
+    parked_.clear();
     if (stream) cudaStreamSynchronize(stream);
     for (auto s : side_) cudaStreamDestroy(s);
     for (auto e : side_done_) cudaEventDestroy(e);
@@ -229,6 +251,43 @@ Context::~Context() {
         if (s.done) cudaEventDestroy(s.done);
     }
     if (stream && own_stream) cudaStreamDestroy(stream);
+}
+
+// 64 bytes of OS entropy: getrandom(2), else /dev/urandom; never a weaker source
+static void os_entropy(unsigned char *out, size_t len) {
+    size_t got = 0;
+    while (got < len) {
+        ssize_t r = getrandom(out + got, len - got, 0);
+        if (r <= 0) break;
+        got += (size_t)r;
+    }
+    if (got < len) {
+        FILE *f = fopen("/dev/urandom", "rb");
+        if (f) {
+            got += fread(out + got, 1, len - got, f);
+            fclose(f);
+        }
+    }
+    if (got < len) throw std::runtime_error("fheb200: no OS entropy source (getrandom and /dev/urandom both failed)");
+}
+void Context::reseed_from_os() {
+    unsigned char k[64];
+    os_entropy(k, sizeof(k));
+    set_rng_keys(k);
+    rng_pinned = false;
+    memset(k, 0, sizeof(k));
+}
+void Context::set_rng_keys(const unsigned char *k64) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    rng_secret = RngState(), rng_public = RngState();
+    memcpy(rng_secret.key, k64, 32), memcpy(rng_public.key, k64 + 32, 32);
+    rng_secret.secure = rng_public.secure = 1;
+    rng_pinned = true;
+    nonce = 1;
+}
+void Context::get_rng_keys(unsigned char *k64) const {
+    if (!rng_secret.secure) throw std::runtime_error("fheb200: the context is in the deterministic test mode; it has no key material to share");
+    memcpy(k64, rng_secret.key, 32), memcpy(k64 + 32, rng_public.key, 32);
 }
 
 size_t Context::key_bytes() const { return (evk_rot.size() + (evk_mult ? 1 : 0)) * evk_words() * sizeof(u64); }

@@ -21,7 +21,16 @@ static std::vector<uint32_t> iota_desc(int count, int slot0 = 0, int qp0 = 0) {
 Keys Context::keygen(u64 sd) {
     std::lock_guard<std::recursive_mutex> g(mu);
     FHE_CUDA(cudaSetDevice(device));
-    seed = sd;
+    if (sd != 0) { // TEST-ONLY: 64-bit seeded, non-cryptographic generator shared with the CPU oracle
+        if (!allow_deterministic)
+            throw std::runtime_error("KeyGen: a non-zero seed selects the deterministic test generator, which is refused unless "
+                                     "fheb200_ctx_allow_deterministic_keys(ctx, 1) was called; pass seed 0 for ChaCha20 keyed from OS entropy");
+        rng_secret = RngState(), rng_public = RngState();
+        rng_secret.seed = rng_public.seed = sd;
+        nonce = 1;
+    } else if (!rng_pinned) {
+        reseed_from_os(); // every key pair gets its own 2 x 256 bits
+    }
     const int n = P->n, L = P->L, F = L + P->K;
     auto K = std::make_shared<KeySet>();
     K->s = alloc((size_t)F * n);
@@ -29,13 +38,13 @@ Keys Context::keygen(u64 sd) {
     Mem small = alloc((size_t)n / 2 + 1); // n ints
     int *sm = (int *)small->p;
     const uint32_t *dF = desc(iota_desc(F)), *dL = desc(iota_desc(L));
-    k_sample_small(T, SMALL_TERNARY, seed, stream_id(ST_SK, 0, 0), sm, stream);
+    k_sample_small(T, SMALL_TERNARY, rng_secret, stream_id(ST_SK, 0, 0), sm, stream);
     k_expand_small(T, sm, K->s->p, dF, F, stream);
     k_ntt_fwd(T, K->s->p, dF, F, stream);
     // public key: b = e - a s over the Q limbs
     u64 *b = K->pk->p, *a = K->pk->p + (size_t)L * n;
-    k_sample_uniform(T, seed, stream_id(ST_PK_A, 0, 0), 0, L, a, stream);
-    k_sample_small(T, SMALL_GAUSS, seed, stream_id(ST_PK_E, 0, 0), sm, stream);
+    k_sample_uniform(T, rng_public, stream_id(ST_PK_A, 0, 0), 0, L, a, stream);
+    k_sample_small(T, SMALL_GAUSS, rng_secret, stream_id(ST_PK_E, 0, 0), sm, stream);
     k_expand_small(T, sm, b, dL, L, stream);
     k_ntt_fwd(T, b, dL, L, stream);
     LimbScalars zero;
@@ -53,8 +62,8 @@ u64 *Context::gen_switch_key(u64 key_id, const u64 *s_old, const u64 *s_new) {
     const uint32_t *dF = desc(iota_desc(F));
     for (int j = 0; j < beta; j++) {
         u64 *b = evk + ((size_t)j * 2 + 0) * F * n, *a = evk + ((size_t)j * 2 + 1) * F * n;
-        k_sample_uniform(T, seed, stream_id(ST_EVK_A, j, key_id), 0, F, a, stream);
-        k_sample_small(T, SMALL_GAUSS, seed, stream_id(ST_EVK_E, j, key_id), (int *)small->p, stream);
+        k_sample_uniform(T, rng_public, stream_id(ST_EVK_A, j, key_id), 0, F, a, stream);
+        k_sample_small(T, SMALL_GAUSS, rng_secret, stream_id(ST_EVK_E, j, key_id), (int *)small->p, stream);
         k_expand_small(T, (int *)small->p, b, dF, F, stream);
         k_ntt_fwd(T, b, dF, F, stream);
         LimbScalars pm;
@@ -302,7 +311,7 @@ Ct Context::encrypt(const Keys &k, const Pt &pt) {
     const u64 tags[3] = {ST_ENC_V, ST_ENC_E0, ST_ENC_E1};
     for (int x = 0; x < 3; x++) {
         u64 *dst = tmp->p + (size_t)x * ell * n;
-        k_sample_small(T, x == 0 ? SMALL_TERNARY : SMALL_GAUSS, seed, stream_id(tags[x], 0, nc), (int *)small->p, stream);
+        k_sample_small(T, x == 0 ? SMALL_TERNARY : SMALL_GAUSS, rng_secret, stream_id(tags[x], 0, nc), (int *)small->p, stream);
         k_expand_small(T, (int *)small->p, dst, dq, ell, stream);
         k_ntt_fwd(T, dst, dq, ell, stream);
     }

@@ -148,9 +148,9 @@ void k_dh_accumulate(const DeviceTables &T, const DevicePlan &P, const u64 *acc,
                      uint32_t galois, cudaStream_t st);
 
 // ---- samplers / encode helpers ----
-void k_sample_uniform(const DeviceTables &T, u64 seed, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st);
+void k_sample_uniform(const DeviceTables &T, const RngState &R, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st);
 enum SmallKind { SMALL_TERNARY = 0, SMALL_GAUSS = 1 };
-void k_sample_small(const DeviceTables &T, SmallKind kind, u64 seed, u64 stream, int *out, cudaStream_t st);
+void k_sample_small(const DeviceTables &T, SmallKind kind, const RngState &R, u64 stream, int *out, cudaStream_t st);
 // signed small ints [n] -> residues for the limbs listed in desc (slot,qp); coefficient domain
 void k_expand_small(const DeviceTables &T, const int *small, u64 *out, const uint32_t *d_desc, int count,
                     cudaStream_t st);

@@ -109,7 +109,14 @@ __device__ __forceinline__ u64 fp_to_u64(double v, double q, double qinv) { // a
 }
 __device__ __forceinline__ bool fp_modulus_ok(const ModConst &m) { return m.bits <= 42; }
 
-// counter-based generator shared with the oracle (spec: DESIGN.md "Randomness")
+// ---- randomness ---------------------------------------------------------------------------------------------------
+// Two generators behind one interface (RngState, params.h):
+//   secure = 1 (default): ChaCha20 (RFC 8439 block function, 20 rounds) keyed with 256 bits of OS entropy; block counter =
+//     element index, nonce = stream id (tag | digit | key id / encryption nonce).  Secret material (ternary secret,
+//     Gaussian errors, encryption randomness) and public material (the uniform `a` polynomials of pk / evk) use
+//     independent keys, so nothing public shares generator state with the secret key.
+//   secure = 0: the counter-based mix64 generator below, seeded with 64 bits.  NOT cryptographic (the finaliser is
+//     invertible): TEST-ONLY, used so that the CPU oracle can draw the same keys and noise (DESIGN.md "Randomness").
 __host__ __device__ __forceinline__ u64 mix64(u64 z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
@@ -119,6 +126,37 @@ __host__ __device__ __forceinline__ u64 rng_u64(u64 seed, u64 stream, u64 idx, u
     u64 a = mix64(seed ^ (0x9E3779B97F4A7C15ULL * (stream + 1)));
     u64 b = mix64(a + idx);
     return mix64(b + 0xD1B54A32D192ED03ULL * (word + 1));
+}
+__host__ __device__ __forceinline__ uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+#define FHE_CHACHA_QR(a, b, c, d) \
+    a += b, d ^= a, d = rotl32(d, 16), c += d, b ^= c, b = rotl32(b, 12), a += b, d ^= a, d = rotl32(d, 8), c += d, b ^= c, b = rotl32(b, 7)
+// first 128 bits of the ChaCha20 block (key, counter = idx, nonce = stream)
+__host__ __device__ __forceinline__ void chacha20_128(const uint32_t (&key)[8], u64 stream, u64 idx, u64 &w0, u64 &w1) {
+    uint32_t x[16], in[16];
+    in[0] = 0x61707865u, in[1] = 0x3320646eu, in[2] = 0x79622d32u, in[3] = 0x6b206574u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) in[4 + i] = key[i];
+    in[12] = (uint32_t)idx, in[13] = (uint32_t)(idx >> 32), in[14] = (uint32_t)stream, in[15] = (uint32_t)(stream >> 32);
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = in[i];
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        FHE_CHACHA_QR(x[0], x[4], x[8], x[12]);
+        FHE_CHACHA_QR(x[1], x[5], x[9], x[13]);
+        FHE_CHACHA_QR(x[2], x[6], x[10], x[14]);
+        FHE_CHACHA_QR(x[3], x[7], x[11], x[15]);
+        FHE_CHACHA_QR(x[0], x[5], x[10], x[15]);
+        FHE_CHACHA_QR(x[1], x[6], x[11], x[12]);
+        FHE_CHACHA_QR(x[2], x[7], x[8], x[13]);
+        FHE_CHACHA_QR(x[3], x[4], x[9], x[14]);
+    }
+    w0 = (u64)(x[0] + in[0]) | ((u64)(x[1] + in[1]) << 32);
+    w1 = (u64)(x[2] + in[2]) | ((u64)(x[3] + in[3]) << 32);
+}
+// 128 random bits for element idx of a stream
+__host__ __device__ __forceinline__ void rng_draw128(const RngState &R, u64 stream, u64 idx, u64 &w0, u64 &w1) {
+    if (R.secure) chacha20_128(R.key, stream, idx, w0, w1);
+    else w0 = rng_u64(R.seed, stream, idx, 0), w1 = rng_u64(R.seed, stream, idx, 1);
 }
 
 } // namespace fheb200

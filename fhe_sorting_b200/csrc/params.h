@@ -29,6 +29,14 @@ struct ModConst {
     uint32_t pad;
 };
 
+// generator state handed to the sampling kernels by value (modarith.cuh "randomness")
+struct RngState {
+    u64 seed = 0;            // secure == 0: 64-bit seed of the test-only deterministic generator
+    uint32_t key[8] = {0};   // secure == 1: 256-bit ChaCha20 key
+    int secure = 0;
+    int pad = 0;
+};
+
 u64 mulmod_h(u64 a, u64 b, u64 q);
 u64 powmod_h(u64 a, u64 e, u64 q);
 u64 invmod_h(u64 a, u64 q);

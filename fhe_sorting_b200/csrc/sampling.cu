@@ -19,17 +19,19 @@ __constant__ u64 c_cdt[29] = {
     0x7ffffffffffffffdULL}; // tools/gen_cdt.py
 
 // uniform mod q from 128 random bits; element index = qp*n + j
-__global__ void __launch_bounds__(SP_THREADS) sp_uniform(DeviceTables T, u64 seed, u64 stream, int qp0, u64 *out) {
+__global__ void __launch_bounds__(SP_THREADS) sp_uniform(DeviceTables T, RngState R, u64 stream, int qp0, u64 *out) {
     const int j = blockIdx.x * SP_THREADS + threadIdx.x, qp = qp0 + blockIdx.y;
     if (j >= T.n) return;
     const u64 idx = (u64)qp * T.n + j;
-    u64 hi = rng_u64(seed, stream, idx, 0), lo = rng_u64(seed, stream, idx, 1);
+    u64 hi, lo;
+    rng_draw128(R, stream, idx, hi, lo);
     out[(size_t)blockIdx.y * T.n + j] = reduce128(hi, lo, T.mc[qp]);
 }
-__global__ void __launch_bounds__(SP_THREADS) sp_small(DeviceTables T, int kind, u64 seed, u64 stream, int *out) {
+__global__ void __launch_bounds__(SP_THREADS) sp_small(DeviceTables T, int kind, RngState R, u64 stream, int *out) {
     const int j = blockIdx.x * SP_THREADS + threadIdx.x;
     if (j >= T.n) return;
-    u64 u = rng_u64(seed, stream, (u64)j, 0);
+    u64 u, unused;
+    rng_draw128(R, stream, (u64)j, u, unused);
     int v;
     if (kind == SMALL_TERNARY) {
         u64 r = u % 3;
@@ -100,11 +102,11 @@ __global__ void __launch_bounds__(SP_THREADS) sp_decrypt_core(DeviceTables T, co
 
 static inline dim3 g1(const DeviceTables &T, int y) { return dim3((T.n + SP_THREADS - 1) / SP_THREADS, y); }
 
-void k_sample_uniform(const DeviceTables &T, u64 seed, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st) {
-    g_launches++, sp_uniform<<<g1(T, limbs), SP_THREADS, 0, st>>>(T, seed, stream, qp0, out);
+void k_sample_uniform(const DeviceTables &T, const RngState &R, u64 stream, int qp0, int limbs, u64 *out, cudaStream_t st) {
+    g_launches++, sp_uniform<<<g1(T, limbs), SP_THREADS, 0, st>>>(T, R, stream, qp0, out);
 }
-void k_sample_small(const DeviceTables &T, SmallKind kind, u64 seed, u64 stream, int *out, cudaStream_t st) {
-    g_launches++, sp_small<<<g1(T, 1), SP_THREADS, 0, st>>>(T, (int)kind, seed, stream, out);
+void k_sample_small(const DeviceTables &T, SmallKind kind, const RngState &R, u64 stream, int *out, cudaStream_t st) {
+    g_launches++, sp_small<<<g1(T, 1), SP_THREADS, 0, st>>>(T, (int)kind, R, stream, out);
 }
 void k_expand_small(const DeviceTables &T, const int *small, u64 *out, const uint32_t *d_desc, int count, cudaStream_t st) {
     g_launches++, sp_expand_small<<<g1(T, count), SP_THREADS, 0, st>>>(T, small, out, d_desc);

@@ -219,7 +219,9 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     // ---- keys (tests/DirectSortTest.cpp:43-47)
     KeyPair<DCRTPoly> KeyGen() {
         auto k = std::make_shared<KeySetImpl>();
-        fheb200_check(fheb200_keygen(ctx, seed_next(), &k->h));
+        const uint64_t seed = seed_next(); // 0 unless SetKeySeed was called: ChaCha20 from OS entropy
+        if (seed) fheb200_check(fheb200_ctx_allow_deterministic_keys(ctx, 1));
+        fheb200_check(fheb200_keygen(ctx, seed, &k->h));
         KeyPair<DCRTPoly> kp;
         kp.publicKey.k = k;
         kp.secretKey.k = k;
@@ -403,6 +405,8 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         allReduceWords(ptr, words);
         fheb200_check(fheb200_ct_reduce_partial_sums(ctx, a->h));
     }
+    // TEST ONLY (not an OpenFHE call): a non-zero seed makes the following KeyGen calls deterministic (seed, seed + 1, ...)
+    // with the non-cryptographic generator the CPU oracle shares; 0 restores the default (OS entropy)
     static void SetKeySeed(uint64_t s) { seed_state() = s; }
 
   private:
@@ -412,8 +416,7 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     }
     static uint64_t seed_next() {
         uint64_t &s = seed_state();
-        if (s == 0) s = ((uint64_t)std::random_device{}() << 32) ^ std::random_device{}();
-        return s++;
+        return s == 0 ? 0 : s++;
     }
     CT binary(int (*fn)(fheb200_ctx *, fheb200_ct *, fheb200_ct *, fheb200_ct **), const CT &a, const CT &b) {
         need(a), need(b);

@@ -38,6 +38,7 @@ struct SessionBase {
     std::shared_ptr<DebugEncryption> enc;
     std::vector<int> rotations;
     int len = 0, depth = 0;
+    bool seeded = false; // created with a non-zero (test-only, deterministic) key seed
     double setup_ms = 0;
     virtual ~SessionBase() = default;
     virtual Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) = 0;
@@ -117,7 +118,8 @@ SessionBase *make_mehp24_session(int N, int log_ring_dim, int depth_override, ui
     p.SetMultiplicativeDepth(depth_override > 0 ? depth_override : mehp24_depth(N));
     p.SetScalingModSize(40);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
-    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    CryptoContextImpl::SetKeySeed(seed); // 0: OS entropy (ChaCha20); non-zero: TEST-ONLY deterministic keys
+    s->seeded = seed != 0;
 #ifdef REFERENCE_DRIVERS
     setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
     s->cc = GenCryptoContext(p);
@@ -178,7 +180,8 @@ template <int N> SessionBase *make_kway_session(int k, int M, int log_ring_dim, 
     p.SetRingDim(1u << log_ring_dim);
     if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
-    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    CryptoContextImpl::SetKeySeed(seed); // 0: OS entropy (ChaCha20); non-zero: TEST-ONLY deterministic keys
+    s->seeded = seed != 0;
 #ifdef REFERENCE_DRIVERS
     setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
     s->cc = GenCryptoContext(p);
@@ -244,7 +247,8 @@ template <int N> SessionBase *make_bitonic_session(int log_ring_dim, int depth_o
     p.SetBatchSize(N);
     p.SetRingDim(1u << log_ring_dim);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
-    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    CryptoContextImpl::SetKeySeed(seed); // 0: OS entropy (ChaCha20); non-zero: TEST-ONLY deterministic keys
+    s->seeded = seed != 0;
 #ifdef REFERENCE_DRIVERS
     setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
     s->cc = GenCryptoContext(p);
@@ -279,7 +283,8 @@ template <int N> SessionBase *make_session(int log_ring_dim, int depth_override,
     }
     if (depth_override > 0) p.SetMultiplicativeDepth(depth_override);
     p.SetSecurityLevel(log_ring_dim >= 17 ? HEStd_128_classic : HEStd_NotSet);
-    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    CryptoContextImpl::SetKeySeed(seed); // 0: OS entropy (ChaCha20); non-zero: TEST-ONLY deterministic keys
+    s->seeded = seed != 0;
 #ifdef REFERENCE_DRIVERS
     setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
     s->cc = GenCryptoContext(p);
@@ -322,7 +327,8 @@ SessionBase *make_toolkit_session(int log_ring_dim, int depth, int scaling_bits,
     p.SetScalingModSize(scaling_bits);
     p.SetBatchSize(batch);
     p.SetSecurityLevel(HEStd_NotSet);
-    if (seed) CryptoContextImpl::SetKeySeed(seed);
+    CryptoContextImpl::SetKeySeed(seed); // 0: OS entropy (ChaCha20); non-zero: TEST-ONLY deterministic keys
+    s->seeded = seed != 0;
 #ifdef REFERENCE_DRIVERS
     setenv("FHEB200_DEVICE", std::to_string(device).c_str(), 1);
     s->cc = GenCryptoContext(p);
@@ -479,6 +485,12 @@ int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_a
         if (!s) throw std::invalid_argument("null argument: session");
         if (world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("set_shard: bad rank / world");
         if (world > 1 && !fn) throw std::invalid_argument("set_shard: an all-reduce callback is required when world > 1");
+        // partial residues (< 2^60 for the first, extra and special limbs) are summed as int64: 16 summands cannot wrap
+        if (world > 16) throw std::invalid_argument("set_shard: at most 16 ranks (the all-reduce sums raw residues below 2^60 in 64 bits)");
+        // every rank must hold the same keys: with OS-entropy keys (seed 0) each rank would draw its own
+        if (world > 1 && !s->s->seeded)
+            throw std::invalid_argument("set_shard: sharding needs replicated keys - create the session on every rank with the same "
+                                        "non-zero seed (the sessions of this library have no key-exchange step)");
         s->s->shard(rank, world);
         if (world > 1)
             s->s->cc->allReduceWords = [fn, user](void *p, size_t w) {

@@ -203,10 +203,24 @@ class Context(_Handle):
         return g.value
 
     # -- keys
-    def keygen(self, seed):
+    def keygen(self, seed=0):
+        """seed = 0: ChaCha20 keyed from OS entropy (the default).  seed != 0: TEST-ONLY deterministic key material from the
+        64-bit seeded generator the CPU oracle shares (enables fheb200_ctx_allow_deterministic_keys on this context)."""
+        if seed:
+            _ck(_lib.fheb200_ctx_allow_deterministic_keys(self.h, 1))
         h = C.c_void_p()
         _ck(_lib.fheb200_keygen(self.h, C.c_uint64(seed), C.byref(h)))
         return Keys(h)
+
+    def rng_keys(self):
+        """64 bytes of generator key material (treat like the secret key): hand them to set_rng_keys on the other ranks."""
+        buf = (C.c_ubyte * 64)()
+        _ck(_lib.fheb200_ctx_get_rng_keys(self.h, buf))
+        return bytes(buf)
+
+    def set_rng_keys(self, keys64):
+        assert len(keys64) == 64
+        _ck(_lib.fheb200_ctx_set_rng_keys(self.h, (C.c_ubyte * 64)(*keys64)))
 
     def eval_mult_keygen(self, keys):
         _ck(_lib.fheb200_eval_mult_keygen(self.h, keys.h))

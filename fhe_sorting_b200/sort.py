@@ -43,8 +43,10 @@ class DirectSortSession:
 
     _create = "fhesort_session_create"
 
-    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=1, device=0, lib=None):
-        """lib: another library with the same C ABI (tests pass the reference's own drivers built under oracle/_ref)."""
+    def __init__(self, n, log_ring_dim=17, mult_depth=0, seed=0, device=0, lib=None):
+        """seed = 0: keys from OS entropy (ChaCha20); seed != 0: TEST-ONLY deterministic keys (needed for replicated keys
+        across ranks and for comparisons with the oracle).  lib: another library with the same C ABI (tests pass the
+        reference's own drivers built under oracle/_ref)."""
         L = self.L = lib or load_sort()
         h = C.c_void_p()
         _ck(getattr(L, self._create)(n, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
@@ -190,7 +192,7 @@ class KWaySortSession(DirectSortSession):
     """tests/k-way/KWaySort2Test.cpp's fixture: the HKC+21 k-way sorting network on N = k^M values with bootstrapping
     (depth 40, first modulus 60, scaling 59 bits, EvalBootstrapSetup + KeyGen).  Only sort() applies."""
 
-    def __init__(self, k, m, log_ring_dim=17, mult_depth=0, seed=1, device=0, lib=None):
+    def __init__(self, k, m, log_ring_dim=17, mult_depth=0, seed=0, device=0, lib=None):
         L = self.L = lib or load_sort()
         h = C.c_void_p()
         _ck(L.fhesort_kway_session_create(k, m, log_ring_dim, mult_depth, C.c_uint64(seed), device, C.byref(h)), L)
@@ -243,7 +245,7 @@ class ToolkitSession(DirectSortSession):
     utils/sign_characterizer.cpp): a context with the given depth / scaling size / batch / rotation keys and, optionally,
     bootstrapping with level budget {b, b}; no sorter."""
 
-    def __init__(self, log_ring_dim, mult_depth, scaling_mod_size, batch, rotation_keys=(), bootstrap_budget=0, seed=1, device=0,
+    def __init__(self, log_ring_dim, mult_depth, scaling_mod_size, batch, rotation_keys=(), bootstrap_budget=0, seed=0, device=0,
                  lib=None):
         L = self.L = lib or load_sort()
         h = C.c_void_p()

@@ -66,7 +66,18 @@ int fheb200_params_chain(const fheb200_params *p, uint64_t *moduli, uint64_t *ps
                          int *digit_size);
 
 /* ---- keys: KeyGen / EvalMultKeyGen / EvalRotateKeyGen (tests/DirectSortTest.cpp:43-47) ---- */
+/* Randomness (reference: OpenFHE's cryptographic PRNG behind KeyGen / Encrypt, tests/DirectSortTest.cpp:43).  By default
+ * (seed = 0) all key material and encryption noise comes from ChaCha20 keyed with 2 x 256 bits of OS entropy drawn per key
+ * pair; secret material and the public uniform polynomials use independent keys.  seed != 0 selects a 64-bit seeded,
+ * NON-cryptographic generator that the CPU oracle shares - TEST ONLY, refused unless allow_deterministic_keys(ctx, 1) was
+ * called first.  get/set_rng_keys copy the 64 bytes of key material so that the ranks of one job can replicate keys
+ * (set before KeyGen on every rank; treat the bytes like the secret key). */
+int fheb200_ctx_allow_deterministic_keys(fheb200_ctx *ctx, int allow);
+int fheb200_ctx_get_rng_keys(fheb200_ctx *ctx, unsigned char *keys64);
+int fheb200_ctx_set_rng_keys(fheb200_ctx *ctx, const unsigned char *keys64);
 int fheb200_keygen(fheb200_ctx *ctx, uint64_t seed, fheb200_keys **out);
+/* first 128 bits of the ChaCha20 block (key, counter = index, nonce = stream) as the samplers draw them; host-only, for tests */
+int fheb200_rng_block(const uint32_t *key8, uint64_t stream, uint64_t index, uint64_t *out2);
 int fheb200_keys_release(fheb200_keys *k);
 int fheb200_eval_mult_keygen(fheb200_ctx *ctx, fheb200_keys *k);
 int fheb200_eval_rotate_keygen(fheb200_ctx *ctx, fheb200_keys *k, const int *indices, size_t count);
