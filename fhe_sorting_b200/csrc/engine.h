@@ -189,6 +189,13 @@ class Context : public std::enable_shared_from_this<Context> {
     void fork(int k);
     void use_stream(int i);
     void join();
+    // ---- multi-GPU (comm.cu): the engine's own NCCL communicator
+    void comm_init(const unsigned char *id128, int rank, int world);
+    void comm_destroy();
+    void all_reduce_sum(const Ct &a); // in place, on `stream`: 64-bit integer sum over the ranks, then every word mod q_limb
+    void *comm_ = nullptr;            // ncclComm_t
+    int comm_rank_ = 0, comm_world_ = 1;
+
     bool forked() const { return forked_; }
     bool park_if_shared(u64 *p, unsigned buf_epoch); // DevMem release inside a forked region (see DevMem::~DevMem)
     bool usable(const Mem &m) const { return !forked_ || m->stream == stream || m->epoch < fork_epoch_; }

@@ -229,6 +229,10 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
 
 Context::~Context() {
     if (forked_) stream = main_stream_;
+    try {
+        comm_destroy();
+    } catch (...) {
+    }
     if (copy_stream_) cudaStreamSynchronize(copy_stream_), cudaStreamSynchronize(out_stream_);
     for (auto &c : pending_) cudaEventDestroy(c.done);
     pending_.clear();

@@ -395,8 +395,19 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     // Multi-GPU extension (not an OpenFHE call): sum a partial ciphertext over the ranks that share this job.  `reduce`
     // sums the device buffer in place across ranks as 64-bit integers (NCCL all-reduce supplied by the launcher).
     std::function<void(void *device_ptr, size_t words)> allReduceWords;
+    // preferred: the engine's own NCCL communicator (fheb200_ctx_comm_init): the all-reduce and the fix-up are queued on the
+    // engine's stream, nothing waits on the host.  id128 from fheb200_comm_unique_id on rank 0.
+    bool nativeComm = false;
+    void CommInit(const unsigned char *id128, int rank, int world) {
+        fheb200_check(fheb200_ctx_comm_init(ctx, id128, rank, world));
+        nativeComm = world > 1;
+    }
     void AllReduceSum(CT &a) {
         need(a);
+        if (nativeComm) {
+            fheb200_check(fheb200_ct_all_reduce_sum(ctx, a->h));
+            return;
+        }
         if (!allReduceWords) return;
         void *ptr = nullptr;
         size_t words = 0;

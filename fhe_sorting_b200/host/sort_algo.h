@@ -223,12 +223,15 @@ template <int N> class DirectSort : public SortBase<N> {
     // Shifted copies for batch `is`: copy c of the result holds the array rotated left by is*P + c.
     // Baby-step / giant-step: group j gathers, from the np pre-rotated inputs, the copies np*j .. np*j+np-1 (masks are
     // pre-rotated right by the giant step so that one rotation by is*P + j*np puts everything in place).
-    CT vecRotsOpt(const std::vector<CT> &preRotatedArrays, int num_partition, int num_slots, int np, int is) {
-        std::vector<CT> groups(num_partition / np);
+    // shard_groups (multi-GPU, lengths with a single batch): this rank evaluates the giant-step groups j = rank mod world
+    // only and the partial sums are combined by AllReduceSum - the groups are independent (src/sort_algo.h:349-362)
+    CT vecRotsOpt(const std::vector<CT> &preRotatedArrays, int num_partition, int num_slots, int np, int is, bool shard_groups = false) {
+        std::vector<CT> groups;
         // every mask is the N-wide block of ones moved somewhere else: encode the block once, then each mask is a Galois
         // permutation of that encoding (RotatePlaintext) instead of a 65536-point FFT and one NTT per limb
         auto block0 = m_cc->MakeCKKSPackedPlaintext(generateMaskVector(num_slots, 0), 1, 0, nullptr, num_slots);
         for (int j = 0; j < num_partition / np; j++) {
+            if (shard_groups && j % m_world != m_rank) continue;
             const int giant = is * num_partition + j * np;
             CT T;
             for (int i = 0; i < np; i++) {
@@ -236,10 +239,14 @@ template <int N> class DirectSort : public SortBase<N> {
                 auto pmsk = m_cc->RotatePlaintext(block0, -((np * j + i) * N + giant));
                 m_cc->EvalMultAddInPlace(T, preRotatedArrays[i], pmsk);
             }
-            groups[j] = rot.rotate(T, giant);
+            groups.push_back(rot.rotate(T, giant));
         }
-        return m_cc->EvalAddMany(groups);
+        CT sum = groups.size() == 1 ? groups[0] : m_cc->EvalAddMany(groups);
+        if (shard_groups) m_cc->AllReduceSum(sum);
+        return sum;
     }
+    // single-batch lengths are sharded over the giant-step groups when every rank gets the same number of them
+    bool groupSharded(int B, int groups) const { return m_world > 1 && !sharded(B) && groups >= m_world && groups % m_world == 0; }
 
     // rank_i = #{ j : a_j < a_i } + 1/2 - 1/2  (all-pairs comparison, SIMD over P shifted copies, B batches)
     CT constructRank(const CT &input_array, SignFunc SignFunc, SignConfig &Cfg) {
@@ -251,7 +258,7 @@ template <int N> class DirectSort : public SortBase<N> {
             for (int b = 0; b < sh.B; b++) {
                 if (!mine(b, sh.B)) continue;
                 streams.next();
-                CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b);
+                CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b, groupSharded(sh.B, sh.P / sh.np_rank));
                 CT dup = input_array->Clone();
                 dup->SetSlots(sh.S);
                 parts.push_back(comp.compare(m_cc, dup, shifted, SignFunc, Cfg));
@@ -267,10 +274,11 @@ template <int N> class DirectSort : public SortBase<N> {
 
     // masked_inputs[j] = (one-hot mask * input) rotated left by j.  Copy c of the one-hot mask selects the elements whose
     // rank says "move left by ib*P + c"; group i collects copies np*i .. np*i+np-1 and rotates them by ib*P + i*np.
-    CT blindRotationOptN(const std::vector<CT> &masked_inputs, int num_slots, int np, int ib, int num_partition) {
+    CT blindRotationOptN(const std::vector<CT> &masked_inputs, int num_slots, int np, int ib, int num_partition, bool shard_groups = false) {
         CT result;
         auto block0 = m_cc->MakeCKKSPackedPlaintext(generateMaskVectorN(num_slots, 0), 1, masked_inputs[0]->GetLevel(), nullptr, num_slots);
         for (int i = 0; i < (num_slots / N) / np; i++) {
+            if (shard_groups && i % m_world != m_rank) continue; // independent groups (src/sort_algo.h:561-584)
             CT tmp;
             for (int j = 0; j < np; j++) {
                 // = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j), see vecRotsOpt
@@ -281,6 +289,7 @@ template <int N> class DirectSort : public SortBase<N> {
             if (result) m_cc->EvalAddInPlace(result, tmp);
             else result = tmp;
         }
+        if (shard_groups) m_cc->AllReduceSum(result);
         return result;
     }
 
@@ -306,7 +315,7 @@ template <int N> class DirectSort : public SortBase<N> {
             r = m_cc->EvalChebyshevSeriesPS(r, coeffs, -1, 1);
             CT masked = m_cc->EvalMult(r, input_array);
             std::vector<CT> masked_inputs = babySteps(masked, sh.np_idx, sh.S);
-            parts.push_back(blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P));
+            parts.push_back(blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P, groupSharded(sh.B, (sh.S / N) / sh.np_idx)));
         }
         }
         CT output = parts.size() == 1 ? parts[0] : m_cc->EvalAddMany(parts);

@@ -500,6 +500,26 @@ int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_a
     })
 }
 
+// the same with the engine's own NCCL communicator (fheb200_comm_unique_id / fheb200_ctx_comm_init): no callback, no host
+// synchronisation around the all-reduce
+int fhesort_session_comm_init(fhesort_session *s, const unsigned char *id128, int rank, int world) {
+    GUARD({
+        if (!s) throw std::invalid_argument("null argument: session");
+        if (world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("comm_init: bad rank / world");
+        if (world > 1 && !id128) throw std::invalid_argument("comm_init: the 128-byte NCCL id is required when world > 1");
+        if (world > 1 && !s->s->seeded)
+            throw std::invalid_argument("comm_init: sharding needs replicated keys - create the session on every rank with the same "
+                                        "non-zero seed (the sessions of this library have no key-exchange step)");
+#ifdef REFERENCE_DRIVERS
+        if (world > 1) throw std::runtime_error("the reference's drivers have no multi-GPU sharding");
+#else
+        s->s->cc->CommInit(id128, rank, world);
+        s->s->cc->allReduceWords = nullptr;
+        s->s->shard(rank, world);
+#endif
+    })
+}
+
 int fhesort_session_set_streams(fhesort_session *s, int k) {
     GUARD({
         if (!s) throw std::invalid_argument("null argument: session");

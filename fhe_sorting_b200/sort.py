@@ -70,8 +70,25 @@ class DirectSortSession:
         """Concurrent CUDA streams over the independent batches of a phase (default 4)."""
         _ck(self.L.fhesort_session_set_streams(self.h, int(k)), self.L)
 
-    def set_shard(self, rank, world):
-        """Shard the sort's batches over `world` ranks of an initialised torch.distributed NCCL group (one GPU each)."""
+    def set_shard(self, rank, world, native=True):
+        """Shard the sort's batches over `world` ranks of an initialised torch.distributed group (one GPU each).
+        native=True: the engine opens its own NCCL communicator (the 128-byte id of rank 0 travels through
+        torch.distributed.broadcast_object_list) and all-reduces on its own stream; native=False: torch's all_reduce
+        through a callback (round-1 path, kept for comparison)."""
+        if world > 1 and native:
+            import torch.distributed as dist
+            from .lib import load
+            ident = [None]
+            if rank == 0:
+                buf = (C.c_ubyte * 128)()
+                E = load()
+                if E.fheb200_comm_unique_id(buf) != 0:
+                    raise FheError(E.fheb200_last_error().decode())
+                ident = [bytes(buf)]
+            dist.broadcast_object_list(ident, src=0)
+            _ck(self.L.fhesort_session_comm_init(self.h, (C.c_ubyte * 128)(*ident[0]), rank, world), self.L)
+            self._cb = None
+            return
         if world <= 1:
             _ck(self.L.fhesort_session_set_shard(self.h, 0, 1, None, None), self.L)
             self._cb = None

@@ -181,6 +181,16 @@ int fheb200_bootstrap_plan_apply(int ring_dim, int slots, int budget_enc, int bu
 /* ---- multi-GPU combine of partial ciphertexts: the device buffer [2][limbs][n] of a ciphertext, to be
  * summed element-wise across ranks as 64-bit integers (NCCL all-reduce; <= 16 summands of < 2^60 cannot wrap), then
  * brought back to [0, q_limb) by fheb200_ct_reduce_partial_sums.  The caller orders the streams (fheb200_ctx_sync). */
+/* The engine's own NCCL communicator (multi-GPU extension, no OpenFHE counterpart; SURVEY.md 8e: partial rank / output
+ * ciphertexts of a sharded sort, reference batches src/sort_algo.h:475-491, 713-742).  Rank 0 draws a 128-byte id and gives
+ * it to the other ranks by any means; every rank then calls comm_init (world <= 16).  all_reduce_sum replaces the ciphertext
+ * by the sum over all ranks, limb by limb modulo its modulus, on the engine's stream (ncclAllReduce + fix-up kernel; no host
+ * synchronisation).  NCCL is loaded with dlopen on first use. */
+int fheb200_comm_unique_id(unsigned char *id128);
+int fheb200_ctx_comm_init(fheb200_ctx *ctx, const unsigned char *id128, int rank, int world);
+int fheb200_ctx_comm_destroy(fheb200_ctx *ctx);
+int fheb200_ctx_comm_info(fheb200_ctx *ctx, int *rank, int *world, int *nccl_version);
+int fheb200_ct_all_reduce_sum(fheb200_ctx *ctx, fheb200_ct *ct);
 int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words);
 int fheb200_ct_reduce_partial_sums(fheb200_ctx *ctx, fheb200_ct *ct);
 

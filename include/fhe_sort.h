@@ -48,6 +48,8 @@ int fhesort_run(fhesort_session *s, int stage, const double *input, const double
  * all-reduce, SUM, int64) and return 0 after the result is visible to other streams. */
 typedef int (*fhesort_allreduce_fn)(void *user, void *device_ptr, size_t words);
 int fhesort_session_set_shard(fhesort_session *s, int rank, int world, fhesort_allreduce_fn fn, void *user);
+/* Sharding over the engine's own NCCL communicator: id128 = fheb200_comm_unique_id() of rank 0, handed to every rank */
+int fhesort_session_comm_init(fhesort_session *s, const unsigned char *id128, int rank, int world);
 /* Concurrent CUDA streams over the batches this process evaluates (default 4, or FHESORT_STREAMS; 1 = one stream). */
 int fhesort_session_set_streams(fhesort_session *s, int k);
 /* RotationComposer<N>::rotate (src/rotation.h:215-233) */
