@@ -34,7 +34,40 @@ typedef __int128 i128;
 static int g_threads = 1;
 
 /* ------------------------------------------------------------------ modular arithmetic */
-static inline u64 mulmod(u64 a, u64 b, u64 q) { return (u64)((u128)a * b % q); }
+/* a*b mod q.  With reduced operands the 128-bit product has a high word below q, so one hardware 128/64 division gives
+ * the remainder (x86-64 divq); any other case goes through the compiler's 128-bit remainder.  Hot loops with a constant
+ * factor (NTT butterflies) use the Shoup form below instead, as OpenFHE's native backend does (ModMulFastConst). */
+static inline u64 mulmod(u64 a, u64 b, u64 q) {
+    u128 z = (u128)a * b;
+#if defined(__x86_64__)
+    u64 hi = (u64)(z >> 64), lo = (u64)z;
+    if (hi < q) {
+        u64 quo, rem;
+        __asm__("divq %4" : "=a"(quo), "=d"(rem) : "a"(lo), "d"(hi), "r"(q) : "cc");
+        (void)quo;
+        return rem;
+    }
+#endif
+    return (u64)(z % q);
+}
+/* 128-bit value mod q (lazy sums of products are reduced once) */
+static inline u64 reduce128(u128 z, u64 q) {
+#if defined(__x86_64__)
+    u64 hi = (u64)(z >> 64) % q, lo = (u64)z, quo, rem;
+    __asm__("divq %4" : "=a"(quo), "=d"(rem) : "a"(lo), "d"(hi), "r"(q) : "cc");
+    (void)quo;
+    return rem;
+#else
+    return (u64)(z % q);
+#endif
+}
+/* Shoup multiplication by a constant w < q with ws = floor(w 2^64 / q): exact result in [0, q) for any a < 2^64 */
+static inline u64 shoup_of(u64 w, u64 q) { return (u64)(((u128)w << 64) / q); }
+static inline u64 mulmod_shoup(u64 a, u64 w, u64 ws, u64 q) {
+    u64 h = (u64)(((u128)a * ws) >> 64);
+    u64 r = a * w - h * q;
+    return r >= q ? r - q : r;
+}
 static inline u64 addmod(u64 a, u64 b, u64 q) {
     u64 s = a + b;
     return s >= q ? s - q : s;
@@ -119,6 +152,8 @@ static u64 min_primitive_root(u64 m, u64 q) {
 struct ModTables {
     u64 q, psi, psi_inv, n_inv;
     std::vector<u64> psi_br, psi_inv_br; /* psi^bitrev(i), psi^-bitrev(i) */
+    std::vector<u64> psi_br_s, psi_inv_br_s; /* their Shoup companions */
+    u64 n_inv_s;
 };
 struct LevelTables { /* per ell: partial-digit base-conversion constants */
     int beta;
@@ -146,11 +181,16 @@ static void build_mod(ModTables &t, u64 q, int logn) {
     t.n_inv = invmod((u64)n, q);
     t.psi_br.resize(n);
     t.psi_inv_br.resize(n);
+    t.psi_br_s.resize(n);
+    t.psi_inv_br_s.resize(n);
+    t.n_inv_s = shoup_of(t.n_inv, q);
     u64 p = 1, pi = 1;
     for (int i = 0; i < n; i++) {
         uint32_t r = bitrev((uint32_t)i, logn);
         t.psi_br[r] = p;
         t.psi_inv_br[r] = pi;
+        t.psi_br_s[r] = shoup_of(p, q);
+        t.psi_inv_br_s[r] = shoup_of(pi, q);
         p = mulmod(p, t.psi, q);
         pi = mulmod(pi, t.psi_inv, q);
     }
@@ -287,10 +327,10 @@ extern "C" void orc_ntt_fwd(const orc_ctx *c, int idx, u64 *a) {
     for (int m = 1; m < n; m <<= 1) {
         t >>= 1;
         for (int i = 0; i < m; i++) {
-            u64 w = T.psi_br[m + i];
+            const u64 w = T.psi_br[m + i], ws = T.psi_br_s[m + i];
             int j1 = 2 * i * t;
             for (int j = j1; j < j1 + t; j++) {
-                u64 u = a[j], v = mulmod(a[j + t], w, q);
+                u64 u = a[j], v = mulmod_shoup(a[j + t], w, ws, q);
                 a[j] = addmod(u, v, q);
                 a[j + t] = submod(u, v, q);
             }
@@ -305,17 +345,17 @@ extern "C" void orc_ntt_inv(const orc_ctx *c, int idx, u64 *a) {
     for (int m = n; m > 1; m >>= 1) {
         int h = m >> 1, j1 = 0;
         for (int i = 0; i < h; i++) {
-            u64 w = T.psi_inv_br[h + i];
+            const u64 w = T.psi_inv_br[h + i], ws = T.psi_inv_br_s[h + i];
             for (int j = j1; j < j1 + t; j++) {
                 u64 u = a[j], v = a[j + t];
                 a[j] = addmod(u, v, q);
-                a[j + t] = mulmod(submod(u, v, q), w, q);
+                a[j + t] = mulmod_shoup(submod(u, v, q), w, ws, q);
             }
             j1 += 2 * t;
         }
         t <<= 1;
     }
-    for (int j = 0; j < n; j++) a[j] = mulmod(a[j], T.n_inv, q);
+    for (int j = 0; j < n; j++) a[j] = mulmod_shoup(a[j], T.n_inv, T.n_inv_s, q);
 }
 
 /* ------------------------------------------------------------------ automorphisms */
@@ -513,9 +553,9 @@ extern "C" void orc_modup(const orc_ctx *c, int ell, const u64 *cin, u64 *digits
         int s = T.dstart[j], d = T.dsize[j];
         u64 *D = digits + (size_t)j * W * n;
         std::vector<u64> x((size_t)d * n);
-        for (int i = 0; i < d; i++) {
-            u64 qi = c->mods[s + i].q;
-            for (int k = 0; k < n; k++) x[(size_t)i * n + k] = mulmod(coef[(size_t)(s + i) * n + k], T.hat_inv[j][i], qi);
+        PAR_LIMBS for (int i = 0; i < d; i++) {
+            const u64 qi = c->mods[s + i].q, h = T.hat_inv[j][i], hs = shoup_of(h, qi);
+            for (int k = 0; k < n; k++) x[(size_t)i * n + k] = mulmod_shoup(coef[(size_t)(s + i) * n + k], h, hs, qi);
         }
         PAR_LIMBS for (int t = 0; t < W; t++) {
             u64 *dst = D + (size_t)t * n;
@@ -525,10 +565,12 @@ extern "C" void orc_modup(const orc_ctx *c, int ell, const u64 *cin, u64 *digits
             }
             int qp = qp_of(c, ell, t);
             u64 mt = c->mods[qp].q;
+            /* sum_i x_i * hat_i accumulated in 128 bits (d <= 16 terms below 2^120) and reduced once: the same residue
+             * as reducing every term */
             for (int k = 0; k < n; k++) {
-                u64 acc = 0;
-                for (int i = 0; i < d; i++) acc = addmod(acc, mulmod(x[(size_t)i * n + k] % mt, T.hat[j][i][t], mt), mt);
-                dst[k] = acc;
+                u128 acc = 0;
+                for (int i = 0; i < d; i++) acc += (u128)x[(size_t)i * n + k] * T.hat[j][i][t];
+                dst[k] = reduce128(acc, mt);
             }
             orc_ntt_fwd(c, qp, dst);
         }
@@ -542,16 +584,16 @@ extern "C" void orc_inner_product(const orc_ctx *c, int ell, const u64 *digits, 
         int qp = qp_of(c, ell, t);
         u64 q = c->mods[qp].q;
         for (int k = 0; k < n; k++) {
-            u64 s0 = 0, s1 = 0;
+            u128 s0 = 0, s1 = 0; /* beta <= 8 products below 2^122 */
             for (int j = 0; j < beta; j++) {
                 u64 d = digits[((size_t)j * W + t) * n + k];
                 const u64 *kb = evk + (((size_t)j * 2 + 0) * F + qp) * n;
                 const u64 *ka = evk + (((size_t)j * 2 + 1) * F + qp) * n;
-                s0 = addmod(s0, mulmod(d, kb[k], q), q);
-                s1 = addmod(s1, mulmod(d, ka[k], q), q);
+                s0 += (u128)d * kb[k];
+                s1 += (u128)d * ka[k];
             }
-            acc0[(size_t)t * n + k] = s0;
-            acc1[(size_t)t * n + k] = s1;
+            acc0[(size_t)t * n + k] = reduce128(s0, q);
+            acc1[(size_t)t * n + k] = reduce128(s1, q);
         }
     }
 }
@@ -571,9 +613,9 @@ extern "C" void orc_moddown(const orc_ctx *c, int ell, const u64 *acc, u64 *out)
         u64 q = c->mods[i].q;
         std::vector<u64> t(n);
         for (int j = 0; j < n; j++) {
-            u64 s = 0;
-            for (int k = 0; k < K; k++) s = addmod(s, mulmod(x[(size_t)k * n + j] % q, T.p_hat[k][i], q), q);
-            t[j] = s;
+            u128 s = 0;
+            for (int k = 0; k < K; k++) s += (u128)x[(size_t)k * n + j] * T.p_hat[k][i];
+            t[j] = reduce128(s, q);
         }
         orc_ntt_fwd(c, i, t.data());
         for (int j = 0; j < n; j++) out[(size_t)i * n + j] = mulmod(submod(acc[(size_t)i * n + j], t[j], q), T.p_inv[i], q);
