@@ -179,7 +179,15 @@ def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)
     B = N / P independent batches of both phases are sharded over the ranks (N = 1024: 16 batches) and partial
     ciphertexts combined by NCCL all-reduce; lengths with a single batch run replicated."""
     import torch
+    import fhe_sorting_b200 as F
     from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input, shard_batches
+    peak, _ = peaks()
+
+    def roof(bytes_per_sort, seconds):
+        """sort-level roofline: algorithmic bytes of every scheme operation of one sort on THIS rank (operands
+        read once, results written once) / run time / measured HBM peak"""
+        gbs = bytes_per_sort / seconds / 1e9
+        return {"algo_bytes_per_rank": bytes_per_sort, "gbs": gbs, "frac": gbs / peak}
     out = {}
     for n in sizes:
         s = DirectSortSession(n, 17, seed=SEED + n, device=local_rank)
@@ -189,15 +197,19 @@ def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)
         runs = []
         for _ in range(3):
             barrier()
+            b0 = F.algo_bytes()
             t0 = time.perf_counter()
             res, _, level = s.sort(x)
             dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+            nbytes = F.algo_bytes() - b0
             if dist is not None:
                 dist.all_reduce(dt, op=dist.ReduceOp.MAX)
             runs.append(float(dt.item()))
         out[str(n)] = {"seconds": sorted(runs)[1], "runs": runs, "max_abs_err": float(np.abs(res - np.sort(x)).max()),
                        "final_level": level, "mult_depth": s.mult_depth, "rotation_keys": s.num_rotation_keys,
-                       "sharded_over_ranks": shard_batches(n, rank, world)[1]}
+                       "sharded_over_ranks": shard_batches(n, rank, world)[1] or (world > 1 and n <= 256),
+                       "sharding": ("batches" if shard_batches(n, rank, world)[1] else "giant-step groups" if world > 1 else "none"),
+                       "roofline": roof(nbytes, sorted(runs)[1])}
         s.close()
     # MEHP24 ranking sort, N = 256 (BASELINE.json config 4; tests/mehp24/Mehp24SortTest.cpp): one 65536-slot ciphertext,
     # strictly sequential -> every rank runs the same sort ("replicas only"), the slowest is reported
@@ -264,6 +276,98 @@ def bootstrap_latency(device):
     err = float(np.abs(ctx.decrypt(keys, o, 1024) - z).max())
     return {"ms": ms, "max_abs_err": err, "levels_consumed": ctx.bootstrap_depth(1024), "output_level": o.level,
             "key_bytes_resident": ctx.key_bytes()}
+
+
+def microbench(ctx, keys, ct, device):
+    """BASELINE.json config 2: EvalRotate / EvalFastRotation (k = 1..14, benchmarks/RotationBenchmark.cpp:78-125), HMult+relin,
+    rescale, EvalAdd and EvalChebyshevSeriesPS (degree 126 / 1662 / 6510: the doubled-sinc tables of N = 16 / 256 / 1024) across
+    levels l in {L, 3L/4, L/2, L/4, 2} at the DirectSort N = 1024 parameter set, compositeSign<3>(dg, 2) (tests/SignTest.cpp:41-70)
+    on a 65536-slot ciphertext, and the literal RotationBenchmark parameters (ring 2^12, depth 1, scale 50) next to the only
+    rotation numbers the reference publishes.  GB/s = SURVEY.md 8d algorithmic bytes / time; device time (CUDA events) for the
+    rotations, host clock around a synchronised loop for the rest."""
+    import fhe_sorting_b200 as F
+    peak, _ = peaks()
+    n, L, K, alpha = ctx.n, ctx.L, ctx.K, ctx.alpha
+    rng = np.random.default_rng(7)
+
+    def host_ms(fn, reps):
+        fn()
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        ctx.sync()
+        return (time.perf_counter() - t0) / reps * 1e3
+
+    def entry(ms, nbytes):
+        return {"ms": ms, "gbs": nbytes / (ms * 1e-3) / 1e9, "frac": nbytes / (ms * 1e-3) / 1e9 / peak}
+
+    out = {"levels": {}, "fast_rotations": {}, "chebyshev_ps": {}}
+    cur = ct
+    for ell in sorted({L, 3 * L // 4, L // 2, L // 4, 2}, reverse=True):
+        while cur.limbs > ell:
+            if cur.info()["nsd"] == 1:
+                cur = ctx.mult(cur, 1.0)
+            cur = ctx.rescale(cur)
+        beta = (ell + alpha - 1) // alpha
+        ks = 8.0 * n * (4 * ell + 2 * beta * (ell + K))
+        lv = {"beta": beta}
+        ctx.bench_rotations(cur, INDICES[:4], 2)
+        lv["rotate"] = entry(ctx.bench_rotations(cur, INDICES[:4], 5) / 20, ks)
+        lv["rotate"]["rotations_per_s"] = 1e3 / lv["rotate"]["ms"]
+        one = cur if cur.info()["nsd"] == 1 else ctx.rescale(cur)
+        if one.limbs >= 2:
+            le = one.limbs
+            be = (le + alpha - 1) // alpha
+            lv["mult_relin"] = entry(host_ms(lambda: ctx.mult(one, one), 10), 8.0 * n * (6 * le + 2 * be * (le + K)))
+            prod = ctx.mult(one, one)
+            lv["rescale"] = entry(host_ms(lambda: ctx.rescale(prod), 10), 8.0 * n * (2 * le + 2 * (le - 1)))
+            lv["add"] = entry(host_ms(lambda: ctx.add(one, one), 20), 8.0 * n * 6 * le)
+        out["levels"][str(ell)] = lv
+        if ell in (L, L // 2):
+            fr = {}
+            for k in range(1, 15):
+                idx = INDICES[:k]
+                ctx.bench_rotations(cur, idx, 1, hoisted=True)
+                fr[str(k)] = {"fast_ms": ctx.bench_rotations(cur, idx, 3, hoisted=True) / 3,
+                              "plain_ms": ctx.bench_rotations(cur, idx, 3) / 3}
+            out["fast_rotations"][str(ell)] = fr
+        for deg in (126, 1662, 6510):
+            depth = int(np.ceil(np.log2(deg + 1))) + 1
+            if ell in (L, L // 2) and cur.limbs > depth + 1:
+                coeffs = rng.uniform(-1, 1, deg + 1) / np.arange(1, deg + 2)
+                b0 = F.algo_bytes()
+                ctx.chebyshev(cur, coeffs, -1.0, 1.0)
+                nbytes = F.algo_bytes() - b0
+                e = entry(host_ms(lambda: ctx.chebyshev(cur, coeffs, -1.0, 1.0), 3), nbytes)
+                out["chebyshev_ps"].setdefault(str(ell), {})[str(deg)] = e
+    # compositeSign<3>(dg, df = 2) through the C++ sign() of host/sign.cpp, 65536 slots, fresh ciphertext of the same chain
+    from fhe_sorting_b200.sort import ToolkitSession
+    sess = ToolkitSession(LOGN, DEPTH, SCALE_BITS, 65536, seed=SEED + 3, device=device)
+    x = rng.uniform(-1, 1, 65536)
+    x[np.abs(x) < 0.02] = 0.5
+    sign = {}
+    for dg in (2, 4, 5):
+        sess.sign("CompositeSign", x, 3, dg, 2)
+        vals, level, ms = sess.sign("CompositeSign", x, 3, dg, 2)
+        sign["3_%d_2" % dg] = {"ms": ms, "levels": level, "max_abs_err": float(np.abs(vals - np.sign(x)).max())}
+    sess.close()
+    out["composite_sign"] = sign
+    # the literal parameters of benchmarks/RotationBenchmark.cpp:62-76 (ring 2^12 under HEStd_NotSet, depth 1, scale 50)
+    small = F.Context(12, 1, 50, 60, batch=8, device=device)
+    sk = small.keygen(SEED)
+    small.eval_rotate_keygen(sk, list(range(1, 15)))
+    sc = small.encrypt(sk, small.make_plaintext(np.arange(8.0), 1, 0, 8))
+    lit = {"reference_published_ms": {"BM_Rotations/1": 4.94, "BM_Rotations/14": 74.5, "BM_FastRotations/1": 4.91,
+                                      "BM_FastRotations/14": 49.6, "hardware": "8 x 2488 MHz laptop CPU, OpenFHE"}}
+    for k in (1, 14):
+        idx = list(range(1, k + 1))
+        small.bench_rotations(sc, idx, 3)
+        lit["BM_Rotations/%d_ms" % k] = small.bench_rotations(sc, idx, 20) / 20
+        small.bench_rotations(sc, idx, 3, hoisted=True)
+        lit["BM_FastRotations/%d_ms" % k] = small.bench_rotations(sc, idx, 20, hoisted=True) / 20
+    out["rotation_benchmark_ring_2^12"] = lit
+    return out
 
 
 def run_ours(args, rank, world, local_rank):
@@ -353,6 +457,7 @@ def run_ours(args, rank, world, local_rank):
         if dist is not None:
             dist.destroy_process_group()
         return
+    micro = None if args.skip_micro else microbench(ctx, keys, ct, local_rank)
 
     # ---- per-kernel roofline (isolated kernels, CUDA events inside the library, inputs > L2)
     peak, peak_src = peaks()
@@ -371,17 +476,23 @@ def run_ours(args, rank, world, local_rank):
     top = max(kernels, key=lambda k: kernels[k]["share_of_rotate"])
     rot_ms = ms / (ROT_PER_STEP * args.steps)
     ab = algo_bytes_rotate(n, ell, K, alpha)
-    traffic, traffic_src = None, None
+    traffic, traffic_src, tj_pipe = None, None, None
     try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", "ncu_traffic.json")))
+        prof = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles")
+        tj = json.load(open(os.path.join(prof, "r02" if os.path.exists(os.path.join(prof, "r02", "ncu_traffic.json")) else "r01",
+                                         "ncu_traffic.json")))
         t = tj.get(top, {})
         traffic = t.get("dram_bytes_per_launch", t.get("dram_bytes_per_limb", 0) * ell) or None
         traffic_src = tj["source"] + "; " + t.get("note", "")
+        tj_pipe = t.get("pipe")  # ncu: FP64 / issue / occupancy of the dominant kernel (north star: pipe utilisation for the NTT)
     except (OSError, ValueError, KeyError):
         pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": kernels[top]["gbs"], "peak": peak, "unit": "GB/s",
                 "frac": kernels[top]["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src,
+                "pipe": tj_pipe,
+                "isolated_kernels": "CUDA events around 20 launches; the NTTs cycle over six disjoint 41-limb regions (258 MB > L2), "
+                                    "the other kernels stream > 150 MB per launch",
                 "kernels": kernels,
                 "whole_rotate": {"algo_bytes": ab, "ms": rot_ms, "gbs": ab / (rot_ms * 1e-3) / 1e9,
                                  "frac": ab / (rot_ms * 1e-3) / 1e9 / peak}}
@@ -399,9 +510,13 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": limb_bytes, "d2h_bytes_per_step": limb_bytes},
         "roofline": roofline,
         "sort_latency": sort_latency,
+        "microbench": micro,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "3 EvalRotate of the same ciphertext at the full parameter set (41 limbs)",
-                         "bit_exact_vs_gpu": parity},
+                         "bit_exact_vs_gpu": parity,
+                         "note": "oracle port of the published algorithm (Shoup NTT, lazy 128-bit base conversion, OpenMP over limbs), "
+                                 "NOT OpenFHE: OpenFHE is absent from this image; the oracle has no scheme layer, so no CPU sort "
+                                 "latency can be reported beside sort_latency"},
     }
     emit(out)
     if dist is not None:
@@ -415,6 +530,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skip-sort", action="store_true", help="leave out the DirectSort latencies (profiling runs)")
+    ap.add_argument("--skip-micro", action="store_true", help="leave out the config-2 microbench across levels")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -50,6 +50,7 @@ static void h2d(Context &C, void *dst, const void *src, size_t bytes) {
 extern "C" {
 
 unsigned long long fheb200_launch_count(void) { return g_launches.load(); }
+unsigned long long fheb200_algo_bytes(void) { return g_algo_bytes.load(); }
 
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words) {
     GUARD({
@@ -421,9 +422,16 @@ int fheb200_bench_kernel(fheb200_ctx *ctx, const char *name, int ell, int reps, 
             FHE_CUDA(cudaMemcpyAsync(lc_tab->p, blob.data(), blob.size() * 8, cudaMemcpyHostToDevice, C.stream));
             FHE_CUDA(cudaStreamSynchronize(C.stream));
         }
+        // the NTTs walk over six disjoint regions of ell limbs (6 x 43 MB at 41 limbs: more than the 126 MB L2), so that no
+        // launch finds its input in L2 from the launch before
+        int iter = 0;
+        auto region = [&]() {
+            const int r = iter++ % 6;
+            return (r < 3 ? a->p : b->p) + (size_t)(r % 3) * D.width * n;
+        };
         auto run = [&]() {
-            if (k == "ntt_fwd") { k_ntt_fwd(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
-            else if (k == "ntt_inv") { k_ntt_inv(C.T, a->p, D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
+            if (k == "ntt_fwd") { k_ntt_fwd(C.T, region(), D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
+            else if (k == "ntt_inv") { k_ntt_inv(C.T, region(), D.desc_q, ell, C.stream); bytes = 2.0 * ell * limb; }
             else if (k == "inner_product") { k_inner_product(C.T, D, a->p, C.evk_mult, b->p, C.stream); bytes = (3.0 * D.beta + 2.0) * D.width * limb; }
             else if (k == "modup_conv_scalar") { k_modup(C.T, D, b->p, b->p, a->p, C.stream); bytes = (double)(ell + D.beta * D.width) * limb; }
             else if (k == "moddown_conv_scalar") { k_moddown_conv(C.T, D, b->p, a->p, C.stream); bytes = 2.0 * (D.K + ell) * limb; }

@@ -80,6 +80,7 @@ Ct Context::add(const Ct &a0, const Ct &b0) {
     r->mem = alloc((size_t)2 * a->ell * n);
     r->slots = std::max(a->slots, b->slots);
     for (int p = 0; p < 2; p++) k_binary(T, OP_ADD, a->ell, a->poly(p, n), b->poly(p, n), r->poly(p, n), stream);
+    count_algo(8.0 * n * 6.0 * a->ell);
     return r;
 }
 Ct Context::sub(const Ct &a0, const Ct &b0) {
@@ -92,6 +93,7 @@ Ct Context::sub(const Ct &a0, const Ct &b0) {
     r->mem = alloc((size_t)2 * a->ell * n);
     r->slots = std::max(a->slots, b->slots);
     for (int p = 0; p < 2; p++) k_binary(T, OP_SUB, a->ell, a->poly(p, n), b->poly(p, n), r->poly(p, n), stream);
+    count_algo(8.0 * n * 6.0 * a->ell);
     return r;
 }
 Ct Context::add_many(const std::vector<Ct> &v) {
@@ -138,6 +140,7 @@ Ct Context::mult_pt(const Ct &a0, const Pt &p) {
     r->mem = alloc((size_t)2 * a->ell * n);
     r->slots = std::max(a->slots, p->slots);
     k_mul_pt(T, a->ell, a->poly(0, n), a->poly(1, n), enc->p, r->poly(0, n), r->poly(1, n), 0, stream);
+    count_algo(8.0 * n * 5.0 * a->ell);
     r->nsd = a->nsd + 1;
     r->scale = a->scale * ps;
     return r;
@@ -161,6 +164,7 @@ Ct Context::mult_pt_add(const Ct &acc, const Ct &a0, const Pt &p) {
             r->reduced_cache.reset();
             r->slots = std::max(std::max(acc->slots, a->slots), p->slots);
             k_mul_pt(T, a->ell, a->poly(0, n), a->poly(1, n), enc->p, r->poly(0, n), r->poly(1, n), 1, stream);
+            count_algo(8.0 * n * 7.0 * a->ell);
             return r;
         }
     }
@@ -182,6 +186,7 @@ Ct Context::mult_lazy(const Ct &a0, const Ct &b0) {
     r->mem = alloc((size_t)3 * ell * n);
     r->slots = std::max(a->slots, b->slots);
     k_tensor(T, ell, a->poly(0, n), a->poly(1, n), b->poly(0, n), b->poly(1, n), r->poly(0, n), r->poly(1, n), r->poly(2, n), stream);
+    count_algo(8.0 * n * 7.0 * ell); // tensor: 4 polynomials in, 3 out
     r->nsd = a->nsd + b->nsd;
     r->scale = a->scale * b->scale;
     return r;
@@ -200,6 +205,7 @@ Ct Context::relinearize(const Ct &a) {
     r->npoly = 2;
     r->mem = alloc((size_t)2 * ell * n);
     keyswitch_digits(ell, digits->p, evk_mult, a->poly(0, n), a->poly(1, n), r->poly(0, n), r->poly(1, n), 1u);
+    count_algo(8.0 * n * (5.0 * ell + 2.0 * D.beta * D.width)); // 3 polynomials in, the evk stream, 2 out
     return r;
 }
 Ct Context::add_lazy(const Ct &a0, const Ct &b0) {

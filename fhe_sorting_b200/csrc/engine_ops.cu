@@ -84,6 +84,7 @@ Ct Context::rotate(const Ct &a, int index) {
     const DevicePlan &D = plan(ell);
     Mem digits = alloc((size_t)D.beta * D.width * n);
     modup(ell, a->poly(1, n), digits->p);
+    count_algo(8.0 * n * (4.0 * ell + 2.0 * D.beta * D.width));
     Ct r = new_like(this, a, 2, ell);
     keyswitch_digits(ell, digits->p, it->second, a->poly(0, n), nullptr, r->poly(0, n), r->poly(1, n), g);
     return r;
@@ -106,6 +107,10 @@ Ct Context::fast_rotation(const Ct &a, int index, const std::shared_ptr<Precomp>
     auto it = evk_rot.find(g);
     if (it == evk_rot.end()) throw std::runtime_error("EvalFastRotation: no evaluation key for rotation index " + std::to_string(index));
     const int n = P->n;
+    {
+        const DevicePlan &D = plan(a->ell);
+        count_algo(8.0 * n * (4.0 * a->ell + 2.0 * D.beta * D.width));
+    }
     Ct r = new_like(this, a, 2, a->ell);
     keyswitch_digits(a->ell, pre->digits->p, it->second, a->poly(0, n), nullptr, r->poly(0, n), r->poly(1, n), g);
     return r;
@@ -133,6 +138,7 @@ Ct Context::mod_reduce(const Ct &a) {
     LOCK;
     if (a->ell < 2) throw std::runtime_error("rescale: no limbs left (multiplicative depth exhausted)");
     Ct r = new_like(this, a, a->npoly, a->ell - 1);
+    count_algo(8.0 * P->n * a->npoly * (2.0 * a->ell - 1.0));
     rescale_poly(a->ell, a->npoly, a->mem->p, r->mem->p);
     r->nsd = a->nsd - 1;
     r->scale = a->scale / (double)P->moduli[a->ell - 1];
@@ -169,6 +175,7 @@ Ct Context::mult_core_const(const Ct &a, double c) { // EvalMultCoreInPlace: tim
     LimbScalars s = scalars_for((long double)c * (long double)sfl, a->ell, true);
     Ct r = new_like(this, a, a->npoly, a->ell);
     for (int p = 0; p < a->npoly; p++) k_mul_scalar(T, a->ell, a->poly(p, n), s, r->poly(p, n), stream);
+    count_algo(8.0 * n * a->npoly * 2.0 * a->ell);
     r->nsd = a->nsd + 1;
     r->scale = a->scale * sfl;
     return r;
@@ -191,6 +198,7 @@ std::vector<Ct> Context::lincomb(const std::vector<Ct> &in, const std::vector<st
     // FHEB200_LINCOMB=6: the sums on the integer tensor cores, 8 outputs per pass over the inputs (baseconv.cu: lc_tc)
     static const bool tc = [] { const char *e = getenv("FHEB200_LINCOMB"); return e ? atoi(e) == 6 : true; }();
     const bool use_tc = tc && count >= 8;
+    count_algo(8.0 * n * npoly * ell * ((double)count + (double)live.size()));
     const size_t per_pass = use_tc ? 8 : 4;
     for (size_t g0 = 0; g0 < live.size(); g0 += per_pass) {
         const int G = (int)std::min<size_t>(per_pass, live.size() - g0);

@@ -9,6 +9,12 @@
 namespace fheb200 {
 
 extern std::atomic<unsigned long long> g_launches; // kernels launched by this library (bench.py gpu_launches)
+// ALGORITHMIC bytes of the scheme operations issued so far (operands read once, results written once, every
+// intermediate assumed on chip): key switch 8n[4l + 2b(l+K)], HMult+relin 8n[6l + 2b(l+K)], rescale 8n(2l - 1) per
+// polynomial, element-wise 8n * 3l per polynomial, leaf sums 8n * l (k + G) per polynomial.  bench.py divides the sum over
+// one sort by its run time for the sort-level roofline fraction.
+extern std::atomic<unsigned long long> g_algo_bytes;
+inline void count_algo(double bytes) { g_algo_bytes += (unsigned long long)bytes; }
 
 struct DeviceTables {            // resident per context
     int logn = 0, n = 0, F = 0;  // F = L + K moduli

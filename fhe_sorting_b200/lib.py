@@ -56,6 +56,13 @@ def launch_count():
     return int(L.fheb200_launch_count())
 
 
+def algo_bytes():
+    """Algorithmic bytes (SURVEY.md 8d formulas) of the scheme operations issued by this process so far."""
+    L = load()
+    L.fheb200_algo_bytes.restype = C.c_ulonglong
+    return int(L.fheb200_algo_bytes())
+
+
 def params_chain(logn, depth, scale_bits=40, first_bits=60, dnum=3):
     """Host-only: modulus chain / roots / (L, K, alpha) for a parameter set (no GPU needed)."""
     L = load()

@@ -32,6 +32,8 @@ const char *fheb200_last_error(void);
 const char *fheb200_version(void);
 /* number of CUDA kernels this library has launched in the process so far */
 unsigned long long fheb200_launch_count(void);
+/* algorithmic bytes (SURVEY.md 8d formulas) of the scheme operations issued by this process so far: roofline numerator */
+unsigned long long fheb200_algo_bytes(void);
 
 /* ---- context: CCParams<CryptoContextCKKSRNS> setters + GenCryptoContext (tests/DirectSortTest.cpp:24-41) ---- */
 typedef struct {

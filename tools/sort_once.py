@@ -12,7 +12,10 @@ n = int(sys.argv[1])
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 s = DirectSortSession(n, 17, seed=1000 + n)
 x = uniform_gap_input(n)
-for _ in range(reps):
+import torch  # noqa: E402
+for rep in range(reps):
+    if rep == reps - 1:
+        torch.cuda.profiler.start()  # ncu --profile-from-start off: the last sort only
     t0 = time.perf_counter()
     out, ms, level = s.sort(x)
     print("N=%d sort %.1f ms wall %.1f ms err %.2e" % (n, ms, 1e3 * (time.perf_counter() - t0), np.abs(out - np.sort(x)).max()),
