@@ -130,6 +130,7 @@ void Context::rescale_poly(int ell, int npoly, const u64 *in, u64 *out) {
     for (int i = 0; i < ell - 1; i++) // limb-major: the polys' limbs of one modulus share their twiddles in L2
         for (int p = 0; p < npoly; p++) dt.push_back(((uint32_t)(p * (ell - 1) + i) << 8) | (uint32_t)i);
     k_ntt_inv(T, in + (size_t)(ell - 1) * n, last->p, desc(dl), npoly, stream);
+    if (k_rescale_ntt_fused(T, ell, npoly, last->p, in, tmp->p, out, desc(dt), qi, stream)) return;
     k_rescale_lift(T, ell, npoly, last->p, (size_t)ell * n, tmp->p, stream);
     k_ntt_fwd(T, tmp->p, desc(dt), npoly * (ell - 1), stream);
     k_rescale_finish(T, ell - 1, npoly, in, tmp->p, qi, out, stream);

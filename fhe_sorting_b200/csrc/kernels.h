@@ -87,6 +87,11 @@ void k_rescale_lift(const DeviceTables &T, int ell, int npoly, const u64 *last_c
 void k_rescale_finish(const DeviceTables &T, int ell_out, int npoly, const u64 *in, const u64 *tmp, const LimbScalars &qlinv,
                       u64 *out, cudaStream_t st);
 
+// lift + forward NTT + finish in two launches (ntt.cu, n = 2^17 only; false = not applicable, use the three calls above):
+// last = dropped limbs in coefficient form (poly p at slot p * ell), d_desc = the (slot, limb) batch of the ell - 1 kept limbs
+bool k_rescale_ntt_fused(const DeviceTables &T, int ell, int npoly, const u64 *last, const u64 *in, u64 *tmp, u64 *out,
+                         const uint32_t *d_desc, const LimbScalars &qlinv, cudaStream_t st);
+
 // ---- bootstrapping: ModRaise ----
 // src: coefficient-domain limb 0 of each poly (poly p at src + p * src_stride); out[p][ell_out][n] <- the centred integer
 // on limbs 0..ell_out-1 (coefficient domain; NTT it afterwards)

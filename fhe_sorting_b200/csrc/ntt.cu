@@ -59,6 +59,23 @@ __device__ __forceinline__ void gs_bf(u64 &x, u64 &y, const ulonglong2 w, u64 nq
 }
 __device__ __forceinline__ int pad(int e) { return e + (e >> 3); }
 
+// Optional epilogue of a forward pass B whose 8 outputs per thread are contiguous (rescale: out = (in - ntt) * w mod q):
+// `in` is addressed like the output plus in_off words
+struct FwdEpilogue {
+    const u64 *in = nullptr;
+    size_t in_off = 0;
+    u64 w = 0, ws = 0;
+};
+__device__ __forceinline__ void apply_epilogue(const FwdEpilogue &E, u64 (&o)[8], size_t at, u64 q) {
+    const ulonglong2 *a = reinterpret_cast<const ulonglong2 *>(E.in + at + E.in_off);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const ulonglong2 t = a[k];
+        o[2 * k] = shoup_mul(sub_mod(t.x, o[2 * k], q), E.w, E.ws, q);
+        o[2 * k + 1] = shoup_mul(sub_mod(t.y, o[2 * k + 1], q), E.w, E.ws, q);
+    }
+}
+
 // three (or the top NS of three) forward stages on the thread's 8 values; s = global stage of the triple's top bit
 template <int NS, bool LAZY>
 __device__ __forceinline__ void fwd_chunk(u64 (&v)[8], const ulonglong2 *__restrict__ tw, int s, int logn, uint32_t g0, u64 nq,
@@ -135,7 +152,7 @@ __device__ __forceinline__ uint32_t g_step(const PassGeom &G, int p) {
 template <bool LAZY, bool CG>
 __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                               const uint32_t d, const PassGeom &G, int final_reduce, u64 *sm, uint32_t tile,
-                                              const u64 *pre = nullptr) {
+                                              const u64 *pre = nullptr, const FwdEpilogue *epi = nullptr) {
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
     const ModConst mc = T.mc[qp];
@@ -186,6 +203,7 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
         }
     }
     if (!G.pass_a && p == 0) {
+        if (epi) apply_epilogue(*epi, v, off + g0, q);
         ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) o[k] = make_ulonglong2(v[2 * k], v[2 * k + 1]);
@@ -259,7 +277,7 @@ __device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__res
 template <bool CG>
 __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu, uint32_t tile,
-                                                 const u64 *pre = nullptr) {
+                                                 const u64 *pre = nullptr, const FwdEpilogue *epi = nullptr) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
@@ -305,6 +323,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
 #pragma unroll
     for (int k = 0; k < 8; k++) o[k] = last ? fp_to_u64(v[k], q, qinv) : (u64)__double_as_longlong(v[k]);
     if (!G.pass_a && p == 0) {
+        if (epi) apply_epilogue(*epi, o, off + g0, T.mc[qp].q);
         ulonglong2 *op = reinterpret_cast<ulonglong2 *>(dst + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) op[k] = make_ulonglong2(o[2 * k], o[2 * k + 1]);
@@ -703,6 +722,57 @@ __global__ void __launch_bounds__(NTT_TILE / 8, CTAS) ntt_inv_persist(DeviceTabl
         __syncthreads();
     }
 }
+// ---------------------------------------------------------------- rescale fused into the forward NTT (n = 2^17)
+// Rescale = inverse NTT of the dropped limb, centred lift onto the remaining limbs, forward NTT of those, then
+// out = (in - lifted) * q_last^-1.  The lift is the PROLOGUE of pass A (each CTA reads its 8 x 256 coefficients of the
+// dropped limb - 1 MiB per polynomial, L2 resident - and switches modulus in registers) and the last step the EPILOGUE of
+// pass B: no lift kernel, no finish kernel, and the lifted polynomial never exists in HBM in coefficient form.
+// desc[y] = (slot << 8) | limb with slot = poly * (ell - 1) + limb; `last` holds the dropped limb of poly p (coefficient
+// domain) at slot p * ell; `in` has ell limbs per polynomial, tmp / out have ell - 1.
+template <int LOGN, int S, int LC>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_rescale_pass_a(DeviceTables T, const u64 *__restrict__ last, u64 *__restrict__ tmp,
+                                                                      const uint32_t *__restrict__ desc, int ell) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, 0, LC, NTT_TILE_LOG, 1};
+    const uint32_t d = desc[blockIdx.y];
+    const int qp = d & 0xff, poly = (int)(d >> 8) / (ell - 1);
+    u64 pre[8];
+    tile_prefetch<false>(last, ((uint32_t)(poly * ell) << 8) | (uint32_t)qp, G, blockIdx.x, T.n, pre);
+    const ModConst m = T.mc[qp];
+    const u64 ql = T.mc[ell - 1].q, half = ql >> 1;
+#pragma unroll
+    for (int k = 0; k < 8; k++) pre[k] = switch_modulus(pre[k], ql, half, m);
+    if (fp_ok(T, qp)) fp_fwd_pass_body<false>(T, last, tmp, d, G, 1, 0, sm, blockIdx.x, pre);
+    else if (lazy_ok(T, qp)) fwd_pass_body<true, false>(T, last, tmp, d, G, 0, sm, blockIdx.x, pre);
+    else fwd_pass_body<false, false>(T, last, tmp, d, G, 0, sm, blockIdx.x, pre);
+}
+template <int LOGN, int S0>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_rescale_pass_b(DeviceTables T, const u64 *__restrict__ tmp, u64 *__restrict__ out,
+                                                                      const uint32_t *__restrict__ desc, int ell,
+                                                                      const u64 *__restrict__ in, LimbScalars qlinv) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, LOGN - S0, S0, 0, NTT_TILE_LOG, 0};
+    const uint32_t d = desc[blockIdx.y];
+    const int qp = d & 0xff, poly = (int)(d >> 8) / (ell - 1);
+    FwdEpilogue E;
+    E.in = in, E.in_off = (size_t)poly * T.n, E.w = qlinv.v[qp], E.ws = qlinv.s[qp]; // in: one more limb per polynomial
+    if (fp_ok(T, qp)) fp_fwd_pass_body<false>(T, tmp, out, d, G, 0, 1, sm, blockIdx.x, nullptr, &E);
+    else if (lazy_ok(T, qp)) fwd_pass_body<true, false>(T, tmp, out, d, G, 1, sm, blockIdx.x, nullptr, &E);
+    else fwd_pass_body<false, false>(T, tmp, out, d, G, 1, sm, blockIdx.x, nullptr, &E);
+}
+// FHEB200_RESCALE_FUSED=0 keeps the separate lift / finish kernels
+bool k_rescale_ntt_fused(const DeviceTables &T, int ell, int npoly, const u64 *last, const u64 *in, u64 *tmp, u64 *out,
+                         const uint32_t *d_desc, const LimbScalars &qlinv, cudaStream_t st) {
+    static const bool on = [] { const char *e = getenv("FHEB200_RESCALE_FUSED"); return !(e && *e == '0'); }();
+    if (!on || T.logn != 17 || ell < 2) return false;
+    const int tile = NTT_TILE, count = npoly * (ell - 1);
+    const dim3 grid(T.n / tile, count);
+    const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    g_launches++, ntt_rescale_pass_a<17, 8, NTT_TILE_LOG - 8><<<grid, tile / 8, smem, st>>>(T, last, tmp, d_desc, ell);
+    g_launches++, ntt_rescale_pass_b<17, 8><<<grid, tile / 8, smem, st>>>(T, tmp, out, d_desc, ell, in, qlinv);
+    return true;
+}
+
 // FHEB200_NTT_PERSIST = 0 (one tile per CTA), 3 or 4 (persistent CTAs per SM)
 static int ntt_persist() {
     static const int v = [] {

@@ -12,5 +12,12 @@ ncu --set full --clock-control none --import-source on --profile-from-start off 
 python tools/sort_once.py 256 2 > $OUT/sort256_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $OUT/sort256_launches.csv \
     python tools/sort_once.py 256 2 > $OUT/sort256_ncu.log 2>&1
+# summaries here (the reports are too large to travel back: 64 MiB limit), then drop the reports
+python tools/ncu_raw.py $OUT/rot.ncu-rep > $OUT/ncu_full_rot.txt 2>&1
+python tools/ncu_raw.py $OUT/misc.ncu-rep > $OUT/ncu_full_misc.txt 2>&1
+ncu -i $OUT/rot.ncu-rep --page source --csv --kernel-name regex:ntt_fwd_pass_c 2>/dev/null | gzip > $OUT/source_ntt_fwd.csv.gz
+ncu -i $OUT/rot.ncu-rep --page source --csv --kernel-name regex:bc_convert 2>/dev/null | gzip > $OUT/source_bc_convert.csv.gz
+python tools/ncu_launch_summary.py $OUT/sort256_launches.csv > $OUT/sort256_kernels.txt 2>&1
+rm -f $OUT/rot.ncu-rep $OUT/misc.ncu-rep
 tail -n 2 $OUT/*_plain.log
 ls -la $OUT
