@@ -69,6 +69,7 @@ void Context::moddown(int ell, u64 *acc, const u64 *add0, const u64 *add1, u64 *
         k_ntt_inv(T, acc, D.desc_p2, 2 * D.K, stream);
         k_moddown_conv(T, D, acc, conv->p, stream);
     }
+    if (k_moddown_ntt_fused(T, D, conv->p, acc, add0, add1, out0, out1, galois == 1u ? 1u : P->galois_inverse(galois), stream)) return;
     k_ntt_fwd(T, conv->p, D.desc_q2, 2 * ell, stream);
     k_moddown_finish(T, D, acc, conv->p, add0, add1, out0, out1, galois, stream);
 }

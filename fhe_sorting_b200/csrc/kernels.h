@@ -152,6 +152,10 @@ void k_moddown_conv(const DeviceTables &T, const DevicePlan &P, const u64 *acc, 
 void k_moddown_finish(const DeviceTables &T, const DevicePlan &P, const u64 *acc, const u64 *conv, const u64 *add0,
                       const u64 *add1, u64 *out0, u64 *out1, uint32_t galois, cudaStream_t st);
 
+// forward NTT of conv + k_moddown_finish in two launches (ntt.cu, n = 2^17 only; false = not applicable)
+bool k_moddown_ntt_fused(const DeviceTables &T, const DevicePlan &P, u64 *conv, const u64 *acc, const u64 *add0, const u64 *add1,
+                         u64 *out0, u64 *out1, uint32_t galois_inverse, cudaStream_t st);
+
 // double hoisting (bootstrapping's linear transforms): S_b[t][p] += pt[t][p] * v_b[t][sigma_g(p)] over the level limbs t of
 // the extended basis (Q 0..ell-1, then P), with v_0 = acc_0 + cP_0, v_1 = acc_1 (acc = an evk inner product) or, when acc
 // is null, v_b = cP_b; cP = P * c_b on the Q limbs ([2][ell][n]).  The sum is brought back to Q by one ModDown per stage.

@@ -59,14 +59,20 @@ __device__ __forceinline__ void gs_bf(u64 &x, u64 &y, const ulonglong2 w, u64 nq
 }
 __device__ __forceinline__ int pad(int e) { return e + (e >> 3); }
 
-// Optional epilogue of a forward pass B whose 8 outputs per thread are contiguous (rescale: out = (in - ntt) * w mod q):
-// `in` is addressed like the output plus in_off words
+// Optional epilogue of a forward pass B whose 8 outputs per thread are contiguous:
+//   rescale  : out = (in - ntt) * w mod q, stored by the pass itself               (`in` addressed like the output + in_off)
+//   ModDown  : out[sigma^-1(g)] = (in - ntt) * w + add mod q, stored HERE through the inverse Galois map (scatter != null)
 struct FwdEpilogue {
     const u64 *in = nullptr;
     size_t in_off = 0;
     u64 w = 0, ws = 0;
+    const u64 *add = nullptr; // this limb of the polynomial that is added (may be null)
+    u64 *scatter = nullptr;   // this limb of the output polynomial; null = the pass stores to its own destination
+    uint32_t ginv = 1;        // inverse Galois element (1 = identity)
+    int logn = 0;
 };
-__device__ __forceinline__ void apply_epilogue(const FwdEpilogue &E, u64 (&o)[8], size_t at, u64 q) {
+// returns true when the values have been stored
+__device__ __forceinline__ bool apply_epilogue(const FwdEpilogue &E, u64 (&o)[8], size_t at, uint32_t g0, u64 q) {
     const ulonglong2 *a = reinterpret_cast<const ulonglong2 *>(E.in + at + E.in_off);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -74,6 +80,30 @@ __device__ __forceinline__ void apply_epilogue(const FwdEpilogue &E, u64 (&o)[8]
         o[2 * k] = shoup_mul(sub_mod(t.x, o[2 * k], q), E.w, E.ws, q);
         o[2 * k + 1] = shoup_mul(sub_mod(t.y, o[2 * k + 1], q), E.w, E.ws, q);
     }
+    if (!E.scatter) return false;
+    if (E.add) {
+        const ulonglong2 *b = reinterpret_cast<const ulonglong2 *>(E.add + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const ulonglong2 t = b[k];
+            o[2 * k] = add_mod(o[2 * k], t.x, q), o[2 * k + 1] = add_mod(o[2 * k + 1], t.y, q);
+        }
+    }
+    if (E.ginv == 1u) {
+        ulonglong2 *d = reinterpret_cast<ulonglong2 *>(E.scatter + g0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) d[k] = make_ulonglong2(o[2 * k], o[2 * k + 1]);
+    } else { // value at bit-reversed position s belongs at p with s = src(p): p = brev(((2 brev(s) + 1) g^-1 mod 2n) >> 1)
+        const int sh = 32 - E.logn;
+        const uint32_t mask = (2u << E.logn) - 1u;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t idx = __brev(g0 + k) >> sh;
+            const uint32_t j = (((2u * idx + 1u) * E.ginv) & mask) >> 1;
+            E.scatter[__brev(j) >> sh] = o[k];
+        }
+    }
+    return true;
 }
 
 // three (or the top NS of three) forward stages on the thread's 8 values; s = global stage of the triple's top bit
@@ -203,7 +233,7 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
         }
     }
     if (!G.pass_a && p == 0) {
-        if (epi) apply_epilogue(*epi, v, off + g0, q);
+        if (epi && apply_epilogue(*epi, v, off + g0, g0, q)) return;
         ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) o[k] = make_ulonglong2(v[2 * k], v[2 * k + 1]);
@@ -323,7 +353,7 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
 #pragma unroll
     for (int k = 0; k < 8; k++) o[k] = last ? fp_to_u64(v[k], q, qinv) : (u64)__double_as_longlong(v[k]);
     if (!G.pass_a && p == 0) {
-        if (epi) apply_epilogue(*epi, o, off + g0, T.mc[qp].q);
+        if (epi && apply_epilogue(*epi, o, off + g0, g0, T.mc[qp].q)) return;
         ulonglong2 *op = reinterpret_cast<ulonglong2 *>(dst + off + g0);
 #pragma unroll
         for (int k = 0; k < 4; k++) op[k] = make_ulonglong2(o[2 * k], o[2 * k + 1]);
@@ -770,6 +800,45 @@ bool k_rescale_ntt_fused(const DeviceTables &T, int ell, int npoly, const u64 *l
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
     g_launches++, ntt_rescale_pass_a<17, 8, NTT_TILE_LOG - 8><<<grid, tile / 8, smem, st>>>(T, last, tmp, d_desc, ell);
     g_launches++, ntt_rescale_pass_b<17, 8><<<grid, tile / 8, smem, st>>>(T, tmp, out, d_desc, ell, in, qlinv);
+    return true;
+}
+
+// ---------------------------------------------------------------- ModDown's last step fused into the forward NTT (n = 2^17)
+// conv[2][ell][n] (coefficient domain, the base-converted P part) -> forward NTT -> out_b = sigma_g((acc_b - conv_b) P^-1 + add_b):
+// pass A is the plain kernel, pass B applies the rest as its epilogue and scatters through the inverse Galois map (coalesced
+// reads of acc / add, one scattered store) instead of a separate kernel with three gathered reads.
+template <int LOGN, int S0>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_moddown_pass_b(DeviceTables T, u64 *__restrict__ conv, const uint32_t *__restrict__ desc,
+                                                                      int ell, int width, const u64 *__restrict__ p_inv,
+                                                                      const u64 *__restrict__ p_inv_s, const u64 *__restrict__ acc,
+                                                                      const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t ginv) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, LOGN - S0, S0, 0, NTT_TILE_LOG, 0};
+    const uint32_t d = desc[blockIdx.y];
+    const int qp = d & 0xff, slot = (int)(d >> 8), b = slot / ell; // slot = b * ell + limb, limb == qp
+    const size_t n = T.n;
+    FwdEpilogue E;
+    E.in = acc, E.in_off = (size_t)b * (width - ell) * n; // acc is [2][width][n]: skip the K special limbs of the polynomials before
+    E.w = __ldg(p_inv + qp), E.ws = __ldg(p_inv_s + qp);
+    const u64 *add = b ? add1 : add0;
+    E.add = add ? add + (size_t)qp * n : nullptr;
+    E.scatter = (b ? out1 : out0) + (size_t)qp * n;
+    E.ginv = ginv, E.logn = LOGN;
+    if (fp_ok(T, qp)) fp_fwd_pass_body<false>(T, conv, conv, d, G, 0, 1, sm, blockIdx.x, nullptr, &E);
+    else if (lazy_ok(T, qp)) fwd_pass_body<true, false>(T, conv, conv, d, G, 1, sm, blockIdx.x, nullptr, &E);
+    else fwd_pass_body<false, false>(T, conv, conv, d, G, 1, sm, blockIdx.x, nullptr, &E);
+}
+// FHEB200_MODDOWN_FUSED=0 keeps the separate finish kernel
+bool k_moddown_ntt_fused(const DeviceTables &T, const DevicePlan &P, u64 *conv, const u64 *acc, const u64 *add0, const u64 *add1,
+                         u64 *out0, u64 *out1, uint32_t galois_inverse, cudaStream_t st) {
+    static const bool on = [] { const char *e = getenv("FHEB200_MODDOWN_FUSED"); return !(e && *e == '0'); }();
+    if (!on || T.logn != 17) return false;
+    const int tile = NTT_TILE, count = 2 * P.ell;
+    const dim3 grid(T.n / tile, count);
+    const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
+    g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, conv, conv, P.desc_q2, 1, 0);
+    g_launches++, ntt_moddown_pass_b<17, 8><<<grid, tile / 8, smem, st>>>(T, conv, P.desc_q2, P.ell, P.width, P.p_inv, P.p_inv_s, acc, add0,
+                                                                          add1, out0, out1, galois_inverse);
     return true;
 }
 
