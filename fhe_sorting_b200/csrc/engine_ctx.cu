@@ -203,6 +203,7 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
     std::vector<double> qd(2 * (size_t)F);
     for (int i = 0; i < F; i++) qd[2 * i] = (double)P.moduli[i], qd[2 * i + 1] = (double)(1.0L / (long double)P.moduli[i]);
     T.qd = (double2 *)C->owned_alloc(sizeof(double) * qd.size(), qd.data());
+    ntt_register_moduli(T, P.mc.data());
     std::vector<std::vector<double>> fwd(F), iwd(F);
     std::vector<std::vector<u64>> fw(F), iw(F);
 #pragma omp parallel for schedule(dynamic)

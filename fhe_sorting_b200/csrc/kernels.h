@@ -27,6 +27,8 @@ struct DeviceTables {            // resident per context
     u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
 };
 
+void ntt_register_moduli(const DeviceTables &T, const ModConst *host_mc); // host copy of the modulus records (ntt.cu)
+
 constexpr int MAX_LIMBS = 96;    // upper bound on L+K (by-value kernel parameter blocks)
 struct LimbScalars {             // per-limb scalar + Shoup companion, passed by value
     u64 v[MAX_LIMBS];
@@ -36,6 +38,8 @@ struct LimbScalars {             // per-limb scalar + Shoup companion, passed by
 // ---- NTT (batched over limbs) ----
 // host copy of a descriptor array that lives at `dev` (the fused n = 2^17 kernels take descriptors as kernel parameters)
 void ntt_register_desc(const uint32_t *dev, const uint32_t *host, size_t count);
+// host copy of the modulus records of a context (the n = 2^17 kernels take (q, 1/q, path) per modulus as kernel parameters)
+
 // src and dst share the slot layout of the descriptors; src == dst transforms in place
 void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st);
 void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *d_desc, int count, cudaStream_t st,

@@ -15,6 +15,7 @@
 // thread is fewer issue slots than the 48 SHFL a 64-bit 8x8 lane transpose needs, so shared memory is used.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <stdexcept>
@@ -35,8 +36,16 @@ std::atomic<unsigned long long> g_algo_bytes{0};
 #ifndef NTT_PERSIST_DEFAULT
 #define NTT_PERSIST_DEFAULT 0
 #endif
+// stages of the last pass at n = 2^17 (the first pass runs the other 17 - NTT_SB on rows of 2^(NTT_TILE_LOG - 17 + NTT_SB) words)
+#ifndef NTT_SB
+#define NTT_SB 9
+#endif
+#define NTT_SA (17 - NTT_SB)
 constexpr int NTT_TILE_LOG = NTT_TILE_LOG_V;
-constexpr int NTT_CTAS = 8192 / (1 << NTT_TILE_LOG_V); // resident CTAs per SM: 1024 threads of 64 registers
+#ifndef NTT_CTAS_X
+#define NTT_CTAS_X (8192 / (1 << NTT_TILE_LOG_V)) // 4 resident CTAs per SM: 1024 threads of 64 registers
+#endif
+constexpr int NTT_CTAS = NTT_CTAS_X; // (5: 48 registers, 6: 40 registers - the integer paths spill a few words)
 constexpr int NTT_TILE = 1 << NTT_TILE_LOG;            // coefficients per CTA tile
 constexpr int NTT_PAD_WORDS = NTT_TILE + NTT_TILE / 8; // e -> e + (e >> 3) keeps every exchange pattern conflict free
 
@@ -252,7 +261,16 @@ __device__ __forceinline__ void fwd_pass_body(const DeviceTables &T, const u64 *
 // (6 DP instructions, no per-twiddle companion value to load or compute)
 // g == y*w (mod q) and |g| < 0.7 q for |y| < 2^50 (emulated exhaustively in tests/test_fp_modmul.py).  No conditional
 // corrections inside the butterflies: forward values grow by < q per stage, inverse sums are re-centred every <= 8 stages.
+// NTT_EXP (timing experiments only, results are wrong): 1 = constant twiddles, 2 = no shared-memory exchange, 3 = no butterfly
+// arithmetic, in the FP64 forward path
+#ifndef NTT_EXP
+#define NTT_EXP 0
+#endif
 __device__ __forceinline__ void fp_ct(double &x, double &y, double w, double qinv, double q) {
+    if (NTT_EXP == 3 || NTT_EXP == 4) {
+        x = __dadd_rn(x, w);
+        return;
+    }
     const double g = fp_mulmod(y, w, qinv, q);
     y = __dadd_rn(x, -g);
     x = __dadd_rn(x, g);
@@ -266,18 +284,18 @@ template <int NS>
 __device__ __forceinline__ void fp_fwd_chunk(double (&v)[8], const double *__restrict__ tw, int s, int logn, uint32_t g0,
                                              double q, double qinv) {
     {
-        const double w = __ldg(tw + (1u << s) + (g0 >> (logn - s)));
+        const double w = (NTT_EXP == 1 || NTT_EXP >= 4) ? 3.0 : __ldg(tw + (1u << s) + (g0 >> (logn - s)));
 #pragma unroll
         for (int k = 0; k < 4; k++) fp_ct(v[k], v[k + 4], w, qinv, q);
     }
     if (NS >= 2) {
-        const double2 w = __ldg(reinterpret_cast<const double2 *>(tw + (2u << s) + (g0 >> (logn - s - 1))));
+        const double2 w = (NTT_EXP == 1 || NTT_EXP >= 4) ? make_double2(5.0, 7.0) : __ldg(reinterpret_cast<const double2 *>(tw + (2u << s) + (g0 >> (logn - s - 1))));
         fp_ct(v[0], v[2], w.x, qinv, q), fp_ct(v[1], v[3], w.x, qinv, q);
         fp_ct(v[4], v[6], w.y, qinv, q), fp_ct(v[5], v[7], w.y, qinv, q);
     }
     if (NS >= 3) {
         const double2 *p = reinterpret_cast<const double2 *>(tw + (4u << s) + (g0 >> (logn - s - 2)));
-        const double2 w0 = __ldg(p), w1 = __ldg(p + 1);
+        const double2 w0 = (NTT_EXP == 1 || NTT_EXP >= 4) ? make_double2(9.0, 11.0) : __ldg(p), w1 = (NTT_EXP == 1 || NTT_EXP >= 4) ? make_double2(13.0, 15.0) : __ldg(p + 1);
         fp_ct(v[0], v[1], w0.x, qinv, q), fp_ct(v[2], v[3], w0.y, qinv, q);
         fp_ct(v[4], v[5], w1.x, qinv, q), fp_ct(v[6], v[7], w1.y, qinv, q);
     }
@@ -307,11 +325,11 @@ __device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__res
 template <bool CG>
 __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu, uint32_t tile,
-                                                 const u64 *pre = nullptr, const FwdEpilogue *epi = nullptr) {
+                                                 const u64 *pre = nullptr, const FwdEpilogue *epi = nullptr, const double2 *qdv = nullptr) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
-    const double2 qd = T.qd[qp];
+    const double2 qd = qdv ? *qdv : T.qd[qp];
     const double q = qd.x, qinv = qd.y;
     const double *tw = T.twf + (size_t)qp * n;
     const int lowbit = G.pass_a ? G.lc : 0;
@@ -336,15 +354,19 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
     bool firstx = true;
 #pragma unroll
     for (int pn = p - c_first; pn >= lowbit; pn -= 3) {
-        if (!firstx) __syncthreads();
-        firstx = false;
+        if (NTT_EXP != 2 && NTT_EXP < 4) {
+            if (!firstx) __syncthreads();
+            firstx = false;
 #pragma unroll
-        for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
-        __syncthreads();
+            for (int k = 0; k < 8; k++) sm[pad(base | (k << p))] = v[k];
+            __syncthreads();
+        }
         p = pn;
         base = triple_base(tid, p);
+        if (NTT_EXP != 2 && NTT_EXP < 4) {
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+            for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
+        }
         g0 = tile_to_g(G, base, tile);
         fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
         s += 3;
@@ -368,11 +390,11 @@ template <bool CG>
 __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                  const uint32_t d, const PassGeom &G, int first, int last, u64 *smu,
                                                  const u64 *__restrict__ custom, const u64 *__restrict__ custom_s, uint32_t tile,
-                                                 uint32_t bidx, const u64 *pre = nullptr) {
+                                                 uint32_t bidx, const u64 *pre = nullptr, const double2 *qdv = nullptr) {
     double *sm = reinterpret_cast<double *>(smu);
     const int qp = d & 0xff, n = T.n, tid = threadIdx.x;
     const size_t off = (size_t)(d >> 8) * n;
-    const double2 qd = T.qd[qp];
+    const double2 qd = qdv ? *qdv : T.qd[qp];
     const double q = qd.x, qinv = qd.y;
     const double *tw = T.twif + (size_t)qp * n;
     const int lowbit = G.pass_a ? G.lc : 0;
@@ -601,7 +623,7 @@ template <int LOGN>
 __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_fused(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
                                                                  NttBatch B, int count, unsigned *done) {
     extern __shared__ u64 sm[];
-    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - 9;
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - NTT_SB;
     const uint32_t tile = blockIdx.x & (TILES - 1);
     int phase, limb;
     fused_item(blockIdx.x >> LT, count, phase, limb);
@@ -614,7 +636,7 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_fused(DeviceTa
         else fwd_pass_body<false, false>(T, src, dst, d, G, 0, sm, tile);
         fused_publish(done, limb, TILES);
     } else {
-        const PassGeom G{LOGN, 9, SA, 0, NTT_TILE_LOG, 0};
+        const PassGeom G{LOGN, NTT_SB, SA, 0, NTT_TILE_LOG, 0};
         fused_wait(done, limb, TILES);
         if (fp_ok(T, qp)) fp_fwd_pass_body<true>(T, dst, dst, d, G, 0, 1, sm, tile);
         else if (lazy_ok(T, qp)) fwd_pass_body<true, true>(T, dst, dst, d, G, 1, sm, tile);
@@ -627,14 +649,14 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_fused(DeviceTa
                                                                  NttBatch B, int count, unsigned *done, const u64 *__restrict__ custom,
                                                                  const u64 *__restrict__ custom_s) {
     extern __shared__ u64 sm[];
-    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - 9;
+    constexpr int TILES = (1 << LOGN) / NTT_TILE, LT = LOGN - NTT_TILE_LOG, SA = LOGN - NTT_SB;
     const uint32_t tile = blockIdx.x & (TILES - 1);
     int phase, limb;
     fused_item(blockIdx.x >> LT, count, phase, limb);
     const uint32_t d = B.desc[limb];
     const int qp = d & 0xff;
     if (phase == 0) { // the 9 small-stride stages first
-        const PassGeom G{LOGN, 9, SA, 0, NTT_TILE_LOG, 0};
+        const PassGeom G{LOGN, NTT_SB, SA, 0, NTT_TILE_LOG, 0};
         if (fp_ok(T, qp)) fp_inv_pass_body<false>(T, src, dst, d, G, 1, 0, sm, nullptr, nullptr, tile, limb);
         else if (lazy_ok(T, qp)) inv_pass_body<true, false>(T, src, dst, d, G, 0, sm, nullptr, nullptr, tile, limb);
         else inv_pass_body<false, false>(T, src, dst, d, G, 0, sm, nullptr, nullptr, tile, limb);
@@ -798,8 +820,8 @@ bool k_rescale_ntt_fused(const DeviceTables &T, int ell, int npoly, const u64 *l
     const int tile = NTT_TILE, count = npoly * (ell - 1);
     const dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
-    g_launches++, ntt_rescale_pass_a<17, 8, NTT_TILE_LOG - 8><<<grid, tile / 8, smem, st>>>(T, last, tmp, d_desc, ell);
-    g_launches++, ntt_rescale_pass_b<17, 8><<<grid, tile / 8, smem, st>>>(T, tmp, out, d_desc, ell, in, qlinv);
+    g_launches++, ntt_rescale_pass_a<17, NTT_SA, NTT_TILE_LOG - NTT_SA><<<grid, tile / 8, smem, st>>>(T, last, tmp, d_desc, ell);
+    g_launches++, ntt_rescale_pass_b<17, NTT_SA><<<grid, tile / 8, smem, st>>>(T, tmp, out, d_desc, ell, in, qlinv);
     return true;
 }
 
@@ -836,8 +858,8 @@ bool k_moddown_ntt_fused(const DeviceTables &T, const DevicePlan &P, u64 *conv, 
     const int tile = NTT_TILE, count = 2 * P.ell;
     const dim3 grid(T.n / tile, count);
     const size_t smem = (size_t)(tile + tile / 8) * sizeof(u64);
-    g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<grid, tile / 8, smem, st>>>(T, conv, conv, P.desc_q2, 1, 0);
-    g_launches++, ntt_moddown_pass_b<17, 8><<<grid, tile / 8, smem, st>>>(T, conv, P.desc_q2, P.ell, P.width, P.p_inv, P.p_inv_s, acc, add0,
+    g_launches++, ntt_fwd_pass_c<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<grid, tile / 8, smem, st>>>(T, conv, conv, P.desc_q2, 1, 0);
+    g_launches++, ntt_moddown_pass_b<17, NTT_SA><<<grid, tile / 8, smem, st>>>(T, conv, P.desc_q2, P.ell, P.width, P.p_inv, P.p_inv_s, acc, add0,
                                                                           add1, out0, out1, galois_inverse);
     return true;
 }
@@ -858,6 +880,67 @@ static int sm_count() {
     if (dev < 0 || dev >= 64) return 148;
     if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
     return sms[dev] > 0 ? sms[dev] : 148;
+}
+
+// ---------------------------------------------------------------- constants in the parameter bank (n = 2^17)
+// Ablation on B200 (profiles/r02/ntt_ablation.txt): the butterflies are free - a pass with the arithmetic, the twiddles and the
+// exchanges removed still takes 74 % of the time, and a CTA lives only ~4 us.  Its prologue was a chain of three dependent
+// global loads (descriptor -> modulus record -> (q, 1/q)) before the first data load could issue.  Here the batch descriptors
+// and the per-modulus constants the FP64 path needs travel as kernel parameters (constant bank): the data loads go out first.
+struct NttLimbConsts {
+    double q[MAX_LIMBS], qinv[MAX_LIMBS];
+    unsigned char kind[MAX_LIMBS]; // 0 = FP64 path, 1 = lazy integer, 2 = strict integer
+};
+template <int LOGN, int S, int S0, int LC, int PA>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_k(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                  const NttBatch B, const NttLimbConsts C, int first, int final_reduce) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    const uint32_t d = B.desc[blockIdx.y];
+    const int qp = d & 0xff, kind = C.kind[qp];
+    if (kind == 0) {
+        const double2 qd = make_double2(C.q[qp], C.qinv[qp]);
+        fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, blockIdx.x, nullptr, nullptr, &qd);
+    } else if (kind == 1) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
+    else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, blockIdx.x);
+}
+template <int LOGN, int S, int S0, int LC, int PA>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_k(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                  const NttBatch B, const NttLimbConsts C, int first, int scale,
+                                                                  const u64 *__restrict__ custom, const u64 *__restrict__ custom_s) {
+    extern __shared__ u64 sm[];
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    const uint32_t d = B.desc[blockIdx.y];
+    const int qp = d & 0xff, kind = C.kind[qp];
+    if (kind == 0) {
+        const double2 qd = make_double2(C.q[qp], C.qinv[qp]);
+        fp_inv_pass_body<false>(T, src, dst, d, G, first, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y, nullptr, &qd);
+    } else if (kind == 1) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+    else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
+}
+static std::mutex g_consts_mu;
+static std::map<const ModConst *, NttLimbConsts> g_consts;
+void ntt_register_moduli(const DeviceTables &T, const ModConst *host_mc) {
+    NttLimbConsts C;
+    memset(&C, 0, sizeof(C));
+    for (int i = 0; i < T.F && i < MAX_LIMBS; i++) {
+        C.q[i] = (double)host_mc[i].q, C.qinv[i] = (double)(1.0L / (long double)host_mc[i].q); // as DeviceTables::qd
+        C.kind[i] = (host_mc[i].bits <= 42 && T.logn <= 17) ? 0 : ((int)host_mc[i].bits + T.logn + 1 <= 63 ? 1 : 2);
+    }
+    std::lock_guard<std::mutex> lock(g_consts_mu);
+    g_consts[T.mc] = C;
+}
+static bool limb_consts(const DeviceTables &T, NttLimbConsts &out) {
+    std::lock_guard<std::mutex> lock(g_consts_mu);
+    auto it = g_consts.find(T.mc);
+    if (it == g_consts.end()) return false;
+    out = it->second;
+    return true;
+}
+// FHEB200_NTT_PARAMS=0: descriptors and constants from global memory (round-1 form)
+static bool ntt_params() {
+    static const bool on = [] { const char *e = getenv("FHEB200_NTT_PARAMS"); return !(e && *e == '0'); }();
+    return on;
 }
 
 // host copies of the descriptor arrays (Context::desc registers them): the fused kernels take descriptors by value
@@ -891,7 +974,7 @@ static void passes(const DeviceTables &T, PassGeom &A, PassGeom &B, int &tile) {
         B = PassGeom{logn, logn, 0, 0, logn, 0};
     } else {
         tile = NTT_TILE;
-        const int SB = 9, SA = logn - SB;
+        const int SB = logn == 17 ? NTT_SB : 9, SA = logn - SB;
         A = PassGeom{logn, SA, 0, NTT_TILE_LOG - SA, NTT_TILE_LOG, 1};
         B = PassGeom{logn, SB, SA, 0, NTT_TILE_LOG, 0};
     }
@@ -923,12 +1006,24 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
             std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
             const int gridp = std::min(gc * (T.n / tile), pc * sm_count());
             if (pc == 3) {
-                g_launches++, ntt_fwd_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
-                g_launches++, ntt_fwd_persist<17, 9, 8, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
+                g_launches++, ntt_fwd_persist<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
+                g_launches++, ntt_fwd_persist<17, NTT_SB, NTT_SA, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
             } else {
-                g_launches++, ntt_fwd_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
-                g_launches++, ntt_fwd_persist<17, 9, 8, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
+                g_launches++, ntt_fwd_persist<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0);
+                g_launches++, ntt_fwd_persist<17, NTT_SB, NTT_SA, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1);
             }
+        }
+        return;
+    }
+    NttLimbConsts LC_;
+    if (T.logn == 17 && ntt_params() && host_desc(d_desc, count, hd) && limb_consts(T, LC_)) {
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            const dim3 gg(T.n / tile, gc);
+            g_launches++, ntt_fwd_pass_k<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<gg, tile / 8, smem, st>>>(T, src, dst, B, LC_, 1, 0);
+            g_launches++, ntt_fwd_pass_k<17, NTT_SB, NTT_SA, 0, 0><<<gg, tile / 8, smem, st>>>(T, dst, dst, B, LC_, 0, 1);
         }
         return;
     }
@@ -939,8 +1034,8 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
         const int group = ntt_group();
         for (int c0 = 0; c0 < count; c0 += group) {
             const dim3 gg(T.n / tile, std::min(group, count - c0));
-            g_launches++, ntt_fwd_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0);
-            g_launches++, ntt_fwd_pass_c<17, 9, 8, 0, 0><<<gg, tile / 8, smem, st>>>(T, dst, dst, d_desc + c0, 0, 1);
+            g_launches++, ntt_fwd_pass_c<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0);
+            g_launches++, ntt_fwd_pass_c<17, NTT_SB, NTT_SA, 0, 0><<<gg, tile / 8, smem, st>>>(T, dst, dst, d_desc + c0, 0, 1);
         }
         return;
     }
@@ -981,12 +1076,25 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
             const int gridp = std::min(gc * (T.n / tile), pc * sm_count());
             const u64 *cu = custom ? custom + c0 : nullptr, *cs = custom ? custom + count + c0 : nullptr;
             if (pc == 3) {
-                g_launches++, ntt_inv_persist<17, 9, 8, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
-                g_launches++, ntt_inv_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
+                g_launches++, ntt_inv_persist<17, NTT_SB, NTT_SA, 0, 0, 3><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
+                g_launches++, ntt_inv_persist<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1, 3><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
             } else {
-                g_launches++, ntt_inv_persist<17, 9, 8, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
-                g_launches++, ntt_inv_persist<17, 8, 0, NTT_TILE_LOG - 8, 1, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
+                g_launches++, ntt_inv_persist<17, NTT_SB, NTT_SA, 0, 0, 4><<<gridp, tile / 8, smem, st>>>(T, src, dst, B, gc, 1, 0, nullptr, nullptr);
+                g_launches++, ntt_inv_persist<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1, 4><<<gridp, tile / 8, smem, st>>>(T, dst, dst, B, gc, 0, 1, cu, cs);
             }
+        }
+        return;
+    }
+    NttLimbConsts LC_;
+    if (T.logn == 17 && ntt_params() && host_desc(d_desc, count, hd) && limb_consts(T, LC_)) {
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            const dim3 gg(T.n / tile, gc);
+            g_launches++, ntt_inv_pass_k<17, NTT_SB, NTT_SA, 0, 0><<<gg, tile / 8, smem, st>>>(T, src, dst, B, LC_, 1, 0, nullptr, nullptr);
+            g_launches++, ntt_inv_pass_k<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<gg, tile / 8, smem, st>>>(
+                T, dst, dst, B, LC_, 0, 1, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
         }
         return;
     }
@@ -997,8 +1105,8 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
             const dim3 gg(T.n / tile, gc);
             // custom scalars are indexed by blockIdx.y with the Shoup companions gridDim.y further on: hand each group its
             // own window [c0, c0 + gc) + [count + c0, ...) through the two-pointer form
-            g_launches++, ntt_inv_pass_c<17, 9, 8, 0, 0><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0, nullptr, nullptr);
-            g_launches++, ntt_inv_pass_c<17, 8, 0, NTT_TILE_LOG - 8, 1><<<gg, tile / 8, smem, st>>>(
+            g_launches++, ntt_inv_pass_c<17, NTT_SB, NTT_SA, 0, 0><<<gg, tile / 8, smem, st>>>(T, src, dst, d_desc + c0, 1, 0, nullptr, nullptr);
+            g_launches++, ntt_inv_pass_c<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<gg, tile / 8, smem, st>>>(
                 T, dst, dst, d_desc + c0, 0, 1, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
         }
         return;
