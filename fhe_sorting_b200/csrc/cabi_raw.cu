@@ -140,6 +140,62 @@ int fheb200_evk_export(fheb200_ctx *ctx, uint32_t galois, uint64_t *out, size_t 
         d2h(C, out, src, C.evk_words() * 8);
     })
 }
+// ---- raw import of key material (the other half of keys_export / evk_export: serialisation, src/sort.h:31-73)
+// public key (b, a), each [L][n], evaluation domain; the resulting key set has no secret key (evaluation-only party)
+int fheb200_keys_import_public(fheb200_ctx *ctx, const uint64_t *b, const uint64_t *a, size_t words_each, fheb200_keys **out) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(b, "b"); need(a, "a"); need(out, "out");
+        const size_t w = (size_t)C.P->L * n;
+        if (words_each != w) throw std::invalid_argument("keys_import_public: expected L * ring_dim words per polynomial");
+        auto K = std::make_shared<KeySet>();
+        K->pk = C.alloc(2 * w);
+        h2d(C, K->pk->p, b, w * 8);
+        h2d(C, K->pk->p + w, a, w * 8);
+        *out = new fheb200_keys{K};
+    })
+}
+// evaluation key [digit][2][L+K][n] for Galois element `galois` (0 = the relinearisation key); replaces a key already present
+int fheb200_evk_import(fheb200_ctx *ctx, uint32_t galois, const uint64_t *data, size_t words) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(data, "data");
+        if (words != C.evk_words()) throw std::invalid_argument("evk_import: wrong size for this context");
+        if (galois != 0 && (galois & 1u) == 0) throw std::invalid_argument("evk_import: Galois elements are odd");
+        u64 *dst = nullptr;
+        FHE_CUDA(cudaMalloc((void **)&dst, words * 8));
+        h2d(C, dst, data, words * 8);
+        u64 *&slot = galois == 0 ? C.evk_mult : C.evk_rot[galois];
+        if (slot) cudaFree(slot);
+        slot = dst;
+    })
+}
+// Galois elements of the rotation keys present, ascending
+int fheb200_evk_list(fheb200_ctx *ctx, uint32_t *out, size_t capacity, size_t *count) {
+    GUARD({
+        LOCKCTX(ctx);
+        size_t k = 0;
+        for (auto &kv : C.evk_rot) {
+            if (out && k < capacity) out[k] = kv.first;
+            k++;
+        }
+        if (count) *count = k;
+    })
+}
+int fheb200_has_mult_key(fheb200_ctx *ctx, int *present) {
+    GUARD({ LOCKCTX(ctx); need(present, "present"); *present = C.evk_mult != nullptr; })
+}
+int fheb200_ctx_evk_words(fheb200_ctx *ctx, size_t *words) {
+    GUARD({ LOCKCTX(ctx); need(words, "words"); *words = C.evk_words(); })
+}
+int fheb200_ctx_params(fheb200_ctx *ctx, fheb200_params *p) {
+    GUARD({
+        LOCKCTX(ctx);
+        need(p, "params");
+        p->log_ring_dim = C.P->logn, p->mult_depth = C.P->depth, p->scaling_mod_size = C.P->scale_bits;
+        p->first_mod_size = C.P->first_bits, p->batch_size = C.batch, p->num_large_digits = C.P->dnum, p->device = C.device;
+    })
+}
 int fheb200_galois_for_rotation(fheb200_ctx *ctx, int index, uint32_t *g) { GUARD({ need(ctx, "ctx"); *g = ctx->c->P->galois_for_rotation(index); }) }
 
 int fheb200_raw_ntt(fheb200_ctx *ctx, int inverse, int qp, uint64_t *poly) {

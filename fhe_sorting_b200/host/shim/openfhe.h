@@ -16,6 +16,7 @@
 #include <numeric>
 #include <set>
 #include <cstdint>
+#include <cstring>
 #include <functional>
 #include <iostream>
 #include <memory>
@@ -36,6 +37,13 @@ struct DCRTPoly {                    // tag: polynomials live in HBM behind the 
 };
 struct CryptoContextCKKSRNS {};
 enum SecurityLevel { HEStd_128_classic, HEStd_192_classic, HEStd_256_classic, HEStd_NotSet };
+// OpenFHE's serialisation selector (src/sort.h:34-71 uses SerType::BINARY only; JSON is not provided)
+namespace SerType {
+struct SERBINARY {};
+struct SERJSON {};
+static const SERBINARY BINARY{};
+static const SERJSON JSON{};
+} // namespace SerType
 enum PKESchemeFeature { PKE = 1, KEYSWITCH = 2, PRE = 4, LEVELEDSHE = 8, ADVANCEDSHE = 16, MULTIPARTY = 32, FHE = 64 };
 
 inline void fheb200_check(int rc) {
@@ -416,6 +424,65 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
         allReduceWords(ptr, words);
         fheb200_check(fheb200_ct_reduce_partial_sums(ctx, a->h));
     }
+    // ---- serialisation of evaluation keys (src/sort.h:47-66: DeserializeEvalMultKey / DeserializeEvalAutomorphismKey are
+    // called through the context pointer).  Wire format: this engine's own raw-limb container (see Serial below), NOT OpenFHE's
+    // cereal archives - those cannot be produced or checked on a machine without OpenFHE.
+    bool SerializeEvalMultKey(std::ostream &os, const SerType::SERBINARY &) {
+        int have = 0;
+        fheb200_check(fheb200_has_mult_key(ctx, &have));
+        if (!have) return false;
+        return ser_evk_block(os, 0);
+    }
+    bool DeserializeEvalMultKey(std::istream &is, const SerType::SERBINARY &) { return deser_evk_stream(is, true); }
+    bool SerializeEvalAutomorphismKey(std::ostream &os, const SerType::SERBINARY &) {
+        size_t cnt = 0;
+        fheb200_check(fheb200_evk_list(ctx, nullptr, 0, &cnt));
+        std::vector<uint32_t> g(cnt);
+        fheb200_check(fheb200_evk_list(ctx, g.data(), cnt, &cnt));
+        ser_u64(os, SER_MAGIC_EVKS), ser_u64(os, cnt);
+        for (uint32_t x : g)
+            if (!ser_evk_block(os, x)) return false;
+        return (bool)os;
+    }
+    bool DeserializeEvalAutomorphismKey(std::istream &is, const SerType::SERBINARY &) {
+        if (deser_u64(is) != SER_MAGIC_EVKS) return false;
+        const uint64_t cnt = deser_u64(is);
+        for (uint64_t i = 0; i < cnt; i++)
+            if (!deser_evk_stream(is, false)) return false;
+        return true;
+    }
+    static constexpr uint64_t SER_MAGIC_CC = 0x3143433030324246ull, SER_MAGIC_PK = 0x314b503030324246ull,
+                              SER_MAGIC_EVK = 0x4b56453030324246ull, SER_MAGIC_EVKS = 0x534b563030324246ull,
+                              SER_MAGIC_CT = 0x3154433030324246ull;
+    static void ser_u64(std::ostream &os, uint64_t v) { os.write(reinterpret_cast<const char *>(&v), 8); }
+    static uint64_t deser_u64(std::istream &is) {
+        uint64_t v = 0;
+        is.read(reinterpret_cast<char *>(&v), 8);
+        if (!is) throw std::runtime_error("Deserialize: truncated stream");
+        return v;
+    }
+    bool ser_evk_block(std::ostream &os, uint32_t galois) {
+        size_t words = 0;
+        fheb200_check(fheb200_ctx_evk_words(ctx, &words));
+        std::vector<uint64_t> buf(words);
+        fheb200_check(fheb200_evk_export(ctx, galois, buf.data(), words));
+        ser_u64(os, SER_MAGIC_EVK), ser_u64(os, galois), ser_u64(os, words);
+        os.write(reinterpret_cast<const char *>(buf.data()), (std::streamsize)(words * 8));
+        return (bool)os;
+    }
+    bool deser_evk_stream(std::istream &is, bool want_mult) {
+        if (deser_u64(is) != SER_MAGIC_EVK) return false;
+        const uint64_t galois = deser_u64(is), words = deser_u64(is);
+        size_t expect = 0;
+        fheb200_check(fheb200_ctx_evk_words(ctx, &expect));
+        if (words != expect || (want_mult && galois != 0)) return false;
+        std::vector<uint64_t> buf(words);
+        is.read(reinterpret_cast<char *>(buf.data()), (std::streamsize)(words * 8));
+        if (!is) return false;
+        fheb200_check(fheb200_evk_import(ctx, (uint32_t)galois, buf.data(), words));
+        return true;
+    }
+
     // TEST ONLY (not an OpenFHE call): a non-zero seed makes the following KeyGen calls deterministic (seed, seed + 1, ...)
     // with the non-cryptographic generator the CPU oracle shares; 0 restores the default (OS entropy)
     static void SetKeySeed(uint64_t s) { seed_state() = s; }
@@ -541,5 +608,135 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     impl->batch = p.GetBatchSize() ? p.GetBatchSize() : ring / 2;
     return CryptoContext<DCRTPoly>(impl);
 }
+
+// ---- Serial::SerializeToFile / DeserializeFromFile for the three object kinds the reference moves through files
+// (src/sort.h:34-45, 69-73, 97-101): crypto context (parameters only), public key, ciphertext.  Container: 8-byte magic,
+// fixed header of 64-bit fields, then raw little-endian limbs [poly][limb][n] as the engine exports them.  OpenFHE's cereal
+// BINARY archives are a different format; reading them needs OpenFHE's class layout and is unverifiable on this machine.
+namespace Serial {
+inline void put(std::ostream &os, uint64_t v) { CryptoContextImpl::ser_u64(os, v); }
+inline uint64_t get(std::istream &is) { return CryptoContextImpl::deser_u64(is); }
+inline void put_double(std::ostream &os, double d) {
+    uint64_t v;
+    memcpy(&v, &d, 8);
+    put(os, v);
+}
+inline double get_double(std::istream &is) {
+    uint64_t v = get(is);
+    double d;
+    memcpy(&d, &v, 8);
+    return d;
+}
+inline bool Serialize(const CryptoContext<DCRTPoly> &cc, std::ostream &os) {
+    fheb200_params p;
+    fheb200_check(fheb200_ctx_params(cc->ctx, &p));
+    put(os, CryptoContextImpl::SER_MAGIC_CC);
+    for (int v : {p.log_ring_dim, p.mult_depth, p.scaling_mod_size, p.first_mod_size, p.batch_size, p.num_large_digits}) put(os, (uint64_t)v);
+    put(os, cc->features);
+    return (bool)os;
+}
+inline bool Deserialize(CryptoContext<DCRTPoly> &cc, std::istream &is) {
+    if (get(is) != CryptoContextImpl::SER_MAGIC_CC) return false;
+    fheb200_params q;
+    q.log_ring_dim = (int)get(is), q.mult_depth = (int)get(is), q.scaling_mod_size = (int)get(is), q.first_mod_size = (int)get(is);
+    q.batch_size = (int)get(is), q.num_large_digits = (int)get(is);
+    const uint64_t features = get(is);
+    const char *e = getenv("FHEB200_DEVICE");
+    q.device = e ? atoi(e) : 0;
+    auto impl = std::make_shared<CryptoContextImpl>();
+    fheb200_check(fheb200_ctx_create(&q, &impl->ctx));
+    impl->ringDim = 1u << q.log_ring_dim, impl->depth = (usint)q.mult_depth;
+    impl->batch = q.batch_size ? (usint)q.batch_size : impl->ringDim / 2;
+    impl->features = (usint)features;
+    cc = CryptoContext<DCRTPoly>(impl);
+    return true;
+}
+// the public key file carries its context's parameters so that it can be checked against the context it is loaded into
+inline bool Serialize(const PublicKey<DCRTPoly> &pk, std::ostream &os, const CryptoContext<DCRTPoly> &cc) {
+    int n = 0, L = 0;
+    fheb200_check(fheb200_ctx_info(cc->ctx, &n, &L, nullptr, nullptr, nullptr));
+    const size_t w = (size_t)L * n;
+    std::vector<uint64_t> b(w), a(w);
+    fheb200_check(fheb200_keys_export(cc->ctx, pk.k->h, 1, b.data(), w));
+    fheb200_check(fheb200_keys_export(cc->ctx, pk.k->h, 2, a.data(), w));
+    put(os, CryptoContextImpl::SER_MAGIC_PK), put(os, w);
+    os.write(reinterpret_cast<const char *>(b.data()), (std::streamsize)(w * 8));
+    os.write(reinterpret_cast<const char *>(a.data()), (std::streamsize)(w * 8));
+    return (bool)os;
+}
+inline bool Deserialize(PublicKey<DCRTPoly> &pk, std::istream &is, const CryptoContext<DCRTPoly> &cc) {
+    if (get(is) != CryptoContextImpl::SER_MAGIC_PK) return false;
+    const uint64_t w = get(is);
+    std::vector<uint64_t> b(w), a(w);
+    is.read(reinterpret_cast<char *>(b.data()), (std::streamsize)(w * 8));
+    is.read(reinterpret_cast<char *>(a.data()), (std::streamsize)(w * 8));
+    if (!is) return false;
+    pk.k = std::make_shared<KeySetImpl>();
+    fheb200_check(fheb200_keys_import_public(cc->ctx, b.data(), a.data(), w, &pk.k->h));
+    return true;
+}
+inline bool Serialize(const Ciphertext<DCRTPoly> &ct, std::ostream &os) {
+    int level = 0, nsd = 0, slots = 0, limbs = 0;
+    double scale = 0;
+    fheb200_check(fheb200_ct_info(ct->h, &level, &nsd, &slots, &limbs, &scale));
+    int n = 0;
+    fheb200_check(fheb200_ctx_info(ct->cc->ctx, &n, nullptr, nullptr, nullptr, nullptr));
+    const size_t w = (size_t)limbs * n;
+    std::vector<uint64_t> c0(w), c1(w);
+    fheb200_check(fheb200_ct_export(ct->cc->ctx, ct->h, c0.data(), c1.data(), w));
+    put(os, CryptoContextImpl::SER_MAGIC_CT), put(os, (uint64_t)limbs), put(os, (uint64_t)nsd), put(os, (uint64_t)slots), put(os, w);
+    put_double(os, scale);
+    os.write(reinterpret_cast<const char *>(c0.data()), (std::streamsize)(w * 8));
+    os.write(reinterpret_cast<const char *>(c1.data()), (std::streamsize)(w * 8));
+    return (bool)os;
+}
+inline bool Deserialize(Ciphertext<DCRTPoly> &ct, std::istream &is, const CryptoContext<DCRTPoly> &cc) {
+    if (get(is) != CryptoContextImpl::SER_MAGIC_CT) return false;
+    const int limbs = (int)get(is), nsd = (int)get(is), slots = (int)get(is);
+    const uint64_t w = get(is);
+    const double scale = get_double(is);
+    std::vector<uint64_t> c0(w), c1(w);
+    is.read(reinterpret_cast<char *>(c0.data()), (std::streamsize)(w * 8));
+    is.read(reinterpret_cast<char *>(c1.data()), (std::streamsize)(w * 8));
+    if (!is) return false;
+    fheb200_ct *h = nullptr;
+    fheb200_check(fheb200_ct_import(cc->ctx, c0.data(), c1.data(), limbs, nsd, scale, slots, &h));
+    ct = Ciphertext<DCRTPoly>(std::make_shared<CiphertextImpl>(h, cc.ptr()));
+    return true;
+}
+// OpenFHE deserialises keys and ciphertexts into the context registered for their parameters; here that is the context
+// most recently deserialised or generated in this process (src/sort.h loads the context first)
+inline CryptoContext<DCRTPoly> &CurrentContext() {
+    static CryptoContext<DCRTPoly> cc;
+    return cc;
+}
+inline bool SerializeToFile(const std::string &path, const CryptoContext<DCRTPoly> &cc, const SerType::SERBINARY &) {
+    std::ofstream f(path, std::ios::binary);
+    CurrentContext() = cc;
+    return f.is_open() && Serialize(cc, f);
+}
+inline bool SerializeToFile(const std::string &path, const PublicKey<DCRTPoly> &pk, const SerType::SERBINARY &) {
+    std::ofstream f(path, std::ios::binary);
+    return f.is_open() && CurrentContext() && Serialize(pk, f, CurrentContext());
+}
+inline bool SerializeToFile(const std::string &path, const Ciphertext<DCRTPoly> &ct, const SerType::SERBINARY &) {
+    std::ofstream f(path, std::ios::binary);
+    return f.is_open() && Serialize(ct, f);
+}
+inline bool DeserializeFromFile(const std::string &path, CryptoContext<DCRTPoly> &cc, const SerType::SERBINARY &) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f.is_open() || !Deserialize(cc, f)) return false;
+    CurrentContext() = cc;
+    return true;
+}
+inline bool DeserializeFromFile(const std::string &path, PublicKey<DCRTPoly> &pk, const SerType::SERBINARY &) {
+    std::ifstream f(path, std::ios::binary);
+    return f.is_open() && CurrentContext() && Deserialize(pk, f, CurrentContext());
+}
+inline bool DeserializeFromFile(const std::string &path, Ciphertext<DCRTPoly> &ct, const SerType::SERBINARY &) {
+    std::ifstream f(path, std::ios::binary);
+    return f.is_open() && CurrentContext() && Deserialize(ct, f, CurrentContext());
+}
+} // namespace Serial
 
 } // namespace lbcrypto

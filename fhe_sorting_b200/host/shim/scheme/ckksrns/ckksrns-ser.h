@@ -1,0 +1,3 @@
+// forwarding header: the serialisation entry points live in openfhe.h (namespace lbcrypto::Serial)
+#pragma once
+#include "../../openfhe.h"

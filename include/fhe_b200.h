@@ -214,6 +214,14 @@ int fheb200_pt_export(fheb200_ctx *ctx, fheb200_pt *pt, uint64_t *out, size_t wo
 int fheb200_keys_export(fheb200_ctx *ctx, fheb200_keys *k, int which, uint64_t *out, size_t words);
 /* evaluation key [digit][2][L+K][n]; galois = 0 selects the relinearisation key */
 int fheb200_evk_export(fheb200_ctx *ctx, uint32_t galois, uint64_t *out, size_t words);
+/* raw import of key material and context parameters: what Serial::DeserializeFromFile / DeserializeEvalMultKey /
+ * DeserializeEvalAutomorphismKey need (reference src/sort.h:31-73) */
+int fheb200_keys_import_public(fheb200_ctx *ctx, const uint64_t *b, const uint64_t *a, size_t words_each, fheb200_keys **out);
+int fheb200_evk_import(fheb200_ctx *ctx, uint32_t galois, const uint64_t *data, size_t words);
+int fheb200_evk_list(fheb200_ctx *ctx, uint32_t *galois_out, size_t capacity, size_t *count);
+int fheb200_has_mult_key(fheb200_ctx *ctx, int *present);
+int fheb200_ctx_evk_words(fheb200_ctx *ctx, size_t *words);
+int fheb200_ctx_params(fheb200_ctx *ctx, fheb200_params *p);
 int fheb200_galois_for_rotation(fheb200_ctx *ctx, int index, uint32_t *galois);
 /* single primitives on host buffers (H2D, kernel, D2H) */
 int fheb200_raw_ntt(fheb200_ctx *ctx, int inverse, int qp_index, uint64_t *poly);
