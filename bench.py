@@ -253,6 +253,48 @@ def sort_latencies(rank, world, local_rank, dist, barrier, sizes=(64, 256, 1024)
     return out
 
 
+def cpu_sort_baseline(device, n=16):
+    """One whole encrypted DirectSort on the host cores beside the same sort on the GPU: the reference's unmodified drivers
+    (oracle/_ref/libref_sort_cpu.so when it was built; else this repository's drivers, oracle/libfhesort_cpu.so) over the
+    CPU scheme layer of the oracle (oracle/cpu_scheme.cpp) at DirectSort<16>'s own parameters (ring 2^17, depth 25).
+    Bounded sample: N = 16 is the largest length the host finishes in well under a minute.  cpu_baseline leg only."""
+    import ctypes as C
+    from fhe_sorting_b200.sort import DirectSortSession, uniform_gap_input
+    here = os.path.dirname(os.path.abspath(__file__))
+    cands = [("reference drivers (unmodified) over the oracle's CPU scheme layer", os.path.join(here, "oracle", "_ref", "libref_sort_cpu.so")),
+             ("this repository's drivers over the oracle's CPU scheme layer", os.path.join(here, "oracle", "libfhesort_cpu.so"))]
+    kind, path = next(((k, p) for k, p in cands if os.path.exists(p)), (None, None))
+    if path is None:
+        return {"unavailable": "oracle/libfhesort_cpu.so not built"}
+    x = uniform_gap_input(n)
+    g = DirectSortSession(n, 17, seed=SEED + n, device=device)
+    g.sort(x)
+    t0 = time.perf_counter()
+    gout, _, glevel = g.sort(x)
+    gsec = time.perf_counter() - t0
+    g.close()
+    L = C.CDLL(path)
+    L.fhesort_last_error.restype = C.c_char_p
+    devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(1)  # the reference drivers print their progress on stdout
+    sys.stdout.flush()
+    os.dup2(devnull, 1)
+    try:
+        c = DirectSortSession(n, 17, seed=SEED + n, lib=L)
+        t0 = time.perf_counter()
+        cout, _, clevel = c.sort(x)
+        csec = time.perf_counter() - t0
+        c.close()
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(devnull)
+        os.close(saved)
+    return {"n": n, "gpu_seconds": gsec, "cpu_seconds": csec, "cpu_cores": os.cpu_count() or 1, "cpu_kind": kind,
+            "gpu_vs_cpu_max_abs_diff": float(np.abs(gout - cout).max()), "cpu_max_abs_err": float(np.abs(cout - np.sort(x)).max()),
+            "gpu_max_abs_err": float(np.abs(gout - np.sort(x)).max()), "final_level": [glevel, clevel], "mult_depth": g.mult_depth,
+            "sample": "one DirectSort<16>::sort (same keys seed, same input, ring 2^17) on each side"}
+
+
 def bootstrap_latency(device):
     """EvalBootstrap at the k-way parameter set (ring 2^17, depth 40, 59-bit scaling, 1024 slots, budget {5,5}): mean
     latency of 5 calls on a ciphertext at the second-to-last level, and the error against the encrypted values."""
@@ -458,6 +500,8 @@ def run_ours(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
     micro = None if args.skip_micro else microbench(ctx, keys, ct, local_rank)
+    if sort_latency is not None and world == 1 and not args.skip_cpu_sort:
+        sort_latency["16_cpu_vs_gpu"] = cpu_sort_baseline(local_rank)
 
     # ---- per-kernel roofline (isolated kernels, CUDA events inside the library, inputs > L2)
     peak, peak_src = peaks()
@@ -515,8 +559,8 @@ def run_ours(args, rank, world, local_rank):
                          "sample": "3 EvalRotate of the same ciphertext at the full parameter set (41 limbs)",
                          "bit_exact_vs_gpu": parity,
                          "note": "oracle port of the published algorithm (Shoup NTT, lazy 128-bit base conversion, OpenMP over limbs), "
-                                 "NOT OpenFHE: OpenFHE is absent from this image; the oracle has no scheme layer, so no CPU sort "
-                                 "latency can be reported beside sort_latency"},
+                                 "NOT OpenFHE: OpenFHE is absent from this image; a whole CPU sort (N = 16) is timed beside the "
+                                 "GPU's under sort_latency['16_cpu_vs_gpu']"},
     }
     emit(out)
     if dist is not None:
@@ -530,6 +574,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skip-sort", action="store_true", help="leave out the DirectSort latencies (profiling runs)")
+    ap.add_argument("--skip-cpu-sort", action="store_true", help="leave out the N = 16 DirectSort on the host cores (about a minute)")
     ap.add_argument("--skip-micro", action="store_true", help="leave out the config-2 microbench across levels")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
