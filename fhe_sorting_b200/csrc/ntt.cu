@@ -22,6 +22,8 @@
 #include <string>
 #include <vector>
 
+#include <cooperative_groups.h>
+
 #include "kernels.h"
 #include "modarith.cuh"
 
@@ -32,6 +34,9 @@ std::atomic<unsigned long long> g_algo_bytes{0};
 
 #ifndef NTT_TILE_LOG_V
 #define NTT_TILE_LOG_V 11
+#endif
+#ifndef NTT_CLUSTER_MIN_DEFAULT
+#define NTT_CLUSTER_MIN_DEFAULT 0 // 0 = off
 #endif
 #ifndef NTT_PERSIST_DEFAULT
 #define NTT_PERSIST_DEFAULT 0
@@ -918,6 +923,23 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_k(DeviceT
     } else if (kind == 1) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
     else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
 }
+#include "ntt_cluster.cuh"
+// FHEB200_NTT_CLUSTER=0 keeps the two-pass kernels everywhere; =k (k >= 1) uses the cluster transform for batches of at least k
+// limbs (a cluster owns 8 SMs: small batches fill the GPU better with 64 independent tiles per limb)
+static int ntt_cluster_min() {
+    static const int v = [] {
+        const char *e = getenv("FHEB200_NTT_CLUSTER");
+        return e ? atoi(e) : NTT_CLUSTER_MIN_DEFAULT;
+    }();
+    return v;
+}
+static bool cluster_ready() {
+    static const bool ok = [] {
+        return cudaFuncSetAttribute(ntt_fwd_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CLN_FWD_SMEM) == cudaSuccess &&
+               cudaFuncSetAttribute(ntt_inv_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CLN_INV_SMEM) == cudaSuccess;
+    }();
+    return ok;
+}
 static std::mutex g_consts_mu;
 static std::map<const ModConst *, NttLimbConsts> g_consts;
 void ntt_register_moduli(const DeviceTables &T, const ModConst *host_mc) {
@@ -1016,6 +1038,16 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
         return;
     }
     NttLimbConsts LC_;
+    if (T.logn == 17 && ntt_cluster_min() > 0 && count >= ntt_cluster_min() && host_desc(d_desc, count, hd) && limb_consts(T, LC_) &&
+        cluster_ready()) {
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            g_launches++, ntt_fwd_cluster<<<dim3(CLN_CTAS, gc), CLN_THREADS, CLN_FWD_SMEM, st>>>(T, src, dst, B, LC_);
+        }
+        return;
+    }
     if (T.logn == 17 && ntt_params() && host_desc(d_desc, count, hd) && limb_consts(T, LC_)) {
         for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
             const int gc = std::min(NTT_FUSED_MAX, count - c0);
@@ -1086,6 +1118,17 @@ void k_ntt_inv(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
         return;
     }
     NttLimbConsts LC_;
+    if (T.logn == 17 && ntt_cluster_min() > 0 && count >= ntt_cluster_min() && host_desc(d_desc, count, hd) && limb_consts(T, LC_) &&
+        cluster_ready()) {
+        for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
+            const int gc = std::min(NTT_FUSED_MAX, count - c0);
+            NttBatch B;
+            std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
+            g_launches++, ntt_inv_cluster<<<dim3(CLN_CTAS, gc), CLN_THREADS, CLN_INV_SMEM, st>>>(
+                T, src, dst, B, LC_, custom ? custom + c0 : nullptr, custom ? custom + count + c0 : nullptr);
+        }
+        return;
+    }
     if (T.logn == 17 && ntt_params() && host_desc(d_desc, count, hd) && limb_consts(T, LC_)) {
         for (int c0 = 0; c0 < count; c0 += NTT_FUSED_MAX) {
             const int gc = std::min(NTT_FUSED_MAX, count - c0);
