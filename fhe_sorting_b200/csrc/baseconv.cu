@@ -493,6 +493,7 @@ void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS,
     // FHEB200_BC_PERSIST=1: persistent CTAs with the B fragments in shared memory (bc_convert_p); default: one
     // 32-coefficient tile per warp, operands straight from global memory (bc_convert)
     static const bool persist = [] { const char *e = getenv("FHEB200_BC_PERSIST"); return e && *e == '1'; }();
+    if (bc5_enabled() && k_base_convert_tcgen05(T, A, count, KS, st)) return;
     int NT = 0;
     for (int i = 0; i < count; i++) NT = std::max(NT, A.inst[i].tab.NT);
     const size_t smem = bcp_smem(KS, NT);

@@ -122,6 +122,9 @@ struct ConvArgs {
     ConvInstance inst[8];
 };
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
+// tcgen05 / TMEM form of the same conversion (baseconv_tcgen05.cu, FHEB200_BC_TCGEN05=1); false = shape not covered
+bool bc5_enabled();
+bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
 
 struct DevicePlan {              // device copy of a LevelPlan
     int ell = 0, beta = 0, width = 0, K = 0;

@@ -6,10 +6,10 @@ import sys
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 rows = list(csv.reader(sys.stdin))
-hdr = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+hdr = next(i for i, r in enumerate(rows) if r and "Source" in r and "# Samples" in r)
 H = rows[hdr]
 si, ii, smp = H.index("Source"), H.index("Instructions Executed"), H.index("# Samples")
-body = [r for r in rows[hdr + 1:] if len(r) > smp and r[0].startswith("0x")]
+body = [r for r in rows[hdr + 1:] if len(r) > smp and (r[smp] or "0").isdigit()]
 total = sum(int(r[smp] or 0) for r in body)
 print("instructions %d, samples %d" % (len(body), total))
 order = sorted(range(len(body)), key=lambda i: -int(body[i][smp] or 0))[:n]
