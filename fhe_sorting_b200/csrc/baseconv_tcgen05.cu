@@ -15,8 +15,6 @@
 // coefficients (256-byte runs per warp and target).
 #include <algorithm>
 #include <cstdlib>
-#include <map>
-#include <mutex>
 #include <stdexcept>
 
 #include "kernels.h"
@@ -248,23 +246,24 @@ __global__ void __launch_bounds__(BC5_THREADS, 2) bc_convert_t5(DeviceTables T, 
 }
 
 // ---- host side
-static std::mutex g_bc5_mu;
-static std::map<const uint2 *, unsigned char *> g_bc5_tables;
-static const unsigned char *bc5_table(const ConvTable &C, int chunks, cudaStream_t st) {
-    std::lock_guard<std::mutex> lock(g_bc5_mu);
-    auto it = g_bc5_tables.find(C.B);
-    if (it != g_bc5_tables.end()) return it->second;
+// B chunks of one conversion table in the UMMA layout (called by the context when it creates the table; the context owns and
+// frees the buffer).  nullptr = shape outside what bc_convert_t5 covers.
+unsigned char *bc5_make_table(const uint2 *frag, int KS, int NT) {
+    if (KS < 1 || KS > 4 || (NT + 1) / 2 > BC5_MAX_CHUNKS) return nullptr;
     unsigned char *d = nullptr;
-    if (cudaMalloc(&d, (size_t)chunks * BC5_TILE_BYTES) != cudaSuccess) throw std::runtime_error("fheb200: cudaMalloc failed (tcgen05 conversion table)");
-    const int total = chunks * BC5_TILE_BYTES;
-    g_launches++, bc5_build<<<(total + 255) / 256, 256, 0, st>>>(C.B, C.KS, C.NT, chunks, d);
-    g_bc5_tables[C.B] = d;
+    const int total = BC5_MAX_CHUNKS * BC5_TILE_BYTES; // always the full size: zero beyond the table's own targets
+    if (cudaMalloc(&d, (size_t)total) != cudaSuccess) throw std::runtime_error("fheb200: cudaMalloc failed (tcgen05 conversion table)");
+    g_launches++, bc5_build<<<(total + 255) / 256, 256>>>(frag, KS, NT, BC5_MAX_CHUNKS, d);
+    if (cudaStreamSynchronize(0) != cudaSuccess) throw std::runtime_error("fheb200: building the tcgen05 conversion table failed");
     return d;
 }
-bool bc5_enabled() {
-    static const bool on = [] { const char *e = getenv("FHEB200_BC_TCGEN05"); return e && *e == '1'; }();
-    return on;
+// FHEB200_BC_TCGEN05: 0 = never, 1 = every shape the kernel covers, unset = where it measured faster than bc_convert on B200
+// (profiles/r02/baseconv_tcgen05.txt: full digits of 14 sources with at least 17 targets, i.e. ModUp at ell >= 24)
+int bc5_mode() {
+    static const int m = [] { const char *e = getenv("FHEB200_BC_TCGEN05"); return e ? (*e == '1' ? 1 : 0) : 2; }();
+    return m;
 }
+bool bc5_enabled() { return bc5_mode() != 0; }
 // returns false when the shape is outside what the kernel covers (the caller falls back to bc_convert)
 bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
     if (KS < 1 || KS > 4 || T.n % BC5_M != 0 || count > 8) return false;
@@ -272,10 +271,12 @@ bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count,
     for (int i = 0; i < count; i++) NT = std::max(NT, A.inst[i].tab.NT);
     const int chunks = (NT + 1) / 2;
     if (chunks > BC5_MAX_CHUNKS) return false;
+    if (bc5_mode() == 2 && !(KS == 4 && NT >= 3)) return false;
     Bc5Tables BT;
     for (int i = 0; i < count; i++) {
         if (A.inst[i].tab.KS != KS) return false;
-        BT.bt[i] = bc5_table(A.inst[i].tab, BC5_MAX_CHUNKS, st); // always the full size: zero beyond the table's own targets
+        if (!A.inst[i].tab.B5) return false;
+        BT.bt[i] = A.inst[i].tab.B5;
     }
     static int sms = [] { int d = 0, v = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d); return v; }();
     // two CTAs per SM hold all 512 TMEM columns; a third resident CTA would sit in tcgen05.alloc until one of them exits, so the

@@ -400,6 +400,7 @@ const DevicePlan &Context::plan(int ell) {
         }
         t.tconst = (const uint4 *)owned_alloc(sizeof(uint32_t) * tconst.size(), tconst.data());
         t.planes = (const unsigned char *)owned_alloc(planes.size(), planes.data());
+        if (unsigned char *b5 = bc5_make_table(t.B, t.KS, t.NT)) owned_.push_back(b5), t.B5 = b5;
         return t;
     };
     auto shoup_of = [&](u64 v, u64 q) { return (u64)(((u128)v << 64) / q); };

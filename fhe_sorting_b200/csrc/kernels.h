@@ -108,6 +108,7 @@ struct ConvTable {
     const int *tslot = nullptr;  // [NT * 8] output limb slot of each target column, -1 = padding
     const uint4 *tconst = nullptr; // [NT * 8] (p lo, p hi, floor(2^(bits+31) / p), bits) of each target column
     const unsigned char *planes = nullptr; // [NT] 6 or 8 byte planes
+    const unsigned char *B5 = nullptr;     // the same constants as 16-target chunks in the UMMA K-major layout (baseconv_tcgen05.cu)
     int nsrc = 0, KS = 0, NT = 0;
 };
 struct ConvInstance {
@@ -124,6 +125,7 @@ struct ConvArgs {
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
 // tcgen05 / TMEM form of the same conversion (baseconv_tcgen05.cu, FHEB200_BC_TCGEN05=1); false = shape not covered
 bool bc5_enabled();
+unsigned char *bc5_make_table(const uint2 *frag, int KS, int NT);
 bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
 
 struct DevicePlan {              // device copy of a LevelPlan
