@@ -476,6 +476,8 @@ void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, 
                   u64 *const *out, u64 *scratch, cudaStream_t st, int force_ring) {
     if (G < 1 || G > 8) throw std::invalid_argument("lincomb (tensor cores): 1..8 outputs per pass");
     const int KS = (count + 3) / 4;
+    // tcgen05 / TMEM form (baseconv_tcgen05.cu): FHEB200_LC_TCGEN05=1; force_ring >= 0 (tests, kernel comparisons) keeps the mma.sync kernels
+    if (force_ring < 0 && lc5_mode() == 1 && k_lincomb_tcgen05(T, ell, limbs2, count, G, in, w, out, scratch, st)) return;
     g_launches++, lc_build_tables<<<dim3(KS, ell), 64, 0, st>>>(T, ell, count, G, KS, w, reinterpret_cast<uint32_t *>(scratch));
     const dim3 grid((T.n + LC_WARPS * 16 * LC_MT - 1) / (LC_WARPS * 16 * LC_MT), limbs2);
     // FHEB200_LINCOMB_RING=0: A fragments straight from global memory (lc_tc) instead of through the cp.async rings

@@ -295,4 +295,208 @@ bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count,
     return true;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Weighted sums of many polynomials (Paterson-Stockmeyer leaf sums: up to 8 outputs = sum_t w[g][t] in_t over up to 63 inputs) on
+// tcgen05: the contraction of baseconv.cu's lc_tc_ring with the accumulators in tensor memory.
+//   D[128 coefficients][(plane b, output g)] += A[128 coefficients][(input t, byte a)] x B[(input t, byte a)][(plane b, output g)]
+// K = 8 bytes x up to 64 inputs is cut into K blocks of 16 inputs: one "granule" = the [128 rows x 128 bytes] swizzled A block of
+// one tile and K block (16 KB).  A CTA (512 threads, one per SM) streams its contiguous range of (limb, tile) work through a ring of
+// 12 granules filled by cp.async (11 in flight: ~176 KB per SM, no registers held), issues the 4 MMAs (M128 N64 K32) of a granule as
+// soon as it has landed, and after the last K block of a tile reads the 64 TMEM columns back (tcgen05.ld 32x32b.x2: plane b of the two
+// outputs of this warp), recombines the planes and reduces the 128-bit value exactly as lc_tc_ring does.  The B operand of the
+// current limb (8 planes x 8 outputs rows, 32 KB) lives in shared memory and is reloaded when the range crosses into the next limb.
+constexpr int LC5_THREADS = 512, LC5_RING = 12, LC5_N = 64;
+constexpr int LC5_GRAN = BC5_TILE_BYTES;      // 16 KB
+constexpr int LC5_BBLOCK = 64 * 128;          // B rows of one K block
+// w: split weights [(g * count + t) * ell + limb] (lo30, hi30); out: [ell][KB][64 rows x 128 bytes] swizzled
+__global__ void __launch_bounds__(512) lc5_build(DeviceTables T, int ell, int count, int G, int KB, const uint2 *__restrict__ w,
+                                                 unsigned char *__restrict__ out) {
+    const int li = blockIdx.x, j = threadIdx.x >> 3, g = threadIdx.x & 7;
+    if (j >= 16 * KB) return;
+    const ModConst m = T.mc[li];
+    u64 word[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (g < G && j < count) {
+        const uint2 sp = __ldg(w + (size_t)(g * count + j) * ell + li);
+        const u64 c0 = (u64)sp.x | ((u64)sp.y << 30);
+#pragma unroll
+        for (int a = 0; a < 8; a++) {
+            const u64 cp = mul_mod(c0, reduce64(1ull << (8 * a), m), m);
+#pragma unroll
+            for (int b = 0; b < 8; b++) word[b] |= ((cp >> (8 * b)) & 0xffull) << (8 * a);
+        }
+    }
+    unsigned char *blk = out + ((size_t)li * KB + (j >> 4)) * LC5_BBLOCK;
+#pragma unroll
+    for (int b = 0; b < 8; b++) *reinterpret_cast<u64 *>(blk + bc5_swz(b * 8 + g, 8 * (j & 15))) = word[b];
+}
+__device__ __forceinline__ void bc5_ld2(uint32_t taddr, uint32_t (&r)[2]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t mbar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}\n" ::"r"(mbar) : "memory");
+}
+// Roles: warps 0..15 fetch (cp.async), signal "granule landed" (full[slot], 512 arrivals), retire granules `lag` iterations
+// later (done[g & 3] <- tcgen05.commit: the slot is free again; after the last K block of a tile also the epilogue, then
+// tfree[buffer], 512 arrivals); thread 512 only issues MMAs: it waits for full[slot] (and for tfree before reusing a TMEM buffer),
+// so no CTA-wide barrier sits between a granule landing and its MMAs.  CTA-wide barriers only where the B operand changes (a CTA's
+// range crosses into the next limb at most once or twice).
+__global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, int ell, int limbs2, int count, int G, int KS,
+                                                                const u64 *const *__restrict__ in, const unsigned char *__restrict__ Bt,
+                                                                u64 *const *__restrict__ out) {
+    extern __shared__ unsigned char lc5_raw[];
+    __shared__ __align__(8) unsigned long long mbar_store[LC5_RING + 4 + 2];
+    __shared__ uint32_t tmem_slot;
+    __shared__ const u64 *ptr[64];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n = T.n;
+    const bool producer = tid < LC5_THREADS;
+    const int KB = (KS + 3) >> 2, tl_log = T.logn - 7; // tiles per limb = n / 128 (a power of two)
+    const int lag = 3;                                 // granule g is retired at iteration g + lag
+    const int row = 32 * (warp & 3) + lane, q = warp >> 2; // epilogue role: outputs 2q, 2q + 1
+    const int lrow = tid & 127, jg = (tid >> 7) & 3;       // loader role
+    unsigned char *base = lc5_raw + ((1024u - (smem_u32(lc5_raw) & 1023u)) & 1023u);
+    unsigned char *sB = base, *sA = base + 4 * LC5_BBLOCK;
+    const uint32_t full0 = smem_u32(&mbar_store[0]), done0 = full0 + 8 * LC5_RING, tfree0 = done0 + 8 * 4;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(2 * LC5_N) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid < LC5_RING) mbar_init(full0 + 8 * tid, LC5_THREADS);
+    else if (tid < LC5_RING + 4) mbar_init(full0 + 8 * tid, 1);
+    else if (tid < LC5_RING + 6) mbar_init(full0 + 8 * tid, LC5_THREADS);
+    if (tid < 64) ptr[tid] = in[tid < count ? tid : 0]; // padding reads input 0 (its weights are zero)
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_slot;
+    const uint32_t idesc = (2u << 4) | ((uint32_t)(LC5_N >> 3) << 17) | ((uint32_t)(BC5_M >> 4) << 24);
+    // this CTA's contiguous range of tiles in (limb-polynomial, tile) order, and of granules
+    const long long total_tiles = (long long)limbs2 << tl_log;
+    const int t_begin = (int)(total_tiles * blockIdx.x / gridDim.x), t_end = (int)(total_tiles * (blockIdx.x + 1) / gridDim.x);
+    const int total = (t_end - t_begin) * KB;
+
+    // the three walks over this CTA's granules (fetch, issue / signal, retire) keep their own (tile, K block, ring slot) counters
+    int f_gi = 0, f_tile = t_begin, f_kb = 0, f_slot = 0;
+    auto fetch = [&]() { // next granule -> its ring slot
+        if (f_gi < total) {
+            const size_t goff = (size_t)(f_tile >> tl_log) * n + (size_t)(f_tile & ((1 << tl_log) - 1)) * BC5_M + lrow;
+            const uint32_t sdst = smem_u32(sA) + f_slot * LC5_GRAN + bc5_swz(lrow, 8 * jg);
+            const u64 *const *pp = ptr + 16 * f_kb + jg;
+#pragma unroll
+            for (int i = 0; i < 4; i++) // input 16 kb + jg + 4 i: 32 bytes further along the row, i.e. two 16-byte chunks (XOR 2 i)
+                if (16 * f_kb + jg + 4 * i < 4 * KS) bc5_cp8(sdst ^ (uint32_t)(i << 5), pp[4 * i] + goff);
+            if (++f_kb == KB) f_kb = 0, f_tile++;
+            if (++f_slot == LC5_RING) f_slot = 0;
+        }
+        f_gi++;
+        asm volatile("cp.async.commit_group;" ::: "memory"); // one group per granule (empty past the end)
+    };
+    if (producer)
+        for (int gi = 0; gi < LC5_RING - lag; gi++) fetch();
+
+    int cur_lp = -1, next_epi = 0;
+    ModConst m = T.mc[0];
+    int np = 8;
+    // granule ge: wait for its MMAs (its ring slot is then free); if it closed a tile, read that tile's accumulators back
+    int r_tl = 0, r_kb = 0;
+    auto retire = [&](int ge) {
+        mbar_wait(done0 + 8 * (ge & 3), (ge >> 2) & 1);
+        const int tl = r_tl, kb = r_kb;
+        if (++r_kb == KB) r_kb = 0, r_tl++;
+        if (kb != KB - 1) return;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int tile = t_begin + tl;
+        const uint32_t tbase = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (tl & 1) * LC5_N + 2 * q;
+        uint32_t s[8][2];
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            if (b < np) bc5_ld2(tbase + b * 8, s[b]);
+            else s[b][0] = s[b][1] = 0;
+        }
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(tfree0 + 8 * (tl & 1)); // this thread is done with the TMEM buffer
+        const size_t at = (size_t)(tile >> tl_log) * n + (size_t)(tile & ((1 << tl_log) - 1)) * BC5_M + row;
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const int g = 2 * q + k;
+            if (g >= G) continue;
+            uint32_t sv[8];
+#pragma unroll
+            for (int b = 0; b < 8; b++) sv[b] = s[b][k];
+            const u64 lo4 = bc5_lo(sv);
+            const u64 hi4 = mad_wide(sv[7], 1u << 24, mad_wide(sv[6], 1u << 16, mad_wide(sv[5], 1u << 8, (u64)sv[4])));
+            const u64 vlo = lo4 + (hi4 << 32), vhi = (hi4 >> 32) + (vlo < lo4);
+            out[g][at] = reduce128(vhi, vlo, m);
+        }
+    };
+    int tl = 0, kb = 0, slot = 0, slot_phase = 0;
+#pragma unroll 1
+    for (int gi = 0; gi < total + lag; gi++, (++kb == KB ? (kb = 0, tl++) : 0), (++slot == LC5_RING ? (slot = 0, slot_phase ^= 1) : 0)) {
+        const int lp = (t_begin + tl) >> tl_log;
+        if (gi < total && kb == 0 && lp != cur_lp) { // new limb: everything that used the old B operand and modulus finishes first
+            if (producer)
+                while (next_epi < gi) retire(next_epi++);
+            __syncthreads();
+            cur_lp = lp;
+            const int li = lp % ell;
+            m = T.mc[li];
+            np = (int)(m.bits + 7) >> 3;
+            if (producer) {
+                const uint4 *g = reinterpret_cast<const uint4 *>(Bt + (size_t)li * KB * LC5_BBLOCK);
+                uint4 *sdst = reinterpret_cast<uint4 *>(sB);
+                for (int i = tid; i < KB * (LC5_BBLOCK / 16); i += LC5_THREADS) sdst[i] = g[i];
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            }
+            __syncthreads();
+        }
+        if (producer) {
+            if (gi < total) { // this thread's part of granule gi has landed (RING - lag + gi groups committed so far)
+                asm volatile("cp.async.wait_group %0;" ::"n"(LC5_RING - 4) : "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(full0 + 8 * slot);
+            }
+            while (next_epi <= gi - lag && next_epi < total) retire(next_epi++);
+            fetch(); // granule gi + RING - lag, into the slot of granule gi - lag
+        } else if (tid == LC5_THREADS && gi < total) {
+            mbar_wait(full0 + 8 * slot, slot_phase);
+            if (kb == 0 && tl >= 2) mbar_wait(tfree0 + 8 * (tl & 1), ((tl >> 1) - 1) & 1); // the epilogue of tile tl - 2 has read this buffer
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t aaddr = smem_u32(sA) + slot * LC5_GRAN, baddr = smem_u32(sB + kb * LC5_BBLOCK);
+            const int steps = min(4, KS - 4 * kb);
+            for (int ks = 0; ks < steps; ks++)
+                bc5_mma(tmem + (tl & 1) * LC5_N, bc5_desc(aaddr + ks * 32), bc5_desc(baddr + ks * 32), idesc, (kb | ks) != 0);
+            bc5_commit(done0 + 8 * (gi & 3));
+        }
+        if (!producer) __syncwarp(); // the idle lanes of the issuing warp stay with lane 0
+    }
+    if (producer) asm volatile("cp.async.wait_all;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * LC5_N) : "memory");
+}
+
+// FHEB200_LC_TCGEN05: 0 = never, 1 = whenever the shape is covered, unset = default selection (see k_lincomb_tc)
+int lc5_mode() {
+    static const int m = [] { const char *e = getenv("FHEB200_LC_TCGEN05"); return e ? (*e == '1' ? 1 : 0) : 2; }();
+    return m;
+}
+// scratch: at least lincomb_tc_scratch_words(ell, count) words
+bool k_lincomb_tcgen05(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w, u64 *const *out,
+                       u64 *scratch, cudaStream_t st) {
+    const int KS = (count + 3) / 4, KB = (KS + 3) / 4;
+    if (count < 1 || count > 64 || G < 1 || G > 8 || T.n % BC5_M != 0) return false;
+    unsigned char *Bt = reinterpret_cast<unsigned char *>(scratch);
+    g_launches++, lc5_build<<<ell, 512, 0, st>>>(T, ell, count, G, KB, w, Bt);
+    static int sms = [] { int d = 0, v = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d); return v; }();
+    const size_t smem = (size_t)4 * LC5_BBLOCK + (size_t)LC5_RING * LC5_GRAN + 1024;
+    static bool attr = false;
+    if (!attr) cudaFuncSetAttribute(lc_tc_t5, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), attr = true;
+    const long long tiles = (long long)limbs2 * (T.n / BC5_M);
+    const int grid = (int)std::min<long long>(tiles, sms);
+    g_launches++, lc_tc_t5<<<grid, LC5_THREADS + 32, smem, st>>>(T, ell, limbs2, count, G, KS, in, Bt, out);
+    return true;
+}
+
 } // namespace fheb200

@@ -263,6 +263,11 @@ int fheb200_raw_lincomb(fheb200_ctx *ctx, int ell, int limbs2, int count, int G,
         h2d(C, d->p, blob.data(), blob.size() * 8);
         if (variant == 2) {
             k_lincomb(C.T, ell, limbs2, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G), (u64 *const *)(d->p + count), C.stream);
+        } else if (variant == 3) { // tcgen05 / TMEM form
+            Mem tables = C.alloc(lincomb_tc_scratch_words(ell, count));
+            if (!k_lincomb_tcgen05(C.T, ell, limbs2, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G), (u64 *const *)(d->p + count),
+                                   tables->p, C.stream))
+                throw std::invalid_argument("raw_lincomb: shape not covered by the tcgen05 kernel");
         } else {
             Mem tables = C.alloc(lincomb_tc_scratch_words(ell, count));
             k_lincomb_tc(C.T, ell, limbs2, count, G, (const u64 *const *)d->p, (const uint2 *)(d->p + count + G), (u64 *const *)(d->p + count),

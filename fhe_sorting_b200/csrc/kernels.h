@@ -78,7 +78,14 @@ void k_lincomb(const DeviceTables &T, int ell, int limbs2, int count, int G, con
 // (force_ring: -1 = FHEB200_LINCOMB_RING decides [default: ring], 0 = lc_tc, 1 = lc_tc_ring)
 void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w,
                   u64 *const *out, u64 *scratch, cudaStream_t st, int force_ring = -1);
-inline size_t lincomb_tc_scratch_words(int ell, int count) { return (size_t)ell * ((count + 3) / 4) * 256; }
+// (the tcgen05 form keeps [ell][ceil(count / 16)] blocks of 64 rows x 128 bytes = 1024 words instead)
+inline size_t lincomb_tc_scratch_words(int ell, int count) {
+    const size_t frag = (size_t)ell * ((count + 3) / 4) * 256, umma = (size_t)ell * ((count + 15) / 16) * 1024;
+    return frag > umma ? frag : umma;
+}
+int lc5_mode();
+bool k_lincomb_tcgen05(const DeviceTables &T, int ell, int limbs2, int count, int G, const u64 *const *in, const uint2 *w, u64 *const *out,
+                       u64 *scratch, cudaStream_t st);
 // a[limb][k] <- a[limb][k] mod q_limb for arbitrary 64-bit words (sums of residues from several ranks)
 void k_reduce_words(const DeviceTables &T, int ell, u64 *a, cudaStream_t st);
 // Galois automorphism (eval domain, bit-reversed order) on `limbs` limbs

@@ -67,12 +67,13 @@ def test_leaf_sums_all_variants(pair, ell, count, G):
     rows = np.concatenate([np.arange(40), rng.integers(0, orc.n, 88), [orc.n - 1]])
     want = _exact_lincomb(inputs, weights, orc.moduli, ell, rows)
     outs = {}
-    for variant, name in ((0, "lc_tc_ring"), (1, "lc_tc"), (2, "ew_lincomb")):
+    for variant, name in ((0, "lc_tc_ring"), (1, "lc_tc"), (2, "ew_lincomb"), (3, "lc_tc_t5")):
         g_lim = min(G, 4) if variant == 2 else G
         outs[name] = ctx.raw_lincomb(inputs, weights[:g_lim], variant)
         assert np.array_equal(outs[name][:, :, rows], want[:g_lim]), name
     # and everywhere else the three kernels agree with each other
     assert np.array_equal(outs["lc_tc_ring"], outs["lc_tc"])
+    assert np.array_equal(outs["lc_tc_ring"], outs["lc_tc_t5"]), "tcgen05 leaf sums differ from the mma.sync ones"
     assert np.array_equal(outs["lc_tc_ring"][:outs["ew_lincomb"].shape[0]], outs["ew_lincomb"])
 
 
