@@ -336,11 +336,13 @@ __device__ __forceinline__ void bc5_ld2(uint32_t taddr, uint32_t (&r)[2]) {
 __device__ __forceinline__ void mbar_arrive(uint32_t mbar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}\n" ::"r"(mbar) : "memory");
 }
-// Roles: warps 0..15 fetch (cp.async), signal "granule landed" (full[slot], 512 arrivals), retire granules `lag` iterations
-// later (done[g & 3] <- tcgen05.commit: the slot is free again; after the last K block of a tile also the epilogue, then
-// tfree[buffer], 512 arrivals); thread 512 only issues MMAs: it waits for full[slot] (and for tfree before reusing a TMEM buffer),
-// so no CTA-wide barrier sits between a granule landing and its MMAs.  CTA-wide barriers only where the B operand changes (a CTA's
-// range crosses into the next limb at most once or twice).
+// Roles.  Warps 0..15 (thread = coefficient row tid & 127, group g = tid >> 7): per tile, group g copies K block g (its 16 inputs,
+// cp.async 8 bytes each) two tiles ahead, signals "K block g of tile i landed" (full[(i % 3) * 4 + g], 128 arrivals), and retires
+// tile i - 1: waits for done[(i - 1) & 3] (tcgen05.commit after the tile's last MMA: its ring slots are free again), reads its 64
+// TMEM columns back (tcgen05.ld 32x32b.x2: plane b of outputs 2g, 2g + 1), signals tfree[buffer] (512 arrivals), recombines the
+// planes and reduces the 128-bit value exactly as lc_tc_ring does.  Thread 512 only issues MMAs: per tile it waits for tfree of the
+// buffer (tile i - 2 read back) and for each full[.], so no CTA-wide barrier sits between a block landing and its MMAs.
+// CTA-wide barriers only where the B operand changes (a CTA's contiguous range crosses into the next limb at most once or twice).
 __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, int ell, int limbs2, int count, int G, int KS,
                                                                 const u64 *const *__restrict__ in, const unsigned char *__restrict__ Bt,
                                                                 u64 *const *__restrict__ out) {
@@ -348,12 +350,10 @@ __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, 
     __shared__ __align__(8) unsigned long long mbar_store[LC5_RING + 4 + 2];
     __shared__ uint32_t tmem_slot;
     __shared__ const u64 *ptr[64];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n = T.n;
+    const int tid = threadIdx.x, warp = tid >> 5, n = T.n;
     const bool producer = tid < LC5_THREADS;
     const int KB = (KS + 3) >> 2, tl_log = T.logn - 7; // tiles per limb = n / 128 (a power of two)
-    const int lag = 3;                                 // granule g is retired at iteration g + lag
-    const int row = 32 * (warp & 3) + lane, q = warp >> 2; // epilogue role: outputs 2q, 2q + 1
-    const int lrow = tid & 127, jg = (tid >> 7) & 3;       // loader role
+    const int row = tid & 127, g = (tid >> 7) & 3;     // coefficient row (= TMEM lane), K block copied / output pair read back
     unsigned char *base = lc5_raw + ((1024u - (smem_u32(lc5_raw) & 1023u)) & 1023u);
     unsigned char *sB = base, *sA = base + 4 * LC5_BBLOCK;
     const uint32_t full0 = smem_u32(&mbar_store[0]), done0 = full0 + 8 * LC5_RING, tfree0 = done0 + 8 * 4;
@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(2 * LC5_N) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    if (tid < LC5_RING) mbar_init(full0 + 8 * tid, LC5_THREADS);
+    if (tid < LC5_RING) mbar_init(full0 + 8 * tid, 128);
     else if (tid < LC5_RING + 4) mbar_init(full0 + 8 * tid, 1);
     else if (tid < LC5_RING + 6) mbar_init(full0 + 8 * tid, LC5_THREADS);
     if (tid < 64) ptr[tid] = in[tid < count ? tid : 0]; // padding reads input 0 (its weights are zero)
@@ -371,43 +371,36 @@ __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, 
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_slot;
     const uint32_t idesc = (2u << 4) | ((uint32_t)(LC5_N >> 3) << 17) | ((uint32_t)(BC5_M >> 4) << 24);
-    // this CTA's contiguous range of tiles in (limb-polynomial, tile) order, and of granules
+    // this CTA's contiguous range of tiles in (limb-polynomial, tile) order
     const long long total_tiles = (long long)limbs2 << tl_log;
     const int t_begin = (int)(total_tiles * blockIdx.x / gridDim.x), t_end = (int)(total_tiles * (blockIdx.x + 1) / gridDim.x);
-    const int total = (t_end - t_begin) * KB;
+    const int ntiles = t_end - t_begin;
+    const int ncopy = min(16, 4 * KS - 16 * g); // inputs of this thread's K block (<= 0: the group only takes part in the epilogue)
+    // ring slot of (tile i, K block g): ((i % 3) * 4 + g); row base inside the slot with the swizzle term of this row folded in
+    const uint32_t a_row = smem_u32(sA) + g * LC5_GRAN + (row >> 3) * 1024 + (row & 7) * 128 + ((row & 7) << 4);
 
-    // the three walks over this CTA's granules (fetch, issue / signal, retire) keep their own (tile, K block, ring slot) counters
-    int f_gi = 0, f_tile = t_begin, f_kb = 0, f_slot = 0;
-    auto fetch = [&]() { // next granule -> its ring slot
-        if (f_gi < total) {
-            const size_t goff = (size_t)(f_tile >> tl_log) * n + (size_t)(f_tile & ((1 << tl_log) - 1)) * BC5_M + lrow;
-            const uint32_t sdst = smem_u32(sA) + f_slot * LC5_GRAN + bc5_swz(lrow, 8 * jg);
-            const u64 *const *pp = ptr + 16 * f_kb + jg;
+    auto fetch = [&](int i) { // K block g of tile i -> its ring slot
+        if (i < ntiles && ncopy > 0) {
+            const int tile = t_begin + i;
+            const size_t goff = (size_t)(tile >> tl_log) * n + (size_t)(tile & ((1 << tl_log) - 1)) * BC5_M + row;
+            const uint32_t sdst = a_row + (uint32_t)(i % 3) * (4 * LC5_GRAN);
+            const u64 *const *pp = ptr + 16 * g;
 #pragma unroll
-            for (int i = 0; i < 4; i++) // input 16 kb + jg + 4 i: 32 bytes further along the row, i.e. two 16-byte chunks (XOR 2 i)
-                if (16 * f_kb + jg + 4 * i < 4 * KS) bc5_cp8(sdst ^ (uint32_t)(i << 5), pp[4 * i] + goff);
-            if (++f_kb == KB) f_kb = 0, f_tile++;
-            if (++f_slot == LC5_RING) f_slot = 0;
+            for (int jl = 0; jl < 16; jl++) // input jl of the block: 16-byte chunk jl >> 1 (XOR row & 7, folded into a_row), half jl & 1
+                if (jl < ncopy) bc5_cp8((sdst ^ (uint32_t)((jl >> 1) << 4)) + ((jl & 1) << 3), pp[jl] + goff);
         }
-        f_gi++;
-        asm volatile("cp.async.commit_group;" ::: "memory"); // one group per granule (empty past the end)
+        asm volatile("cp.async.commit_group;" ::: "memory"); // one group per tile (empty past the end)
     };
-    if (producer)
-        for (int gi = 0; gi < LC5_RING - lag; gi++) fetch();
+    if (producer) fetch(0), fetch(1);
 
-    int cur_lp = -1, next_epi = 0;
+    int cur_lp = -1;
     ModConst m = T.mc[0];
     int np = 8;
-    // granule ge: wait for its MMAs (its ring slot is then free); if it closed a tile, read that tile's accumulators back
-    int r_tl = 0, r_kb = 0;
-    auto retire = [&](int ge) {
-        mbar_wait(done0 + 8 * (ge & 3), (ge >> 2) & 1);
-        const int tl = r_tl, kb = r_kb;
-        if (++r_kb == KB) r_kb = 0, r_tl++;
-        if (kb != KB - 1) return;
+    auto retire = [&](int i) { // tile i: wait for its MMAs (its slots are free again), read the accumulators back, store
+        mbar_wait(done0 + 8 * (i & 3), (i >> 2) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int tile = t_begin + tl;
-        const uint32_t tbase = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (tl & 1) * LC5_N + 2 * q;
+        const int tile = t_begin + i;
+        const uint32_t tbase = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (i & 1) * LC5_N + 2 * g;
         uint32_t s[8][2];
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -416,58 +409,60 @@ __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, 
         }
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        mbar_arrive(tfree0 + 8 * (tl & 1)); // this thread is done with the TMEM buffer
+        mbar_arrive(tfree0 + 8 * (i & 1)); // this thread is done with the TMEM buffer
         const size_t at = (size_t)(tile >> tl_log) * n + (size_t)(tile & ((1 << tl_log) - 1)) * BC5_M + row;
 #pragma unroll
         for (int k = 0; k < 2; k++) {
-            const int g = 2 * q + k;
-            if (g >= G) continue;
+            const int o = 2 * g + k;
+            if (o >= G) continue;
             uint32_t sv[8];
 #pragma unroll
             for (int b = 0; b < 8; b++) sv[b] = s[b][k];
             const u64 lo4 = bc5_lo(sv);
             const u64 hi4 = mad_wide(sv[7], 1u << 24, mad_wide(sv[6], 1u << 16, mad_wide(sv[5], 1u << 8, (u64)sv[4])));
             const u64 vlo = lo4 + (hi4 << 32), vhi = (hi4 >> 32) + (vlo < lo4);
-            out[g][at] = reduce128(vhi, vlo, m);
+            out[o][at] = reduce128(vhi, vlo, m);
         }
     };
-    int tl = 0, kb = 0, slot = 0, slot_phase = 0;
+    int retired = 0, i3 = 0, phase3 = 0; // i3 = i % 3, phase3 = (i / 3) & 1
 #pragma unroll 1
-    for (int gi = 0; gi < total + lag; gi++, (++kb == KB ? (kb = 0, tl++) : 0), (++slot == LC5_RING ? (slot = 0, slot_phase ^= 1) : 0)) {
-        const int lp = (t_begin + tl) >> tl_log;
-        if (gi < total && kb == 0 && lp != cur_lp) { // new limb: everything that used the old B operand and modulus finishes first
+    for (int i = 0; i < ntiles + 1; i++, (++i3 == 3 ? (i3 = 0, phase3 ^= 1) : 0)) {
+        const int lp = (t_begin + i) >> tl_log;
+        if (i < ntiles && lp != cur_lp) { // new limb: everything that used the old B operand and modulus finishes first
             if (producer)
-                while (next_epi < gi) retire(next_epi++);
+                while (retired < i) retire(retired++);
             __syncthreads();
             cur_lp = lp;
             const int li = lp % ell;
             m = T.mc[li];
             np = (int)(m.bits + 7) >> 3;
             if (producer) {
-                const uint4 *g = reinterpret_cast<const uint4 *>(Bt + (size_t)li * KB * LC5_BBLOCK);
+                const uint4 *gsrc = reinterpret_cast<const uint4 *>(Bt + (size_t)li * KB * LC5_BBLOCK);
                 uint4 *sdst = reinterpret_cast<uint4 *>(sB);
-                for (int i = tid; i < KB * (LC5_BBLOCK / 16); i += LC5_THREADS) sdst[i] = g[i];
+                for (int k = tid; k < KB * (LC5_BBLOCK / 16); k += LC5_THREADS) sdst[k] = gsrc[k];
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             }
             __syncthreads();
         }
         if (producer) {
-            if (gi < total) { // this thread's part of granule gi has landed (RING - lag + gi groups committed so far)
-                asm volatile("cp.async.wait_group %0;" ::"n"(LC5_RING - 4) : "memory");
+            if (i < ntiles && ncopy > 0) { // this thread's part of tile i has landed (2 + i groups committed so far)
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_arrive(full0 + 8 * slot);
+                mbar_arrive(full0 + 8 * (i3 * 4 + g));
             }
-            while (next_epi <= gi - lag && next_epi < total) retire(next_epi++);
-            fetch(); // granule gi + RING - lag, into the slot of granule gi - lag
-        } else if (tid == LC5_THREADS && gi < total) {
-            mbar_wait(full0 + 8 * slot, slot_phase);
-            if (kb == 0 && tl >= 2) mbar_wait(tfree0 + 8 * (tl & 1), ((tl >> 1) - 1) & 1); // the epilogue of tile tl - 2 has read this buffer
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t aaddr = smem_u32(sA) + slot * LC5_GRAN, baddr = smem_u32(sB + kb * LC5_BBLOCK);
-            const int steps = min(4, KS - 4 * kb);
-            for (int ks = 0; ks < steps; ks++)
-                bc5_mma(tmem + (tl & 1) * LC5_N, bc5_desc(aaddr + ks * 32), bc5_desc(baddr + ks * 32), idesc, (kb | ks) != 0);
-            bc5_commit(done0 + 8 * (gi & 3));
+            while (retired < i) retire(retired++); // tile i - 1
+            fetch(i + 2);                           // into the slots tile i - 1 occupied
+        } else if (tid == LC5_THREADS && i < ntiles) {
+            if (i >= 2) mbar_wait(tfree0 + 8 * (i & 1), ((i >> 1) - 1) & 1); // tile i - 2 has been read out of this TMEM buffer
+            for (int kb = 0; kb < KB; kb++) {
+                mbar_wait(full0 + 8 * (i3 * 4 + kb), phase3);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t aaddr = smem_u32(sA) + (i3 * 4 + kb) * LC5_GRAN, baddr = smem_u32(sB + kb * LC5_BBLOCK);
+                const int steps = min(4, KS - 4 * kb);
+                for (int ks = 0; ks < steps; ks++)
+                    bc5_mma(tmem + (i & 1) * LC5_N, bc5_desc(aaddr + ks * 32), bc5_desc(baddr + ks * 32), idesc, (kb | ks) != 0);
+            }
+            bc5_commit(done0 + 8 * (i & 3));
         }
         if (!producer) __syncwarp(); // the idle lanes of the issuing warp stay with lane 0
     }
