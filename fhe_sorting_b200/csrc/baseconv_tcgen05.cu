@@ -472,9 +472,10 @@ __global__ void __launch_bounds__(LC5_THREADS + 32, 1) lc_tc_t5(DeviceTables T, 
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * LC5_N) : "memory");
 }
 
-// FHEB200_LC_TCGEN05: 0 = never, 1 = whenever the shape is covered, unset = default selection (see k_lincomb_tc)
+// FHEB200_LC_TCGEN05: 0 = never, unset or 1 = whenever the shape is covered (the default since it measured faster than lc_tc_ring
+// at every size tried: profiles/r02/lincomb_tcgen05.txt)
 int lc5_mode() {
-    static const int m = [] { const char *e = getenv("FHEB200_LC_TCGEN05"); return e ? (*e == '1' ? 1 : 0) : 2; }();
+    static const int m = [] { const char *e = getenv("FHEB200_LC_TCGEN05"); return e ? (*e == '0' ? 0 : 1) : 1; }();
     return m;
 }
 // scratch: at least lincomb_tc_scratch_words(ell, count) words
