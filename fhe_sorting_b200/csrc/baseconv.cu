@@ -80,18 +80,19 @@ __global__ void __launch_bounds__(BC_WARPS * 32) bc_convert(DeviceTables T, Conv
     // A fragments: lane (g, tq) holds the (tq & 1) half of sources 4 ks + (tq >> 1) and + 2, rows g and g + 8 of each M tile
     uint32_t a[BC_MT][KS][4];
     {
-        const uint32_t *s32 = reinterpret_cast<const uint32_t *>(I.src);
-        const int half = tq & 1;
+        const uint32_t *s32 = reinterpret_cast<const uint32_t *>(I.src), *e32 = reinterpret_cast<const uint32_t *>(I.extra);
+        const int half = tq & 1, nreal = C.nsrc - (e32 ? 1 : 0);
+        auto word = [&](int s, size_t r) -> uint32_t { // 32-bit half of coefficient r of source s
+            if (s < nreal) return s32[2 * ((size_t)s * n + r) + half];
+            return (e32 && s == nreal) ? e32[2 * r + half] : 0u;
+        };
 #pragma unroll
         for (int ks = 0; ks < KS; ks++) {
             const int s0 = 4 * ks + (tq >> 1), s1 = s0 + 2;
 #pragma unroll
             for (int mt = 0; mt < BC_MT; mt++) {
                 const size_t r0 = (size_t)(coef0 + 16 * mt + g), r1 = r0 + 8;
-                a[mt][ks][0] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r0) + half] : 0u;
-                a[mt][ks][1] = s0 < C.nsrc ? s32[2 * ((size_t)s0 * n + r1) + half] : 0u;
-                a[mt][ks][2] = s1 < C.nsrc ? s32[2 * ((size_t)s1 * n + r0) + half] : 0u;
-                a[mt][ks][3] = s1 < C.nsrc ? s32[2 * ((size_t)s1 * n + r1) + half] : 0u;
+                a[mt][ks][0] = word(s0, r0), a[mt][ks][1] = word(s0, r1), a[mt][ks][2] = word(s1, r0), a[mt][ks][3] = word(s1, r1);
             }
         }
     }
@@ -491,6 +492,19 @@ void k_lincomb_tc(const DeviceTables &T, int ell, int limbs2, int count, int G, 
     g_launches++, lc_tc<<<grid, LC_WARPS * 32, sizeof(u64) * 4 * KS, st>>>(T, ell, count, G, KS, in, reinterpret_cast<const uint2 *>(scratch), out);
 }
 
+__global__ void __launch_bounds__(256) bc_lift_overflow(DeviceTables T, DevicePlan P, const u64 *__restrict__ acc, u64 *__restrict__ u) {
+    const int b = blockIdx.y, n = T.n;
+    const int x = blockIdx.x * 256 + threadIdx.x;
+    if (x >= n) return;
+    const u64 *src = acc + ((size_t)b * P.width + P.ell) * n + x;
+    double v = 0.0;
+    for (int j = 0; j < P.K; j++) v = fma((double)src[(size_t)j * n], __ldg(P.r_recip + j), v);
+    u[(size_t)b * n + x] = (u64)__double2ll_rn(v);
+}
+void k_lift_overflow(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *u, cudaStream_t st) {
+    g_launches++, bc_lift_overflow<<<dim3((T.n + 255) / 256, 2), 256, 0, st>>>(T, P, acc, u);
+}
+
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st) {
     // FHEB200_BC_PERSIST=1: persistent CTAs with the B fragments in shared memory (bc_convert_p); default: one
     // 32-coefficient tile per warp, operands straight from global memory (bc_convert)
@@ -499,7 +513,9 @@ void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS,
     int NT = 0;
     for (int i = 0; i < count; i++) NT = std::max(NT, A.inst[i].tab.NT);
     const size_t smem = bcp_smem(KS, NT);
-    if (persist && BC_MT == 2 && T.n % (16 * BC_MT * BCP_WARPS) == 0 && smem <= 110 * 1024) {
+    bool has_extra = false;
+    for (int i = 0; i < count; i++) has_extra = has_extra || A.inst[i].extra != nullptr;
+    if (persist && !has_extra && BC_MT == 2 && T.n % (16 * BC_MT * BCP_WARPS) == 0 && smem <= 110 * 1024) {
         static int sms = [] { int d = 0, v = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d); return v; }();
         const int tiles = T.n / (16 * BC_MT * BCP_WARPS);
         const dim3 grid(std::max(1, std::min(tiles, 2 * sms / count)), count);
@@ -546,7 +562,8 @@ void k_modup_tc(const DeviceTables &T, const DevicePlan &P, const u64 *coef, con
     }
 }
 // acc: [2][width][n] with the P limbs already through the inverse NTT scaled by DevicePlan::down_scale
-void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st) {
+// extra (merged plans): [2][n] overflow counts, the table's last source
+void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st, const u64 *extra) {
     const size_t n = T.n;
     ConvArgs A;
     for (int b = 0; b < 2; b++) {
@@ -554,6 +571,7 @@ void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *ac
         I.tab = P.down;
         I.src = acc + ((size_t)b * P.width + P.ell) * n;
         I.dst = conv + (size_t)b * P.ell * n;
+        I.extra = extra ? extra + (size_t)b * n : nullptr;
     }
     k_base_convert(T, A, 2, P.down.KS, st);
 }

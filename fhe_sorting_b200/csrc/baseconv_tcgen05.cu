@@ -275,7 +275,7 @@ bool k_base_convert_tcgen05(const DeviceTables &T, const ConvArgs &A, int count,
     Bc5Tables BT;
     for (int i = 0; i < count; i++) {
         if (A.inst[i].tab.KS != KS) return false;
-        if (!A.inst[i].tab.B5) return false;
+        if (!A.inst[i].tab.B5 || A.inst[i].extra) return false;
         BT.bt[i] = A.inst[i].tab.B5;
     }
     static int sms = [] { int d = 0, v = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d); return v; }();

@@ -241,6 +241,7 @@ int fheb200_ct_set_slots(fheb200_ct *ct, int slots) {
 BIN(fheb200_eval_add, ctx->c->add(a->c, b->c))
 BIN(fheb200_eval_sub, ctx->c->sub(a->c, b->c))
 BIN(fheb200_eval_mult, ctx->c->mult(a->c, b->c))
+BIN(fheb200_eval_mult_rescaled, ctx->c->relinearize_reduced(ctx->c->mult_lazy(a->c, b->c)))
 
 int fheb200_eval_add_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
     GUARD({ need(ctx, "ctx"); need(a, "a"); need(p, "p"); *out = wrap(ctx->c->add_pt(a->c, p->p, false)); })

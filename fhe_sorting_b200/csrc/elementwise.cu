@@ -49,6 +49,14 @@ __global__ void __launch_bounds__(EW_THREADS) ew_mul_scalar(DeviceTables T, cons
     A.x = shoup_mul(A.x, w, ws, q), A.y = shoup_mul(A.y, w, ws, q);
     st2(o, x, A);
 }
+// io += a * s (per-limb scalar): lifts the unswitched polynomials of a relinearisation into the QP accumulator (times P)
+__global__ void __launch_bounds__(EW_THREADS) ew_scalar_mad(DeviceTables T, const u64 *a, LimbScalars s, u64 *io) {
+    EW_INDEX
+    const u64 q = T.mc[limb].q, w = s.v[limb], ws = s.s[limb];
+    v2 A = ld2(a, x), O = ld2(io, x);
+    O.x = add_mod(O.x, shoup_mul(A.x, w, ws, q), q), O.y = add_mod(O.y, shoup_mul(A.y, w, ws, q), q);
+    st2(io, x, O);
+}
 __global__ void __launch_bounds__(EW_THREADS) ew_add_scalar(DeviceTables T, const u64 *a, LimbScalars s, u64 *o) {
     EW_INDEX
     const u64 q = T.mc[limb].q, w = s.v[limb];
@@ -419,6 +427,9 @@ void k_negate(const DeviceTables &T, int ell, const u64 *a, u64 *out, cudaStream
 }
 void k_mul_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
     g_launches++, ew_mul_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);
+}
+void k_scalar_mad(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *io, cudaStream_t st) {
+    g_launches++, ew_scalar_mad<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, io);
 }
 void k_add_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st) {
     g_launches++, ew_add_scalar<<<ew_grid(T, ell), EW_THREADS, 0, st>>>(T, a, s, out);

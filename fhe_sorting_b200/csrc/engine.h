@@ -144,6 +144,7 @@ class Context : public std::enable_shared_from_this<Context> {
     Ct mult(const Ct &a, const Ct &b);       // EvalMult / EvalMultAndRelinearize / EvalSquare (a.get()==b.get())
     Ct mult_lazy(const Ct &a, const Ct &b);  // tensor product only: 3 polynomials, relinearise() later
     Ct relinearize(const Ct &a);             // 3 -> 2 polynomials (no-op on 2)
+    Ct relinearize_reduced(const Ct &a);     // == reduced(relinearize(a)) up to rounding: one ModDown by P * q_last
     Ct add_lazy(const Ct &a, const Ct &b);   // EvalAdd where either side may still carry its s^2 polynomial
     Ct mult_pt(const Ct &a, const Pt &p);
     Ct mult_pt_add(const Ct &acc, const Ct &a, const Pt &p); // acc + a * p, one pass
@@ -169,6 +170,7 @@ class Context : public std::enable_shared_from_this<Context> {
                     std::vector<std::tuple<int, double, Mem>> *qp_cache = nullptr);
     Mem encode_qp(const Plaintext &pt, int ell, double scale);   // [ell + K][n]: Q limbs 0..ell-1, then the P limbs
     void moddown(int ell, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois);
+    void moddown_plan(const DevicePlan &D, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois);
     std::map<int, std::shared_ptr<BootState>> boot;
 
     // ---- polynomial evaluation (poly_eval.cpp)
@@ -178,6 +180,8 @@ class Context : public std::enable_shared_from_this<Context> {
 
     // ---- raw access for parity tests and benchmarks
     const DevicePlan &plan(int ell);
+    const DevicePlan &plan_merged(int ell); // ModDown by P * q_{ell-1}
+    ConvTable make_conv_table(const std::vector<u64> &C, int cstride, int nsrc, std::vector<std::pair<int, int>> tg, const std::vector<int> &tpos);
     const uint32_t *desc(const std::vector<uint32_t> &d);
     Mem alloc(size_t words);
     void sync();
@@ -253,7 +257,7 @@ class Context : public std::enable_shared_from_this<Context> {
     Pt new_plaintext(size_t count, int nsd, int level, int slots);
     std::map<int, std::pair<double2 *, int *>> fft_tabs_; // per slot count: (ksi, rot) tables of the special FFT in HBM
     std::pair<double2 *, int *> fft_device_tables(int slots);
-    std::map<int, DevicePlan> plans_;
+    std::map<int, DevicePlan> plans_, plans_m_;
     std::map<std::vector<uint32_t>, uint32_t *> descs_;
     std::vector<void *> owned_;
     void *owned_alloc(size_t bytes, const void *init);

@@ -307,6 +307,58 @@ const uint32_t *Context::desc(const std::vector<uint32_t> &d) {
     return p;
 }
 
+// C[src * cstride + tgt_pos]; targets = (output slot, modulus index) pairs (tensor-core base conversion tables, baseconv.cu)
+ConvTable Context::make_conv_table(const std::vector<u64> &C, int cstride, int nsrc, std::vector<std::pair<int, int>> tg,
+                               const std::vector<int> &tpos) {
+typedef unsigned __int128 u128;
+auto bits_of = [&](int qp) { return P->mc[qp].bits; };
+    // targets needing 8 byte planes first, so that as few column groups as possible carry them
+    std::vector<int> order(tg.size());
+    for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return (bits_of(tg[a].second) > 48) > (bits_of(tg[b].second) > 48); });
+    ConvTable t;
+    t.nsrc = nsrc, t.KS = (nsrc + 3) / 4, t.NT = ((int)tg.size() + 7) / 8;
+    std::vector<int> tslot(t.NT * 8, -1), tqp(t.NT * 8, 0);
+    std::vector<unsigned char> planes(t.NT, 6);
+    std::vector<uint32_t> B((size_t)t.KS * t.NT * 8 * 32 * 2, 0);
+    for (size_t c = 0; c < order.size(); c++) {
+        tslot[c] = tg[order[c]].first, tqp[c] = tg[order[c]].second;
+        if (bits_of(tqp[c]) > 48) planes[c / 8] = 8;
+    }
+    for (int ks = 0; ks < t.KS; ks++)
+        for (int nt = 0; nt < t.NT; nt++)
+            for (int lane = 0; lane < 32; lane++) {
+                const int g = lane >> 2, tq = lane & 3, col = 8 * nt + g;
+                if (col >= (int)order.size()) continue;
+                const u64 p = P->moduli[tqp[col]];
+                for (int reg = 0; reg < 2; reg++) {
+                    const int j = 4 * ks + 2 * reg + (tq >> 1);
+                    if (j >= nsrc) continue;
+                    const u64 c0 = C[(size_t)j * cstride + tpos[order[col]]] % p;
+                    for (int i = 0; i < 4; i++) {
+                        const int a = 4 * (tq & 1) + i;
+                        const u64 cp = (u64)(((u128)c0 << (8 * a)) % p);
+                        for (int b = 0; b < 8; b++)
+                            B[(((size_t)(ks * t.NT + nt) * 8 + b) * 32 + lane) * 2 + reg] |= (uint32_t)((cp >> (8 * b)) & 0xff) << (8 * i);
+                    }
+                }
+            }
+    t.B = (const uint2 *)owned_alloc(sizeof(uint32_t) * B.size(), B.data());
+    t.tslot = (const int *)owned_alloc(sizeof(int) * tslot.size(), tslot.data());
+    std::vector<uint32_t> tconst(tqp.size() * 4, 0);
+    for (size_t c = 0; c < order.size(); c++) {
+        const u64 p = P->moduli[tqp[c]];
+        const int bits = bits_of(tqp[c]);
+        if (bits < 17 || bits > 62) throw std::runtime_error("fheb200: modulus size outside the base conversion's range");
+        tconst[4 * c] = (uint32_t)p, tconst[4 * c + 1] = (uint32_t)(p >> 32);
+        tconst[4 * c + 2] = (uint32_t)(((u128)1 << (bits + 31)) / p), tconst[4 * c + 3] = (uint32_t)bits;
+    }
+    t.tconst = (const uint4 *)owned_alloc(sizeof(uint32_t) * tconst.size(), tconst.data());
+    t.planes = (const unsigned char *)owned_alloc(planes.size(), planes.data());
+    if (unsigned char *b5 = bc5_make_table(t.B, t.KS, t.NT)) owned_.push_back(b5), t.B5 = b5;
+    return t;
+}
+
 const DevicePlan &Context::plan(int ell) {
     std::lock_guard<std::recursive_mutex> g(mu);
     auto it = plans_.find(ell);
@@ -351,58 +403,7 @@ const DevicePlan &Context::plan(int ell) {
         for (int b = 0; b < 2; b++) dp2.push_back(((uint32_t)(b * H.width + ell + k) << 8) | (uint32_t)(P->L + k));
     for (int i = 0; i < ell; i++)
         for (int b = 0; b < 2; b++) dq2.push_back(((uint32_t)(b * ell + i) << 8) | (uint32_t)i);
-    // ---- tensor-core base conversion tables (baseconv.cu)
     typedef unsigned __int128 u128;
-    auto bits_of = [&](int qp) { return P->mc[qp].bits; };
-    // C[src * cstride + tgt_pos]; targets = (output slot, modulus index) pairs
-    auto make_conv_table = [&](const std::vector<u64> &C, int cstride, int nsrc, std::vector<std::pair<int, int>> tg,
-                               const std::vector<int> &tpos) {
-        // targets needing 8 byte planes first, so that as few column groups as possible carry them
-        std::vector<int> order(tg.size());
-        for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
-        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return (bits_of(tg[a].second) > 48) > (bits_of(tg[b].second) > 48); });
-        ConvTable t;
-        t.nsrc = nsrc, t.KS = (nsrc + 3) / 4, t.NT = ((int)tg.size() + 7) / 8;
-        std::vector<int> tslot(t.NT * 8, -1), tqp(t.NT * 8, 0);
-        std::vector<unsigned char> planes(t.NT, 6);
-        std::vector<uint32_t> B((size_t)t.KS * t.NT * 8 * 32 * 2, 0);
-        for (size_t c = 0; c < order.size(); c++) {
-            tslot[c] = tg[order[c]].first, tqp[c] = tg[order[c]].second;
-            if (bits_of(tqp[c]) > 48) planes[c / 8] = 8;
-        }
-        for (int ks = 0; ks < t.KS; ks++)
-            for (int nt = 0; nt < t.NT; nt++)
-                for (int lane = 0; lane < 32; lane++) {
-                    const int g = lane >> 2, tq = lane & 3, col = 8 * nt + g;
-                    if (col >= (int)order.size()) continue;
-                    const u64 p = P->moduli[tqp[col]];
-                    for (int reg = 0; reg < 2; reg++) {
-                        const int j = 4 * ks + 2 * reg + (tq >> 1);
-                        if (j >= nsrc) continue;
-                        const u64 c0 = C[(size_t)j * cstride + tpos[order[col]]] % p;
-                        for (int i = 0; i < 4; i++) {
-                            const int a = 4 * (tq & 1) + i;
-                            const u64 cp = (u64)(((u128)c0 << (8 * a)) % p);
-                            for (int b = 0; b < 8; b++)
-                                B[(((size_t)(ks * t.NT + nt) * 8 + b) * 32 + lane) * 2 + reg] |= (uint32_t)((cp >> (8 * b)) & 0xff) << (8 * i);
-                        }
-                    }
-                }
-        t.B = (const uint2 *)owned_alloc(sizeof(uint32_t) * B.size(), B.data());
-        t.tslot = (const int *)owned_alloc(sizeof(int) * tslot.size(), tslot.data());
-        std::vector<uint32_t> tconst(tqp.size() * 4, 0);
-        for (size_t c = 0; c < order.size(); c++) {
-            const u64 p = P->moduli[tqp[c]];
-            const int bits = bits_of(tqp[c]);
-            if (bits < 17 || bits > 62) throw std::runtime_error("fheb200: modulus size outside the base conversion's range");
-            tconst[4 * c] = (uint32_t)p, tconst[4 * c + 1] = (uint32_t)(p >> 32);
-            tconst[4 * c + 2] = (uint32_t)(((u128)1 << (bits + 31)) / p), tconst[4 * c + 3] = (uint32_t)bits;
-        }
-        t.tconst = (const uint4 *)owned_alloc(sizeof(uint32_t) * tconst.size(), tconst.data());
-        t.planes = (const unsigned char *)owned_alloc(planes.size(), planes.data());
-        if (unsigned char *b5 = bc5_make_table(t.B, t.KS, t.NT)) owned_.push_back(b5), t.B5 = b5;
-        return t;
-    };
     auto shoup_of = [&](u64 v, u64 q) { return (u64)(((u128)v << 64) / q); };
     auto mulmod = [&](u64 a, u64 b, u64 q) { return (u64)((u128)a * b % q); };
     {
@@ -438,6 +439,66 @@ const DevicePlan &Context::plan(int ell) {
     D.desc_p2 = (uint32_t *)desc(dp2);
     D.desc_q2 = (uint32_t *)desc(dq2);
     return plans_.emplace(ell, D).first->second;
+}
+
+// ModDown by R = P * q_{ell-1} (relinearise-and-rescale in one division, engine_arith.cu: relinearize_reduced): the same ModDown
+// routines run on a plan whose "special" limbs are q_{ell-1} followed by the K primes of P (positions ell-1 .. ell+K-1 of an
+// accumulator, contiguous) and whose ordinary limbs are q_0 .. q_{ell-2}.  Only the fields ModDown reads are filled.
+const DevicePlan &Context::plan_merged(int ell) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = plans_m_.find(ell);
+    if (it != plans_m_.end()) return it->second;
+    if (ell < 2) throw std::out_of_range("merged ModDown plan: needs at least two limbs");
+    const LevelPlan &H = P->plan(ell);
+    const int K1 = P->K + 1, le = ell - 1;
+    std::vector<int> sp; // modulus index of special limb j
+    sp.push_back(ell - 1);
+    for (int k = 0; k < P->K; k++) sp.push_back(P->L + k);
+    auto prod_except = [&](int skip, u64 mod) { // product of the special moduli except sp[skip] (skip < 0: all), modulo mod
+        u64 r = 1;
+        for (int x = 0; x < K1; x++)
+            if (x != skip) r = mulmod_h(r, P->moduli[sp[x]] % mod, mod);
+        return r;
+    };
+    DevicePlan D;
+    D.ell = le, D.beta = 0, D.width = H.width, D.K = K1;
+    D.qp = (int *)owned_alloc(sizeof(int) * H.qp.size(), H.qp.data());
+    // conversion table with one more source: u = round(sum_j y_j / r_j) times (-R mod q_i) makes the lift exact (centred)
+    std::vector<u64> r_hat((size_t)(K1 + 1) * le), r_inv(le), r_inv_s(le), down(4 * (size_t)K1, 0);
+    std::vector<double> recip(K1);
+    for (int j = 0; j < K1; j++) {
+        const u64 rj = P->moduli[sp[j]];
+        const u64 hat_inv = invmod_h(prod_except(j, rj), rj);
+        const u64 v = mulmod_h(P->n_inv[sp[j]], hat_inv, rj);
+        for (int b = 0; b < 2; b++) down[2 * j + b] = v, down[2 * K1 + 2 * j + b] = shoup_h(v, rj); // entry order of desc_p2
+        for (int i = 0; i < le; i++) r_hat[(size_t)j * le + i] = prod_except(j, P->moduli[i]);
+        recip[j] = (double)(1.0L / (long double)rj);
+    }
+    for (int i = 0; i < le; i++) {
+        const u64 qi = P->moduli[i], R = prod_except(-1, qi);
+        r_hat[(size_t)K1 * le + i] = R ? qi - R : 0;
+    }
+    D.exact_lift = 1;
+    D.r_recip = (double *)owned_alloc(sizeof(double) * K1, recip.data());
+    for (int i = 0; i < le; i++) {
+        const u64 qi = P->moduli[i];
+        r_inv[i] = invmod_h(prod_except(-1, qi), qi), r_inv_s[i] = shoup_h(r_inv[i], qi);
+    }
+    D.p_inv = (u64 *)owned_alloc(sizeof(u64) * le, r_inv.data());
+    D.p_inv_s = (u64 *)owned_alloc(sizeof(u64) * le, r_inv_s.data());
+    D.down_scale = (u64 *)owned_alloc(sizeof(u64) * down.size(), down.data());
+    std::vector<std::pair<int, int>> tg;
+    std::vector<int> tpos;
+    for (int i = 0; i < le; i++) tg.push_back({i, i}), tpos.push_back(i);
+    D.down = make_conv_table(r_hat, le, K1 + 1, tg, tpos);
+    std::vector<uint32_t> dp2, dq2;
+    for (int j = 0; j < K1; j++)
+        for (int b = 0; b < 2; b++) dp2.push_back(((uint32_t)(b * H.width + le + j) << 8) | (uint32_t)sp[j]);
+    for (int i = 0; i < le; i++)
+        for (int b = 0; b < 2; b++) dq2.push_back(((uint32_t)(b * le + i) << 8) | (uint32_t)i);
+    D.desc_p2 = (uint32_t *)desc(dp2);
+    D.desc_q2 = (uint32_t *)desc(dq2);
+    return plans_m_.emplace(ell, D).first->second;
 }
 
 LimbScalars Context::scalars_for(long double value, int ell, bool shoup) const {

@@ -59,12 +59,20 @@ void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const
 }
 // acc[2][ell + K][n] (evaluation domain, overwritten) -> out_b = sigma_g(round(acc_b / P) + add_b) on the ell Q limbs
 void Context::moddown(int ell, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois) {
-    const DevicePlan &D = plan(ell);
-    const int n = P->n;
+    moddown_plan(plan(ell), acc, add0, add1, out0, out1, galois);
+}
+// D: the level's own plan (special limbs = P) or a merged one (special limbs = q_last and P, Context::plan_merged)
+void Context::moddown_plan(const DevicePlan &D, u64 *acc, const u64 *add0, const u64 *add1, u64 *out0, u64 *out1, uint32_t galois) {
+    const int n = P->n, ell = D.ell;
     Mem conv = alloc((size_t)2 * ell * n);
-    if (tensor_core_conv()) {
+    if (tensor_core_conv() || D.K != P->K) { // (the CUDA-core conversion is instantiated for K special limbs only)
         k_ntt_inv(T, acc, acc, D.desc_p2, 2 * D.K, stream, D.down_scale);
-        k_moddown_conv_tc(T, D, acc, conv->p, stream);
+        Mem over;
+        if (D.exact_lift) { // the quotient is final here (no rescale follows to absorb the lift's overshoot): make the lift exact
+            over = alloc((size_t)2 * n);
+            k_lift_overflow(T, D, acc, over->p, stream);
+        }
+        k_moddown_conv_tc(T, D, acc, conv->p, stream, over ? over->p : nullptr);
     } else {
         k_ntt_inv(T, acc, D.desc_p2, 2 * D.K, stream);
         k_moddown_conv(T, D, acc, conv->p, stream);

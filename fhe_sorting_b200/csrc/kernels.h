@@ -62,6 +62,7 @@ void k_binary(const DeviceTables &T, BinOp op, int ell, const u64 *a, const u64 
 void k_negate(const DeviceTables &T, int ell, const u64 *a, u64 *out, cudaStream_t st);
 void k_mul_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st);
 void k_add_scalar(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *out, cudaStream_t st);
+void k_scalar_mad(const DeviceTables &T, int ell, const u64 *a, const LimbScalars &s, u64 *io, cudaStream_t st); // io += a * s
 // out0/out1 += a0/a1 * pt (pt eval domain) ; accumulate = 0 writes, 1 adds
 void k_mul_pt(const DeviceTables &T, int ell, const u64 *a0, const u64 *a1, const u64 *pt, u64 *o0, u64 *o1,
               int accumulate, cudaStream_t st);
@@ -122,6 +123,8 @@ struct ConvInstance {
     ConvTable tab;
     const u64 *src = nullptr;    // nsrc source limbs [nsrc][n], coefficient domain, already times (Q/q_j)^-1
     u64 *dst = nullptr;          // target limb of column c is dst + tslot[c] * n
+    const u64 *extra = nullptr;  // optional last source (index nsrc - 1) that lives elsewhere: one limb [n] (merged ModDown: the
+                                 // overflow count of the lift, Context::moddown_plan)
     const u64 *copy_src = nullptr; // copy_limbs limbs copied verbatim (ModUp: the digit's own limbs)
     u64 *copy_dst = nullptr;
     int copy_limbs = 0;
@@ -130,6 +133,7 @@ struct ConvArgs {
     ConvInstance inst[8];
 };
 void k_base_convert(const DeviceTables &T, const ConvArgs &A, int count, int KS, cudaStream_t st);
+
 // tcgen05 / TMEM form of the same conversion (baseconv_tcgen05.cu, FHEB200_BC_TCGEN05=1); false = shape not covered
 bool bc5_enabled();
 unsigned char *bc5_make_table(const uint2 *frag, int KS, int NT);
@@ -149,6 +153,8 @@ struct DevicePlan {              // device copy of a LevelPlan
     uint32_t *desc_p2 = nullptr;       // iNTT batch: P limbs of two stacked accumulators [2][width]
     uint32_t *desc_q2 = nullptr;       // NTT batch: Q limbs of two stacked [2][ell] buffers
     ConvTable up[8], down;             // tensor-core base conversion tables per digit / for ModDown
+    int exact_lift = 0;                // merged plan: down has one more source, u = round(sum_j y_j / r_j), with constant -R mod q_i
+    double *r_recip = nullptr;         // [K] 1 / r_j of the special limbs (exact_lift)
     u64 *up_scale = nullptr;           // [ell] + [ell] Shoup: n^-1 (Q_j/q_i)^-1 mod q_i, final scaling of ModUp's inverse NTT
     u64 *down_scale = nullptr;         // [2K] + [2K] Shoup: n^-1 (P/p_k)^-1 mod p_k for the desc_p2 batch
 };
@@ -158,7 +164,10 @@ void k_modup(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const 
              cudaStream_t st);
 // tensor-core variants (baseconv.cu): inputs pre-scaled by the inverse NTT (DevicePlan::up_scale / down_scale)
 void k_modup_tc(const DeviceTables &T, const DevicePlan &P, const u64 *coef, const u64 *c_eval, u64 *digits, cudaStream_t st);
-void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st);
+void k_moddown_conv_tc(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *conv, cudaStream_t st, const u64 *extra = nullptr);
+// u_b[x] = round(sum_j y_j[x] / r_j) over the K special limbs of accumulator b (coefficient domain, already times (R/r_j)^-1):
+// how many multiples of R the fast base conversion of those residues overshoots the centred representative by (Halevi-Polyakov-Shoup)
+void k_lift_overflow(const DeviceTables &T, const DevicePlan &P, const u64 *acc, u64 *u, cudaStream_t st);
 // acc[2][width][n] = sum_j digits[j] * evk[j][{b,a}]   (evk stored at full chain: [digit][2][F][n])
 void k_inner_product(const DeviceTables &T, const DevicePlan &P, const u64 *digits, const u64 *evk, u64 *acc,
                      cudaStream_t st);

@@ -169,7 +169,9 @@ static Ct eval_inner(PSState &S, const Poly &f, int m) {
         g_split_ms += ts.lap();
     }
     Ct cu = weighted_sum(S, c, k - 1);
-    Ct qu = S.C->relinearize(eval_inner(S, q, m - 1)); // a multiplicand has to be relinearised ...
+    // a multiplicand has to be relinearised and brought to degree 1: one merged division where the recursion returned the
+    // unrelinearised degree-2 sum (Context::relinearize_reduced)
+    Ct qu = S.C->relinearize_reduced(eval_inner(S, q, m - 1));
     Ct su = eval_inner(S, s2, m - 1);                   // ... a summand not: it may keep its s^2 polynomial
     Ct left = cu ? S.C->add(S.T2[m - 1], cu) : S.T2[m - 1];
     if (c[0] != 0.0) left = S.C->add_const(left, c[0]);

@@ -325,6 +325,10 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     CT EvalMult(const CT &a, const CT &b) { return binary(fheb200_eval_mult, a, b); }
     CT EvalMultAndRelinearize(const CT &a, const CT &b) { return binary(fheb200_eval_mult, a, b); }
     CT EvalSquare(const CT &a) { return binary(fheb200_eval_mult, a, a); }
+    // Extension (not in OpenFHE): the square already brought to degree 1, i.e. what the next multiplication's lazy ModReduce would
+    // make of it, computed as one division by P * q_last (include/fhe_b200.h: fheb200_eval_mult_rescaled).  For powers that are only
+    // ever multiplied again (x^2, x^4 of the composite-sign polynomials); the reference's drivers keep calling EvalSquare.
+    CT EvalSquareReduced(const CT &a) { return binary(fheb200_eval_mult_rescaled, a, a); }
     CT EvalMult(const CT &a, const Plaintext &p) { return plain(fheb200_eval_mult_plain, a, p); }
     CT EvalMult(const Plaintext &p, const CT &a) { return plain(fheb200_eval_mult_plain, a, p); }
     // extension (not lbcrypto): acc += a * p in one pass; acc may be empty

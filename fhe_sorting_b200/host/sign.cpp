@@ -13,8 +13,8 @@ typedef Ciphertext<DCRTPoly> CT;
 // odd degree-7 polynomial c1 x + c3 x^3 + c5 x^5 + c7 x^7 in depth 3:
 //   y = c1 x + (c3 x) x^2 + ((c5 x) + (c7 x) x^2) x^4       (reference: src/sign.cpp:23-35)
 CT odd7(const CT &x, const CryptoContext<DCRTPoly> &cc, double c1, double c3, double c5, double c7) {
-    CT x2 = cc->EvalSquare(x);
-    CT x4 = cc->EvalSquare(x2);
+    CT x2 = cc->EvalSquareReduced(x); // the even powers are only ever multiplicands: squared and rescaled in one division
+    CT x4 = cc->EvalSquareReduced(x2);
     CT y = cc->EvalMult(x, c1);
     cc->EvalAddInPlace(y, cc->EvalMultAndRelinearize(cc->EvalMult(x, c3), x2));
     CT hi = cc->EvalAdd(cc->EvalMult(x, c5), cc->EvalMultAndRelinearize(cc->EvalMult(x, c7), x2));
@@ -50,12 +50,12 @@ template <> struct Family<4> {
     static CT f(const CT &x, const CryptoContext<DCRTPoly> &cc) {
         static const double c[8] = {3.14208984375,  -7.33154296875, 13.19677734375, -15.71044921875,
                                     12.21923828125, -5.99853515625, 1.69189453125,  -0.20947265625};
-        CT x2 = cc->EvalSquare(x);
+        CT x2 = cc->EvalSquareReduced(x);
         CT t[8];
         for (int i = 0; i < 8; i++) t[i] = cc->EvalMult(x, c[i]);
-        CT x4 = cc->EvalSquare(x2);
+        CT x4 = cc->EvalSquareReduced(x2);
         for (int i = 1; i < 8; i += 2) t[i] = cc->EvalMultAndRelinearize(t[i], x2); // c3 x^3, c7 x^3, c11 x^3, c15 x^3
-        CT x8 = cc->EvalSquare(x4);
+        CT x8 = cc->EvalSquareReduced(x4);
         CT y = cc->EvalAdd(t[0], t[1]);
         cc->EvalAddInPlace(y, cc->EvalMultAndRelinearize(cc->EvalAdd(t[2], t[3]), x4));
         CT hi = cc->EvalAdd(t[4], t[5]);

@@ -293,6 +293,10 @@ class Context(_Handle):
             return self._un("fheb200_eval_mult_plain", a, b.h)
         return self._un("fheb200_eval_mult_const", a, C.c_double(float(b)))
 
+    def mult_rescaled(self, a, b):
+        """EvalMult + the lazy rescale of the product as one ModDown by P * q_last (engine_arith.cu: relinearize_reduced)."""
+        return self._un("fheb200_eval_mult_rescaled", a, b.h)
+
     def square(self, a):
         return self._un("fheb200_eval_mult", a, a.h)
 

@@ -122,6 +122,11 @@ int fheb200_eval_negate(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct **out);
 int fheb200_eval_add_many(fheb200_ctx *ctx, fheb200_ct *const *cts, size_t count, fheb200_ct **out);
 /* EvalMult(ct, ct) / EvalMultAndRelinearize / EvalSquare when a == b (src/sign.cpp:23-33 ; src/sort_algo.h:730) */
 int fheb200_eval_mult(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
+/* EvalMult followed by the rescale FLEXIBLEAUTOEXT would apply before the product is multiplied again (ModReduceInternal), as ONE
+ * division by P * q_last instead of ModDown then rescale: same level and scale as fheb200_eval_rescale(fheb200_eval_mult(a, b)),
+ * integers within a few units of it.  Used by the Paterson-Stockmeyer evaluator behind fheb200_eval_chebyshev_series; no direct
+ * counterpart in the reference's calls. */
+int fheb200_eval_mult_rescaled(fheb200_ctx *ctx, fheb200_ct *a, fheb200_ct *b, fheb200_ct **out);
 /* EvalMult(ct, pt) (src/sort_algo.h:319,344,359,576) */
 int fheb200_eval_mult_plain(fheb200_ctx *ctx, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out);
 /* acc + a * p in one pass: EvalMult(ct, pt) followed by EvalAddInPlace (src/sort_algo.h:269-276, 616-624), bit-identical to

@@ -600,6 +600,7 @@ int fheb200_ct_set_slots(fheb200_ct *ct, int slots) { GUARD({ need(ct, "ct"); ct
 BIN(fheb200_eval_add, add_sub(C, a->c, b->c, false))
 BIN(fheb200_eval_sub, add_sub(C, a->c, b->c, true))
 BIN(fheb200_eval_mult, mult_ct(C, a->c, b->c))
+BIN(fheb200_eval_mult_rescaled, mod_reduce(C, mult_ct(C, a->c, b->c))) // the two-step form the merged division is compared with
 int fheb200_eval_add_plain(fheb200_ctx *c, fheb200_ct *a, fheb200_pt *p, fheb200_ct **out) {
     GUARD({ fheb200_ctx &C = ctx_of(c); need(a, "a"); need(p, "p"); *out = wrap(add_pt(C, a->c, *p, false)); })
 }

@@ -85,6 +85,24 @@ def test_rotate_hoisted_mult_bit_exact_41_limbs(big):
     assert np.array_equal(r0, e0) and np.array_equal(r1, e1), "EvalMult at 40 limbs"
 
 
+def test_mult_rescaled_one_division_41_limbs(big):
+    """fheb200_eval_mult_rescaled at the full parameter set: level / scale of rescale(mult), coefficients within one rounding."""
+    from test_gpu_scheme import _centered_coeff_diff
+    ctx, orc, keys, s = big
+    rng = np.random.default_rng(8)
+    va, vb = rng.uniform(-1, 1, 1024), rng.uniform(-1, 1, 1024)
+    a = ctx.encrypt(keys, ctx.make_plaintext(va, 1, 0, 1024))
+    b = ctx.encrypt(keys, ctx.make_plaintext(vb, 1, 0, 1024))
+    two, one = ctx.rescale(ctx.mult(a, b)), ctx.mult_rescaled(a, b)
+    assert one.info() == two.info() and one.info()["limbs"] == 39
+    assert np.abs(ctx.decrypt(keys, one, 1024) - va * vb).max() < 1e-5
+    assert np.abs(ctx.decrypt(keys, one, 1024) - ctx.decrypt(keys, two, 1024)).max() < 1e-9
+    x0, _ = ctx.ct_export(one)
+    y0, _ = ctx.ct_export(two)
+    worst, same = _centered_coeff_diff(ctx, x0[:3], y0[:3])
+    assert worst <= 1 and same, (worst, same)
+
+
 @pytest.mark.parametrize("n,depth", [(256, 34), (1024, 39)])
 def test_direct_sort_full_parameters(n, depth):
     """tests/DirectSortTest.cpp:172-179 sizes 256 and 1024: ring 2^17, the per-N depth table of src/sort_algo.h:87-201."""

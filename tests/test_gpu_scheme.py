@@ -217,3 +217,40 @@ def test_rotated_plaintext_is_a_galois_permutation_of_the_encoding(env):
     for r in (5, -700):
         got = full.decrypt(k2, full.encrypt(k2, full.rotate_plaintext(b2, r)), 2048)
         assert np.abs(got - np.roll(w, -r)).max() < 1e-7
+
+
+def _centered_coeff_diff(ctx, x, y):
+    """max over limbs and coefficients of |x - y| (centred, coefficient domain) and whether the difference is the same small
+    integer in every limb (x, y: [ell][n] evaluation-domain limbs)"""
+    worst, same = 0, True
+    first = None
+    for i in range(x.shape[0]):
+        q = ctx.moduli[i]
+        d = (ctx.raw_ntt(i, x[i], inverse=True).astype(object) - ctx.raw_ntt(i, y[i], inverse=True).astype(object)) % q
+        d = np.array([int(v) - q if int(v) > q // 2 else int(v) for v in d], dtype=np.int64)
+        worst = max(worst, int(np.abs(d).max()))
+        if first is None:
+            first = d
+        same = same and np.array_equal(d, first)
+    return worst, same
+
+
+def test_mult_rescaled_is_one_division(env):
+    """relinearise + rescale as one ModDown by P * q_last: same level, degree and scale as rescale(mult(a, b)); in the
+    coefficient domain the two results differ by the same small integer in every limb (one rounding instead of two)."""
+    ctx, keys = env
+    rng = np.random.default_rng(5)
+    va, vb = rng.uniform(-1, 1, 8), rng.uniform(-1, 1, 8)
+    a, b = enc(ctx, keys, va), enc(ctx, keys, vb)
+    for _ in range(3):                                   # at several levels
+        two = ctx.rescale(ctx.mult(a, b))
+        one = ctx.mult_rescaled(a, b)
+        assert one.info() == two.info()
+        assert np.abs(ctx.decrypt(keys, one, 8) - va * vb).max() < 1e-9
+        x0, x1 = ctx.ct_export(one)
+        y0, y1 = ctx.ct_export(two)
+        for x, y in ((x0, y0), (x1, y1)):
+            worst, same = _centered_coeff_diff(ctx, x, y)
+            assert worst <= 1 and same, (worst, same)   # exact (centred) lift: at most the double rounding of the two-step form
+        a, vb = one, vb
+        va = va * vb
