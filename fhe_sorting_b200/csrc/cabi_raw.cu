@@ -51,6 +51,7 @@ extern "C" {
 
 unsigned long long fheb200_launch_count(void) { return g_launches.load(); }
 unsigned long long fheb200_algo_bytes(void) { return g_algo_bytes.load(); }
+unsigned long long fheb200_op_count(int which) { return which >= 0 && which < 4 ? g_op_count[which].load() : 0ull; }
 
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words) {
     GUARD({

@@ -227,6 +227,7 @@ Ct Context::relinearize_reduced(const Ct &a) {
     const int n = P->n, ell = a->ell;
     const DevicePlan &D = plan(ell);
     const DevicePlan &Dm = plan_merged(ell);
+    g_op_count[2]++;
     Mem digits = alloc((size_t)D.beta * D.width * n);
     modup(ell, a->poly(2, n), digits->p);
     Mem acc = alloc((size_t)2 * D.width * n);

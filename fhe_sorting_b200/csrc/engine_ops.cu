@@ -55,6 +55,7 @@ void Context::keyswitch_digits(int ell, const u64 *digits, const u64 *evk, const
     const DevicePlan &D = plan(ell);
     Mem acc = alloc((size_t)2 * D.width * P->n);
     k_inner_product(T, D, digits, evk, acc->p, stream);
+    g_op_count[galois == 1u ? 1 : 3]++;
     moddown(ell, acc->p, add0, add1, out0, out1, galois);
 }
 // acc[2][ell + K][n] (evaluation domain, overwritten) -> out_b = sigma_g(round(acc_b / P) + add_b) on the ell Q limbs
@@ -148,6 +149,7 @@ Ct Context::mod_reduce(const Ct &a) {
     LOCK;
     if (a->ell < 2) throw std::runtime_error("rescale: no limbs left (multiplicative depth exhausted)");
     Ct r = new_like(this, a, a->npoly, a->ell - 1);
+    g_op_count[0]++;
     count_algo(8.0 * P->n * a->npoly * (2.0 * a->ell - 1.0));
     rescale_poly(a->ell, a->npoly, a->mem->p, r->mem->p);
     r->nsd = a->nsd - 1;

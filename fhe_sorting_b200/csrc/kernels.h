@@ -15,6 +15,8 @@ extern std::atomic<unsigned long long> g_launches; // kernels launched by this l
 // one sort by its run time for the sort-level roofline fraction.
 extern std::atomic<unsigned long long> g_algo_bytes;
 inline void count_algo(double bytes) { g_algo_bytes += (unsigned long long)bytes; }
+// scheme-operation counters (0: rescales, 1: relinearisations, 2: merged relinearise-and-rescale, 3: rotations / hoisted)
+extern std::atomic<unsigned long long> g_op_count[4];
 
 struct DeviceTables {            // resident per context
     int logn = 0, n = 0, F = 0;  // F = L + K moduli

@@ -31,6 +31,7 @@ namespace fheb200 {
 
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<unsigned long long> g_algo_bytes{0};
+std::atomic<unsigned long long> g_op_count[4];
 
 #ifndef NTT_TILE_LOG_V
 #define NTT_TILE_LOG_V 11

@@ -63,6 +63,13 @@ def algo_bytes():
     return int(L.fheb200_algo_bytes())
 
 
+def op_counts():
+    """(rescales, relinearisations, merged relinearise-and-rescale, rotations) since the library was loaded"""
+    L = load()
+    L.fheb200_op_count.restype = C.c_ulonglong
+    return tuple(int(L.fheb200_op_count(i)) for i in range(4))
+
+
 def params_chain(logn, depth, scale_bits=40, first_bits=60, dnum=3):
     """Host-only: modulus chain / roots / (L, K, alpha) for a parameter set (no GPU needed)."""
     L = load()

@@ -34,6 +34,9 @@ const char *fheb200_version(void);
 unsigned long long fheb200_launch_count(void);
 /* algorithmic bytes (SURVEY.md 8d formulas) of the scheme operations issued by this process so far: roofline numerator */
 unsigned long long fheb200_algo_bytes(void);
+/* process-wide scheme-operation counters for profiling: 0 rescales, 1 relinearisations (ModDown by P), 2 merged relinearise-and-rescale
+ * divisions, 3 key-switched rotations (plain and hoisted) */
+unsigned long long fheb200_op_count(int which);
 
 /* ---- context: CCParams<CryptoContextCKKSRNS> setters + GenCryptoContext (tests/DirectSortTest.cpp:24-41) ---- */
 typedef struct {

@@ -416,6 +416,7 @@ const char *fheb200_last_error(void) { return g_err.c_str(); }
 const char *fheb200_version(void) { return "fheb200-cpu-oracle (test infrastructure)"; }
 unsigned long long fheb200_launch_count(void) { return 0; }
 unsigned long long fheb200_algo_bytes(void) { return 0; }
+unsigned long long fheb200_op_count(int) { return 0; }
 int fheb200_cpu_threads(void) { const char *th = std::getenv("FHEB200_CPU_THREADS"); return th && std::atoi(th) > 0 ? std::atoi(th) : omp_get_max_threads(); }
 
 int fheb200_ctx_create(const fheb200_params *p, fheb200_ctx **out) {

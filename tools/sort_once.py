@@ -16,7 +16,11 @@ import torch  # noqa: E402
 for rep in range(reps):
     if rep == reps - 1:
         torch.cuda.profiler.start()  # ncu --profile-from-start off: the last sort only
+    from fhe_sorting_b200.lib import op_counts
+    c0 = op_counts()
     t0 = time.perf_counter()
     out, ms, level = s.sort(x)
+    c1 = op_counts()
+    print("ops (rescale, relin, merged, rotations):", tuple(b - a for a, b in zip(c0, c1)), flush=True)
     print("N=%d sort %.1f ms wall %.1f ms err %.2e" % (n, ms, 1e3 * (time.perf_counter() - t0), np.abs(out - np.sort(x)).max()),
           flush=True)
