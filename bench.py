@@ -412,9 +412,55 @@ def microbench(ctx, keys, ct, device):
     return out
 
 
+def bind_to_gpu_numa(device):
+    """Run this rank on the CPUs of the GPU's NUMA node, so that the pinned staging buffers of the end-to-end leg (first
+    touched by this process) and the threads feeding the copy engines are local to the GPU's PCIe root.  Returns what was
+    done, for the JSON line; never fails the bench."""
+    info = {"gpu": device, "node": None, "bound": False}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(device)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:  # nvml prints a 32-bit domain, sysfs a 16-bit one
+            bus = bus[4:]
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read().strip())
+        info["node"] = node
+        if node >= 0:
+            cpus = set()
+            for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+            allowed = cpus & os.sched_getaffinity(0)
+            if allowed:
+                os.sched_setaffinity(0, allowed)
+                info["bound"], info["cpus"] = True, len(allowed)
+    except Exception as e:  # noqa: BLE001 - diagnostics only
+        info["error"] = str(e)[:80]
+    return info
+
+
+def pcie_bandwidth(torch, mib=256):
+    """GB/s of one pinned-host -> device and one device -> pinned-host copy (what bounds the end-to-end leg on a slow link)."""
+    h = torch.empty(mib << 20, dtype=torch.uint8).pin_memory()
+    d = torch.empty(mib << 20, dtype=torch.uint8, device="cuda")
+    out = {}
+    for name, (dst, src) in (("h2d_gbs", (d, h)), ("d2h_gbs", (h, d))):
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        dst.copy_(src, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = (mib << 20) / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import fhe_sorting_b200 as F
+    numa = bind_to_gpu_numa(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -477,6 +523,7 @@ def run_ours(args, rank, world, local_rank):
             ctx.ct_export_async(r, outs[s & 1])
         ctx.sync()
 
+    link = pcie_bandwidth(torch)
     e2e_run(max(3, args.warmup))
     want = ctx.ct_export(ctx.rotate(ct, INDICES[-1]))
     if not (np.array_equal(outs[(max(3, args.warmup) - 1) & 1][0], want[0])
@@ -551,7 +598,10 @@ def run_ours(args, rank, world, local_rank):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic", "config": workload_config({"key_bytes_resident": ctx.key_bytes()}),
         "clocks": clocks, "gpu_launches": int(launches),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": limb_bytes, "d2h_bytes_per_step": limb_bytes},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": limb_bytes, "d2h_bytes_per_step": limb_bytes,
+                "link": link, "numa": numa,
+                "note": "each step moves 2 x %.0f MB over PCIe under %.1f ms of kernels: below ~9 GB/s per direction the link, "
+                        "not the GPU, bounds this leg" % (limb_bytes / 1e6, ms / args.steps)},
         "roofline": roofline,
         "sort_latency": sort_latency,
         "microbench": micro,
