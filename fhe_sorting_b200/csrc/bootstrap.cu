@@ -33,6 +33,9 @@ static int env_int(const char *name, int dflt) {
 void Context::bootstrap_setup(int budget_enc, int budget_dec, int slots) {
     LOCK;
     if (slots <= 0) slots = batch;
+    if (slots > P->n / 4 || (slots & (slots - 1)))
+        throw std::invalid_argument("EvalBootstrapSetup: fully packed bootstrapping is unsupported: slots must be a power of two <= ring_dim / 4 (got " +
+                                    std::to_string(slots) + "; the reference's k-way fixture packs <= 1024)");
     auto B = std::make_shared<BootState>();
     B->plan = make_boot_plan(P->n, slots, budget_enc, budget_dec, (double)P->moduli[0], P->sf[RAISE_LEVEL],
                              env_int("FHEB200_BOOT_CORRECTION", 10));

@@ -205,7 +205,9 @@ int fheb200_ct_device_view(fheb200_ct *ct, void **device_ptr, size_t *words);
 int fheb200_ct_reduce_partial_sums(fheb200_ctx *ctx, fheb200_ct *ct);
 
 /* ---- raw RNS access: parity tests against the oracle and the primitive micro-benchmarks ----
- * Polynomials are uint64 [limb][ring_dim] host arrays, limb i reduced mod modulus i (evaluation domain). */
+ * Polynomials are uint64 [limb][ring_dim] host arrays, limb i reduced mod modulus i (evaluation domain).
+ * Import preconditions (NOT validated: the caller is a test or a deserialiser that wrote the data itself): every residue is
+ * below its modulus, noise_scale_deg is 1 or 2 and `scale` is the scaling factor the limbs were produced at. */
 int fheb200_ct_export(fheb200_ctx *ctx, fheb200_ct *ct, uint64_t *c0, uint64_t *c1, size_t words_each);
 int fheb200_ct_import(fheb200_ctx *ctx, const uint64_t *c0, const uint64_t *c1, int num_limbs, int noise_scale_deg,
                       double scale, int slots, fheb200_ct **out);
