@@ -218,6 +218,38 @@ std::shared_ptr<Context> Context::create(int logn, int depth, int scale_bits, in
             iw[i][2 * k] = wi[k], iw[i][2 * k + 1] = wis[k];
         }
     }
+    // factored twiddles of the last three stages (n = 2^17, FP64-path moduli): twa[s - 14][T] = tw[2^s + T 2^(s-6)] / tw[2^s];
+    // kept only if every table entry is reproduced exactly (FHEB200_NTT_TWFACTOR=0 disables)
+    {
+        const char *e = getenv("FHEB200_NTT_TWFACTOR");
+        if (logn == 17 && !(e && *e == '0')) {
+            std::vector<double> fa((size_t)F * 192, 0.0), ia((size_t)F * 192, 0.0);
+            bool ok = true;
+            for (int i = 0; i < F && ok; i++) {
+                if (P.mc[i].bits > 42) continue; // integer path: tables unused
+                const u64 q = P.moduli[i];
+                for (int dir = 0; dir < 2 && ok; dir++) {
+                    const std::vector<u64> &tb = dir ? iw[i] : fw[i]; // (w, Shoup) pairs
+                    for (int s = 14; s <= 16 && ok; s++) {
+                        const u64 inv0 = invmod_h(tb[2 * ((size_t)1 << s)], q);
+                        for (int t = 0; t < 64 && ok; t++) {
+                            const u64 a = mulmod_h(tb[2 * (((size_t)1 << s) + ((size_t)t << (s - 6)))], inv0, q);
+                            (dir ? ia : fa)[(size_t)i * 192 + (s - 14) * 64 + t] = (double)a;
+                            for (size_t r = 0; r < ((size_t)1 << (s - 6)); r++)
+                                if (mulmod_h(tb[2 * (((size_t)1 << s) + r)], a, q) != tb[2 * (((size_t)1 << s) + ((size_t)t << (s - 6)) + r)]) {
+                                    ok = false;
+                                    break;
+                                }
+                        }
+                    }
+                }
+            }
+            if (ok) {
+                T.twa = (double *)C->owned_alloc(sizeof(double) * fa.size(), fa.data());
+                T.twia = (double *)C->owned_alloc(sizeof(double) * ia.size(), ia.data());
+            }
+        }
+    }
     for (int i = 0; i < F; i++) {
         size_t off = (size_t)i * n, b = sizeof(ulonglong2) * n;
         FHE_CUDA(cudaMemcpy(T.tw + off, fw[i].data(), b, cudaMemcpyHostToDevice));

@@ -26,6 +26,10 @@ struct DeviceTables {            // resident per context
     double *twf = nullptr;       // forward twiddles as doubles [F][n] (FP64 NTT path, moduli <= 42 bits)
     double *twif = nullptr;      // inverse twiddles as doubles [F][n]
     double2 *qd = nullptr;       // [F] (q, 1/q) as doubles
+    // n = 2^17, FP64 path: tw[2^s + T 2^(s-6) + r] = tw[2^s + r] * twa[s - 14][T] for the last three stages s = 14..16 (T = 2048-
+    // coefficient tile, r = butterfly group inside the tile): the last pass then reads the 14 KB tile-0 slice of a modulus' table
+    // instead of streaming 896 KB of it (ntt.cu: fp_fwd_chunk_tail).  [F][3][64] each; null = not available
+    double *twa = nullptr, *twia = nullptr;
     u64 *ninv = nullptr;         // [F] n^-1, [F] Shoup
 };
 

@@ -327,6 +327,52 @@ __device__ __forceinline__ void fp_inv_chunk(double (&v)[8], const double *__res
     }
 }
 
+// stages 14, 15, 16 of the last forward pass at n = 2^17 with factored twiddles (DeviceTables::twa): the table entries of tile T
+// are those of tile 0 times one constant per stage, so the loads hit the 14 KB slice every tile of a modulus shares
+__device__ __forceinline__ void fp_fwd_chunk_tail(double (&v)[8], const double *__restrict__ tw, const double *__restrict__ A,
+                                                  uint32_t tile, uint32_t base, double q, double qinv) {
+    const double a14 = __ldg(A + tile), a15 = __ldg(A + 64 + tile), a16 = __ldg(A + 128 + tile);
+    {
+        const double w = fp_mulmod(__ldg(tw + (1u << 14) + (base >> 3)), a14, qinv, q);
+#pragma unroll
+        for (int k = 0; k < 4; k++) fp_ct(v[k], v[k + 4], w, qinv, q);
+    }
+    {
+        const double2 t = __ldg(reinterpret_cast<const double2 *>(tw + (2u << 14) + (base >> 2)));
+        const double wx = fp_mulmod(t.x, a15, qinv, q), wy = fp_mulmod(t.y, a15, qinv, q);
+        fp_ct(v[0], v[2], wx, qinv, q), fp_ct(v[1], v[3], wx, qinv, q);
+        fp_ct(v[4], v[6], wy, qinv, q), fp_ct(v[5], v[7], wy, qinv, q);
+    }
+    {
+        const double2 *p = reinterpret_cast<const double2 *>(tw + (4u << 14) + (base >> 1));
+        const double2 t0 = __ldg(p), t1 = __ldg(p + 1);
+        fp_ct(v[0], v[1], fp_mulmod(t0.x, a16, qinv, q), qinv, q), fp_ct(v[2], v[3], fp_mulmod(t0.y, a16, qinv, q), qinv, q);
+        fp_ct(v[4], v[5], fp_mulmod(t1.x, a16, qinv, q), qinv, q), fp_ct(v[6], v[7], fp_mulmod(t1.y, a16, qinv, q), qinv, q);
+    }
+}
+// the mirror image: stages 16, 15, 14 at the start of the first inverse pass (DeviceTables::twia)
+__device__ __forceinline__ void fp_inv_chunk_head(double (&v)[8], const double *__restrict__ tw, const double *__restrict__ A,
+                                                  uint32_t tile, uint32_t base, double q, double qinv) {
+    const double a14 = __ldg(A + tile), a15 = __ldg(A + 64 + tile), a16 = __ldg(A + 128 + tile);
+    {
+        const double2 *p = reinterpret_cast<const double2 *>(tw + (4u << 14) + (base >> 1));
+        const double2 t0 = __ldg(p), t1 = __ldg(p + 1);
+        fp_gs(v[0], v[1], fp_mulmod(t0.x, a16, qinv, q), qinv, q), fp_gs(v[2], v[3], fp_mulmod(t0.y, a16, qinv, q), qinv, q);
+        fp_gs(v[4], v[5], fp_mulmod(t1.x, a16, qinv, q), qinv, q), fp_gs(v[6], v[7], fp_mulmod(t1.y, a16, qinv, q), qinv, q);
+    }
+    {
+        const double2 t = __ldg(reinterpret_cast<const double2 *>(tw + (2u << 14) + (base >> 2)));
+        const double wx = fp_mulmod(t.x, a15, qinv, q), wy = fp_mulmod(t.y, a15, qinv, q);
+        fp_gs(v[0], v[2], wx, qinv, q), fp_gs(v[1], v[3], wx, qinv, q);
+        fp_gs(v[4], v[6], wy, qinv, q), fp_gs(v[5], v[7], wy, qinv, q);
+    }
+    {
+        const double w = fp_mulmod(__ldg(tw + (1u << 14) + (base >> 3)), a14, qinv, q);
+#pragma unroll
+        for (int k = 0; k < 4; k++) fp_gs(v[k], v[k + 4], w, qinv, q);
+    }
+}
+
 // first: the pass reads reduced u64 input (otherwise doubles left by the previous pass); last: writes reduced u64
 template <bool CG>
 __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u64 *__restrict__ src, u64 *__restrict__ dst,
@@ -374,7 +420,8 @@ __device__ __forceinline__ void fp_fwd_pass_body(const DeviceTables &T, const u6
             for (int k = 0; k < 8; k++) v[k] = sm[pad(base | (k << p))];
         }
         g0 = tile_to_g(G, base, tile);
-        fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
+        if (!G.pass_a && G.logn == 17 && s == 14 && p == 0 && T.twa) fp_fwd_chunk_tail(v, tw, T.twa + (size_t)qp * 192, tile, (uint32_t)base, q, qinv);
+        else fp_fwd_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
         s += 3;
     }
     u64 o[8];
@@ -441,7 +488,8 @@ __device__ __forceinline__ void fp_inv_pass_body(const DeviceTables &T, const u6
             growth = 0;
         }
         const int s = G.S0 + G.S - 1 - (p + 2 - lowbit);
-        fp_inv_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
+        if (!G.pass_a && G.logn == 17 && s == 14 && p == 0 && T.twia) fp_inv_chunk_head(v, tw, T.twia + (size_t)qp * 192, tile, (uint32_t)base, q, qinv);
+        else fp_inv_chunk<3>(v, tw, s, G.logn, g0, q, qinv);
         growth += 3;
         if (i > 0) __syncthreads();
 #pragma unroll
