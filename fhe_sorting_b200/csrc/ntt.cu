@@ -972,6 +972,44 @@ __global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_inv_pass_k(DeviceT
     } else if (kind == 1) inv_pass_body<true, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
     else inv_pass_body<false, false>(T, src, dst, d, G, scale, sm, custom, custom_s, blockIdx.x, blockIdx.y);
 }
+// Two tiles per CTA (FHEB200_NTT_PAIR=1, forward transform): the second tile's input is requested with cp.async (no registers held)
+// before the first tile is transformed, so one of the two load latencies of the CTA is hidden behind arithmetic and there are twice
+// as many bytes in flight per CTA at its start.  Each thread copies exactly the words of its own first access pattern.
+template <int LOGN, int S, int S0, int LC, int PA>
+__global__ void __launch_bounds__(NTT_TILE / 8, NTT_CTAS) ntt_fwd_pass_k2(DeviceTables T, const u64 *__restrict__ src, u64 *__restrict__ dst,
+                                                                   const NttBatch B, const NttLimbConsts C, int first, int final_reduce) {
+    extern __shared__ u64 sm[];
+    u64 *stage = sm + NTT_PAD_WORDS;
+    const PassGeom G{LOGN, S, S0, LC, NTT_TILE_LOG, PA};
+    const uint32_t d = B.desc[blockIdx.y];
+    const int qp = d & 0xff, kind = C.kind[qp], tid = threadIdx.x;
+    const uint32_t t0 = 2 * blockIdx.x, t1 = t0 + 1;
+    {
+        const int p = S - 3 + (PA ? LC : 0), base = triple_base(tid, p);
+        const uint32_t g0 = tile_to_g(G, base, t1), st = g_step(G, p);
+        const u64 *g = src + ((size_t)(d >> 8) << LOGN) + g0;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(stage + k * (NTT_TILE / 8) + tid)), "l"(g + (size_t)k * st) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    const double2 qd = make_double2(C.q[qp], C.qinv[qp]);
+    if (kind == 0) fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, t0, nullptr, nullptr, &qd);
+    else if (kind == 1) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, t0);
+    else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, t0);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    u64 pre[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) pre[k] = stage[k * (NTT_TILE / 8) + tid];
+    __syncthreads(); // the exchange buffer is reused by the second tile
+    if (kind == 0) fp_fwd_pass_body<false>(T, src, dst, d, G, first, final_reduce, sm, t1, pre, nullptr, &qd);
+    else if (kind == 1) fwd_pass_body<true, false>(T, src, dst, d, G, final_reduce, sm, t1, pre);
+    else fwd_pass_body<false, false>(T, src, dst, d, G, final_reduce, sm, t1, pre);
+}
+static bool ntt_pair() {
+    static const bool on = [] { const char *e = getenv("FHEB200_NTT_PAIR"); return e && *e == '1'; }();
+    return on;
+}
 #include "ntt_cluster.cuh"
 // FHEB200_NTT_CLUSTER=0 keeps the two-pass kernels everywhere; =k (k >= 1) uses the cluster transform for batches of at least k
 // limbs (a cluster owns 8 SMs: small batches fill the GPU better with 64 independent tiles per limb)
@@ -1103,6 +1141,13 @@ void k_ntt_fwd(const DeviceTables &T, const u64 *src, u64 *dst, const uint32_t *
             NttBatch B;
             std::copy(hd.begin() + c0, hd.begin() + c0 + gc, B.desc);
             const dim3 gg(T.n / tile, gc);
+            if (ntt_pair()) {
+                const dim3 g2(T.n / tile / 2, gc);
+                const size_t smem2 = smem + (size_t)tile * sizeof(u64);
+                g_launches++, ntt_fwd_pass_k2<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<g2, tile / 8, smem2, st>>>(T, src, dst, B, LC_, 1, 0);
+                g_launches++, ntt_fwd_pass_k2<17, NTT_SB, NTT_SA, 0, 0><<<g2, tile / 8, smem2, st>>>(T, dst, dst, B, LC_, 0, 1);
+                continue;
+            }
             g_launches++, ntt_fwd_pass_k<17, NTT_SA, 0, NTT_TILE_LOG - NTT_SA, 1><<<gg, tile / 8, smem, st>>>(T, src, dst, B, LC_, 1, 0);
             g_launches++, ntt_fwd_pass_k<17, NTT_SB, NTT_SA, 0, 0><<<gg, tile / 8, smem, st>>>(T, dst, dst, B, LC_, 0, 1);
         }
