@@ -20,7 +20,7 @@
 namespace fheb200 {
 
 #define LOCK                                           \
-    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    CtxLock lock__(*this);                             \
     FHE_CUDA(cudaSetDevice(device))
 
 static const int RAISE_LEVEL = 1; // the raised ciphertext lives at level 1 (the FLEXIBLEAUTOEXT extra limb stays unused)

@@ -98,7 +98,7 @@ int fheb200_ctx_release(fheb200_ctx *ctx) { GUARD({ delete ctx; }) }
 int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *s) {
     GUARD({
         need(ctx, "ctx");
-        std::lock_guard<std::recursive_mutex> g(ctx->c->mu);
+        CtxLock g(*ctx->c);
         ctx->c->sync();
         if (ctx->c->own_stream && ctx->c->stream) cudaStreamDestroy(ctx->c->stream);
         ctx->c->stream = (cudaStream_t)s;
@@ -108,6 +108,8 @@ int fheb200_ctx_set_stream(fheb200_ctx *ctx, void *s) {
 int fheb200_ctx_sync(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->sync(); }) }
 int fheb200_ctx_fork(fheb200_ctx *ctx, int k) { GUARD({ need(ctx, "ctx"); ctx->c->fork(k); }) }
 int fheb200_ctx_use_stream(fheb200_ctx *ctx, int i) { GUARD({ need(ctx, "ctx"); ctx->c->use_stream(i); }) }
+int fheb200_ctx_bind_thread(fheb200_ctx *ctx, int i) { GUARD({ need(ctx, "ctx"); ctx->c->bind_thread(i); }) }
+int fheb200_ctx_unbind_thread(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->unbind_thread(); }) }
 int fheb200_ctx_join(fheb200_ctx *ctx) { GUARD({ need(ctx, "ctx"); ctx->c->join(); }) }
 int fheb200_ctx_info(fheb200_ctx *ctx, int *n, int *nq, int *np, int *alpha, int *batch) {
     GUARD({

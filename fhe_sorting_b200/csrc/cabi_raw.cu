@@ -42,7 +42,7 @@ static void h2d(Context &C, void *dst, const void *src, size_t bytes) {
 #define LOCKCTX(ctx)                                              \
     need(ctx, "ctx");                                             \
     Context &C = *ctx->c;                                         \
-    std::lock_guard<std::recursive_mutex> lock__(C.mu);           \
+    CtxLock lock__(C);                                            \
     FHE_CUDA(cudaSetDevice(C.device));                            \
     const int n = C.P->n;                                         \
     (void)n

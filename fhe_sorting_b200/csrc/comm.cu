@@ -77,7 +77,7 @@ void nccl_check(ncclResult_t r, const char *what) {
 
 namespace fheb200 {
 void Context::comm_init(const unsigned char *id128, int rank, int world) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("comm_init: bad rank / world");
     // residues below 2^60 (first, extra and special limbs) are summed as 64-bit integers before the fix-up
     if (world > 16) throw std::invalid_argument("comm_init: at most 16 ranks (raw residues are summed in 64 bits)");
@@ -92,7 +92,7 @@ void Context::comm_init(const unsigned char *id128, int rank, int world) {
     comm_ = c, comm_rank_ = rank, comm_world_ = world;
 }
 void Context::comm_destroy() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (comm_) {
         cudaStreamSynchronize(stream);
         nccl().comm_destroy((ncclComm_t)comm_);
@@ -101,7 +101,7 @@ void Context::comm_destroy() {
 }
 // a <- sum over ranks of a (every limb modulo its modulus), in place, on the engine's stream
 void Context::all_reduce_sum(const Ct &a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (!a) throw std::invalid_argument("AllReduceSum: null ciphertext");
     if (!comm_) throw std::runtime_error("AllReduceSum: no communicator (fheb200_ctx_comm_init)");
     if (forked_) throw std::runtime_error("AllReduceSum: not inside a forked stream region");

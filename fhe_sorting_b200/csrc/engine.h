@@ -231,9 +231,17 @@ class Context : public std::enable_shared_from_this<Context> {
     void adjust_pair_to_one(Ct &a, Ct &b);         // AdjustLevelsAndDepthToOneInPlace
     LimbScalars scalars_for(long double value, int ell, bool shoup) const;
 
+    // Host threads inside a forked region: a thread that called bind_thread(i) issues everything on side stream i (i < 0: the main
+    // stream) whatever the other threads do; `stream` is re-pointed under the context mutex at the top of every operation
+    // (CtxLock), so the many uses of `stream` below stay as they are.  Unbound threads keep the fork() / use_stream() selection.
+    void bind_thread(int i);
+    void unbind_thread();
+    void bind_thread_stream(); // called with `mu` held
+
   private:
     friend struct DevMem;
-    cudaStream_t main_stream_ = nullptr;
+    friend struct CtxLock;
+    cudaStream_t main_stream_ = nullptr, fork_current_ = nullptr; // fork_current_: what fork() / use_stream() selected (unbound threads)
     std::vector<cudaStream_t> side_;
     std::vector<cudaEvent_t> side_done_;
     cudaEvent_t fork_ev_ = nullptr, free_ev_ = nullptr;
@@ -274,5 +282,11 @@ std::vector<double> chebyshev_coefficients(const std::function<double(double)> &
         if (e__ != cudaSuccess)                                                                              \
             throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e__) + " at " #call);  \
     } while (0)
+
+// the context mutex + this thread's stream binding, for the duration of one operation
+struct CtxLock {
+    std::lock_guard<std::recursive_mutex> g;
+    explicit CtxLock(Context &c) : g(c.mu) { c.bind_thread_stream(); }
+};
 
 } // namespace fheb200

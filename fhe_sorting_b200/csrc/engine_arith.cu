@@ -10,7 +10,7 @@
 namespace fheb200 {
 
 #define LOCK                                           \
-    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    CtxLock lock__(*this);                             \
     FHE_CUDA(cudaSetDevice(device))
 
 // bring x (shallower) to the level, degree and scale of t — restates OpenFHE's AdjustLevelsAndDepthInPlace

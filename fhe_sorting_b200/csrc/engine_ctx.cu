@@ -14,8 +14,24 @@
 
 namespace fheb200 {
 
+static thread_local const Context *tls_ctx = nullptr;
+static thread_local int tls_idx = 0;
+void Context::bind_thread(int i) { tls_ctx = this, tls_idx = i; }
+void Context::unbind_thread() {
+    if (tls_ctx == this) tls_ctx = nullptr;
+}
+void Context::bind_thread_stream() {
+    if (!forked_) return;
+    if (tls_ctx == this) stream = tls_idx < 0 ? main_stream_ : side_[tls_idx % fork_k_];
+    else stream = fork_current_;
+}
+
 DevMem::~DevMem() {
     if (!p || !ctx) return;
+    // handles are dropped by whichever host thread holds the last reference: take the context's lock (and that thread's stream)
+    // unless the context itself is going away
+    std::unique_ptr<CtxLock> lock;
+    if (keep) lock.reset(new CtxLock(*ctx));
     cudaStream_t s = stream ? stream : ctx->stream;
     // Inside a forked region a buffer that existed before the fork is readable by EVERY side stream, so no single event
     // orders its release: park it; join() frees it on the main stream once all side streams have been joined.
@@ -41,7 +57,7 @@ void Context::sync() {
     if (copy_stream_) {
         FHE_CUDA(cudaStreamSynchronize(copy_stream_));
         FHE_CUDA(cudaStreamSynchronize(out_stream_));
-        std::lock_guard<std::recursive_mutex> g(mu);
+        CtxLock g(*this);
         drain_copies(true);
     }
     if (forked_)
@@ -70,7 +86,7 @@ void Context::drain_copies(bool wait) {
     }
 }
 void Context::copy_in(void *dst, const void *src, size_t bytes, const Mem &owner) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (!copy_stream_) {
         FHE_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
         FHE_CUDA(cudaStreamCreateWithFlags(&out_stream_, cudaStreamNonBlocking));
@@ -86,14 +102,14 @@ void Context::copy_in(void *dst, const void *src, size_t bytes, const Mem &owner
     inbound_[owner.get()] = done;
 }
 void Context::wait_copy_in(const Mem &owner) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     auto it = inbound_.find(owner.get());
     if (it == inbound_.end()) return;
     FHE_CUDA(cudaStreamWaitEvent(stream, it->second, 0));
     inbound_.erase(it);
 }
 void Context::copy_out(void *dst, const void *src, size_t bytes, const Mem &owner) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (!copy_stream_) {
         FHE_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
         FHE_CUDA(cudaStreamCreateWithFlags(&out_stream_, cudaStreamNonBlocking));
@@ -109,7 +125,7 @@ void Context::copy_out(void *dst, const void *src, size_t bytes, const Mem &owne
 }
 
 void Context::fork(int k) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (forked_) throw std::runtime_error("fork: already forked");
     if (k < 1 || k > 16) throw std::invalid_argument("fork: 1..16 streams");
     FHE_CUDA(cudaSetDevice(device));
@@ -124,18 +140,18 @@ void Context::fork(int k) {
         FHE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         side_.push_back(s), side_done_.push_back(e);
     }
-    main_stream_ = stream;
+    main_stream_ = fork_current_ = stream;
     FHE_CUDA(cudaEventRecord(fork_ev_, main_stream_));
     for (int i = 0; i < k; i++) FHE_CUDA(cudaStreamWaitEvent(side_[i], fork_ev_, 0));
     fork_k_ = k, forked_ = true, fork_epoch_ = ++epoch;
 }
 void Context::use_stream(int i) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (!forked_) throw std::runtime_error("use_stream: not forked");
-    stream = i < 0 ? main_stream_ : side_[i % fork_k_];
+    stream = fork_current_ = i < 0 ? main_stream_ : side_[i % fork_k_];
 }
 void Context::join() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     if (!forked_) return;
     for (int i = 0; i < fork_k_; i++) {
         FHE_CUDA(cudaEventRecord(side_done_[i], side_[i]));
@@ -315,7 +331,7 @@ void Context::reseed_from_os() {
     memset(k, 0, sizeof(k));
 }
 void Context::set_rng_keys(const unsigned char *k64) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     rng_secret = RngState(), rng_public = RngState();
     memcpy(rng_secret.key, k64, 32), memcpy(rng_public.key, k64 + 32, 32);
     rng_secret.secure = rng_public.secure = 1;
@@ -330,7 +346,7 @@ void Context::get_rng_keys(unsigned char *k64) const {
 size_t Context::key_bytes() const { return (evk_rot.size() + (evk_mult ? 1 : 0)) * evk_words() * sizeof(u64); }
 
 const uint32_t *Context::desc(const std::vector<uint32_t> &d) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     auto it = descs_.find(d);
     if (it != descs_.end()) return it->second;
     uint32_t *p = (uint32_t *)owned_alloc(sizeof(uint32_t) * d.size(), d.data());
@@ -392,7 +408,7 @@ auto bits_of = [&](int qp) { return P->mc[qp].bits; };
 }
 
 const DevicePlan &Context::plan(int ell) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     auto it = plans_.find(ell);
     if (it != plans_.end()) return it->second;
     const LevelPlan &H = P->plan(ell);
@@ -477,7 +493,7 @@ const DevicePlan &Context::plan(int ell) {
 // routines run on a plan whose "special" limbs are q_{ell-1} followed by the K primes of P (positions ell-1 .. ell+K-1 of an
 // accumulator, contiguous) and whose ordinary limbs are q_0 .. q_{ell-2}.  Only the fields ModDown reads are filled.
 const DevicePlan &Context::plan_merged(int ell) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     auto it = plans_m_.find(ell);
     if (it != plans_m_.end()) return it->second;
     if (ell < 2) throw std::out_of_range("merged ModDown plan: needs at least two limbs");

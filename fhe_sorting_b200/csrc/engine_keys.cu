@@ -19,7 +19,7 @@ static std::vector<uint32_t> iota_desc(int count, int slot0 = 0, int qp0 = 0) {
 }
 
 Keys Context::keygen(u64 sd) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     if (sd != 0) { // TEST-ONLY: 64-bit seeded, non-cryptographic generator shared with the CPU oracle
         if (!allow_deterministic)
@@ -80,7 +80,7 @@ u64 *Context::gen_switch_key(u64 key_id, const u64 *s_old, const u64 *s_new) {
 }
 
 void Context::gen_mult_key(const Keys &k) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     if (!k || !k->s) throw std::runtime_error("EvalMultKeyGen: secret key required");
     const int n = P->n, F = P->L + P->K;
@@ -93,7 +93,7 @@ void Context::gen_mult_key(const Keys &k) {
 }
 
 void Context::gen_rot_keys(const Keys &k, const std::vector<int> &indices) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     if (!k || !k->s) throw std::runtime_error("EvalRotateKeyGen: secret key required");
     const int n = P->n, F = P->L + P->K;
@@ -224,7 +224,7 @@ void Context::upload(void *dst, const void *src, size_t bytes) {
 }
 
 Mem Context::encode_at(const Plaintext &pt, int ell, double scale) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     const int n = P->n, slots = pt.slots;
     if (pt.base) { // rotation of an encoded plaintext = the automorphism X -> X^(5^rot) of its polynomial: one permutation
@@ -296,7 +296,7 @@ Pt Context::make_plaintext_real(const double *vals, size_t count, int nsd, int l
 }
 
 Ct Context::encrypt(const Keys &k, const Pt &pt) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     if (!k || !k->pk) throw std::runtime_error("Encrypt: public key required");
     if (!pt) throw std::runtime_error("Encrypt: null plaintext");
@@ -321,7 +321,7 @@ Ct Context::encrypt(const Keys &k, const Pt &pt) {
 }
 
 Pt Context::decrypt(const Keys &k, const Ct &ct) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     FHE_CUDA(cudaSetDevice(device));
     if (!k || !k->s) throw std::runtime_error("Decrypt: secret key required");
     if (!ct || ct->npoly != 2) throw std::runtime_error("Decrypt: expected a 2-element ciphertext");

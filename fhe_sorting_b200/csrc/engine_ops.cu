@@ -9,7 +9,7 @@
 namespace fheb200 {
 
 #define LOCK                                           \
-    std::lock_guard<std::recursive_mutex> lock__(mu); \
+    CtxLock lock__(*this);                             \
     FHE_CUDA(cudaSetDevice(device))
 
 static Ct new_like(Context *C, const Ct &a, int npoly, int ell) {

@@ -221,7 +221,7 @@ static std::vector<Ct> chebyshev_basis(Context *C, const Ct &u, int count) {
 }
 
 Ct Context::eval_chebyshev_linear(const Ct &x, const std::vector<double> &coeffs, double a, double b) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     int n = degree_of(coeffs);
     if (n < 1) throw std::invalid_argument("EvalChebyshevSeries: degree must be >= 1");
     Ct u = to_unit_interval(this, x, a, b);
@@ -237,7 +237,7 @@ Ct Context::eval_chebyshev_linear(const Ct &x, const std::vector<double> &coeffs
 }
 
 Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, double a, double b) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     static const bool pstime = getenv("FHEB200_PSTIME") != nullptr;
     HostTimer tm;
     double t_basis = 0, t_giant = 0, t_collect = 0, t_lincomb = 0;
@@ -289,7 +289,7 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
 
 // power-basis evaluation with binary powers, depth ceil(log2 deg) + 1
 Ct Context::eval_poly_linear(const Ct &x, const std::vector<double> &coeffs) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    CtxLock g(*this);
     int n = degree_of(coeffs);
     if (n < 1) throw std::invalid_argument("EvalPoly: degree must be >= 1");
     std::vector<char> need(n + 1, 0);

@@ -403,6 +403,8 @@ class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl>
     // Engine extension (not an OpenFHE call): concurrent streams for independent sub-computations, see fheb200_ctx_fork
     void ForkStreams(int k) { fheb200_check(fheb200_ctx_fork(ctx, k)); }
     void UseStream(int i) { fheb200_check(fheb200_ctx_use_stream(ctx, i)); }
+    void BindThreadStream(int i) { fheb200_check(fheb200_ctx_bind_thread(ctx, i)); } // this host thread -> side stream i
+    void UnbindThreadStream() { fheb200_check(fheb200_ctx_unbind_thread(ctx)); }
     void JoinStreams() { fheb200_check(fheb200_ctx_join(ctx)); }
     // Multi-GPU extension (not an OpenFHE call): sum a partial ciphertext over the ranks that share this job.  `reduce`
     // sums the device buffer in place across ranks as 64-bit integers (NCCL all-reduce supplied by the launcher).

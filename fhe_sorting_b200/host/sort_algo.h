@@ -13,7 +13,9 @@
 #include <cmath>
 #include <iostream>
 #include <memory>
+#include <exception>
 #include <set>
+#include <thread>
 #include <vector>
 
 #include "comparison.h"
@@ -92,6 +94,43 @@ class BatchStreams {
         if (forked) cc->JoinStreams();
     }
 };
+// The same with one host thread per stream (opt-in, FHESORT_THREADS=1): a launching thread cannot run more than a launch queue
+// (~1000 kernels) ahead of the GPU, and one batch is several thousand kernels, so from one thread the streams overlap only at the
+// seams between batches.  Measured on B200 (DESIGN.md, round-2 results): 1456 -> 1448 ms at N = 1024 - the batches do not have
+// idle GPU time to give each other, so the single launching thread stays the default.  body(i) evaluates the i-th of `count` batches into its own result
+// slot; the first batch runs alone on the calling thread (it fills the caches that hang off the shared inputs), the rest are
+// dealt round-robin to k threads, each bound to its side stream (fheb200_ctx_bind_thread).
+template <class Body> inline void forEachBatch(CryptoContext<DCRTPoly> cc, int streams, int count, Body body) {
+    static const bool threads = [] { const char *e = getenv("FHESORT_THREADS"); return e && *e == '1'; }();
+    if (count <= 0) return;
+    if (!threads || streams <= 1 || count <= 2) {
+        BatchStreams bs(cc, streams);
+        for (int i = 0; i < count; i++) bs.next(), body(i);
+        return;
+    }
+    body(0);
+    const int k = std::min(streams, count - 1);
+    cc->ForkStreams(k);
+    std::vector<std::exception_ptr> err(k);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < k; t++)
+        pool.emplace_back([&, t] {
+            try {
+                cc->BindThreadStream(t);
+                for (int i = 1 + t; i < count; i += k) body(i);
+            } catch (...) {
+                err[t] = std::current_exception();
+            }
+            try {
+                cc->UnbindThreadStream();
+            } catch (...) {
+            }
+        });
+    for (auto &th : pool) th.join();
+    cc->JoinStreams();
+    for (auto &e : err)
+        if (e) std::rethrow_exception(e);
+}
 inline int DirectSortDefaultStreams() {
     const char *e = getenv("FHESORT_STREAMS");
     const int v = e ? atoi(e) : 0;
@@ -252,18 +291,16 @@ template <int N> class DirectSort : public SortBase<N> {
     CT constructRank(const CT &input_array, SignFunc SignFunc, SignConfig &Cfg) {
         const DirectSortShape sh(N, max_batch);
         std::vector<CT> baby = babySteps(input_array, sh.np_rank, sh.S);
-        std::vector<CT> parts;
-        {
-            BatchStreams streams(m_cc, m_streams);
-            for (int b = 0; b < sh.B; b++) {
-                if (!mine(b, sh.B)) continue;
-                streams.next();
-                CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b, groupSharded(sh.B, sh.P / sh.np_rank));
-                CT dup = input_array->Clone();
-                dup->SetSlots(sh.S);
-                parts.push_back(comp.compare(m_cc, dup, shifted, SignFunc, Cfg));
-            }
-        }
+        const std::vector<int> batches = DirectSortBatchesOf(sh.B, m_rank, m_world);
+        std::vector<CT> parts(batches.size());
+        forEachBatch(m_cc, m_streams, (int)batches.size(), [&](int i) {
+            const int b = batches[i];
+            CT shifted = vecRotsOpt(baby, sh.P, sh.S, sh.np_rank, b, groupSharded(sh.B, sh.P / sh.np_rank));
+            CT dup = input_array->Clone();
+            dup->SetSlots(sh.S);
+            SignConfig cfg = Cfg; // (a copy per batch: the evaluators take it by non-const reference)
+            parts[i] = comp.compare(m_cc, dup, shifted, SignFunc, cfg);
+        });
         CT rank = parts.size() == 1 ? parts[0] : m_cc->EvalAddMany(parts);
         parts.clear();
         if (sharded(sh.B)) m_cc->AllReduceSum(rank);
@@ -302,12 +339,10 @@ template <int N> class DirectSort : public SortBase<N> {
         index_minus_rank->SetSlots(sh.S);
         input_array->SetSlots(sh.S);
         static const std::vector<double> &coeffs = selectDoubledSincCoefficients<N>();
-        std::vector<CT> parts;
-        {
-            BatchStreams streams(m_cc, m_streams);
-        for (int b = 0; b < sh.B; b++) {
-            if (!mine(b, sh.B)) continue;
-            streams.next();
+        const std::vector<int> batches = DirectSortBatchesOf(sh.B, m_rank, m_world);
+        std::vector<CT> parts(batches.size());
+        forEachBatch(m_cc, m_streams, (int)batches.size(), [&](int i) {
+            const int b = batches[i];
             auto chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(sh.S, b * sh.P), 1, index_minus_rank->GetLevel(),
                                                      nullptr, sh.S);
             CT r = m_cc->EvalSub(index_minus_rank, chk);
@@ -315,9 +350,8 @@ template <int N> class DirectSort : public SortBase<N> {
             r = m_cc->EvalChebyshevSeriesPS(r, coeffs, -1, 1);
             CT masked = m_cc->EvalMult(r, input_array);
             std::vector<CT> masked_inputs = babySteps(masked, sh.np_idx, sh.S);
-            parts.push_back(blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P, groupSharded(sh.B, (sh.S / N) / sh.np_idx)));
-        }
-        }
+            parts[i] = blindRotationOptN(masked_inputs, sh.S, sh.np_idx, b, sh.P, groupSharded(sh.B, (sh.S / N) / sh.np_idx));
+        });
         CT output = parts.size() == 1 ? parts[0] : m_cc->EvalAddMany(parts);
         parts.clear();
         if (sharded(sh.B)) m_cc->AllReduceSum(output);

@@ -61,6 +61,12 @@ int fheb200_ctx_sync(fheb200_ctx *ctx);
 int fheb200_ctx_fork(fheb200_ctx *ctx, int k);
 int fheb200_ctx_use_stream(fheb200_ctx *ctx, int i);
 int fheb200_ctx_join(fheb200_ctx *ctx);
+/* Host threads inside a fork()ed region (what the reference's `#pragma omp parallel for` over batches becomes on one GPU): after
+ * bind_thread(i) every call the CALLING THREAD makes on this context runs on side stream i (i < 0: the main stream), whatever other
+ * threads do; unbind_thread() returns the thread to the fork() / use_stream() selection.  One launching thread cannot run more than
+ * a launch queue (~1000 kernels) ahead of the GPU, so batch chains longer than that only overlap when several threads feed them. */
+int fheb200_ctx_bind_thread(fheb200_ctx *ctx, int i);
+int fheb200_ctx_unbind_thread(fheb200_ctx *ctx);
 /* GetRingDimension / GetCyclotomicOrder (src/rotation.h:262, src/sort_algo.h:80) and chain geometry */
 int fheb200_ctx_info(fheb200_ctx *ctx, int *ring_dim, int *num_q, int *num_p, int *digit_size, int *batch);
 int fheb200_ctx_modulus(fheb200_ctx *ctx, int qp_index, uint64_t *q, uint64_t *psi);

@@ -445,6 +445,8 @@ int fheb200_ctx_set_stream(fheb200_ctx *, void *) { return 0; }
 int fheb200_ctx_sync(fheb200_ctx *) { return 0; }
 int fheb200_ctx_fork(fheb200_ctx *, int) { return 0; }
 int fheb200_ctx_use_stream(fheb200_ctx *, int) { return 0; }
+int fheb200_ctx_bind_thread(fheb200_ctx *, int) { return 0; }
+int fheb200_ctx_unbind_thread(fheb200_ctx *) { return 0; }
 int fheb200_ctx_join(fheb200_ctx *) { return 0; }
 int fheb200_ctx_info(fheb200_ctx *c, int *n, int *nq, int *np, int *digit, int *batch) {
     GUARD({
