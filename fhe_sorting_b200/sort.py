@@ -70,12 +70,12 @@ class DirectSortSession:
         """Concurrent CUDA streams over the independent batches of a phase (default 4)."""
         _ck(self.L.fhesort_session_set_streams(self.h, int(k)), self.L)
 
-    def set_shard(self, rank, world, native=True):
+    def set_shard(self, rank, world, native=True, host=False):
         """Shard the sort's batches over `world` ranks of an initialised torch.distributed group (one GPU each).
         native=True: the engine opens its own NCCL communicator (the 128-byte id of rank 0 travels through
         torch.distributed.broadcast_object_list) and all-reduces on its own stream; native=False: torch's all_reduce
         through a callback (round-1 path, kept for comparison)."""
-        if world > 1 and native:
+        if world > 1 and native and not host:
             import torch.distributed as dist
             from .lib import load
             ident = [None]
@@ -102,6 +102,10 @@ class DirectSortSession:
 
         def allreduce(user, ptr, words):
             try:
+                if host:  # a library whose ciphertexts live in host memory (the CPU scheme layer under tests/): gloo on the words
+                    a = np.ctypeslib.as_array((C.c_int64 * words).from_address(ptr))
+                    dist.all_reduce(torch.from_numpy(a), op=dist.ReduceOp.SUM)
+                    return 0
                 t = torch.as_tensor(_View(ptr, words), device="cuda")
                 dist.all_reduce(t, op=dist.ReduceOp.SUM)
                 torch.cuda.current_stream().synchronize()

@@ -32,6 +32,7 @@ typedef unsigned __int128 u128;
 
 struct CtData {
     std::vector<u64> c0, c1; // [ell][n], evaluation domain
+    std::vector<u64> view;   // c0 || c1 while a caller's all-reduce works on the words (fheb200_ct_device_view)
     int ell = 0, level = 0, nsd = 1, slots = 0;
     double scale = 1.0;
 };
@@ -699,8 +700,32 @@ ABSENT(fheb200_eval_bootstrap_setup(fheb200_ctx *, int, int, int), "EvalBootstra
 ABSENT(fheb200_eval_bootstrap_keygen(fheb200_ctx *, fheb200_keys *, int), "EvalBootstrapKeyGen")
 ABSENT(fheb200_eval_bootstrap(fheb200_ctx *, fheb200_ct *, fheb200_ct **), "EvalBootstrap")
 ABSENT(fheb200_eval_bootstrap_iterated(fheb200_ctx *, fheb200_ct *, int, int, fheb200_ct **), "EvalBootstrap")
-ABSENT(fheb200_ct_device_view(fheb200_ct *, void **, size_t *), "device view")
-ABSENT(fheb200_ct_reduce_partial_sums(fheb200_ctx *, fheb200_ct *), "partial-sum reduction")
+// The callback form of the multi-rank combine (include/fhe_b200.h): the caller sums the words of the partial ciphertexts of all
+// ranks as 64-bit integers (gloo all-reduce in tests/test_multi_rank.py), then every word is reduced modulo its limb's modulus
+int fheb200_ct_device_view(fheb200_ct *ct, void **ptr, size_t *words) {
+    GUARD({
+        need(ct, "ct"); need(ptr, "ptr"); need(words, "words");
+        CtData &a = *ct->c;
+        a.view = a.c0;
+        a.view.insert(a.view.end(), a.c1.begin(), a.c1.end());
+        *ptr = a.view.data(), *words = a.view.size();
+    })
+}
+int fheb200_ct_reduce_partial_sums(fheb200_ctx *c, fheb200_ct *ct) {
+    GUARD({
+        fheb200_ctx &C = ctx_of(c);
+        need(ct, "ct");
+        CtData &a = *ct->c;
+        const size_t n = C.n, half = (size_t)a.ell * n;
+        if (a.view.size() != 2 * half) throw std::runtime_error("reduce_partial_sums: no view taken of this ciphertext");
+        for (int i = 0; i < a.ell; i++)
+            for (size_t k = 0; k < n; k++) {
+                a.c0[(size_t)i * n + k] = a.view[(size_t)i * n + k] % C.q[i];
+                a.c1[(size_t)i * n + k] = a.view[half + (size_t)i * n + k] % C.q[i];
+            }
+        a.view.clear(), a.view.shrink_to_fit();
+    })
+}
 ABSENT(fheb200_ct_all_reduce_sum(fheb200_ctx *, fheb200_ct *), "all-reduce")
 ABSENT(fheb200_comm_unique_id(unsigned char *), "NCCL")
 ABSENT(fheb200_ctx_comm_init(fheb200_ctx *, const unsigned char *, int, int), "NCCL")

@@ -59,3 +59,53 @@ def test_partial_ciphertext_combine_world2_gloo():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def _sort_worker(rank, world, port, q):
+    """A whole sharded DirectSort on two ranks with no GPU: this repository's drivers over the CPU scheme layer
+    (oracle/libfhesort_cpu.so), the partial ciphertexts combined by a gloo all-reduce of their words + the mod-q fix-up."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), FHEB200_CPU_THREADS="4")
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    res = {}
+    try:
+        import refdrivers
+        L = refdrivers.cpu_library("own")
+        n = 16                                             # one batch, 4 giant-step groups: sharded over the groups
+        x = S.uniform_gap_input(n, seed=2)
+        s = S.DirectSortSession(n, 12, seed=91, lib=L)
+        base, _, level0 = s.sort(x)
+        s.set_shard(rank, world, native=False, host=True)
+        out, _, level = s.sort(x)
+        ranks, _, _ = s.rank(x)
+        s.close()
+        res = {"err": float(np.abs(out - np.sort(x)).max()), "vs_unsharded": float(np.abs(out - base).max()),
+               "rank_err": float(np.abs(ranks - np.argsort(np.argsort(x))).max()), "level": (level, level0)}
+    except Exception as e:  # noqa: BLE001
+        res = {"error": repr(e)}
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, res))
+
+
+def test_sharded_direct_sort_world2_gloo_on_the_cpu_scheme_layer():
+    if not os.path.exists(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "libfhesort_cpu.so")):
+        import pytest
+        pytest.skip("oracle/libfhesort_cpu.so not built")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sort_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=600) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    for rank in (0, 1):
+        r = got[rank]
+        assert "error" not in r, r
+        assert r["err"] < 1e-3 and r["vs_unsharded"] < 1e-5 and r["rank_err"] < 1e-3 and r["level"][0] == r["level"][1], (rank, r)
