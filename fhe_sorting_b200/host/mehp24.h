@@ -144,12 +144,13 @@ inline CT indicator(const CT &c, double a1, double b1, double lo, double hi, uin
 
 // reference: mehp24_utils.cpp:185-214 — every index the folds above use for side length m (capped at 256 per ciphertext),
 // plus multiples of 256 for split / combine of longer arrays
-inline std::vector<int32_t> getRotationIndices(size_t m) {
+// (sideMax: values per ciphertext; 256 in the reference, less on small test rings)
+inline std::vector<int32_t> getRotationIndices(size_t m, size_t sideMax = 256) {
     std::vector<int32_t> idx;
     size_t side = m;
-    if (m > 256) {
-        for (size_t i = 0; i < m / 256; i++) idx.push_back((int32_t)(i * 256)), idx.push_back(-(int32_t)(i * 256));
-        side = 256;
+    if (m > sideMax) {
+        for (size_t i = 1; i < m / sideMax; i++) idx.push_back((int32_t)(i * sideMax)), idx.push_back(-(int32_t)(i * sideMax));
+        side = sideMax;
     }
     const size_t lg = log2ceil(side);
     for (size_t i = 0; i < lg; i++) {
@@ -193,6 +194,7 @@ struct Comparator {
     SignFunc func = SignFunc::CompositeSign;
     SignConfig *cfg = nullptr;
     CryptoContext<DCRTPoly> cc;
+    int rank = 0, world = 1; // multi-GPU: this process evaluates the units u of the several-ciphertext sort with u % world == rank
     CT operator()(const CT &a, const CT &b) const {
         return comp ? comp->compare(cc, a, b, func, *cfg) : utils::compareAdv(a, b, dg, df);
     }
@@ -245,24 +247,59 @@ inline std::vector<CT> sortFGWith(const std::vector<CT> &c, size_t m, const Comp
         replR[j] = replicateRow(c[j], m);
         replC[j] = replicateColumn(transposeRow(c[j], m, true), m);
     }
-    std::vector<CT> Cv(parts), Ch(parts);
-    for (size_t j = 0; j < parts; j++)
-        for (size_t k = j; k < parts; k++) {
-            CT Cjk = cmp(replR[j], replC[k]);
-            accumulate(Cv[j], Cjk);
-            if (j != k) accumulate(Ch[k], cc->EvalSub(1.0, Cjk));
+    // multi-GPU ("MEHP24 N = 1024"): the parts (parts + 1) / 2 comparison blocks and the parts^2 indicator
+    // products are independent; rank r evaluates unit u when u % world == r, a rank without a contribution to some sum puts
+    // in a zero of the same level and scale, and the sums are all-reduced (partial Cv / Ch after phase 1, partial `sorted`
+    // after phase 2; the folds in between are cheap and run replicated)
+    const bool sharded = cmp.world > 1;
+    auto mine = [&](size_t unit) { return !sharded || (int)(unit % (size_t)cmp.world) == cmp.rank; };
+    auto reduce = [&](std::vector<CT> &v, size_t first, const CT &sample) {
+        if (!sharded) return;
+        if (!sample) throw std::runtime_error("mehp24: more ranks than independent units");
+        CT zero = cc->EvalSub(sample, sample);
+        for (size_t j = first; j < v.size(); j++) {
+            if (!v[j]) v[j] = zero->Clone();
+            cc->AllReduceSum(v[j]);
         }
+    };
+    std::vector<CT> Cv(parts), Ch(parts);
+    {
+        size_t unit = 0;
+        CT sample;
+        for (size_t j = 0; j < parts; j++)
+            for (size_t k = j; k < parts; k++) {
+                if (!mine(unit++)) continue;
+                CT Cjk = cmp(replR[j], replC[k]);
+                sample = Cjk;
+                accumulate(Cv[j], Cjk);
+                if (j != k) accumulate(Ch[k], cc->EvalSub(1.0, Cjk));
+            }
+        reduce(Cv, 0, sample);
+        reduce(Ch, 1, sample);
+    }
     // s[j]: rank of every element of part j among all parts, replicated over the rows
     std::vector<CT> s(parts);
     for (size_t j = 0; j < parts; j++) {
         accumulate(s[j], sumRows(Cv[j], m));
         if (j > 0) accumulate(s[j], replicateRow(transposeColumn(sumColumns(Ch[j], m, true), m, true), m));
     }
+    // s[0] has no column-sum term and sits one mask multiplication higher than the others: bring it to their level, so that every
+    // indicator product - whichever rank evaluates it - has the same level and scale and the partial sums can be all-reduced
+    if (sharded && parts > 1) s[0] = cc->EvalAdd(s[0], cc->EvalSub(s[1], s[1]));
     std::vector<CT> sorted(parts);
-    for (size_t j = 0; j < parts; j++) {
-        Plaintext offs = cc->MakeCKKSPackedPlaintext(rankOffsets(m, j * m));
-        for (size_t k = 0; k < parts; k++)
-            accumulate(sorted[j], cc->EvalMult(indicatorAdv(cc->EvalAdd(s[k], offs), (double)total, dg_i, df_i), replR[k]));
+    {
+        size_t unit = 0;
+        CT sample;
+        for (size_t j = 0; j < parts; j++) {
+            Plaintext offs = cc->MakeCKKSPackedPlaintext(rankOffsets(m, j * m));
+            for (size_t k = 0; k < parts; k++) {
+                if (!mine(unit++)) continue;
+                CT term = cc->EvalMult(indicatorAdv(cc->EvalAdd(s[k], offs), (double)total, dg_i, df_i), replR[k]);
+                sample = term;
+                accumulate(sorted[j], term);
+            }
+        }
+        reduce(sorted, 0, sample);
     }
     for (size_t j = 0; j < parts; j++) sorted[j] = transposeColumn(sumColumns(sorted[j], m, true), m, true);
     return sorted;
@@ -274,9 +311,10 @@ inline std::vector<CT> sortFG(const std::vector<CT> &c, size_t subVectorLength, 
     return sortFGWith(c, subVectorLength, cmp, dg_i, df_i);
 }
 inline std::vector<CT> sortFG(const std::vector<CT> &c, size_t subVectorLength, SignFunc func, SignConfig &cfg,
-                              std::unique_ptr<Comparison> &comp, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> cc) {
+                              std::unique_ptr<Comparison> &comp, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> cc,
+                              int rank = 0, int world = 1) {
     Comparator cmp;
-    cmp.comp = comp.get(), cmp.func = func, cmp.cfg = &cfg, cmp.cc = cc;
+    cmp.comp = comp.get(), cmp.func = func, cmp.cfg = &cfg, cmp.cc = cc, cmp.rank = rank, cmp.world = world;
     return sortFGWith(c, subVectorLength, cmp, dg_i, df_i);
 }
 
@@ -287,9 +325,11 @@ inline CT sortLargeArrayFG(const CT &c, size_t totalLength, size_t subLength, ui
                                     subLength, cc);
 }
 inline CT sortLargeArrayFG(const CT &c, size_t totalLength, size_t subLength, SignFunc func, SignConfig &cfg,
-                           std::unique_ptr<Comparison> &comp, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> cc) {
+                           std::unique_ptr<Comparison> &comp, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> cc, int rank = 0,
+                           int world = 1) {
     return utils::combineCiphertext(
-        sortFG(utils::splitCiphertext(c, totalLength, subLength, cc), subLength, func, cfg, comp, dg_i, df_i, cc), subLength, cc);
+        sortFG(utils::splitCiphertext(c, totalLength, subLength, cc), subLength, func, cfg, comp, dg_i, df_i, cc, rank, world),
+        subLength, cc);
 }
 
 // reference: mehp24_sort.cpp:23-47 — Chebyshev-function variant (degrees instead of f/g compositions)

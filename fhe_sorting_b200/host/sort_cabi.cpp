@@ -81,18 +81,28 @@ template <int N> struct Session : SessionBase {
 // N x N slot matrix (N <= 256), longer arrays split into 256-value ciphertexts
 struct Mehp24Session : SessionBase {
     std::unique_ptr<Comparison> comp;
+    int side = 256;               // values per ciphertext (side x side slot matrix)
+    int m_rank = 0, m_world = 1;  // multi-GPU: units of the several-ciphertext sort (host/mehp24.h)
     Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly> &in, SignConfig &cfg) override {
         const uint32_t dg_i = (uint32_t)((std::log2((double)len) + 1) / 2), df_i = 2;
-        if (len <= 256) return mehp24::sortFG(in, (size_t)len, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
-        return mehp24::sortLargeArrayFG(in, (size_t)len, 256, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
+        if (len <= side) return mehp24::sortFG(in, (size_t)len, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
+#ifdef REFERENCE_DRIVERS
+        return mehp24::sortLargeArrayFG(in, (size_t)len, (size_t)side, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc);
+#else
+        return mehp24::sortLargeArrayFG(in, (size_t)len, (size_t)side, SignFunc::CompositeSign, cfg, comp, dg_i, df_i, cc, m_rank, m_world);
+#endif
     }
     Ciphertext<DCRTPoly> rank(const Ciphertext<DCRTPoly> &, SignConfig &) override { throw std::runtime_error("mehp24: sort only"); }
     Ciphertext<DCRTPoly> place(const Ciphertext<DCRTPoly> &, const Ciphertext<DCRTPoly> &) override {
         throw std::runtime_error("mehp24: sort only");
     }
     Ciphertext<DCRTPoly> composed_rotate(const Ciphertext<DCRTPoly> &, int) override { throw std::runtime_error("mehp24: sort only"); }
-    void shard(int, int world) override {
-        if (world > 1) throw std::runtime_error("mehp24: the single-ciphertext sort is sequential (replicas only)");
+    void shard(int rank, int world) override {
+#ifdef REFERENCE_DRIVERS
+        if (world > 1) throw std::runtime_error("the reference's drivers have no multi-GPU sharding");
+#endif
+        if (world > 1 && len <= side) throw std::runtime_error("mehp24: the single-ciphertext sort is sequential (replicas only)");
+        m_rank = rank, m_world = world;
     }
 };
 int mehp24_depth(int N) { // tests/mehp24/Mehp24SortTest.cpp:31-62
@@ -110,8 +120,11 @@ int mehp24_depth(int N) { // tests/mehp24/Mehp24SortTest.cpp:31-62
 SessionBase *make_mehp24_session(int N, int log_ring_dim, int depth_override, uint64_t seed, int device) {
     auto t0 = std::chrono::steady_clock::now();
     auto s = std::make_unique<Mehp24Session>();
-    const int side = N < 256 ? N : 256, slots = std::min(side * side, (1 << log_ring_dim) / 2);
-    if (side * side > slots) throw std::invalid_argument("mehp24: the N x N matrix does not fit the slots of this ring");
+    // values per ciphertext: N up to 256 (the reference's split length), less on small test rings whose slots hold a smaller matrix
+    int side = N < 256 ? N : 256;
+    while (side > 2 && side * side > (1 << log_ring_dim) / 2) side >>= 1;
+    const int slots = side * side;
+    s->side = side;
     CCParams<CryptoContextCKKSRNS> p;
     p.SetRingDim(1u << log_ring_dim);
     p.SetBatchSize(slots);
@@ -128,7 +141,11 @@ SessionBase *make_mehp24_session(int N, int log_ring_dim, int depth_override, ui
 #endif
     s->cc->Enable(PKE), s->cc->Enable(KEYSWITCH), s->cc->Enable(LEVELEDSHE), s->cc->Enable(ADVANCEDSHE);
     s->keys = s->cc->KeyGen();
+    #ifdef REFERENCE_DRIVERS
     s->rotations = mehp24::utils::getRotationIndices((size_t)N);
+#else
+    s->rotations = mehp24::utils::getRotationIndices((size_t)N, (size_t)side);
+#endif
     s->cc->EvalRotateKeyGen(s->keys.secretKey, s->rotations);
     s->cc->EvalMultKeyGen(s->keys.secretKey);
     s->enc = std::make_shared<DebugEncryption>(s->cc, s->keys);

@@ -71,6 +71,16 @@ def _worker(rank, world, port, q):
             s.close()
             res["sort%d" % n] = (float(np.abs(out - np.sort(x)).max()), float(np.abs(out - base).max()),
                                  float(np.abs(ranks - ranks0).max()), level == level0)
+        # ---- MEHP24 over several ciphertexts: 64 values as two 32 x 32 matrices on ring 2^12, the 3 comparison
+        # blocks and 4 indicator products dealt over the ranks, partial sums all-reduced
+        from fhe_sorting_b200.sort import Mehp24SortSession
+        x = uniform_gap_input(64, seed=9)
+        m = Mehp24SortSession(64, 12, 48, seed=777, device=rank)
+        base, _, level0 = m.sort(x)
+        m.set_shard(rank, world)
+        out, _, level = m.sort(x)
+        m.close()
+        res["mehp24"] = (float(np.abs(out - np.sort(x)).max()), float(np.abs(out - base).max()), level == level0)
     except Exception as e:  # noqa: BLE001
         res["error"] = repr(e)
     dist.barrier()
@@ -89,7 +99,7 @@ def test_native_allreduce_and_sharded_sorts_two_gpus():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = dict(q.get(timeout=600) for _ in procs)
+    got = dict(q.get(timeout=300) for _ in procs)
     for p in procs:
         p.join(timeout=60)
     for rank in (0, 1):
@@ -99,3 +109,5 @@ def test_native_allreduce_and_sharded_sorts_two_gpus():
         for n in (128, 64):
             err, vs_unsharded, rank_diff, same_level = r["sort%d" % n]
             assert err < 0.01 and vs_unsharded < 1e-3 and rank_diff < 1e-3 and same_level, (rank, n, r["sort%d" % n])
+        err, vs_unsharded, same_level = r["mehp24"]
+        assert err < 0.01 and vs_unsharded < 1e-4 and same_level, (rank, r["mehp24"])

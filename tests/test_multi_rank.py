@@ -82,6 +82,15 @@ def _sort_worker(rank, world, port, q):
         s.close()
         res = {"err": float(np.abs(out - np.sort(x)).max()), "vs_unsharded": float(np.abs(out - base).max()),
                "rank_err": float(np.abs(ranks - np.argsort(np.argsort(x))).max()), "level": (level, level0)}
+        # MEHP24 over several ciphertexts: 32 values as two 16 x 16 matrices on ring 2^10, the 3 comparison blocks and
+        # 4 indicator products dealt over the two ranks, partial sums combined the same way
+        x = S.uniform_gap_input(32, seed=9)
+        m = S.Mehp24SortSession(32, 10, 48, seed=777, lib=L)
+        base, _, l0 = m.sort(x)
+        m.set_shard(rank, world, native=False, host=True)
+        out, _, l1 = m.sort(x)
+        m.close()
+        res["mehp24"] = (float(np.abs(out - np.sort(x)).max()), float(np.abs(out - base).max()), l0 == l1)
     except Exception as e:  # noqa: BLE001
         res = {"error": repr(e)}
     dist.barrier()
@@ -109,3 +118,4 @@ def test_sharded_direct_sort_world2_gloo_on_the_cpu_scheme_layer():
         r = got[rank]
         assert "error" not in r, r
         assert r["err"] < 1e-3 and r["vs_unsharded"] < 1e-5 and r["rank_err"] < 1e-3 and r["level"][0] == r["level"][1], (rank, r)
+        assert r["mehp24"][0] < 1e-3 and r["mehp24"][1] < 1e-5 and r["mehp24"][2], (rank, r)
