@@ -249,10 +249,30 @@ Ct Context::eval_chebyshev(const Ct &x, const std::vector<double> &coeffs, doubl
     const int k = S.k, m = S.m;
     Ct u = to_unit_interval(this, x, a, b);
     S.T = chebyshev_basis(this, u, k);
-    for (int i = 0; i + 1 < k; i++) { // one alignment of all baby steps to the deepest one
-        Ct t = S.T[i], d = S.T[k - 1];
-        adjust_pair(t, d);
-        S.T[i] = t;
+    // One alignment of all baby steps to the deepest one.  Only their degree-1 forms are ever used below (the scalar products of
+    // the leaf sums), so the alignment is done on those: one scalar product + one rescale per baby step instead of aligning the
+    // degree-2 forms and rescaling them again (FHEB200_PS_ALIGN_REDUCED=0 restores that).
+    static const bool align_reduced = [] { const char *e = getenv("FHEB200_PS_ALIGN_REDUCED"); return !(e && *e == '0'); }();
+    if (align_reduced) {
+        S.Tr.resize(k);
+        const Ct d1 = S.T[k - 1]->nsd == 2 ? reduced(S.T[k - 1]) : S.T[k - 1];
+        for (int i = 0; i + 1 < k; i++) {
+            Ct t = S.T[i]->nsd == 2 ? reduced(S.T[i]) : S.T[i], d = d1;
+            adjust_pair(t, d);
+            if (t->nsd != 1 || t->ell != d1->ell) { // (not the shape the shortcut assumes: fall back for this one)
+                Ct t2 = S.T[i], d2 = S.T[k - 1];
+                adjust_pair(t2, d2);
+                S.T[i] = t2;
+                continue;
+            }
+            S.Tr[i] = t;
+        }
+    } else {
+        for (int i = 0; i + 1 < k; i++) {
+            Ct t = S.T[i], d = S.T[k - 1];
+            adjust_pair(t, d);
+            S.T[i] = t;
+        }
     }
     t_basis = tm.lap();
     S.T2.resize(m);
