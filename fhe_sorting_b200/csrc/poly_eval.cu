@@ -208,10 +208,19 @@ static Ct to_unit_interval(Context *C, const Ct &x, double a, double b) {
 static std::vector<Ct> chebyshev_basis(Context *C, const Ct &u, int count) {
     std::vector<Ct> T(count);
     T[0] = u;
+    // T_1 brought to the level and degree of a product is the same ciphertext for every product of that level: align it once per
+    // level instead of once per odd index (each alignment is a scalar product and a rescale)
+    std::map<std::pair<int, int>, Ct> t1_at;
     for (int i = 2; i <= count; i++) {
         if (i & 1) {
             Ct prod = C->mult(T[i / 2 - 1], T[i / 2]);
-            T[i - 1] = C->sub(double_ct(C, prod), T[0]);
+            Ct &t1 = t1_at[{prod->level, prod->nsd}];
+            if (!t1) {
+                Ct t = T[0], d = prod;
+                C->adjust_pair(t, d);
+                if (d.get() == prod.get()) t1 = t; // (the product itself was not touched: t is T_1 in its shape)
+            }
+            T[i - 1] = C->sub(double_ct(C, prod), t1 ? t1 : T[0]);
         } else {
             Ct sq = C->mult(T[i / 2 - 1], T[i / 2 - 1]);
             T[i - 1] = C->add_const(double_ct(C, sq), -1.0);
